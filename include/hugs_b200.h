@@ -1,0 +1,255 @@
+/*
+ * hugs_b200.h -- C ABI of the B200-native HUGS splat hot path.
+ *
+ * One shared library (libhugs_b200.so), plain C linkage, raw device pointers and sizes only:
+ * no torch / pybind / C++ types cross this boundary.  Every entry point names the reference
+ * interface it replaces (paths relative to the apple/ml-hugs tree):
+ *
+ *   DGR = submodules/diff-gaussian-rasterization
+ *   CR  = submodules/diff-gaussian-rasterization/cuda_rasterizer
+ *
+ * Ownership: all device memory is caller-owned (torch-owned in the Python host).  The library
+ * never allocates or frees device memory; growable workspaces are obtained through caller
+ * supplied resize callbacks, exactly like the reference's std::function<char*(size_t)>
+ * arguments (CR/rasterizer.h:31-34).  All work is enqueued on the caller's stream; the only
+ * host synchronisation is the 4-byte read-back of the number of (Gaussian, tile) pairs that
+ * the reference also performs (CR/rasterizer_impl.cu:281).
+ *
+ * Return value: 0 on success, a positive cudaError_t, or a negative HUGS_B200_E* code.
+ * hugs_b200_last_error() returns a thread-local, human-readable message for the last failure.
+ */
+#ifndef HUGS_B200_H
+#define HUGS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+#define HUGS_B200_ABI_VERSION 1
+
+#define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
+#define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
+#define HUGS_B200_EUNSUP   (-3)  /* unsupported configuration (e.g. SH degree > 3)           */
+
+/* Opaque CUDA stream handle (cudaStream_t). NULL = legacy default stream. */
+typedef void* hugs_b200_stream_t;
+
+/* Grow-callback: must return a device pointer to at least `nbytes` bytes (256-B aligned), valid
+ * until the matching backward call has finished.  Replaces the std::function<char*(size_t)>
+ * geometryBuffer / binningBuffer / imageBuffer arguments of
+ * CudaRasterizer::Rasterizer::forward (CR/rasterizer.h:31-34) and the resizeFunctional lambdas
+ * of DGR/rasterize_points.cu:27-33. */
+typedef char* (*hugs_b200_resize_fn)(void* user, size_t nbytes);
+
+int         hugs_b200_abi_version(void);
+const char* hugs_b200_last_error(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Rasterizer forward.  Replaces CudaRasterizer::Rasterizer::forward (CR/rasterizer.h:31-57,
+ * CR/rasterizer_impl.cu:198-336), i.e. what DGR/rasterize_points.cu:35-115
+ * (RasterizeGaussiansCUDA) calls.
+ *
+ *   preprocess (CR/forward.cu:155-256) -> inclusive scan (CR/rasterizer_impl.cu:277)
+ *   -> read R (..:281) -> duplicateWithKeys (..:70-111) -> radix sort on 32+bit bits (..:300-308)
+ *   -> identifyTileRanges (..:116-138) -> per-tile blend (CR/forward.cu:261-374)
+ *
+ * Argument meaning is the reference's: all tensors are float32 device arrays, matrices are the
+ * row-major-transposed 4x4 the reference expects (CR/auxiliary.h:58-77), shs is [P,M,3] AoS,
+ * rotations are (r,x,y,z), any of shs / colors_precomp / scales / rotations / cov3D_precomp may be
+ * NULL subject to the reference's exactly-one-of rule.  out_color is [3,H,W], radii is int32[P].
+ * *num_rendered receives R.  debug != 0 synchronises and checks after every stage
+ * (CR/auxiliary.h:166-173).
+ * ------------------------------------------------------------------------------------------- */
+int hugs_b200_rasterize_forward(
+    hugs_b200_resize_fn geometry_buffer, void* geometry_user,
+    hugs_b200_resize_fn binning_buffer,  void* binning_user,
+    hugs_b200_resize_fn image_buffer,    void* image_user,
+    int P, int D, int M,
+    const float* background,
+    int width, int height,
+    const float* means3D,
+    const float* shs,
+    const float* colors_precomp,
+    const float* opacities,
+    const float* scales,
+    float scale_modifier,
+    const float* rotations,
+    const float* cov3D_precomp,
+    const float* viewmatrix,
+    const float* projmatrix,
+    const float* cam_pos,
+    float tan_fovx, float tan_fovy,
+    int prefiltered,
+    float* out_color,
+    int* radii,
+    int debug,
+    hugs_b200_stream_t stream,
+    int* num_rendered);
+
+/* ---------------------------------------------------------------------------------------------
+ * Rasterizer backward.  Replaces CudaRasterizer::Rasterizer::backward (CR/rasterizer.h:59-84,
+ * CR/rasterizer_impl.cu:340-434), i.e. what DGR/rasterize_points.cu:117-196 calls:
+ *   per-tile reverse blend (CR/backward.cu:399-557) -> cov2D backward (..:144-274)
+ *   -> projection / SH / cov3D backward (..:346-396, 20-139, 278-341).
+ *
+ * geom/binning/image buffers are the ones forward filled.  Outputs (all float32, caller
+ * allocated, NOT required to be zeroed -- the library clears what it accumulates into):
+ *   dL_dmean2D [P,3] (z column zero), dL_dconic [P,4] (x,y,-,w as CR/backward.cu:549-551),
+ *   dL_dopacity [P], dL_dcolor [P,3], dL_dmean3D [P,3], dL_dcov3D [P,6], dL_dsh [P,M,3],
+ *   dL_dscale [P,3], dL_drot [P,4].
+ * ------------------------------------------------------------------------------------------- */
+int hugs_b200_rasterize_backward(
+    int P, int D, int M, int R,
+    const float* background,
+    int width, int height,
+    const float* means3D,
+    const float* shs,
+    const float* colors_precomp,
+    const float* scales,
+    float scale_modifier,
+    const float* rotations,
+    const float* cov3D_precomp,
+    const float* viewmatrix,
+    const float* projmatrix,
+    const float* cam_pos,
+    float tan_fovx, float tan_fovy,
+    const int* radii,
+    char* geom_buffer,
+    char* binning_buffer,
+    char* image_buffer,
+    const float* dL_dpix,
+    float* dL_dmean2D,
+    float* dL_dconic,
+    float* dL_dopacity,
+    float* dL_dcolor,
+    float* dL_dmean3D,
+    float* dL_dcov3D,
+    float* dL_dsh,
+    float* dL_dscale,
+    float* dL_drot,
+    int debug,
+    hugs_b200_stream_t stream);
+
+/* Replaces CudaRasterizer::Rasterizer::markVisible (CR/rasterizer.h:23-29,
+ * CR/rasterizer_impl.cu:141-153; kernel checkFrustum :54-66).  present is uint8/bool [P]. */
+int hugs_b200_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                           const float* projmatrix, uint8_t* present, hugs_b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Workspace introspection (used by the parity tests to read sort keys, the sorted Gaussian
+ * list, tile ranges and per-pixel contributor counts out of the opaque byte buffers; the
+ * reference's layout is CR/rasterizer_impl.cu:155-194, ours is in DESIGN.md).
+ * Each call fills byte offsets from the buffer base; returns the number of entries written.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct hugs_b200_geom_layout {
+    size_t depths;         /* f32  [P]   view-space z                                   */
+    size_t means2D;        /* f32x2[P]   pixel-space centre                             */
+    size_t conic_opacity;  /* f32x4[P]   (conic.x, conic.y, conic.z, opacity)           */
+    size_t rgb;            /* f32x4[P]   (r,g,b,unused) from SH                         */
+    size_t clamped;        /* u8   [P]   bit c set <=> channel c clamped at 0           */
+    size_t tiles_touched;  /* u32  [P]                                                  */
+    size_t point_offsets;  /* u32  [P]   inclusive prefix sum of tiles_touched          */
+    size_t scan_temp;      /* decoupled look-back state                                 */
+    size_t total;          /* bytes required                                            */
+} hugs_b200_geom_layout;
+
+typedef struct hugs_b200_image_layout {
+    size_t accum_alpha;    /* f32  [H*W] final transmittance T                          */
+    size_t n_contrib;      /* u32  [H*W] last contributing list position (1-based)      */
+    size_t ranges;         /* u32x2[tiles] [first,last) into the sorted list            */
+    size_t total;
+} hugs_b200_image_layout;
+
+typedef struct hugs_b200_binning_layout {
+    size_t point_list_keys;           /* u64[R] sorted keys  (tile<<32 | depth bits)   */
+    size_t point_list;                /* u32[R] sorted Gaussian indices                */
+    size_t point_list_keys_unsorted;  /* u64[R]                                        */
+    size_t point_list_unsorted;       /* u32[R]                                        */
+    size_t sort_temp;                 /* histograms + look-back state                  */
+    size_t total;
+} hugs_b200_binning_layout;
+
+int hugs_b200_geom_layout_of(int P, hugs_b200_geom_layout* out);
+int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out);
+int hugs_b200_binning_layout_of(int R, hugs_b200_binning_layout* out);
+
+/* ---------------------------------------------------------------------------------------------
+ * Stand-alone stages, exported so each can be parity-tested and timed on its own.
+ * ------------------------------------------------------------------------------------------- */
+
+/* Number of key bits the reference sorts on: 32 + getHigherMsb(tiles) (CR/rasterizer_impl.cu:35-50,300). */
+int hugs_b200_sort_bits(int width, int height);
+
+/* Bytes of temp storage hugs_b200_sort_pairs needs for n pairs. */
+size_t hugs_b200_sort_temp_bytes(int n);
+
+/* Stable LSD radix sort of (u64 key, u32 value) pairs on key bits [0, end_bit): hand-written
+ * onesweep (one histogram pass + ceil(end_bit/8) decoupled-look-back scatter passes).  Replaces
+ * cub::DeviceRadixSort::SortPairs at CR/rasterizer_impl.cu:303-308.  keys_in/vals_in are
+ * clobbered (used as the ping-pong buffer); the result is always in keys_out/vals_out. */
+int hugs_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                         int n, int end_bit, void* temp, size_t temp_bytes, hugs_b200_stream_t stream);
+
+/* Bytes of temp storage hugs_b200_inclusive_scan needs for n items. */
+size_t hugs_b200_scan_temp_bytes(int n);
+
+/* Single-pass decoupled-look-back inclusive prefix sum of u32.  Replaces
+ * cub::DeviceScan::InclusiveSum at CR/rasterizer_impl.cu:277. */
+int hugs_b200_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
+                             hugs_b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * SMPL linear-blend-skinning deformation of the human Gaussians (fused).  Replaces the PyTorch
+ * chain  lbs_extra (hugs/models/modules/lbs.py:19-73, with disable_posedirs=True: v_posed=v_shaped)
+ *  + the deformation tail hugs/models/hugs_trimlp.py:510-518
+ *  + matrix_to_quaternion (hugs/utils/rotations.py:105-156):
+ *
+ *   T_i   = sum_j w_ij A_fj            (A: [F,J,4,4] row-major joint transforms, w: [N,J])
+ *   xyz'  = (T_i [xyz_i;1])[:3] * smpl_scale + transl_f
+ *   R'_i  = T_i[:3,:3] R_i ;  q_i = matrix_to_quaternion(R'_i)   (real first, NOT normalised)
+ *   s'_i  = s_i * smpl_scale
+ *
+ * F pose frames are processed in one launch (F=1 for training; F=300 for the animation config).
+ * Inputs: A [F,J,16], xyz [N,3], weights [N,J], rotmat [N,9] row-major, scales [N,3] (may be
+ * NULL), transl [F,3] (may be NULL => 0), smpl_scale scalar.
+ * Outputs: out_xyz [F,N,3], out_rotq [F,N,4], out_scales [F,N,3] (if scales), out_T [F,N,16]
+ * (optional, NULL to skip; the reference materialises it).
+ * ------------------------------------------------------------------------------------------- */
+int hugs_b200_lbs_forward(int F, int N, int J,
+                          const float* A, const float* xyz, const float* weights,
+                          const float* rotmat, const float* scales,
+                          const float* transl, float smpl_scale,
+                          float* out_xyz, float* out_rotq, float* out_scales, float* out_T,
+                          hugs_b200_stream_t stream);
+
+/* Backward of hugs_b200_lbs_forward (the reference relies on torch autograd through the chain
+ * above).  Upstream grads: g_xyz [F,N,3], g_rotq [F,N,4], g_scales [F,N,3] (may be NULL).
+ * Outputs (caller allocated; the library zero-fills what it accumulates into):
+ *   dA [F,J,16], d_xyz [N,3], d_weights [N,J], d_rotmat [N,9], d_scales [N,3] (if scales),
+ *   d_transl [F,3] (may be NULL), d_smpl_scale [1] (may be NULL). */
+int hugs_b200_lbs_backward(int F, int N, int J,
+                           const float* A, const float* xyz, const float* weights,
+                           const float* rotmat, const float* scales,
+                           const float* transl, float smpl_scale,
+                           const float* g_xyz, const float* g_rotq, const float* g_scales,
+                           float* dA, float* d_xyz, float* d_weights, float* d_rotmat,
+                           float* d_scales, float* d_transl, float* d_smpl_scale,
+                           hugs_b200_stream_t stream);
+
+/* Number of kernel launches issued by this library on the calling thread since the last reset
+ * (bench.py reports it as gpu_launches). */
+long long hugs_b200_launch_count(int reset);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* HUGS_B200_H */

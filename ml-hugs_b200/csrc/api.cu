@@ -1,0 +1,435 @@
+// C ABI of libhugs_b200.so (declared in include/hugs_b200.h) and the forward / backward stage
+// orchestration that replaces CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (cuda_rasterizer/rasterizer_impl.cu:141-153,198-336,340-434).
+#include "../../include/hugs_b200.h"
+#include "common.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace hb {
+
+static thread_local char g_error[512] = "";
+static thread_local long long g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+void count_launch(int n) { g_launches += n; }
+
+// ---- workspace carving ---------------------------------------------------------------------
+// All slices are 256-byte aligned relative to the buffer base (the base itself comes from the
+// caller's allocator: torch CUDA allocations are 512-byte aligned).
+template <typename T>
+static T* take(char*& p, size_t count) {
+    T* r = reinterpret_cast<T*>(p);
+    p += align_up(sizeof(T) * count);
+    return r;
+}
+
+GeomView carve_geom(char* base, int P) {
+    GeomView g;
+    char* p = base;
+    const size_t n = (size_t)(P > 0 ? P : 0);
+    g.depths = take<float>(p, n);
+    g.means2D = take<float2>(p, n);
+    g.conic_opacity = take<float4>(p, n);
+    g.rgb = take<float4>(p, n);
+    g.clamped = take<uint8_t>(p, n);
+    g.tiles_touched = take<uint32_t>(p, n);
+    g.point_offsets = take<uint32_t>(p, n);
+    g.scan_temp_bytes = scan_temp_bytes(P);
+    g.scan_temp = take<char>(p, g.scan_temp_bytes);
+    g.total = (size_t)(p - base);
+    return g;
+}
+
+ImageView carve_image(char* base, int W, int H) {
+    ImageView v;
+    char* p = base;
+    const size_t n = (size_t)W * (size_t)H;
+    const size_t tiles = (size_t)cdiv(W, HB_TILE_X) * (size_t)cdiv(H, HB_TILE_Y);
+    v.accum_alpha = take<float>(p, n);
+    v.n_contrib = take<uint32_t>(p, n);
+    v.ranges = take<uint2>(p, tiles);
+    v.total = (size_t)(p - base);
+    return v;
+}
+
+BinningView carve_binning(char* base, int R) {
+    BinningView b;
+    char* p = base;
+    const size_t n = (size_t)(R > 0 ? R : 0);
+    b.keys = take<uint64_t>(p, n);
+    b.list = take<uint32_t>(p, n);
+    b.keys_unsorted = take<uint64_t>(p, n);
+    b.list_unsorted = take<uint32_t>(p, n);
+    b.sort_temp_bytes = sort_temp_bytes(R);
+    b.sort_temp = take<char>(p, b.sort_temp_bytes);
+    b.total = (size_t)(p - base);
+    return b;
+}
+
+// Helper function to find the next-highest bit of the MSB (rasterizer_impl.cu:35-50): the
+// reference sorts on 32 + this many key bits.
+static uint32_t higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4;
+    uint32_t step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step;
+        else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+// Pinned 4-byte landing pad for the number of rendered pairs (one per host thread).
+static int* pinned_counter() {
+    static thread_local int* p = nullptr;
+    if (p == nullptr) {
+        if (cudaHostAlloc(reinterpret_cast<void**>(&p), 64, cudaHostAllocDefault) != cudaSuccess) p = nullptr;
+    }
+    return p;
+}
+
+static Camera make_camera(const float* view, const float* proj, const float* campos, int W, int H, float tan_fovx,
+                          float tan_fovy) {
+    Camera c;
+    c.view = view;
+    c.proj = proj;
+    c.campos = campos;
+    c.W = W;
+    c.H = H;
+    c.tan_fovx = tan_fovx;
+    c.tan_fovy = tan_fovy;
+    // rasterizer_impl.cu:222-223
+    c.focal_y = H / (2.0f * tan_fovy);
+    c.focal_x = W / (2.0f * tan_fovx);
+    c.grid_x = cdiv(W, HB_TILE_X);
+    c.grid_y = cdiv(H, HB_TILE_Y);
+    return c;
+}
+
+#define HB_STAGE(call, name)                                                                  \
+    do {                                                                                      \
+        int _rc = (call);                                                                     \
+        if (_rc) return _rc;                                                                  \
+        if (debug) {                                                                          \
+            cudaError_t _e = cudaStreamSynchronize(stream);                                   \
+            if (_e != cudaSuccess) {                                                          \
+                set_error("stage '%s' failed: %s", name, cudaGetErrorString(_e));             \
+                return (int)_e;                                                               \
+            }                                                                                 \
+        }                                                                                     \
+    } while (0)
+
+}  // namespace hb
+
+using namespace hb;
+
+extern "C" {
+
+int hugs_b200_abi_version(void) { return HUGS_B200_ABI_VERSION; }
+const char* hugs_b200_last_error(void) { return g_error; }
+
+long long hugs_b200_launch_count(int reset) {
+    const long long v = g_launches;
+    if (reset) g_launches = 0;
+    return v;
+}
+
+int hugs_b200_geom_layout_of(int P, hugs_b200_geom_layout* out) {
+    if (!out || P < 0) return HUGS_B200_EINVAL;
+    const GeomView g = carve_geom(nullptr, P);
+    out->depths = (size_t)reinterpret_cast<char*>(g.depths);
+    out->means2D = (size_t)reinterpret_cast<char*>(g.means2D);
+    out->conic_opacity = (size_t)reinterpret_cast<char*>(g.conic_opacity);
+    out->rgb = (size_t)reinterpret_cast<char*>(g.rgb);
+    out->clamped = (size_t)reinterpret_cast<char*>(g.clamped);
+    out->tiles_touched = (size_t)reinterpret_cast<char*>(g.tiles_touched);
+    out->point_offsets = (size_t)reinterpret_cast<char*>(g.point_offsets);
+    out->scan_temp = (size_t)g.scan_temp;
+    out->total = g.total;
+    return 9;
+}
+
+int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out) {
+    if (!out || width <= 0 || height <= 0) return HUGS_B200_EINVAL;
+    const ImageView v = carve_image(nullptr, width, height);
+    out->accum_alpha = (size_t)reinterpret_cast<char*>(v.accum_alpha);
+    out->n_contrib = (size_t)reinterpret_cast<char*>(v.n_contrib);
+    out->ranges = (size_t)reinterpret_cast<char*>(v.ranges);
+    out->total = v.total;
+    return 4;
+}
+
+int hugs_b200_binning_layout_of(int R, hugs_b200_binning_layout* out) {
+    if (!out || R < 0) return HUGS_B200_EINVAL;
+    const BinningView b = carve_binning(nullptr, R);
+    out->point_list_keys = (size_t)reinterpret_cast<char*>(b.keys);
+    out->point_list = (size_t)reinterpret_cast<char*>(b.list);
+    out->point_list_keys_unsorted = (size_t)reinterpret_cast<char*>(b.keys_unsorted);
+    out->point_list_unsorted = (size_t)reinterpret_cast<char*>(b.list_unsorted);
+    out->sort_temp = (size_t)b.sort_temp;
+    out->total = b.total;
+    return 6;
+}
+
+int hugs_b200_sort_bits(int width, int height) {
+    const uint32_t tiles = (uint32_t)(cdiv(width, HB_TILE_X) * cdiv(height, HB_TILE_Y));
+    return 32 + (int)higher_msb(tiles);
+}
+
+size_t hugs_b200_sort_temp_bytes(int n) { return sort_temp_bytes(n); }
+size_t hugs_b200_scan_temp_bytes(int n) { return scan_temp_bytes(n); }
+
+int hugs_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
+                         int end_bit, void* temp, size_t temp_bytes, hugs_b200_stream_t stream) {
+    if (n < 0 || end_bit < 0 || end_bit > 64) {
+        set_error("sort_pairs: bad n / end_bit");
+        return HUGS_B200_EINVAL;
+    }
+    if (n > 0 && (!keys_in || !vals_in || !keys_out || !vals_out)) {
+        set_error("sort_pairs: null buffer");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_sort_pairs(keys_in, vals_in, keys_out, vals_out, n, end_bit, temp, temp_bytes,
+                             static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
+                             hugs_b200_stream_t stream) {
+    if (n < 0 || (n > 0 && (!in || !out))) {
+        set_error("inclusive_scan: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_inclusive_scan(in, out, n, temp, temp_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                           uint8_t* present, hugs_b200_stream_t stream) {
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) {
+        set_error("mark_visible: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    if (P == 0) return 0;
+    return launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geometry_user,
+                                hugs_b200_resize_fn binning_buffer, void* binning_user,
+                                hugs_b200_resize_fn image_buffer, void* image_user, int P, int D, int M,
+                                const float* background, int width, int height, const float* means3D,
+                                const float* shs, const float* colors_precomp, const float* opacities,
+                                const float* scales, float scale_modifier, const float* rotations,
+                                const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered,
+                                float* out_color, int* radii, int debug, hugs_b200_stream_t stream_,
+                                int* num_rendered) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (num_rendered) *num_rendered = 0;
+    if (!geometry_buffer || !binning_buffer || !image_buffer || !num_rendered) {
+        set_error("rasterize_forward: null callback / output");
+        return HUGS_B200_EINVAL;
+    }
+    if (P < 0 || width <= 0 || height <= 0 || !background || !out_color || !viewmatrix || !projmatrix || !cam_pos) {
+        set_error("rasterize_forward: bad size or null camera / output pointer");
+        return HUGS_B200_EINVAL;
+    }
+    if (P > 0 && (!means3D || !opacities || !radii)) {
+        set_error("rasterize_forward: null means3D / opacities / radii");
+        return HUGS_B200_EINVAL;
+    }
+    if (P > 0 && colors_precomp == nullptr) {
+        if (shs == nullptr) {
+            set_error("rasterize_forward: provide exactly one of SHs or precomputed colors");
+            return HUGS_B200_EINVAL;
+        }
+        if (D < 0 || D > 3 || (D + 1) * (D + 1) > M) {
+            set_error("rasterize_forward: SH degree %d needs 0 <= D <= 3 and M >= (D+1)^2 (M=%d)", D, M);
+            return HUGS_B200_EUNSUP;
+        }
+    }
+    if (P > 0 && cov3D_precomp == nullptr && (scales == nullptr || rotations == nullptr)) {
+        set_error("rasterize_forward: provide scale/rotation pair or precomputed 3D covariance");
+        return HUGS_B200_EINVAL;
+    }
+    const Camera cam = make_camera(viewmatrix, projmatrix, cam_pos, width, height, tan_fovx, tan_fovy);
+    const int num_tiles = cam.grid_x * cam.grid_y;
+
+    char* img_base = image_buffer(image_user, carve_image(nullptr, width, height).total);
+    if (!img_base) {
+        set_error("rasterize_forward: image buffer callback returned NULL");
+        return HUGS_B200_ENOMEM;
+    }
+    const ImageView img = carve_image(img_base, width, height);
+
+    int R = 0;
+    GeomView geom;
+    BinningView bin;
+    memset(&geom, 0, sizeof(geom));
+    memset(&bin, 0, sizeof(bin));
+    if (P > 0) {
+        char* geom_base = geometry_buffer(geometry_user, carve_geom(nullptr, P).total);
+        if (!geom_base) {
+            set_error("rasterize_forward: geometry buffer callback returned NULL");
+            return HUGS_B200_ENOMEM;
+        }
+        geom = carve_geom(geom_base, P);
+
+        HB_STAGE(launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
+                                   (scales && rotations) ? nullptr : cov3D_precomp, colors_precomp, cam, radii, geom,
+                                   prefiltered != 0, stream),
+                 "preprocess");
+        HB_STAGE(launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_temp,
+                                       geom.scan_temp_bytes, stream),
+                 "inclusive_scan");
+
+        // Number of (Gaussian, tile) pairs must reach the host to size the binning workspace
+        // (rasterizer_impl.cu:281); pinned landing pad + the caller's stream instead of a
+        // blocking cudaMemcpy on the legacy stream.
+        int* pinned = pinned_counter();
+        if (pinned) {
+            HB_CUDA_OK(cudaMemcpyAsync(pinned, geom.point_offsets + (P - 1), sizeof(int), cudaMemcpyDeviceToHost, stream));
+            HB_CUDA_OK(cudaStreamSynchronize(stream));
+            R = *pinned;
+        } else {
+            HB_CUDA_OK(cudaMemcpyAsync(&R, geom.point_offsets + (P - 1), sizeof(int), cudaMemcpyDeviceToHost, stream));
+            HB_CUDA_OK(cudaStreamSynchronize(stream));
+        }
+        if (R < 0) {
+            set_error("rasterize_forward: more than 2^31 (Gaussian, tile) pairs");
+            return HUGS_B200_EUNSUP;
+        }
+    }
+
+    char* bin_base = binning_buffer(binning_user, carve_binning(nullptr, R).total);
+    if (!bin_base) {
+        set_error("rasterize_forward: binning buffer callback returned NULL");
+        return HUGS_B200_ENOMEM;
+    }
+    bin = carve_binning(bin_base, R);
+
+    if (R > 0) {
+        const int end_bit = 32 + (int)higher_msb((uint32_t)num_tiles);
+        // The sort ping-pongs between the two key/value buffers; emit the unsorted pairs into the
+        // one that makes the last pass land in (keys, list).
+        const int passes = cdiv(end_bit, 8);
+        uint64_t* k_src = (passes % 2 == 0) ? bin.keys : bin.keys_unsorted;
+        uint32_t* v_src = (passes % 2 == 0) ? bin.list : bin.list_unsorted;
+        uint64_t* k_dst = (passes % 2 == 0) ? bin.keys_unsorted : bin.keys;
+        uint32_t* v_dst = (passes % 2 == 0) ? bin.list_unsorted : bin.list;
+        HB_STAGE(launch_duplicate(P, geom.means2D, geom.depths, geom.point_offsets, radii, k_src, v_src, cam.grid_x,
+                                  cam.grid_y, stream),
+                 "duplicate_with_keys");
+        bool in_input = false;
+        HB_STAGE(launch_sort_pairs_pingpong(k_src, v_src, k_dst, v_dst, R, end_bit, bin.sort_temp, bin.sort_temp_bytes,
+                                            stream, &in_input),
+                 "sort_pairs");
+        const bool landed_in_keys = in_input ? (k_src == bin.keys) : (k_dst == bin.keys);
+        if (!landed_in_keys) {
+            HB_CUDA_OK(cudaMemcpyAsync(bin.keys, bin.keys_unsorted, sizeof(uint64_t) * (size_t)R,
+                                       cudaMemcpyDeviceToDevice, stream));
+            HB_CUDA_OK(cudaMemcpyAsync(bin.list, bin.list_unsorted, sizeof(uint32_t) * (size_t)R,
+                                       cudaMemcpyDeviceToDevice, stream));
+        }
+    }
+    HB_STAGE(launch_tile_ranges(R, bin.keys, img.ranges, num_tiles, stream), "identify_tile_ranges");
+
+    const float* feature_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
+    const int stride = colors_precomp != nullptr ? 3 : 4;
+    if (P == 0) {
+        feature_ptr = nullptr;
+    }
+    HB_STAGE(launch_render_forward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y,
+                                   P > 0 ? geom.means2D : nullptr, feature_ptr, stride,
+                                   P > 0 ? geom.conic_opacity : nullptr, img.accum_alpha, img.n_contrib, background,
+                                   out_color, stream),
+             "render_forward");
+    *num_rendered = R;
+    return 0;
+}
+
+int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height,
+                                 const float* means3D, const float* shs, const float* colors_precomp,
+                                 const float* scales, float scale_modifier, const float* rotations,
+                                 const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                 const float* cam_pos, float tan_fovx, float tan_fovy, const int* radii,
+                                 char* geom_buffer, char* binning_buffer, char* image_buffer, const float* dL_dpix,
+                                 float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                                 float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
+                                 float* dL_drot, int debug, hugs_b200_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (P < 0 || R < 0 || width <= 0 || height <= 0) {
+        set_error("rasterize_backward: bad sizes");
+        return HUGS_B200_EINVAL;
+    }
+    if (P == 0) return 0;
+    if (!geom_buffer || !binning_buffer || !image_buffer || !dL_dpix || !radii || !means3D || !background ||
+        !viewmatrix || !projmatrix || !cam_pos || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
+        !dL_dmean3D || !dL_dcov3D) {
+        set_error("rasterize_backward: null pointer argument");
+        return HUGS_B200_EINVAL;
+    }
+    if (colors_precomp == nullptr && (shs == nullptr || dL_dsh == nullptr)) {
+        set_error("rasterize_backward: SH path needs shs and dL_dsh");
+        return HUGS_B200_EINVAL;
+    }
+    const Camera cam = make_camera(viewmatrix, projmatrix, cam_pos, width, height, tan_fovx, tan_fovy);
+    const GeomView geom = carve_geom(geom_buffer, P);
+    const BinningView bin = carve_binning(binning_buffer, R);
+    const ImageView img = carve_image(image_buffer, width, height);
+
+    // The blend backward accumulates into these with atomics.
+    HB_CUDA_OK(cudaMemsetAsync(dL_dmean2D, 0, sizeof(float) * 3 * (size_t)P, stream));
+    HB_CUDA_OK(cudaMemsetAsync(dL_dconic, 0, sizeof(float) * 4 * (size_t)P, stream));
+    HB_CUDA_OK(cudaMemsetAsync(dL_dopacity, 0, sizeof(float) * (size_t)P, stream));
+    HB_CUDA_OK(cudaMemsetAsync(dL_dcolor, 0, sizeof(float) * 3 * (size_t)P, stream));
+
+    const float* color_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
+    const int stride = colors_precomp != nullptr ? 3 : 4;
+    if (R > 0) {
+        HB_STAGE(launch_render_backward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y, background,
+                                        geom.means2D, geom.conic_opacity, color_ptr, stride, img.accum_alpha,
+                                        img.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, stream),
+                 "render_backward");
+    }
+    HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,
+                                        rotations, scale_modifier, cov3D_precomp, cam, dL_dmean2D, dL_dconic,
+                                        dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, stream),
+             "preprocess_backward");
+    return 0;
+}
+
+int hugs_b200_lbs_forward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
+                          const float* rotmat, const float* scales, const float* transl, float smpl_scale,
+                          float* out_xyz, float* out_rotq, float* out_scales, float* out_T,
+                          hugs_b200_stream_t stream) {
+    if (N > 0 && (!A || !xyz || !weights || !rotmat || !out_xyz || !out_rotq)) {
+        set_error("lbs_forward: null pointer argument");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_lbs_forward(F, N, J, A, xyz, weights, rotmat, scales, transl, smpl_scale, out_xyz, out_rotq,
+                              out_scales, out_T, static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_lbs_backward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
+                           const float* rotmat, const float* scales, const float* transl, float smpl_scale,
+                           const float* g_xyz, const float* g_rotq, const float* g_scales, float* dA, float* d_xyz,
+                           float* d_weights, float* d_rotmat, float* d_scales, float* d_transl, float* d_smpl_scale,
+                           hugs_b200_stream_t stream) {
+    if (!dA || (N > 0 && (!A || !xyz || !weights || !rotmat || !g_xyz || !g_rotq || !d_xyz || !d_weights || !d_rotmat))) {
+        set_error("lbs_backward: null pointer argument");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_lbs_backward(F, N, J, A, xyz, weights, rotmat, scales, transl, smpl_scale, g_xyz, g_rotq, g_scales,
+                               dA, d_xyz, d_weights, d_rotmat, d_scales, d_transl, d_smpl_scale,
+                               static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

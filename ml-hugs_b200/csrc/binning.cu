@@ -1,0 +1,167 @@
+// Key duplication and tile-range identification for sm_100a.
+//
+// duplicate: replaces duplicateWithKeys (cuda_rasterizer/rasterizer_impl.cu:70-111).  For every
+// visible Gaussian and every tile of its rectangle it emits key = (tile_id << 32) | depth_bits,
+// value = Gaussian index, at offsets[idx-1] + (y-y0)*w + (x-x0): the same slot and the same
+// (y outer, x inner) emission order as the reference, so that a stable sort reproduces its
+// point_list bit for bit.  Instead of one thread looping over its own rectangle (imbalanced and
+// uncoalesced), a CTA owns 256 consecutive Gaussians and all its threads walk the CTA's
+// contiguous output range together: output slot -> owning Gaussian by binary search over the
+// CTA's 257 offsets in shared memory, so stores are fully coalesced and perfectly balanced.
+// Algorithmic traffic: 24 B per Gaussian + 12 B per emitted pair.
+//
+// tile_ranges: replaces identifyTileRanges (rasterizer_impl.cu:116-138) + the cudaMemset at :310.
+#include "common.cuh"
+
+namespace hb {
+
+namespace {
+constexpr int kDupThreads = 256;
+
+__global__ void __launch_bounds__(kDupThreads)
+    duplicate_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                     const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                     uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, unsigned grid_x, unsigned grid_y) {
+    __shared__ uint32_t s_off[kDupThreads + 1];  // exclusive start offset of each Gaussian, [256] = CTA end
+    __shared__ uint32_t s_depth[kDupThreads];
+    __shared__ uint32_t s_rect[kDupThreads];  // min_x | min_y << 10 | width << 20 (grid <= 1023 tiles per axis)
+    const int tid = threadIdx.x;
+    const int first = blockIdx.x * kDupThreads;
+    const int idx = first + tid;
+
+    uint32_t end_off = 0;
+    if (idx < P) {
+        end_off = __ldg(offsets + idx);
+        const int r = __ldg(radii + idx);
+        uint32_t rect = 0, dbits = 0;
+        if (r > 0) {
+            // getRect (auxiliary.h:46-56), same float sequence as preprocess.
+            const float2 p = __ldg(means2D + idx);
+            const float rf = (float)r;
+            const unsigned min_x = min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.x, -rf), 0.0625f)));
+            const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
+            const unsigned max_x = min(
+                grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
+            rect = min_x | (min_y << 10) | ((max_x - min_x) << 20);
+            dbits = __float_as_uint(__ldg(depths + idx));
+        }
+        s_rect[tid] = rect;
+        s_depth[tid] = dbits;
+    }
+    // s_off[t] = inclusive offset of Gaussian first+t-1 (== exclusive start of first+t)
+    if (tid == 0) s_off[0] = (first == 0) ? 0u : __ldg(offsets + first - 1);
+    const int in_block = min(kDupThreads, P - first);
+    if (tid < in_block) s_off[tid + 1] = end_off;
+    __syncthreads();
+
+    const uint32_t begin = s_off[0];
+    const uint32_t end = s_off[in_block];
+    for (uint32_t o = begin + tid; o < end; o += kDupThreads) {
+        // largest g with s_off[g] <= o  (Gaussians with zero tiles have s_off[g] == s_off[g+1])
+        int lo = 0, hi = in_block;  // invariant: s_off[lo] <= o < s_off[hi]
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (s_off[mid] <= o) lo = mid; else hi = mid;
+        }
+        const uint32_t rect = s_rect[lo];
+        const uint32_t k = o - s_off[lo];
+        const uint32_t w = rect >> 20;
+        const uint32_t y = ((rect >> 10) & 1023u) + k / w;
+        const uint32_t x = (rect & 1023u) + k % w;
+        const uint64_t key = ((uint64_t)(y * grid_x + x) << 32) | (uint64_t)s_depth[lo];
+        keys[o] = key;
+        vals[o] = (uint32_t)(first + lo);
+    }
+}
+
+// Generic fallback for tile grids wider than 1023 tiles per axis (images beyond 16K pixels):
+// one thread per Gaussian, the reference's loop.
+__global__ void __launch_bounds__(kDupThreads)
+    duplicate_serial_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                            const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                            uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, unsigned grid_x,
+                            unsigned grid_y) {
+    const int idx = blockIdx.x * kDupThreads + threadIdx.x;
+    if (idx >= P) return;
+    const int r = __ldg(radii + idx);
+    if (r <= 0) return;
+    uint32_t off = (idx == 0) ? 0u : __ldg(offsets + idx - 1);
+    const float2 p = __ldg(means2D + idx);
+    const float rf = (float)r;
+    const unsigned min_x = min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.x, -rf), 0.0625f)));
+    const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
+    const unsigned max_x =
+        min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
+    const unsigned max_y =
+        min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.y, rf), 16.f), -1.f), 0.0625f)));
+    const uint64_t dbits = __float_as_uint(__ldg(depths + idx));
+    for (unsigned y = min_y; y < max_y; y++)
+        for (unsigned x = min_x; x < max_x; x++) {
+            keys[off] = ((uint64_t)(y * grid_x + x) << 32) | dbits;
+            vals[off] = (uint32_t)idx;
+            off++;
+        }
+}
+
+// ranges[t] = [first, last) of tile t in the sorted list; tiles without pairs keep (0,0).
+// Two keys per thread, 128-bit loads; the neighbour comes from the previous thread's pair or one
+// extra (cached) load.
+__global__ void __launch_bounds__(256)
+    tile_ranges_kernel(int R, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+    const int i0 = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (i0 >= R) return;
+    uint64_t k0, k1 = 0;
+    const bool has1 = i0 + 1 < R;
+    if (has1) {
+        const ulonglong2 kk = __ldg(reinterpret_cast<const ulonglong2*>(keys + i0));
+        k0 = kk.x;
+        k1 = kk.y;
+    } else {
+        k0 = __ldg(keys + i0);
+    }
+    const uint32_t t0 = (uint32_t)(k0 >> 32);
+    if (i0 == 0) {
+        ranges[t0].x = 0;
+    } else {
+        const uint32_t tp = (uint32_t)(__ldg(keys + i0 - 1) >> 32);
+        if (tp != t0) {
+            ranges[tp].y = i0;
+            ranges[t0].x = i0;
+        }
+    }
+    if (has1) {
+        const uint32_t t1 = (uint32_t)(k1 >> 32);
+        if (t1 != t0) {
+            ranges[t0].y = i0 + 1;
+            ranges[t1].x = i0 + 1;
+        }
+        if (i0 + 1 == R - 1) ranges[t1].y = R;
+    } else {
+        ranges[t0].y = R;  // i0 == R-1
+    }
+}
+}  // namespace
+
+int launch_duplicate(int P, const float2* means2D, const float* depths, const uint32_t* offsets, const int* radii,
+                     uint64_t* keys, uint32_t* vals, int grid_x, int grid_y, cudaStream_t stream) {
+    if (P <= 0) return 0;
+    if (grid_x <= 1023 && grid_y <= 1023) {
+        duplicate_kernel<<<cdiv(P, kDupThreads), kDupThreads, 0, stream>>>(P, means2D, depths, offsets, radii, keys,
+                                                                           vals, (unsigned)grid_x, (unsigned)grid_y);
+    } else {
+        duplicate_serial_kernel<<<cdiv(P, kDupThreads), kDupThreads, 0, stream>>>(
+            P, means2D, depths, offsets, radii, keys, vals, (unsigned)grid_x, (unsigned)grid_y);
+    }
+    HB_LAUNCH_OK("duplicate_with_keys", stream, false);
+    return 0;
+}
+
+int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream) {
+    HB_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
+    if (R <= 0) return 0;
+    tile_ranges_kernel<<<cdiv(cdiv(R, 2), 256), 256, 0, stream>>>(R, keys, ranges);
+    HB_LAUNCH_OK("identify_tile_ranges", stream, false);
+    return 0;
+}
+
+}  // namespace hb

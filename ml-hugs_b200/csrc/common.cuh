@@ -1,0 +1,160 @@
+// Shared declarations for the B200 (sm_100a) splat hot path.  Internal header: nothing here
+// crosses the C ABI (include/hugs_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#define HB_TILE_X 16
+#define HB_TILE_Y 16
+#define HB_TILE_PIX (HB_TILE_X * HB_TILE_Y)
+#define HB_ALIGN 256
+
+namespace hb {
+
+// ---- error plumbing (thread-local message, see api.cu) -----------------------------------
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define HB_CUDA_OK(expr)                                                                      \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess) {                                                              \
+            hb::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__,                \
+                          cudaGetErrorString(_e));                                            \
+            return (int)_e;                                                                   \
+        }                                                                                     \
+    } while (0)
+
+// After a kernel launch: always pick up launch-configuration errors; in debug mode also
+// synchronise so that asynchronous faults are attributed to the stage that caused them
+// (same contract as CHECK_CUDA in the reference, cuda_rasterizer/auxiliary.h:166-173).
+#define HB_LAUNCH_OK(stage, stream, debug)                                                    \
+    do {                                                                                      \
+        hb::count_launch();                                                                   \
+        cudaError_t _e = cudaGetLastError();                                                  \
+        if (_e == cudaSuccess && (debug)) _e = cudaStreamSynchronize(stream);                 \
+        if (_e != cudaSuccess) {                                                              \
+            hb::set_error("stage '%s' failed: %s", stage, cudaGetErrorString(_e));            \
+            return (int)_e;                                                                   \
+        }                                                                                     \
+    } while (0)
+
+static inline size_t align_up(size_t x, size_t a = HB_ALIGN) { return (x + a - 1) / a * a; }
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// ---- workspace views --------------------------------------------------------------------
+struct GeomView {
+    float* depths;
+    float2* means2D;
+    float4* conic_opacity;
+    float4* rgb;
+    uint8_t* clamped;
+    uint32_t* tiles_touched;
+    uint32_t* point_offsets;
+    char* scan_temp;
+    size_t scan_temp_bytes;
+    size_t total;
+};
+struct ImageView {
+    float* accum_alpha;
+    uint32_t* n_contrib;
+    uint2* ranges;
+    size_t total;
+};
+struct BinningView {
+    uint64_t* keys;
+    uint32_t* list;
+    uint64_t* keys_unsorted;
+    uint32_t* list_unsorted;
+    char* sort_temp;
+    size_t sort_temp_bytes;
+    size_t total;
+};
+GeomView carve_geom(char* base, int P);
+ImageView carve_image(char* base, int W, int H);
+BinningView carve_binning(char* base, int R);
+
+// ---- stage launchers (one per .cu file) ----------------------------------------------------
+struct Camera {
+    const float* view;   // 16 floats, device
+    const float* proj;   // 16 floats, device
+    const float* campos; // 3 floats, device
+    int W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    int grid_x, grid_y;
+};
+
+int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
+                      const float* rotations, const float* opacities, const float* shs,
+                      const float* cov3D_precomp, const float* colors_precomp, const Camera& cam,
+                      int* radii, const GeomView& g, bool prefiltered, cudaStream_t stream);
+int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj, uint8_t* present,
+                        cudaStream_t stream);
+
+size_t scan_temp_bytes(int n);
+int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
+                          cudaStream_t stream);
+
+int launch_duplicate(int P, const float2* means2D, const float* depths, const uint32_t* offsets,
+                     const int* radii, uint64_t* keys, uint32_t* vals, int grid_x, int grid_y,
+                     cudaStream_t stream);
+int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream);
+
+size_t sort_temp_bytes(int n);
+int launch_sort_pairs_pingpong(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
+                               int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream,
+                               bool* result_in_input);
+int launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
+                      int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream);
+
+int launch_render_forward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
+                          const float2* means2D, const float* colors, int color_stride,
+                          const float4* conic_opacity, float* final_T, uint32_t* n_contrib,
+                          const float* bg, float* out_color, cudaStream_t stream);
+int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
+                           const float* bg, const float2* means2D, const float4* conic_opacity,
+                           const float* colors, int color_stride, const float* final_T,
+                           const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D /*[P,3]*/,
+                           float* dL_dconic /*[P,4]*/, float* dL_dopacity, float* dL_dcolor /*[P,3]*/,
+                           cudaStream_t stream);
+int launch_preprocess_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
+                               const uint8_t* clamped, const float* scales, const float* rotations,
+                               float scale_modifier, const float* cov3D_precomp, const Camera& cam,
+                               const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
+                               float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
+                               float* dL_drot, cudaStream_t stream);
+
+int launch_lbs_forward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
+                       const float* rotmat, const float* scales, const float* transl, float smpl_scale,
+                       float* out_xyz, float* out_rotq, float* out_scales, float* out_T, cudaStream_t stream);
+int launch_lbs_backward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
+                        const float* rotmat, const float* scales, const float* transl, float smpl_scale,
+                        const float* g_xyz, const float* g_rotq, const float* g_scales, float* dA,
+                        float* d_xyz, float* d_weights, float* d_rotmat, float* d_scales, float* d_transl,
+                        float* d_smpl_scale, cudaStream_t stream);
+
+// ---- device helpers ------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ float4 ldg_f4(const float4* p) { return __ldg(p); }
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
+
+// Spherical-harmonics constants (same values as cuda_rasterizer/auxiliary.h:22-39 and
+// hugs/utils/spherical_harmonics.py:30-47).
+#define HB_SH_C0 0.28209479177387814f
+#define HB_SH_C1 0.4886025119029199f
+#define HB_SH_C2_0 1.0925484305920792f
+#define HB_SH_C2_1 (-1.0925484305920792f)
+#define HB_SH_C2_2 0.31539156525252005f
+#define HB_SH_C2_3 (-1.0925484305920792f)
+#define HB_SH_C2_4 0.5462742152960396f
+#define HB_SH_C3_0 (-0.5900435899266435f)
+#define HB_SH_C3_1 2.890611442640554f
+#define HB_SH_C3_2 (-0.4570457994644658f)
+#define HB_SH_C3_3 0.3731763325901154f
+#define HB_SH_C3_4 (-0.4570457994644658f)
+#define HB_SH_C3_5 1.445305721320277f
+#define HB_SH_C3_6 (-0.5900435899266435f)
+#endif
+
+}  // namespace hb

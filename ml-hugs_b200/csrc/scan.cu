@@ -1,0 +1,141 @@
+// Single-pass inclusive prefix sum of u32 with decoupled look-back (chained scan), sm_100a.
+// Replaces cub::DeviceScan::InclusiveSum at cuda_rasterizer/rasterizer_impl.cu:277.
+//
+// One CTA per 2048-item tile, tiles handed out by an atomic ticket so that every predecessor
+// of a running tile has already started (forward progress for the look-back spin).  Per-tile
+// state is one 64-bit word (flag << 32 | value) so flag and value are read atomically.
+// Algorithmic traffic: 4 B read + 4 B written per item.
+#include "common.cuh"
+
+namespace hb {
+
+namespace {
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;
+constexpr unsigned long long kFlagAggregate = 1ull << 32;
+constexpr unsigned long long kFlagInclusive = 2ull << 32;
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kScanThreads) inclusive_scan_kernel(const uint32_t* __restrict__ in,
+                                                                      uint32_t* __restrict__ out, int n,
+                                                                      unsigned long long* state,
+                                                                      unsigned* ticket) {
+    __shared__ unsigned s_tile;
+    __shared__ uint32_t s_warp[kScanThreads / 32];
+    __shared__ uint32_t s_prefix;
+    const int tid = threadIdx.x;
+    const unsigned lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const int tile = (int)s_tile;
+    const int base = tile * kScanTile + tid * kScanItems;
+
+    uint32_t v[kScanItems];
+    if (base + kScanItems <= n) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(in + base));
+        const uint4 b = __ldg(reinterpret_cast<const uint4*>(in + base) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+        v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; i++) v[i] = (base + i < n) ? __ldg(in + base + i) : 0u;
+    }
+#pragma unroll
+    for (int i = 1; i < kScanItems; i++) v[i] += v[i - 1];
+    uint32_t incl = v[kScanItems - 1];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= (unsigned)d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t warp_excl = 0, tile_total = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; w++) {
+        const uint32_t t = s_warp[w];
+        if ((unsigned)w < warp) warp_excl += t;
+        tile_total += t;
+    }
+    const uint32_t thread_excl = warp_excl + incl - v[kScanItems - 1];
+
+    if (warp == 0) {
+        if (lane == 0)
+            st_relaxed_u64(state + tile, (tile == 0 ? kFlagInclusive : kFlagAggregate) | tile_total);
+        uint32_t prefix = 0;
+        int idx = tile - 1;
+        while (idx >= 0) {
+            const int j = idx - (int)lane;
+            unsigned long long w;
+            do {
+                w = (j >= 0) ? ld_relaxed_u64(state + j) : kFlagInclusive;
+            } while (__any_sync(0xffffffffu, (w >> 32) == 0));
+            const unsigned incl_mask = __ballot_sync(0xffffffffu, (w >> 32) == 2);
+            uint32_t val = (uint32_t)w;
+            if (incl_mask) {
+                const unsigned first = __ffs(incl_mask) - 1;
+                if (lane > first) val = 0;
+            }
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+            prefix += val;
+            if (incl_mask) break;
+            idx -= 32;
+        }
+        if (lane == 0) {
+            if (tile != 0) st_relaxed_u64(state + tile, kFlagInclusive | (unsigned long long)(prefix + tile_total));
+            s_prefix = prefix;
+        }
+    }
+    __syncthreads();
+    const uint32_t add = s_prefix + thread_excl;
+    if (base + kScanItems <= n) {
+        uint4 a, b;
+        a.x = v[0] + add; a.y = v[1] + add; a.z = v[2] + add; a.w = v[3] + add;
+        b.x = v[4] + add; b.y = v[5] + add; b.z = v[6] + add; b.w = v[7] + add;
+        reinterpret_cast<uint4*>(out + base)[0] = a;
+        reinterpret_cast<uint4*>(out + base)[1] = b;
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; i++)
+            if (base + i < n) out[base + i] = v[i] + add;
+    }
+}
+}  // namespace
+
+size_t scan_temp_bytes(int n) {
+    const int tiles = cdiv(n > 0 ? n : 1, kScanTile);
+    return align_up(sizeof(unsigned long long) * (size_t)tiles + 256);
+}
+
+int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
+                          cudaStream_t stream) {
+    if (n <= 0) return 0;
+    const size_t need = scan_temp_bytes(n);
+    if (temp == nullptr || temp_bytes < need) {
+        set_error("inclusive_scan: temp storage too small (%zu < %zu)", temp_bytes, need);
+        return -1;
+    }
+    if ((reinterpret_cast<uintptr_t>(in) & 15u) || (reinterpret_cast<uintptr_t>(out) & 15u)) {
+        set_error("inclusive_scan: in/out must be 16-byte aligned");
+        return -1;
+    }
+    const int tiles = cdiv(n, kScanTile);
+    HB_CUDA_OK(cudaMemsetAsync(temp, 0, need, stream));
+    unsigned* ticket = reinterpret_cast<unsigned*>(temp);
+    unsigned long long* state = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(temp) + 256);
+    inclusive_scan_kernel<<<tiles, kScanThreads, 0, stream>>>(in, out, n, state, ticket);
+    HB_LAUNCH_OK("inclusive_scan", stream, false);
+    return 0;
+}
+
+}  // namespace hb

@@ -1,0 +1,132 @@
+"""ctypes binding of libhugs_b200.so (C ABI declared in include/hugs_b200.h).
+
+This is the only place the shared library is loaded.  There is NO fallback: if the CUDA library
+is missing the import fails loudly, and nothing here (or anywhere in the product) imports
+``oracle/``.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_CANDIDATES = [
+    os.environ.get("HUGS_B200_LIB", ""),
+    os.path.join(_HERE, "..", "lib", "libhugs_b200.so"),
+]
+
+
+class NativeLibraryMissing(ImportError):
+    pass
+
+
+def _load():
+    for p in _LIB_CANDIDATES:
+        if p and os.path.exists(p):
+            return C.CDLL(os.path.abspath(p)), os.path.abspath(p)
+    raise NativeLibraryMissing(
+        "libhugs_b200.so not found (looked in %s). Build it with `make -C ml-hugs_b200/csrc` or "
+        "`python -c 'import __graft_entry__ as g; g.build()'`. There is no CPU fallback."
+        % [p for p in _LIB_CANDIDATES if p]
+    )
+
+
+lib, LIB_PATH = _load()
+
+RESIZE_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+fp = C.c_void_p  # device pointers are passed as integers / None
+i32 = C.c_int
+
+
+class GeomLayout(C.Structure):
+    _fields_ = [(n, C.c_size_t) for n in (
+        "depths", "means2D", "conic_opacity", "rgb", "clamped", "tiles_touched", "point_offsets",
+        "scan_temp", "total")]
+
+
+class ImageLayout(C.Structure):
+    _fields_ = [(n, C.c_size_t) for n in ("accum_alpha", "n_contrib", "ranges", "total")]
+
+
+class BinningLayout(C.Structure):
+    _fields_ = [(n, C.c_size_t) for n in (
+        "point_list_keys", "point_list", "point_list_keys_unsorted", "point_list_unsorted", "sort_temp",
+        "total")]
+
+
+def _sig(name, restype, argtypes):
+    f = getattr(lib, name)
+    f.restype = restype
+    f.argtypes = argtypes
+    return f
+
+
+abi_version = _sig("hugs_b200_abi_version", i32, [])
+last_error = _sig("hugs_b200_last_error", C.c_char_p, [])
+launch_count = _sig("hugs_b200_launch_count", C.c_longlong, [i32])
+
+rasterize_forward = _sig("hugs_b200_rasterize_forward", i32, [
+    RESIZE_FN, C.c_void_p, RESIZE_FN, C.c_void_p, RESIZE_FN, C.c_void_p,
+    i32, i32, i32,            # P, D, M
+    fp, i32, i32,             # background, width, height
+    fp, fp, fp, fp,           # means3D, shs, colors_precomp, opacities
+    fp, C.c_float, fp, fp,    # scales, scale_modifier, rotations, cov3D_precomp
+    fp, fp, fp,               # viewmatrix, projmatrix, cam_pos
+    C.c_float, C.c_float, i32,  # tan_fovx, tan_fovy, prefiltered
+    fp, fp, i32, fp,          # out_color, radii, debug, stream
+    C.POINTER(i32),
+])
+
+rasterize_backward = _sig("hugs_b200_rasterize_backward", i32, [
+    i32, i32, i32, i32,       # P, D, M, R
+    fp, i32, i32,             # background, width, height
+    fp, fp, fp,               # means3D, shs, colors_precomp
+    fp, C.c_float, fp, fp,    # scales, scale_modifier, rotations, cov3D_precomp
+    fp, fp, fp,               # viewmatrix, projmatrix, cam_pos
+    C.c_float, C.c_float,     # tan_fovx, tan_fovy
+    fp, fp, fp, fp,           # radii, geom, binning, image
+    fp,                       # dL_dpix
+    fp, fp, fp, fp, fp, fp, fp, fp, fp,  # 9 gradient outputs
+    i32, fp,                  # debug, stream
+])
+
+mark_visible = _sig("hugs_b200_mark_visible", i32, [i32, fp, fp, fp, fp, fp])
+
+geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayout)])
+image_layout_of = _sig("hugs_b200_image_layout_of", i32, [i32, i32, C.POINTER(ImageLayout)])
+binning_layout_of = _sig("hugs_b200_binning_layout_of", i32, [i32, C.POINTER(BinningLayout)])
+
+sort_bits = _sig("hugs_b200_sort_bits", i32, [i32, i32])
+sort_temp_bytes = _sig("hugs_b200_sort_temp_bytes", C.c_size_t, [i32])
+scan_temp_bytes = _sig("hugs_b200_scan_temp_bytes", C.c_size_t, [i32])
+sort_pairs = _sig("hugs_b200_sort_pairs", i32, [fp, fp, fp, fp, i32, i32, fp, C.c_size_t, fp])
+inclusive_scan = _sig("hugs_b200_inclusive_scan", i32, [fp, fp, i32, fp, C.c_size_t, fp])
+
+lbs_forward = _sig("hugs_b200_lbs_forward", i32, [
+    i32, i32, i32, fp, fp, fp, fp, fp, fp, C.c_float, fp, fp, fp, fp, fp])
+lbs_backward = _sig("hugs_b200_lbs_backward", i32, [
+    i32, i32, i32, fp, fp, fp, fp, fp, fp, C.c_float, fp, fp, fp, fp, fp, fp, fp, fp, fp, fp, fp])
+
+EXPORTED_SYMBOLS = [
+    "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
+    "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_mark_visible",
+    "hugs_b200_geom_layout_of", "hugs_b200_image_layout_of", "hugs_b200_binning_layout_of",
+    "hugs_b200_sort_bits", "hugs_b200_sort_temp_bytes", "hugs_b200_sort_pairs",
+    "hugs_b200_scan_temp_bytes", "hugs_b200_inclusive_scan",
+    "hugs_b200_lbs_forward", "hugs_b200_lbs_backward",
+]
+
+
+def check(rc, what):
+    """Raise RuntimeError(last_error) for a non-zero return code (reference: C++ exceptions
+    surfacing as Python RuntimeError, cuda_rasterizer/auxiliary.h:166-173)."""
+    if rc != 0:
+        msg = last_error().decode("utf-8", "replace")
+        raise RuntimeError("%s failed (code %d): %s" % (what, rc, msg))
+
+
+def ptr(t):
+    """Device pointer of a tensor, or None for an absent optional (numel()==0), mirroring the
+    reference's convention of passing torch.Tensor([]) for unused inputs
+    (diff_gaussian_rasterization/__init__.py:197-207)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
