@@ -1,0 +1,520 @@
+#!/usr/bin/env python3
+"""bench.py -- fwd+bwd frames/s of the HUGS splat hot path on N B200s (BASELINE.json metric).
+
+A "step" on each rank is ONE frame of the human+scene workload (BASELINE.json configs[2]: 110 210
+LBS-deformed human Gaussians + 1 000 000 scene Gaussians, SH degree 3, 1920x1080):
+    LBS forward -> rasterizer forward -> loss=(color*G).sum() -> rasterizer backward -> LBS backward
+followed, for N > 1, by one NCCL allreduce(sum) of the flat parameter-gradient buffer (view-batch
+data parallelism; a single view is never split).  Every rank renders its own view each step, so
+the job processes N frames per step ("scaling": "weak").
+
+  value    frames/s with every input already resident in HBM, CUDA-event timed, max over ranks
+  e2e      the same step through the public API with the per-frame inputs (camera, SMPL joint
+           transforms, the image-space loss gradient that stands in for the training target)
+           copied from pinned host memory and the loss read back, inside the timed region
+  roofline the dominant kernel's algorithmic bytes / its CUDA-event time / measured HBM peak
+  stages   the same for every stage (per-stage CUDA events recorded inside the library on the
+           launching stream during a second pass of K steps)
+  cpu_baseline   the CPU oracle port timed on this box's host cores on a bounded sample (N=1 only)
+
+`--impl reference` runs the UNMODIFIED reference (oracle/_ref: the reference's CUDA rasterizer built
+from /root/reference + its PyTorch LBS chain) through its own public API on the same workload; if
+that build is absent it times the CPU oracle port instead.  Nothing on our arm touches oracle/.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "ml-hugs_b200"), os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+METRIC = "fwd+bwd frames/s, 1.1M Gaussians @1080p"
+UNIT = "frames/s"
+WORKLOADS = {
+    # name: (n_human, n_scene, W, H, focal)
+    "human_scene_1080p": (110210, 1_000_000, 1920, 1080, 1400.0),   # BASELINE.json configs[2] (the metric's config)
+    "human_only_1080p": (110210, 0, 1920, 1080, 1400.0),            # configs[1]
+    "smoke_256": (4096, 20000, 256, 256, 187.0),
+}
+SEED = 1002
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="human_scene_1080p", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-baseline-seconds", type=float, default=20.0)
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._pump, daemon=True)
+        self.thread.start()
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            c = [x.strip() for x in r.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0]))
+                mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------
+def make_workload(name, rank, world, device):
+    """Seeded synthetic tensors of the workload.  Parameters are identical on every
+    rank (replicas); each rank gets its own camera (view `rank` of `world` on the orbit), its own
+    SMPL joint transforms and its own image-space loss gradient."""
+    from hugs_b200 import synth
+
+    n_human, n_scene, W, H, focal = WORKLOADS[name]
+    cam = synth.make_camera(W, H, focal, view=rank, n_views=max(world, 1), seed=SEED)
+    h = synth.make_human_gaussians(n_human, seed=SEED + 1)
+    A = synth.make_joint_transforms(1, SEED + 100 + rank)[0]
+    parts = dict(human=h, A=A, cam=cam, W=W, H=H, n_human=n_human, n_scene=n_scene)
+    if n_scene > 0:
+        # scene frustum is laid out for the central camera so every rank holds the same replica
+        cam0 = synth.make_camera(W, H, focal, seed=SEED)
+        parts["scene"] = synth.make_scene_gaussians(n_scene, SEED + 2, cam0["tanfovx"], cam0["tanfovy"])
+    parts["G"] = synth.make_dL_dcolor(W, H, SEED + rank)
+    return parts
+
+
+class Replica:
+    """Device-resident parameter replica + the per-frame inputs, and the frame step itself."""
+
+    def __init__(self, wl, device, module, lbs_impl):
+        self.device = device
+        self.module = module      # a diff_gaussian_rasterization-shaped module (ours or the reference)
+        self.lbs_impl = lbs_impl  # callable(A, xyz, w, rotmat, scales, transl) -> (xyz', rotq, scales')
+        h = wl["human"]
+        d = lambda t: t.to(device).contiguous()  # noqa: E731
+        leaf = lambda t: d(t).requires_grad_(True)  # noqa: E731
+        self.W, self.H = wl["W"], wl["H"]
+        self.n_human, self.n_scene = wl["n_human"], wl["n_scene"]
+        self.h_xyz, self.h_rotmat = leaf(h["xyz"]), leaf(h["rotmat"])
+        self.h_scales, self.h_weights = leaf(h["scales"]), leaf(h["lbs_weights"])
+        opac, shs = [h["opacity"]], [h["shs"]]
+        self.s_means = self.s_scales = self.s_rots = None
+        if self.n_scene > 0:
+            s = wl["scene"]
+            self.s_means, self.s_scales, self.s_rots = leaf(s["means3D"]), leaf(s["scales"]), leaf(s["rotations"])
+            opac.append(s["opacity"])
+            shs.append(s["shs"])
+        # attributes that do not pass through LBS are kept concatenated (human first,
+        # hugs/renderer/gs_renderer.py:33-37)
+        self.opacity = leaf(torch.cat(opac))
+        self.shs = leaf(torch.cat(shs))
+        self.P = self.opacity.shape[0]
+        self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=True)
+        self.transl = d(h["transl"][0])
+        # per-frame inputs: pinned host copies (for e2e) and resident device copies (for value)
+        cam = wl["cam"]
+        self.tanfovx, self.tanfovy = cam["tanfovx"], cam["tanfovy"]
+        self.host = {k: cam[k].clone().pin_memory() for k in ("viewmatrix", "projmatrix", "campos", "bg")}
+        self.host["A"] = wl["A"].clone().pin_memory()
+        self.host["G"] = wl["G"].clone().pin_memory()
+        self.dev = {k: v.to(device) for k, v in self.host.items()}
+        self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host.values())
+
+    def leaves(self):
+        names = ["h_xyz", "h_rotmat", "h_scales", "h_weights", "s_means", "s_scales", "s_rots", "opacity", "shs"]
+        return {n: getattr(self, n) for n in names if getattr(self, n) is not None}
+
+    def zero_grad(self):
+        for p in self.leaves().values():
+            p.grad = None
+        self.means2D.grad = None
+
+    def frame(self, inp):
+        """One forward + backward of one view.  Returns the loss tensor (device)."""
+        A = inp["A"].requires_grad_(True)
+        xyz, rotq, hsc = self.lbs_impl(A, self.h_xyz, self.h_weights, self.h_rotmat, self.h_scales, self.transl)
+        if self.n_scene > 0:
+            means3D = torch.cat([xyz, self.s_means])
+            scales = torch.cat([hsc, self.s_scales])
+            rots = torch.cat([rotq, self.s_rots])
+        else:
+            means3D, scales, rots = xyz, hsc, rotq
+        settings = self.module.GaussianRasterizationSettings(
+            image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=inp["bg"],
+            scale_modifier=1.0, viewmatrix=inp["viewmatrix"], projmatrix=inp["projmatrix"], sh_degree=3,
+            campos=inp["campos"], prefiltered=False, debug=False)
+        color, radii = self.module.GaussianRasterizer(settings)(
+            means3D=means3D, means2D=self.means2D, opacities=self.opacity, shs=self.shs, scales=scales,
+            rotations=rots)
+        loss = (color * inp["G"]).sum()
+        loss.backward()
+        self.last_radii = radii
+        self.last_node = color.grad_fn
+        return loss.detach()
+
+    def step_resident(self):
+        self.zero_grad()
+        return self.frame(dict(self.dev))
+
+    def step_e2e(self):
+        self.zero_grad()
+        inp = {k: v.to(self.device, non_blocking=True) for k, v in self.host.items()}
+        loss = self.frame(inp)
+        return float(loss.item())  # device -> host read of the step's result (4 bytes, synchronises)
+
+    def allreduce_grads(self):
+        import torch.distributed as dist
+        if not dist.is_initialized() or dist.get_world_size() == 1:
+            return
+        for p in self.leaves().values():
+            dist.all_reduce(p.grad, op=dist.ReduceOp.SUM)
+
+
+def our_impl():
+    import diff_gaussian_rasterization as dgr
+    import hugs_b200
+
+    def lbs_impl(A, xyz, w, rotmat, scales, transl):
+        return hugs_b200.deform_gaussians(A, xyz, w, rotmat, scales, smpl_scale=1.0, transl=transl)
+
+    return dgr, lbs_impl
+
+
+def reference_impl():
+    """The unmodified reference: CUDA rasterizer build + PyTorch LBS chain (oracle/_ref)."""
+    import refutil
+
+    ref = refutil.load_ref_rasterizer()
+    lbs, rot = refutil.load_ref_lbs()
+
+    def lbs_impl(A, xyz, w, rotmat, scales, transl):
+        pose = torch.zeros(1, 72, device=xyz.device)
+        # hugs/models/hugs_trimlp.py:470-518 (smpl_scale = 1)
+        verts, _, T, _, _ = lbs.lbs_extra(A[None], xyz[None], None, w, pose, disable_posedirs=True, pose2rot=True)
+        dxyz = verts.squeeze(0) + transl[None]
+        T = T.squeeze(0)
+        return dxyz, rot.matrix_to_quaternion(T[:, :3, :3] @ rotmat), scales * 1.0
+
+    return ref, lbs_impl
+
+
+# ------------------------------------------------------------------------------------------------
+# roofline accounting (algorithmic bytes: SURVEY.md 8(d) / DESIGN.md "Algorithmic bytes")
+# ------------------------------------------------------------------------------------------------
+def stage_bytes(P, visible, R, W, H, n_human, sort_bits):
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    culled = P - visible
+    passes = (sort_bits + 7) // 8
+    return {
+        "lbs_forward": 172 * n_human,
+        "preprocess": 311 * visible + 20 * culled,
+        "inclusive_scan": 8 * P,
+        "duplicate_with_keys": 24 * P + 12 * R,
+        "sort_pairs": (8 + 24 * passes) * R,
+        "identify_tile_ranges": 8 * R + 8 * tiles,
+        "render_forward": 40 * R + 20 * W * H + 8 * tiles,
+        "render_backward": 76 * R + 20 * W * H,
+        "preprocess_backward": 559 * visible + 260 * culled,
+        "lbs_backward": 352 * n_human,
+    }
+
+
+def timed_loop(fn, steps, device, barrier):
+    """EXACTLY `steps` calls of fn between barrier+synchronize brackets, CUDA-event timed."""
+    barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(device)
+    barrier()
+    return e0.elapsed_time(e1)  # ms
+
+
+def cpu_oracle_frames(wl, seconds, min_frames=2):
+    """Time the CPU oracle port (oracle/splat_oracle.c, OpenMP) on full frames of the workload for
+    about `seconds`.  Returns (frames/s, threads, frames run)."""
+    from oracle import oracle as O
+    import numpy as np
+
+    h, cam = wl["human"], wl["cam"]
+    n = lambda t: t.detach().cpu().numpy()  # noqa: E731
+    W, H = wl["W"], wl["H"]
+    threads = os.cpu_count() or 1
+
+    def one():
+        xyz, q, hs, _ = O.lbs_forward(n(wl["A"]), n(h["xyz"]), n(h["lbs_weights"]), n(h["rotmat"]), n(h["scales"]),
+                                      n(h["transl"][0]), 1.0)
+        if wl["n_scene"] > 0:
+            s = wl["scene"]
+            means = np.concatenate([xyz, n(s["means3D"])])
+            scales = np.concatenate([hs, n(s["scales"])])
+            rots = np.concatenate([q, n(s["rotations"])])
+            opac = np.concatenate([n(h["opacity"]), n(s["opacity"])])
+            shs = np.concatenate([n(h["shs"]), n(s["shs"])])
+        else:
+            means, scales, rots, opac, shs = xyz, hs, q, n(h["opacity"]), n(h["shs"])
+        kw = dict(shs=shs, degree=3, scales=scales, rotations=rots)
+        fw = O.forward(means, opac, n(cam["viewmatrix"]), n(cam["projmatrix"]), n(cam["campos"]), n(cam["bg"]), W, H,
+                       cam["tanfovx"], cam["tanfovy"], **kw)
+        O.backward(fw, n(wl["G"]), means, n(cam["viewmatrix"]), n(cam["projmatrix"]), n(cam["campos"]), n(cam["bg"]),
+                   W, H, cam["tanfovx"], cam["tanfovy"], **kw)
+
+    one()  # warm-up (page-in, OpenMP pool)
+    t0 = time.perf_counter()
+    frames = 0
+    while frames < min_frames or (time.perf_counter() - t0) < seconds:
+        one()
+        frames += 1
+        if frames >= 200:
+            break
+    dt = time.perf_counter() - t0
+    return frames / dt, threads, frames
+
+
+# ------------------------------------------------------------------------------------------------
+# main
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != max(args.gpus, 1) and world > 1:
+        print("warning: --gpus %d but WORLD_SIZE=%d" % (args.gpus, world), file=sys.stderr)
+    n_gpus = world
+    n_human, n_scene, W, H, _ = WORKLOADS[args.workload]
+    config = {"workload": args.workload, "n_human": n_human, "n_scene": n_scene, "image": "%dx%d" % (W, H),
+              "sh_degree": 3, "views_per_rank_per_step": 1,
+              "parallelism": "dp%d (view batch; allreduce of parameter gradients)" % n_gpus,
+              "l2": "inputs larger than L2 (per-frame working set > 1 GB vs 126 MB L2), no flush"}
+
+    # ---- reference arm -------------------------------------------------------------------------
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        return run_reference(args, config)
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (our arm) needs a CUDA device: the product has no CPU path")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    from hugs_b200 import _native
+    module, lbs_impl = our_impl()
+    wl = make_workload(args.workload, rank, world, device)
+    rep = Replica(wl, device, module, lbs_impl)
+
+    def step_resident():
+        rep.step_resident()
+        rep.allreduce_grads()
+
+    def step_e2e():
+        rep.step_e2e()
+        rep.allreduce_grads()
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    torch.cuda.synchronize(device)
+    R = int(rep.last_node.num_rendered)
+    visible = int((rep.last_radii > 0).sum())
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    _native.launch_count(1)
+    ms = timed_loop(step_resident, args.steps, device, barrier)
+    launches = int(_native.launch_count(1))
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed_loop(step_e2e, args.steps, device, barrier)
+    clocks = sampler.stop() if sampler else None
+
+    # per-stage device times: same K steps again with the library's stage events switched on
+    _native.read_stage_times(reset=True)
+    _native.stage_timing_enable(1)
+    ms_staged = timed_loop(step_resident, args.steps, device, barrier)
+    _native.stage_timing_enable(0)
+    stage_ms = _native.read_stage_times(reset=True)
+
+    from hugs_b200 import dp
+    ms = dp.max_over_ranks(ms, device)
+    ms_e2e = dp.max_over_ranks(ms_e2e, device)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_kind = peaks()
+    sort_bits = int(_native.sort_bits(W, H))
+    nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits)
+    stages = {}
+    for name, (tot, calls) in stage_ms.items():
+        if calls == 0:
+            continue
+        per = tot / calls
+        gbs = nbytes[name] / (per * 1e-3) / 1e9
+        stages[name] = {"ms": round(per, 4), "bytes": int(nbytes[name]), "gbs": round(gbs, 1),
+                        "frac": round(gbs / peak, 4)}
+    dominant = max(stages, key=lambda k: stages[k]["ms"]) if stages else None
+    roofline = None
+    if dominant:
+        s = stages[dominant]
+        roofline = {"kernel": dominant, "bound": "hbm", "achieved": s["gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": s["frac"], "traffic": None, "peak_source": peak_kind,
+                    "ms_per_launch": s["ms"], "algorithmic_bytes": s["bytes"],
+                    "timed": "per-stage CUDA events on the launching stream, %d steps (%.3f ms/step with events on)"
+                             % (args.steps, ms_staged / args.steps)}
+    frame_bytes = sum(nbytes.values())
+    line = {
+        "metric": METRIC, "value": round(n_gpus * args.steps / (ms * 1e-3), 3), "unit": UNIT, "n_gpus": n_gpus,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": dict(config, P=rep.P, R=R, visible=visible, sort_bits=sort_bits),
+        "e2e": {"value": round(n_gpus * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
+                "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": 4 + 4,
+                "ms_per_step": round(ms_e2e / args.steps, 4)},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roofline,
+        "stages": stages,
+        "frame": {"algorithmic_bytes": int(frame_bytes),
+                  "hbm_frac": round(frame_bytes / (ms / args.steps * 1e-3) / 1e9 / peak, 4)},
+    }
+    if n_gpus == 1 and not args.no_cpu_baseline:
+        fps, threads, frames = cpu_oracle_frames(make_workload(args.workload, 0, 1, "cpu"), args.cpu_baseline_seconds)
+        line["cpu_baseline"] = {"value": round(fps, 4), "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": "%d full frames of %s (LBS fwd + raster fwd + bwd) on the C/OpenMP oracle"
+                                          % (frames, args.workload)}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_reference(args, config):
+    """Reference arm: the unmodified reference through its own public API (rank 0 only)."""
+    import refutil
+
+    n_human, n_scene, W, H, _ = WORKLOADS[args.workload]
+    base = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config}
+    if torch.cuda.is_available() and refutil.ref_available():
+        device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+        torch.cuda.set_device(device)
+        module, lbs_impl = reference_impl()
+        wl = make_workload(args.workload, 0, 1, device)
+        rep = Replica(wl, device, module, lbs_impl)
+        for _ in range(max(args.warmup, 3)):
+            rep.step_resident()
+        sampler = ClockSampler(device.index or 0)
+        sampler.start()
+        ms = timed_loop(rep.step_resident, args.steps, device, lambda: None)
+        for _ in range(2):
+            rep.step_e2e()
+        ms_e2e = timed_loop(rep.step_e2e, args.steps, device, lambda: None)
+        clocks = sampler.stop()
+        v = args.steps / (ms * 1e-3)
+        ve = args.steps / (ms_e2e * 1e-3)
+        base.update({
+            "value": round(v, 3), "ms_per_step": round(ms / args.steps, 4), "clocks": clocks,
+            "e2e": {"value": round(ve, 3), "unit": UNIT, "h2d_bytes_per_step": int(rep.h2d_bytes),
+                    "d2h_bytes_per_step": 8, "ms_per_step": round(ms_e2e / args.steps, 4)},
+            "cpu_baseline": {"value": round(ve, 3), "unit": UNIT, "cores": 0, "kind": "reference",
+                             "sample": "the reference has no CPU rasterizer: this is its own CUDA build "
+                                       "(oracle/_ref, unmodified sources, sm_100) + its PyTorch LBS chain on the "
+                                       "same B200, full frames of " + args.workload},
+            "reference_device": "cuda",
+        })
+        base["config"] = dict(config, P=rep.P, R=int(rep.last_node.num_rendered))
+        print(json.dumps(base), flush=True)
+        return 0
+    # no GPU or no reference build: the CPU oracle port on the host cores
+    fps, threads, frames = cpu_oracle_frames(make_workload(args.workload, 0, 1, "cpu"),
+                                             max(10.0, args.cpu_baseline_seconds), min_frames=max(args.steps, 2))
+    base.update({
+        "value": round(fps, 4), "ms_per_step": round(1e3 / fps, 3),
+        "e2e": {"value": round(fps, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "cpu_baseline": {"value": round(fps, 4), "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": "%d full frames on the C/OpenMP oracle port" % frames},
+        "reference_device": "cpu",
+    })
+    print(json.dumps(base), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

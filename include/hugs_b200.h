@@ -242,9 +242,22 @@ int hugs_b200_lbs_backward(int F, int N, int J,
                            float* d_scales, float* d_transl, float* d_smpl_scale,
                            hugs_b200_stream_t stream);
 
-/* Number of kernel launches issued by this library on the calling thread since the last reset
+/* Number of kernel launches issued by this library (all host threads) since the last reset
  * (bench.py reports it as gpu_launches). */
 long long hugs_b200_launch_count(int reset);
+
+/* ---------------------------------------------------------------------------------------------
+ * Per-stage device timing (measurement aid; the reference has no counterpart -- SURVEY.md 5.1).
+ * While enabled, each stage of the calls above is bracketed by two CUDA events recorded on the
+ * caller's stream.  hugs_b200_stage_timing_read waits for the recorded events, adds them to the
+ * per-stage totals and copies the totals out (ms_sum / calls: HUGS_B200_NUM_STAGES entries each).
+ * Stage order: preprocess, inclusive_scan, duplicate_with_keys, sort_pairs, identify_tile_ranges,
+ * render_forward, render_backward, preprocess_backward, lbs_forward, lbs_backward.
+ * ------------------------------------------------------------------------------------------- */
+#define HUGS_B200_NUM_STAGES 10
+int         hugs_b200_stage_timing_enable(int on); /* returns the previous setting */
+int         hugs_b200_stage_timing_read(double* ms_sum, long long* calls, int reset);
+const char* hugs_b200_stage_name(int stage);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

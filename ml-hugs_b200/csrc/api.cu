@@ -4,14 +4,18 @@
 #include "../../include/hugs_b200.h"
 #include "common.cuh"
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 namespace hb {
 
 static thread_local char g_error[512] = "";
-static thread_local long long g_launches = 0;
+// Process-wide: torch.autograd runs the backward call on its own worker thread.
+static std::atomic<long long> g_launches{0};
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -19,7 +23,79 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_error, sizeof(g_error), fmt, ap);
     va_end(ap);
 }
-void count_launch(int n) { g_launches += n; }
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- optional per-stage device timing ------------------------------------------------------
+// When enabled (hugs_b200_stage_timing_enable), every stage is bracketed by a pair of CUDA events
+// recorded on the stream the stage is launched on; hugs_b200_stage_timing_read drains the pairs.
+// bench.py uses this for the per-stage roofline numbers.  Off by default: no events, no cost.
+enum Stage {
+    ST_PREPROCESS = 0,
+    ST_SCAN,
+    ST_DUPLICATE,
+    ST_SORT,
+    ST_RANGES,
+    ST_RENDER_FWD,
+    ST_RENDER_BWD,
+    ST_PREPROCESS_BWD,
+    ST_LBS_FWD,
+    ST_LBS_BWD,
+    ST_COUNT
+};
+static_assert(ST_COUNT == HUGS_B200_NUM_STAGES, "stage table out of sync with the header");
+static const char* const kStageNames[ST_COUNT] = {
+    "preprocess", "inclusive_scan", "duplicate_with_keys", "sort_pairs", "identify_tile_ranges",
+    "render_forward", "render_backward", "preprocess_backward", "lbs_forward", "lbs_backward"};
+
+struct StageTimer {
+    std::mutex mu;
+    std::atomic<int> enabled{0};
+    struct Pair {
+        int stage;
+        cudaEvent_t a, b;
+    };
+    std::vector<Pair> pending;
+    std::vector<cudaEvent_t> free_events;
+    double ms[ST_COUNT] = {0};
+    long long calls[ST_COUNT] = {0};
+
+    cudaEvent_t get() {
+        if (!free_events.empty()) {
+            cudaEvent_t e = free_events.back();
+            free_events.pop_back();
+            return e;
+        }
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        return e;
+    }
+};
+static StageTimer g_timer;
+
+struct StageScope {
+    int stage;
+    cudaStream_t stream;
+    cudaEvent_t a = nullptr;
+    StageScope(int st, cudaStream_t s) : stage(st), stream(s) {
+        if (g_timer.enabled.load(std::memory_order_relaxed)) {
+            std::lock_guard<std::mutex> lk(g_timer.mu);
+            a = g_timer.get();
+            if (a) cudaEventRecord(a, stream);
+        }
+    }
+    ~StageScope() {
+        if (a) {
+            std::lock_guard<std::mutex> lk(g_timer.mu);
+            cudaEvent_t b = g_timer.get();
+            if (b) {
+                cudaEventRecord(b, stream);
+                g_timer.pending.push_back({stage, a, b});
+            } else {
+                g_timer.free_events.push_back(a);
+            }
+        }
+    }
+};
 
 // ---- workspace carving ---------------------------------------------------------------------
 // All slices are 256-byte aligned relative to the buffer base (the base itself comes from the
@@ -115,9 +191,14 @@ static Camera make_camera(const float* view, const float* proj, const float* cam
     return c;
 }
 
-#define HB_STAGE(call, name)                                                                  \
+#define HB_STAGE(call, stage_id)                                                              \
     do {                                                                                      \
-        int _rc = (call);                                                                     \
+        const char* name = kStageNames[stage_id];                                             \
+        int _rc;                                                                              \
+        {                                                                                     \
+            StageScope _scope(stage_id, stream);                                              \
+            _rc = (call);                                                                     \
+        }                                                                                     \
         if (_rc) return _rc;                                                                  \
         if (debug) {                                                                          \
             cudaError_t _e = cudaStreamSynchronize(stream);                                   \
@@ -138,9 +219,36 @@ int hugs_b200_abi_version(void) { return HUGS_B200_ABI_VERSION; }
 const char* hugs_b200_last_error(void) { return g_error; }
 
 long long hugs_b200_launch_count(int reset) {
-    const long long v = g_launches;
-    if (reset) g_launches = 0;
-    return v;
+    return reset ? g_launches.exchange(0) : g_launches.load();
+}
+
+int hugs_b200_stage_timing_enable(int on) { return g_timer.enabled.exchange(on ? 1 : 0); }
+
+const char* hugs_b200_stage_name(int stage) {
+    return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : nullptr;
+}
+
+int hugs_b200_stage_timing_read(double* ms_sum, long long* calls, int reset) {
+    std::lock_guard<std::mutex> lk(g_timer.mu);
+    for (const StageTimer::Pair& p : g_timer.pending) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+            g_timer.ms[p.stage] += ms;
+            g_timer.calls[p.stage] += 1;
+        }
+        g_timer.free_events.push_back(p.a);
+        g_timer.free_events.push_back(p.b);
+    }
+    g_timer.pending.clear();
+    for (int i = 0; i < ST_COUNT; i++) {
+        if (ms_sum) ms_sum[i] = g_timer.ms[i];
+        if (calls) calls[i] = g_timer.calls[i];
+        if (reset) {
+            g_timer.ms[i] = 0;
+            g_timer.calls[i] = 0;
+        }
+    }
+    return ST_COUNT;
 }
 
 int hugs_b200_geom_layout_of(int P, hugs_b200_geom_layout* out) {
@@ -285,10 +393,10 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         HB_STAGE(launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
                                    (scales && rotations) ? nullptr : cov3D_precomp, colors_precomp, cam, radii, geom,
                                    prefiltered != 0, stream),
-                 "preprocess");
+                 ST_PREPROCESS);
         HB_STAGE(launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_temp,
                                        geom.scan_temp_bytes, stream),
-                 "inclusive_scan");
+                 ST_SCAN);
 
         // Number of (Gaussian, tile) pairs must reach the host to size the binning workspace
         // (rasterizer_impl.cu:281); pinned landing pad + the caller's stream instead of a
@@ -326,11 +434,11 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         uint32_t* v_dst = (passes % 2 == 0) ? bin.list_unsorted : bin.list;
         HB_STAGE(launch_duplicate(P, geom.means2D, geom.depths, geom.point_offsets, radii, k_src, v_src, cam.grid_x,
                                   cam.grid_y, stream),
-                 "duplicate_with_keys");
+                 ST_DUPLICATE);
         bool in_input = false;
         HB_STAGE(launch_sort_pairs_pingpong(k_src, v_src, k_dst, v_dst, R, end_bit, bin.sort_temp, bin.sort_temp_bytes,
                                             stream, &in_input),
-                 "sort_pairs");
+                 ST_SORT);
         const bool landed_in_keys = in_input ? (k_src == bin.keys) : (k_dst == bin.keys);
         if (!landed_in_keys) {
             HB_CUDA_OK(cudaMemcpyAsync(bin.keys, bin.keys_unsorted, sizeof(uint64_t) * (size_t)R,
@@ -339,7 +447,7 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                        cudaMemcpyDeviceToDevice, stream));
         }
     }
-    HB_STAGE(launch_tile_ranges(R, bin.keys, img.ranges, num_tiles, stream), "identify_tile_ranges");
+    HB_STAGE(launch_tile_ranges(R, bin.keys, img.ranges, num_tiles, stream), ST_RANGES);
 
     const float* feature_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
     const int stride = colors_precomp != nullptr ? 3 : 4;
@@ -350,7 +458,7 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                    P > 0 ? geom.means2D : nullptr, feature_ptr, stride,
                                    P > 0 ? geom.conic_opacity : nullptr, img.accum_alpha, img.n_contrib, background,
                                    out_color, stream),
-             "render_forward");
+             ST_RENDER_FWD);
     *num_rendered = R;
     return 0;
 }
@@ -385,24 +493,25 @@ int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* backgr
     const BinningView bin = carve_binning(binning_buffer, R);
     const ImageView img = carve_image(image_buffer, width, height);
 
-    // The blend backward accumulates into these with atomics.
-    HB_CUDA_OK(cudaMemsetAsync(dL_dmean2D, 0, sizeof(float) * 3 * (size_t)P, stream));
-    HB_CUDA_OK(cudaMemsetAsync(dL_dconic, 0, sizeof(float) * 4 * (size_t)P, stream));
-    HB_CUDA_OK(cudaMemsetAsync(dL_dopacity, 0, sizeof(float) * (size_t)P, stream));
-    HB_CUDA_OK(cudaMemsetAsync(dL_dcolor, 0, sizeof(float) * 3 * (size_t)P, stream));
-
     const float* color_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
     const int stride = colors_precomp != nullptr ? 3 : 4;
-    if (R > 0) {
-        HB_STAGE(launch_render_backward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y, background,
-                                        geom.means2D, geom.conic_opacity, color_ptr, stride, img.accum_alpha,
-                                        img.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, stream),
-                 "render_backward");
-    }
+    // The blend backward accumulates into these with atomics, so they are cleared first (part of
+    // the stage's cost).
+    auto blend_backward = [&]() -> int {
+        HB_CUDA_OK(cudaMemsetAsync(dL_dmean2D, 0, sizeof(float) * 3 * (size_t)P, stream));
+        HB_CUDA_OK(cudaMemsetAsync(dL_dconic, 0, sizeof(float) * 4 * (size_t)P, stream));
+        HB_CUDA_OK(cudaMemsetAsync(dL_dopacity, 0, sizeof(float) * (size_t)P, stream));
+        HB_CUDA_OK(cudaMemsetAsync(dL_dcolor, 0, sizeof(float) * 3 * (size_t)P, stream));
+        if (R <= 0) return 0;
+        return launch_render_backward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y, background,
+                                      geom.means2D, geom.conic_opacity, color_ptr, stride, img.accum_alpha,
+                                      img.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, stream);
+    };
+    HB_STAGE(blend_backward(), ST_RENDER_BWD);
     HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,
                                         rotations, scale_modifier, cov3D_precomp, cam, dL_dmean2D, dL_dconic,
                                         dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, stream),
-             "preprocess_backward");
+             ST_PREPROCESS_BWD);
     return 0;
 }
 
@@ -414,6 +523,7 @@ int hugs_b200_lbs_forward(int F, int N, int J, const float* A, const float* xyz,
         set_error("lbs_forward: null pointer argument");
         return HUGS_B200_EINVAL;
     }
+    StageScope scope(ST_LBS_FWD, static_cast<cudaStream_t>(stream));
     return launch_lbs_forward(F, N, J, A, xyz, weights, rotmat, scales, transl, smpl_scale, out_xyz, out_rotq,
                               out_scales, out_T, static_cast<cudaStream_t>(stream));
 }
@@ -427,6 +537,7 @@ int hugs_b200_lbs_backward(int F, int N, int J, const float* A, const float* xyz
         set_error("lbs_backward: null pointer argument");
         return HUGS_B200_EINVAL;
     }
+    StageScope scope(ST_LBS_BWD, static_cast<cudaStream_t>(stream));
     return launch_lbs_backward(F, N, J, A, xyz, weights, rotmat, scales, transl, smpl_scale, g_xyz, g_rotq, g_scales,
                                dA, d_xyz, d_weights, d_rotmat, d_scales, d_transl, d_smpl_scale,
                                static_cast<cudaStream_t>(stream));

@@ -105,7 +105,22 @@ lbs_forward = _sig("hugs_b200_lbs_forward", i32, [
 lbs_backward = _sig("hugs_b200_lbs_backward", i32, [
     i32, i32, i32, fp, fp, fp, fp, fp, fp, C.c_float, fp, fp, fp, fp, fp, fp, fp, fp, fp, fp, fp])
 
+NUM_STAGES = 10
+stage_timing_enable = _sig("hugs_b200_stage_timing_enable", i32, [i32])
+stage_timing_read = _sig("hugs_b200_stage_timing_read", i32, [C.POINTER(C.c_double), C.POINTER(C.c_longlong), i32])
+stage_name = _sig("hugs_b200_stage_name", C.c_char_p, [i32])
+
+
+def read_stage_times(reset=True):
+    """{stage name: (total ms, calls)} accumulated while stage timing was enabled."""
+    ms = (C.c_double * NUM_STAGES)()
+    calls = (C.c_longlong * NUM_STAGES)()
+    stage_timing_read(ms, calls, int(bool(reset)))
+    return {stage_name(i).decode(): (float(ms[i]), int(calls[i])) for i in range(NUM_STAGES)}
+
+
 EXPORTED_SYMBOLS = [
+    "hugs_b200_stage_timing_enable", "hugs_b200_stage_timing_read", "hugs_b200_stage_name",
     "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
     "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_mark_visible",
     "hugs_b200_geom_layout_of", "hugs_b200_image_layout_of", "hugs_b200_binning_layout_of",

@@ -1,0 +1,118 @@
+"""View-batch data parallelism for the splat hot path (one process per GPU, one 8xB200 box).
+
+The reference is single-process, single-GPU, one view per step (hugs/trainer/gs_trainer.py:226-236;
+no torch.distributed anywhere in the tree).  The path shards only across views: every rank holds a
+full replica of the Gaussian parameters, renders its share of the step's views (a single view is
+never split), accumulates parameter gradients locally in fp32 and then takes part in ONE
+allreduce(sum) of the flat gradient buffer (NCCL over NVLink/NVSwitch on the GPU box, gloo in the CPU
+tests).  Nothing else is exchanged: forward-only configs (novel-pose animation, scene rendering)
+shard frames with no collective at all.
+"""
+from typing import Dict, Iterable, List, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
+    """Round-robin assignment of the step's view (or pose-frame) indices to ranks."""
+    if not (0 <= rank < world_size):
+        raise ValueError("rank %d outside world of %d" % (rank, world_size))
+    return list(range(rank, n_views, world_size))
+
+
+class FlatGradBuffer:
+    """All parameter gradients of a replica in one contiguous fp32 buffer.
+
+    ``params`` maps names to leaf tensors.  Each leaf's ``.grad`` is made a view into the flat
+    buffer, so autograd accumulates the per-view gradients in place and the allreduce needs no
+    gather/scatter copies.  Order is the insertion order of ``params`` (identical on every rank).
+    """
+
+    def __init__(self, params: Dict[str, torch.Tensor]):
+        self.names = list(params.keys())
+        self.params = params
+        leaves = [params[n] for n in self.names]
+        if not leaves:
+            raise ValueError("no parameters")
+        dev = leaves[0].device
+        for n, p in params.items():
+            if p.dtype != torch.float32 or p.device != dev or not p.is_leaf:
+                raise ValueError("parameter %s must be a float32 leaf on %s" % (n, dev))
+        # 128-byte aligned slices so every view can be read with 128-bit loads
+        self.offsets, off = [], 0
+        for p in leaves:
+            self.offsets.append(off)
+            off += (p.numel() + 31) // 32 * 32
+        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        for p, o in zip(leaves, self.offsets):
+            p.grad = self.flat[o:o + p.numel()].view_as(p)
+
+    @property
+    def nbytes(self) -> int:
+        return self.flat.numel() * 4
+
+    def zero_(self):
+        self.flat.zero_()
+
+    def grads(self) -> Dict[str, torch.Tensor]:
+        return {n: self.params[n].grad for n in self.names}
+
+    def allreduce(self, group=None, async_op=False):
+        """Sum over ranks (the DP gradient exchange).  No-op without an initialised process group or
+        with a single rank."""
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return None
+        return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+
+def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, world_size: int,
+            group=None) -> float:
+    """One data-parallel step: ``render_view(v)`` must return the scalar loss tensor of view ``v``
+    (forward through LBS + rasterizer); this rank handles ``shard_views`` of ``views``, calls
+    backward on each loss (gradients accumulate in ``buf``), then allreduces.  Returns the local
+    loss sum."""
+    buf.zero_()
+    total = 0.0
+    for i in shard_views(len(views), rank, world_size):
+        loss = render_view(views[i])
+        loss.backward()
+        total += float(loss.detach())
+    buf.allreduce(group)
+    return total
+
+
+def init_from_env(backend: str = None):
+    """torchrun-style initialisation (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT).
+    Returns (rank, local_rank, world_size)."""
+    import os
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
+    return rank, local, world
+
+
+def max_over_ranks(value: float, device=None) -> float:
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(values: Iterable[float], device=None) -> List[float]:
+    vals = [float(v) for v in values]
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return vals
+    t = torch.tensor(vals, dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return [float(x) for x in t.tolist()]
