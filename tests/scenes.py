@@ -56,18 +56,20 @@ def run_module(sc, module, backward=True, colors_precomp=None, cov3D_precomp=Non
     """Run a diff_gaussian_rasterization-shaped module (ours or the reference) through its public API
     and return outputs + gradients + the three opaque buffers."""
     names = ["means3D", "scales", "rotations", "opacity", "shs"]
-    t = {k: sc[k].detach().clone().requires_grad_(backward) for k in names}
-    means2D = torch.zeros_like(t["means3D"], requires_grad=backward)
+    # inputs always require grad so that the autograd node (which holds the three opaque buffers and
+    # num_rendered) exists even when backward is not run
+    t = {k: sc[k].detach().clone().float().requires_grad_(True) for k in names}
+    means2D = torch.zeros_like(t["means3D"], requires_grad=True)
     settings = settings_of(sc, module)
     rast = module.GaussianRasterizer(settings)
     kw = dict(means3D=t["means3D"], means2D=means2D, opacities=t["opacity"])
     if colors_precomp is not None:
-        cp = colors_precomp.detach().clone().requires_grad_(backward)
+        cp = colors_precomp.detach().clone().requires_grad_(True)
         kw["colors_precomp"] = cp
     else:
         kw["shs"] = t["shs"]
     if cov3D_precomp is not None:
-        c3 = cov3D_precomp.detach().clone().requires_grad_(backward)
+        c3 = cov3D_precomp.detach().clone().requires_grad_(True)
         kw["cov3D_precomp"] = c3
     else:
         kw["scales"] = t["scales"]
