@@ -424,7 +424,7 @@ def main():
     for name, (tot, calls) in stage_ms.items():
         if calls == 0:
             continue
-        per = tot / calls
+        per = tot / args.steps  # a stage may be entered more than once per frame (the two sort levels)
         gbs = nbytes[name] / (per * 1e-3) / 1e9
         stages[name] = {"ms": round(per, 4), "bytes": int(nbytes[name]), "gbs": round(gbs, 1),
                         "frac": round(gbs / peak, 4)}

@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 1
+#define HUGS_B200_ABI_VERSION 2
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -154,8 +154,10 @@ typedef struct hugs_b200_geom_layout {
     size_t rgb;            /* f32x4[P]   (r,g,b,unused) from SH                         */
     size_t clamped;        /* u8   [P]   bit c set <=> channel c clamped at 0           */
     size_t tiles_touched;  /* u32  [P]                                                  */
-    size_t point_offsets;  /* u32  [P]   inclusive prefix sum of tiles_touched          */
+    size_t point_offsets;  /* u32  [P]   inclusive prefix sum of tiles_touched, in depth-sorted order */
     size_t scan_temp;      /* decoupled look-back state                                 */
+    size_t sorted_depths;  /* u32  [P]   depth bits ascending (culled Gaussians 0xFFFFFFFF, last) */
+    size_t perm;           /* u32  [P]   Gaussian index at each depth-sorted position   */
     size_t total;          /* bytes required                                            */
 } hugs_b200_geom_layout;
 
@@ -176,8 +178,30 @@ typedef struct hugs_b200_binning_layout {
 } hugs_b200_binning_layout;
 
 int hugs_b200_geom_layout_of(int P, hugs_b200_geom_layout* out);
+/* The binning workspace is laid out for a CAPACITY of pairs that may exceed the R of the call that
+ * filled it (see hugs_b200_set_binning_mode); this recovers the capacity from the buffer size so that
+ * hugs_b200_binning_layout_of(capacity) describes the buffer.  point_list always sits at offset 0. */
+size_t hugs_b200_binning_capacity_of(size_t nbytes);
 int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out);
 int hugs_b200_binning_layout_of(int R, hugs_b200_binning_layout* out);
+
+/* ---------------------------------------------------------------------------------------------
+ * How the forward pass bins (Gaussian, tile) pairs.  All three produce bit-identical keys, lists,
+ * ranges and images; they differ in structure and in when the host learns R.
+ *   ASYNC      (default) depth argsort of the P Gaussians, pairs emitted in depth order, stable sort
+ *              of the pairs on the tile bits only; the workspace is sized from the pair counts of
+ *              earlier calls with the same (P, W, H), the whole stage is enqueued before R reaches
+ *              the host, R is checked before returning and an overflow is redone with the exact size.
+ *   SYNC       same kernels, but the host waits for R before sizing the workspace (what
+ *              cuda_rasterizer/rasterizer_impl.cu:281 does).
+ *   REFERENCE  the reference's structure: pairs emitted in Gaussian-index order, one sort over all
+ *              32+bit key bits (rasterizer_impl.cu:289-308), host waits for R.
+ * Returns the previous mode, or HUGS_B200_EINVAL.  Process-wide.
+ * ------------------------------------------------------------------------------------------- */
+#define HUGS_B200_BINNING_ASYNC     0
+#define HUGS_B200_BINNING_SYNC      1
+#define HUGS_B200_BINNING_REFERENCE 2
+int hugs_b200_set_binning_mode(int mode);
 
 /* ---------------------------------------------------------------------------------------------
  * Stand-alone stages, exported so each can be parity-tested and timed on its own.

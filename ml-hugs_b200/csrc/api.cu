@@ -120,6 +120,12 @@ GeomView carve_geom(char* base, int P) {
     g.point_offsets = take<uint32_t>(p, n);
     g.scan_temp_bytes = scan_temp_bytes(P);
     g.scan_temp = take<char>(p, g.scan_temp_bytes);
+    g.sorted_depths = take<uint32_t>(p, n);
+    g.perm = take<uint32_t>(p, n);
+    g.dsort_keys_tmp = take<uint32_t>(p, n);
+    g.dsort_vals_tmp = take<uint32_t>(p, n);
+    g.dsort_temp_bytes = sort_temp_bytes(P);
+    g.dsort_temp = take<char>(p, g.dsort_temp_bytes);
     g.total = (size_t)(p - base);
     return g;
 }
@@ -140,8 +146,8 @@ BinningView carve_binning(char* base, int R) {
     BinningView b;
     char* p = base;
     const size_t n = (size_t)(R > 0 ? R : 0);
+    b.list = take<uint32_t>(p, n);  // first: the backward pass finds it without knowing the capacity
     b.keys = take<uint64_t>(p, n);
-    b.list = take<uint32_t>(p, n);
     b.keys_unsorted = take<uint64_t>(p, n);
     b.list_unsorted = take<uint32_t>(p, n);
     b.sort_temp_bytes = sort_temp_bytes(R);
@@ -171,6 +177,54 @@ static int* pinned_counter() {
         if (cudaHostAlloc(reinterpret_cast<void**>(&p), 64, cudaHostAllocDefault) != cudaSuccess) p = nullptr;
     }
     return p;
+}
+
+// Event that marks "the pair count has landed in the pinned counter" (one per host thread).
+static cudaEvent_t count_event() {
+    static thread_local cudaEvent_t e = nullptr;
+    if (e == nullptr) {
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) e = nullptr;
+    }
+    return e;
+}
+
+static std::atomic<int> g_binning_mode{HUGS_B200_BINNING_ASYNC};
+
+// Pair-count history per (P, W, H): capacity = recent maximum + 25 % slack, decaying slowly.
+struct CapacityHint {
+    int P, W, H, cap;
+    unsigned long long stamp;
+};
+static thread_local CapacityHint g_hints[8];
+static thread_local unsigned long long g_hint_clock = 0;
+
+static int capacity_hint(int P, int W, int H) {
+    for (CapacityHint& h : g_hints)
+        if (h.cap > 0 && h.P == P && h.W == W && h.H == H) {
+            h.stamp = ++g_hint_clock;
+            return h.cap;
+        }
+    return 0;
+}
+
+static void update_capacity_hint(int P, int W, int H, int R) {
+    const long long want_ll = (long long)R + R / 4 + 4096;
+    const int want = want_ll > 0x7fff0000LL ? 0x7fff0000 : (int)want_ll;
+    CapacityHint* slot = nullptr;
+    for (CapacityHint& h : g_hints)
+        if (h.cap > 0 && h.P == P && h.W == W && h.H == H) slot = &h;
+    if (slot == nullptr) {
+        slot = &g_hints[0];
+        for (CapacityHint& h : g_hints)
+            if (h.stamp < slot->stamp) slot = &h;
+        slot->cap = 0;
+    }
+    const int decayed = (int)(slot->cap * 0.98);
+    slot->P = P;
+    slot->W = W;
+    slot->H = H;
+    slot->cap = want > decayed ? want : decayed;
+    slot->stamp = ++g_hint_clock;
 }
 
 static Camera make_camera(const float* view, const float* proj, const float* campos, int W, int H, float tan_fovx,
@@ -222,6 +276,22 @@ long long hugs_b200_launch_count(int reset) {
     return reset ? g_launches.exchange(0) : g_launches.load();
 }
 
+int hugs_b200_set_binning_mode(int mode) {
+    if (mode < HUGS_B200_BINNING_ASYNC || mode > HUGS_B200_BINNING_REFERENCE) return HUGS_B200_EINVAL;
+    return g_binning_mode.exchange(mode);
+}
+
+size_t hugs_b200_binning_capacity_of(size_t nbytes) {
+    // largest capacity whose layout fits in nbytes (the layout size is monotone in the capacity)
+    size_t lo = 0, hi = nbytes / 24 + 1;
+    while (lo < hi) {
+        const size_t mid = lo + (hi - lo + 1) / 2;
+        if (mid <= 0x7fffffffULL && carve_binning(nullptr, (int)mid).total <= nbytes) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
 int hugs_b200_stage_timing_enable(int on) { return g_timer.enabled.exchange(on ? 1 : 0); }
 
 const char* hugs_b200_stage_name(int stage) {
@@ -262,8 +332,10 @@ int hugs_b200_geom_layout_of(int P, hugs_b200_geom_layout* out) {
     out->tiles_touched = (size_t)reinterpret_cast<char*>(g.tiles_touched);
     out->point_offsets = (size_t)reinterpret_cast<char*>(g.point_offsets);
     out->scan_temp = (size_t)g.scan_temp;
+    out->sorted_depths = (size_t)reinterpret_cast<char*>(g.sorted_depths);
+    out->perm = (size_t)reinterpret_cast<char*>(g.perm);
     out->total = g.total;
-    return 9;
+    return 11;
 }
 
 int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out) {
@@ -382,7 +454,19 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     BinningView bin;
     memset(&geom, 0, sizeof(geom));
     memset(&bin, 0, sizeof(bin));
+    const int tile_bits = (int)higher_msb((uint32_t)num_tiles);
+    const int mode = g_binning_mode.load(std::memory_order_relaxed);
+    // Two-level binning (depth argsort of the Gaussians + tile-bit sort of the pairs) needs the packed
+    // rectangle format of the duplicate kernel; otherwise fall back to the reference's structure.
+    const bool two_level = (mode != HUGS_B200_BINNING_REFERENCE) && cam.grid_x <= 1023 && cam.grid_y <= 1023;
+    uint32_t* R_dev = nullptr;
+    int* pinned = pinned_counter();
+    cudaEvent_t ev = count_event();
     if (P > 0) {
+        if (!pinned || !ev) {
+            set_error("rasterize_forward: could not create the pinned counter / event");
+            return HUGS_B200_ENOMEM;
+        }
         char* geom_base = geometry_buffer(geometry_user, carve_geom(nullptr, P).total);
         if (!geom_base) {
             set_error("rasterize_forward: geometry buffer callback returned NULL");
@@ -394,71 +478,115 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                    (scales && rotations) ? nullptr : cov3D_precomp, colors_precomp, cam, radii, geom,
                                    prefiltered != 0, stream),
                  ST_PREPROCESS);
-        HB_STAGE(launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_temp,
-                                       geom.scan_temp_bytes, stream),
-                 ST_SCAN);
-
-        // Number of (Gaussian, tile) pairs must reach the host to size the binning workspace
-        // (rasterizer_impl.cu:281); pinned landing pad + the caller's stream instead of a
-        // blocking cudaMemcpy on the legacy stream.
-        int* pinned = pinned_counter();
-        if (pinned) {
-            HB_CUDA_OK(cudaMemcpyAsync(pinned, geom.point_offsets + (P - 1), sizeof(int), cudaMemcpyDeviceToHost, stream));
-            HB_CUDA_OK(cudaStreamSynchronize(stream));
-            R = *pinned;
-        } else {
-            HB_CUDA_OK(cudaMemcpyAsync(&R, geom.point_offsets + (P - 1), sizeof(int), cudaMemcpyDeviceToHost, stream));
-            HB_CUDA_OK(cudaStreamSynchronize(stream));
+        if (two_level) {
+            HB_STAGE(launch_depth_argsort(reinterpret_cast<const uint32_t*>(geom.depths), geom.dsort_keys_tmp,
+                                          geom.dsort_vals_tmp, geom.sorted_depths, geom.perm, P, geom.dsort_temp,
+                                          geom.dsort_temp_bytes, stream),
+                     ST_SORT);
         }
+        HB_STAGE(launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_temp,
+                                       geom.scan_temp_bytes, stream, two_level ? geom.perm : nullptr),
+                 ST_SCAN);
+        // The number of (Gaussian, tile) pairs must reach the host (rasterizer_impl.cu:281): async copy
+        // into pinned memory on the caller's stream + an event, instead of a blocking cudaMemcpy.
+        R_dev = geom.point_offsets + (P - 1);
+        HB_CUDA_OK(cudaMemcpyAsync(pinned, R_dev, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        HB_CUDA_OK(cudaEventRecord(ev, stream));
+    }
+    bool R_known = (P == 0);
+    auto wait_R = [&]() -> int {
+        HB_CUDA_OK(cudaEventSynchronize(ev));
+        R = *pinned;
+        R_known = true;
         if (R < 0) {
             set_error("rasterize_forward: more than 2^31 (Gaussian, tile) pairs");
             return HUGS_B200_EUNSUP;
         }
+        return 0;
+    };
+    // Workspace capacity: in the default mode it comes from the pair counts of earlier calls with the
+    // same (P, W, H), so everything below is enqueued before the count has arrived; the count is
+    // checked before returning and an overflow is redone with the exact size.
+    int cap = 0;
+    if (P > 0 && two_level && mode == HUGS_B200_BINNING_ASYNC && !debug) cap = capacity_hint(P, width, height);
+    if (cap <= 0 && !R_known) {
+        const int rc = wait_R();
+        if (rc) return rc;
+        cap = R;
     }
-
-    char* bin_base = binning_buffer(binning_user, carve_binning(nullptr, R).total);
-    if (!bin_base) {
-        set_error("rasterize_forward: binning buffer callback returned NULL");
-        return HUGS_B200_ENOMEM;
-    }
-    bin = carve_binning(bin_base, R);
-
-    if (R > 0) {
-        const int end_bit = 32 + (int)higher_msb((uint32_t)num_tiles);
-        // The sort ping-pongs between the two key/value buffers; emit the unsorted pairs into the
-        // one that makes the last pass land in (keys, list).
-        const int passes = cdiv(end_bit, 8);
-        uint64_t* k_src = (passes % 2 == 0) ? bin.keys : bin.keys_unsorted;
-        uint32_t* v_src = (passes % 2 == 0) ? bin.list : bin.list_unsorted;
-        uint64_t* k_dst = (passes % 2 == 0) ? bin.keys_unsorted : bin.keys;
-        uint32_t* v_dst = (passes % 2 == 0) ? bin.list_unsorted : bin.list;
-        HB_STAGE(launch_duplicate(P, geom.means2D, geom.depths, geom.point_offsets, radii, k_src, v_src, cam.grid_x,
-                                  cam.grid_y, stream),
-                 ST_DUPLICATE);
-        bool in_input = false;
-        HB_STAGE(launch_sort_pairs_pingpong(k_src, v_src, k_dst, v_dst, R, end_bit, bin.sort_temp, bin.sort_temp_bytes,
-                                            stream, &in_input),
-                 ST_SORT);
-        const bool landed_in_keys = in_input ? (k_src == bin.keys) : (k_dst == bin.keys);
-        if (!landed_in_keys) {
-            HB_CUDA_OK(cudaMemcpyAsync(bin.keys, bin.keys_unsorted, sizeof(uint64_t) * (size_t)R,
-                                       cudaMemcpyDeviceToDevice, stream));
-            HB_CUDA_OK(cudaMemcpyAsync(bin.list, bin.list_unsorted, sizeof(uint32_t) * (size_t)R,
-                                       cudaMemcpyDeviceToDevice, stream));
-        }
-    }
-    HB_STAGE(launch_tile_ranges(R, bin.keys, img.ranges, num_tiles, stream), ST_RANGES);
-
     const float* feature_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
     const int stride = colors_precomp != nullptr ? 3 : 4;
-    if (P == 0) {
-        feature_ptr = nullptr;
+    if (P == 0) feature_ptr = nullptr;
+    for (;;) {
+        char* bin_base = binning_buffer(binning_user, carve_binning(nullptr, cap).total);
+        if (!bin_base) {
+            set_error("rasterize_forward: binning buffer callback returned NULL");
+            return HUGS_B200_ENOMEM;
+        }
+        bin = carve_binning(bin_base, cap);
+        const uint32_t* n_dev = nullptr;
+        if (cap > 0 && two_level) {
+            n_dev = R_dev;
+            const SortPassPlan plan = tile_pass_plan(tile_bits);
+            // the last pass must land in (keys, list)
+            const bool even = (plan.num_passes % 2 == 0);
+            uint64_t* k0 = even ? bin.keys : bin.keys_unsorted;
+            uint32_t* v0 = even ? bin.list : bin.list_unsorted;
+            uint64_t* k1 = even ? bin.keys_unsorted : bin.keys;
+            uint32_t* v1 = even ? bin.list_unsorted : bin.list;
+            auto emit = [&]() -> int {
+                const int rc = sort_temp_clear(bin.sort_temp, bin.sort_temp_bytes, cap, stream);
+                if (rc) return rc;
+                return launch_duplicate_sorted(P, geom.perm, geom.sorted_depths, geom.point_offsets, geom.means2D, radii,
+                                               k0, v0, cam.grid_x, cam.grid_y, cap, plan,
+                                               sort_temp_histogram(bin.sort_temp), stream);
+            };
+            HB_STAGE(emit(), ST_DUPLICATE);
+            bool in_first = true;
+            HB_STAGE(launch_tile_sort(k0, v0, k1, v1, cap, n_dev, plan, bin.sort_temp, bin.sort_temp_bytes, stream,
+                                      &in_first),
+                     ST_SORT);
+            if ((in_first ? k0 : k1) != bin.keys) {
+                set_error("rasterize_forward: internal error, sorted pairs landed in the wrong buffer");
+                return HUGS_B200_EINVAL;
+            }
+        } else if (cap > 0) {
+            // Reference structure: pairs emitted in Gaussian-index order, one sort on all 32+bit key bits.
+            const int end_bit = 32 + tile_bits;
+            const int passes = cdiv(end_bit, 8);
+            uint64_t* k_src = (passes % 2 == 0) ? bin.keys : bin.keys_unsorted;
+            uint32_t* v_src = (passes % 2 == 0) ? bin.list : bin.list_unsorted;
+            uint64_t* k_dst = (passes % 2 == 0) ? bin.keys_unsorted : bin.keys;
+            uint32_t* v_dst = (passes % 2 == 0) ? bin.list_unsorted : bin.list;
+            HB_STAGE(launch_duplicate(P, geom.means2D, geom.depths, geom.point_offsets, radii, k_src, v_src, cam.grid_x,
+                                      cam.grid_y, stream),
+                     ST_DUPLICATE);
+            bool in_input = false;
+            HB_STAGE(launch_sort_pairs_pingpong(k_src, v_src, k_dst, v_dst, cap, end_bit, bin.sort_temp,
+                                                bin.sort_temp_bytes, stream, &in_input),
+                     ST_SORT);
+            const bool landed_in_keys = in_input ? (k_src == bin.keys) : (k_dst == bin.keys);
+            if (!landed_in_keys) {
+                HB_CUDA_OK(cudaMemcpyAsync(bin.keys, bin.keys_unsorted, sizeof(uint64_t) * (size_t)cap,
+                                           cudaMemcpyDeviceToDevice, stream));
+                HB_CUDA_OK(cudaMemcpyAsync(bin.list, bin.list_unsorted, sizeof(uint32_t) * (size_t)cap,
+                                           cudaMemcpyDeviceToDevice, stream));
+            }
+        }
+        HB_STAGE(launch_tile_ranges(cap, bin.keys, img.ranges, num_tiles, stream, n_dev), ST_RANGES);
+        HB_STAGE(launch_render_forward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y,
+                                       P > 0 ? geom.means2D : nullptr, feature_ptr, stride,
+                                       P > 0 ? geom.conic_opacity : nullptr, img.accum_alpha, img.n_contrib,
+                                       background, out_color, stream),
+                 ST_RENDER_FWD);
+        if (!R_known) {
+            const int rc = wait_R();
+            if (rc) return rc;
+        }
+        if (R <= cap) break;
+        cap = R;  // the hint was too small: redo the binning with the exact size
     }
-    HB_STAGE(launch_render_forward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y,
-                                   P > 0 ? geom.means2D : nullptr, feature_ptr, stride,
-                                   P > 0 ? geom.conic_opacity : nullptr, img.accum_alpha, img.n_contrib, background,
-                                   out_color, stream),
-             ST_RENDER_FWD);
+    if (P > 0) update_capacity_hint(P, width, height, R);
     *num_rendered = R;
     return 0;
 }

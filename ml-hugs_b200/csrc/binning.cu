@@ -74,6 +74,91 @@ __global__ void __launch_bounds__(kDupThreads)
     }
 }
 
+// Depth-sorted variant used by the rasterizer: CTA b owns the Gaussians at depth-sorted positions
+// [256 b, 256 b + 256) (`perm` = argsort of the depth bits, `sorted_depth` the sorted bits, `offsets`
+// the inclusive scan of tiles_touched in that order).  Pairs therefore leave this kernel ordered by
+// (depth bits, Gaussian index), and a stable sort on the tile bits alone reproduces the reference's
+// order on the full 32+bit key.  While emitting, the CTA also counts the tile digits of the
+// following sort passes (`plan`) into `hist`, so the sort needs no histogram pass of its own.
+// Emission is clamped to `cap` slots: the workspace is sized from the previous frames' pair count
+// before the real count has reached the host (api.cu); an overflow is detected there and redone.
+__global__ void __launch_bounds__(kDupThreads)
+    duplicate_sorted_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ sorted_depth,
+                            const uint32_t* __restrict__ offsets, const float2* __restrict__ means2D,
+                            const int* __restrict__ radii, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                            unsigned grid_x, unsigned grid_y, uint32_t cap, const SortPassPlan plan,
+                            uint32_t* __restrict__ hist) {
+    __shared__ uint32_t s_off[kDupThreads + 1];
+    __shared__ uint32_t s_depth[kDupThreads];
+    __shared__ uint32_t s_rect[kDupThreads];
+    __shared__ uint32_t s_idx[kDupThreads];
+    __shared__ uint32_t s_hist[3][256];
+    const int tid = threadIdx.x;
+    const unsigned lane = tid & 31u;
+    const int first = blockIdx.x * kDupThreads;
+    const int pos = first + tid;
+    for (int i = tid; i < plan.num_passes * 256; i += kDupThreads) s_hist[i >> 8][i & 255] = 0;
+    uint32_t end_off = 0;
+    if (pos < P) {
+        end_off = __ldg(offsets + pos);
+        const uint32_t idx = __ldg(perm + pos);
+        const int r = __ldg(radii + idx);
+        uint32_t rect = 0;
+        if (r > 0) {
+            // getRect (auxiliary.h:46-56), same float sequence as preprocess.
+            const float2 p = __ldg(means2D + idx);
+            const float rf = (float)r;
+            const unsigned min_x = min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.x, -rf), 0.0625f)));
+            const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
+            const unsigned max_x = min(
+                grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
+            rect = min_x | (min_y << 10) | ((max_x - min_x) << 20);
+        }
+        s_rect[tid] = rect;
+        s_depth[tid] = __ldg(sorted_depth + pos);
+        s_idx[tid] = idx;
+    }
+    if (tid == 0) s_off[0] = (first == 0) ? 0u : __ldg(offsets + first - 1);
+    const int in_block = min(kDupThreads, P - first);
+    if (tid < in_block) s_off[tid + 1] = end_off;
+    __syncthreads();
+    const uint32_t begin = s_off[0];
+    const uint32_t end = min(s_off[in_block], cap);
+    for (uint32_t ob = begin; ob < end; ob += kDupThreads) {
+        const uint32_t o = ob + tid;
+        const bool valid = o < end;
+        const unsigned active = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+            int lo = 0, hi = in_block;  // invariant: s_off[lo] <= o < s_off[hi]
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (s_off[mid] <= o) lo = mid; else hi = mid;
+            }
+            const uint32_t rect = s_rect[lo];
+            const uint32_t k = o - s_off[lo];
+            const uint32_t w = rect >> 20;
+            const uint32_t y = ((rect >> 10) & 1023u) + k / w;
+            const uint32_t x = (rect & 1023u) + k % w;
+            const uint32_t tile = y * grid_x + x;
+            keys[o] = ((uint64_t)tile << 32) | (uint64_t)s_depth[lo];
+            vals[o] = s_idx[lo];
+#pragma unroll
+            for (int p = 0; p < 3; p++) {
+                if (p < plan.num_passes) {
+                    const uint32_t d = (tile >> (plan.shift[p] - 32)) & ((1u << plan.bits[p]) - 1u);
+                    const unsigned peers = __match_any_sync(active, d);
+                    if (lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < plan.num_passes * 256; i += kDupThreads) {
+        const uint32_t c = s_hist[i >> 8][i & 255];
+        if (c) atomicAdd(hist + i, c);
+    }
+}
+
 // Generic fallback for tile grids wider than 1023 tiles per axis (images beyond 16K pixels):
 // one thread per Gaussian, the reference's loop.
 __global__ void __launch_bounds__(kDupThreads)
@@ -107,7 +192,9 @@ __global__ void __launch_bounds__(kDupThreads)
 // Two keys per thread, 128-bit loads; the neighbour comes from the previous thread's pair or one
 // extra (cached) load.
 __global__ void __launch_bounds__(256)
-    tile_ranges_kernel(int R, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
+    tile_ranges_kernel(int R, const uint32_t* __restrict__ n_dev, const uint64_t* __restrict__ keys,
+                       uint2* __restrict__ ranges) {
+    if (n_dev != nullptr) R = (int)min((uint32_t)R, __ldg(n_dev));  // R was the capacity
     const int i0 = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
     if (i0 >= R) return;
     uint64_t k0, k1 = 0;
@@ -156,10 +243,28 @@ int launch_duplicate(int P, const float2* means2D, const float* depths, const ui
     return 0;
 }
 
-int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream) {
+int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* sorted_depth, const uint32_t* offsets,
+                            const float2* means2D, const int* radii, uint64_t* keys, uint32_t* vals, int grid_x,
+                            int grid_y, int cap, const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream) {
+    if (P <= 0) return 0;
+    if (grid_x > 1023 || grid_y > 1023 || plan.num_passes > 3) {
+        set_error("duplicate_sorted: tile grid %dx%d too large", grid_x, grid_y);
+        return HUGS_B200_EUNSUP_INTERNAL;
+    }
+    duplicate_sorted_kernel<<<cdiv(P, kDupThreads), kDupThreads, 0, stream>>>(
+        P, perm, sorted_depth, offsets, means2D, radii, keys, vals, (unsigned)grid_x, (unsigned)grid_y, (uint32_t)cap,
+        plan, hist);
+    HB_LAUNCH_OK("duplicate_with_keys", stream, false);
+    return 0;
+}
+
+// R is the pair count, or -- when n_dev is given -- the capacity the launch is sized for while the
+// real count is read from device memory.
+int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream,
+                       const uint32_t* n_dev) {
     HB_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
     if (R <= 0) return 0;
-    tile_ranges_kernel<<<cdiv(cdiv(R, 2), 256), 256, 0, stream>>>(R, keys, ranges);
+    tile_ranges_kernel<<<cdiv(cdiv(R, 2), 256), 256, 0, stream>>>(R, n_dev, keys, ranges);
     HB_LAUNCH_OK("identify_tile_ranges", stream, false);
     return 0;
 }

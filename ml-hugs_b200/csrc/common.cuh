@@ -9,6 +9,7 @@
 #define HB_TILE_Y 16
 #define HB_TILE_PIX (HB_TILE_X * HB_TILE_Y)
 #define HB_ALIGN 256
+#define HUGS_B200_EUNSUP_INTERNAL (-3)
 
 namespace hb {
 
@@ -51,9 +52,15 @@ struct GeomView {
     float4* rgb;
     uint8_t* clamped;
     uint32_t* tiles_touched;
-    uint32_t* point_offsets;
+    uint32_t* point_offsets;  // inclusive scan of tiles_touched in depth-sorted order
     char* scan_temp;
     size_t scan_temp_bytes;
+    uint32_t* sorted_depths;  // depth bits, ascending (culled Gaussians: 0xFFFFFFFF, last)
+    uint32_t* perm;           // Gaussian index at each depth-sorted position
+    uint32_t* dsort_keys_tmp;
+    uint32_t* dsort_vals_tmp;
+    char* dsort_temp;
+    size_t dsort_temp_bytes;
     size_t total;
 };
 struct ImageView {
@@ -75,6 +82,13 @@ GeomView carve_geom(char* base, int P);
 ImageView carve_image(char* base, int W, int H);
 BinningView carve_binning(char* base, int R);
 
+constexpr int kSortMaxPasses = 8;
+struct SortPassPlan {  // pass p sorts on `bits[p]` key bits starting at bit `shift[p]`
+    int num_passes;
+    int shift[kSortMaxPasses];
+    int bits[kSortMaxPasses];
+};
+
 // ---- stage launchers (one per .cu file) ----------------------------------------------------
 struct Camera {
     const float* view;   // 16 floats, device
@@ -94,14 +108,27 @@ int launch_mark_visible(int P, const float* means3D, const float* view, const fl
 
 size_t scan_temp_bytes(int n);
 int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
-                          cudaStream_t stream);
+                          cudaStream_t stream, const uint32_t* gather = nullptr);
 
 int launch_duplicate(int P, const float2* means2D, const float* depths, const uint32_t* offsets,
                      const int* radii, uint64_t* keys, uint32_t* vals, int grid_x, int grid_y,
                      cudaStream_t stream);
-int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream);
+int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* sorted_depth, const uint32_t* offsets,
+                            const float2* means2D, const int* radii, uint64_t* keys, uint32_t* vals, int grid_x,
+                            int grid_y, int cap, const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream);
+int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream,
+                       const uint32_t* n_dev = nullptr);
 
+// ---- radix sort (radix_sort.cu) ------------------------------------------------------------------
 size_t sort_temp_bytes(int n);
+SortPassPlan tile_pass_plan(int tile_bits);  // passes over key bits [32, 32+tile_bits)
+int sort_temp_clear(void* temp, size_t temp_bytes, int n_cap, cudaStream_t stream);
+uint32_t* sort_temp_histogram(void* temp);   // [kSortMaxPasses][256] digit counts, filled by the duplicate kernel
+int launch_depth_argsort(const uint32_t* keys0, uint32_t* kB, uint32_t* vB, uint32_t* kC, uint32_t* vC, int P,
+                         void* temp, size_t temp_bytes, cudaStream_t stream);
+int launch_tile_sort(uint64_t* k0, uint32_t* v0, uint64_t* k1, uint32_t* v1, int n_cap, const uint32_t* n_dev,
+                     const SortPassPlan& plan, void* temp, size_t temp_bytes, cudaStream_t stream,
+                     bool* result_in_first);
 int launch_sort_pairs_pingpong(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
                                int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream,
                                bool* result_in_input);

@@ -147,6 +147,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessArgs a)
         }
         a.radii[idx] = 0;
         a.tiles_touched[idx] = 0;
+        a.depths[idx] = __uint_as_float(0xFFFFFFFFu);  // depth-sort key of a culled Gaussian: last
         return;
     }
 
@@ -218,6 +219,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessArgs a)
     if (det == 0.0f) {
         a.radii[idx] = 0;
         a.tiles_touched[idx] = 0;
+        a.depths[idx] = __uint_as_float(0xFFFFFFFFu);  // depth-sort key of a culled Gaussian: last
         return;
     }
     const float det_inv = __frcp_rn(det);
@@ -248,6 +250,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessArgs a)
     if (tiles == 0) {
         a.radii[idx] = 0;
         a.tiles_touched[idx] = 0;
+        a.depths[idx] = __uint_as_float(0xFFFFFFFFu);  // depth-sort key of a culled Gaussian: last
         return;
     }
 

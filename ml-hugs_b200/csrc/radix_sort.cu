@@ -1,19 +1,30 @@
-// Hand-written onesweep-style LSD radix sort of (u64 key, u32 value) pairs for sm_100a.
+// Hand-written onesweep-style LSD radix sort for sm_100a (u32 or u64 keys, u32 payload).
 // Replaces cub::DeviceRadixSort::SortPairs at cuda_rasterizer/rasterizer_impl.cu:303-308
 // (CUB is used only as a correctness oracle in tests/).
 //
-// Structure (8-bit digits):
-//   1. one histogram kernel reads the keys once and builds the digit histogram of every pass;
-//   2. a tiny kernel turns each histogram into exclusive bin offsets;
-//   3. one scatter kernel per pass.  Each CTA owns a 4096-pair tile (atomic ticket order),
-//      ranks its keys stably with warp-level match_any + per-warp counters, obtains the
-//      tile's per-digit global offset by decoupled look-back over 64-bit (flag|count) words,
-//      stages the tile digit-sorted in shared memory and writes it out in coalesced runs.
+// Building blocks:
+//   * radix_histogram_kernel   one read of the keys builds the digit histogram of every pass;
+//   * radix_offsets_kernel     histogram -> exclusive bin offsets (one CTA per pass);
+//   * radix_onesweep_kernel    one scatter pass.  Each CTA owns a 4096-pair tile (atomic ticket
+//     order), ranks its keys stably with warp-level match_any + per-warp counters, obtains the
+//     tile's per-digit global offset by decoupled look-back over 64-bit (flag|count) words, stages
+//     the tile digit-sorted in shared memory and writes it out in coalesced runs.
 // Stability: a tile is loaded warp-striped (warp w owns 512 consecutive pairs, item k of lane l
-// is pair 32k+l), items are ranked in k order and lanes in lane order, warps in warp order,
-// tiles in ticket == index order.
-// Algorithmic traffic: 8 B/pair (histogram) + 24 B/pair/pass.
+// is pair 32k+l), items are ranked in k order and lanes in lane order, warps in warp order, tiles
+// in ticket == index order.
+//
+// The pair count may live in device memory (`n_dev`): the grid is then sized for a capacity and
+// CTAs beyond the real count retire immediately.  That is what lets the rasterizer enqueue the
+// whole binning stage before the number of (Gaussian, tile) pairs has reached the host.
+//
+// How the rasterizer uses it (api.cu): the reference sorts R pairs on 32+bit key bits
+// (tile | depth) in one go.  The same order -- tile ascending, then depth bits ascending, ties in
+// ascending Gaussian index -- is produced here by (1) sorting the P Gaussians once by depth bits
+// (u32 keys, 4 passes over P items), (2) emitting the pairs in that order and (3) a stable sort
+// of the R pairs on the tile bits only (2 passes at 1080p instead of 6).  See DESIGN.md.
 #include "common.cuh"
+
+#include <cstring>
 
 namespace hb {
 
@@ -24,9 +35,9 @@ constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kSortItems = 16;
 constexpr int kSortTile = kSortThreads * kSortItems;  // 4096 pairs
-constexpr int kMaxPasses = 8;
 constexpr int kHistThreads = 512;
 static_assert(kSortThreads == kRadix, "one thread per digit in the look-back phase");
+static_assert(kSortMaxPasses == 8, "header constant");
 
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
     unsigned long long v;
@@ -38,32 +49,28 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned l
 }
 
 // ---- 1. histograms of all passes in one read of the keys --------------------------------------
-__global__ void __launch_bounds__(kHistThreads) radix_histogram_kernel(const uint64_t* __restrict__ keys, int n,
-                                                                       int num_passes, int end_bit,
-                                                                       uint32_t* __restrict__ hist) {
-    __shared__ uint32_t s_hist[kMaxPasses * kRadix];
-    for (int i = threadIdx.x; i < num_passes * kRadix; i += kHistThreads) s_hist[i] = 0;
+// Pass p looks at `bits[p]` key bits starting at `shift[p]`.
+using PassPlan = SortPassPlan;
+
+template <typename KeyT>
+__global__ void __launch_bounds__(kHistThreads)
+    radix_histogram_kernel(const KeyT* __restrict__ keys, int n, const PassPlan plan, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t s_hist[kSortMaxPasses * kRadix];
+    for (int i = threadIdx.x; i < plan.num_passes * kRadix; i += kHistThreads) s_hist[i] = 0;
     __syncthreads();
     const int stride = gridDim.x * kHistThreads;
-    // Bits at and above end_bit are not part of the sort: mask them so the last digit matches
-    // what the scatter pass extracts.
-    const uint64_t keep = (end_bit >= 64) ? ~0ull : ((1ull << end_bit) - 1ull);
-    const int n2 = n >> 1;  // 128-bit loads, two keys each
-    for (int i = blockIdx.x * kHistThreads + threadIdx.x; i < n2; i += stride) {
-        const ulonglong2 kk = __ldg(reinterpret_cast<const ulonglong2*>(keys) + i);
-        const uint64_t k0 = kk.x & keep, k1 = kk.y & keep;
-        for (int p = 0; p < num_passes; p++) {
-            atomicAdd(&s_hist[p * kRadix + (int)((k0 >> (p * kRadixBits)) & (kRadix - 1))], 1u);
-            atomicAdd(&s_hist[p * kRadix + (int)((k1 >> (p * kRadixBits)) & (kRadix - 1))], 1u);
+    for (int i = blockIdx.x * kHistThreads + threadIdx.x; i < n; i += stride) {
+        const KeyT k = __ldg(keys + i);
+#pragma unroll
+        for (int p = 0; p < kSortMaxPasses; p++) {
+            if (p < plan.num_passes) {
+                const uint32_t d = (uint32_t)(k >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u);
+                atomicAdd(&s_hist[p * kRadix + d], 1u);
+            }
         }
     }
-    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-        const uint64_t k0 = keys[n - 1] & keep;
-        for (int p = 0; p < num_passes; p++)
-            atomicAdd(&s_hist[p * kRadix + (int)((k0 >> (p * kRadixBits)) & (kRadix - 1))], 1u);
-    }
     __syncthreads();
-    for (int i = threadIdx.x; i < num_passes * kRadix; i += kHistThreads) {
+    for (int i = threadIdx.x; i < plan.num_passes * kRadix; i += kHistThreads) {
         const uint32_t c = s_hist[i];
         if (c) atomicAdd(&hist[i], c);
     }
@@ -89,8 +96,9 @@ __global__ void __launch_bounds__(kRadix) radix_offsets_kernel(uint32_t* __restr
 }
 
 // ---- 3. one scatter pass ---------------------------------------------------------------------
+template <typename KeyT>
 struct SortSmem {
-    uint64_t keys[kSortTile];               // 32 KB
+    KeyT keys[kSortTile];                   // 32 KB (u64) / 16 KB (u32)
     uint32_t vals[kSortTile];               // 16 KB
     uint32_t warp_hist[kSortWarps][kRadix]; //  8 KB
     uint32_t local_start[kRadix];           //  1 KB  first staged slot of each digit
@@ -99,28 +107,37 @@ struct SortSmem {
     unsigned tile;
 };
 
+// vals_in == nullptr means "the payload of item i is i" (first pass of an argsort).
+template <typename KeyT>
 __global__ void __launch_bounds__(kSortThreads)
-    radix_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                          uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n, int shift,
-                          uint32_t digit_mask, int pass, const uint32_t* __restrict__ pass_offsets,
-                          unsigned long long* lookback, unsigned* tickets) {
+    radix_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                          KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n_host,
+                          const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask, int pass,
+                          const uint32_t* __restrict__ pass_offsets, unsigned long long* lookback,
+                          unsigned* tickets) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    SortSmem& s = *reinterpret_cast<SortSmem*>(smem_raw);
+    SortSmem<KeyT>& s = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31, warp = tid >> 5;
     const unsigned lanemask_lt = (1u << lane) - 1u;
+
+    // n_host is the capacity the grid was sized for when the real count lives on the device
+    int n = n_host;
+    if (n_dev != nullptr) n = (int)min((uint32_t)n_host, __ldg(n_dev));
 
     if (tid == 0) s.tile = atomicAdd(tickets + pass, 1u);
 #pragma unroll
     for (int w = 0; w < kSortWarps; w++) s.warp_hist[w][tid] = 0;
     __syncthreads();
     const int tile = (int)s.tile;
-    const int tile_base = tile * kSortTile;
+    const long long tile_base_ll = (long long)tile * kSortTile;
+    if (tile_base_ll >= (long long)n) return;  // beyond the real count: nothing to do, nobody waits on us
+    const int tile_base = (int)tile_base_ll;
     const int warp_base = tile_base + (int)warp * (32 * kSortItems);
     const bool full_tile = tile_base + kSortTile <= n;
 
     // Load keys, warp-striped.
-    uint64_t key[kSortItems];
+    KeyT key[kSortItems];
     if (full_tile) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) key[k] = __ldg(keys_in + warp_base + k * 32 + lane);
@@ -128,7 +145,7 @@ __global__ void __launch_bounds__(kSortThreads)
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
             const int i = warp_base + k * 32 + (int)lane;
-            key[k] = (i < n) ? __ldg(keys_in + i) : ~0ull;
+            key[k] = (i < n) ? __ldg(keys_in + i) : (KeyT)~(KeyT)0;
         }
     }
 
@@ -209,7 +226,7 @@ __global__ void __launch_bounds__(kSortThreads)
             const uint32_t d = (uint32_t)(key[k] >> shift) & digit_mask;
             const uint32_t pos = s.local_start[d] + s.warp_hist[warp][d] + rank[k];
             s.keys[pos] = key[k];
-            s.vals[pos] = __ldg(vals_in + i);
+            s.vals[pos] = (vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
         }
     }
     __syncthreads();
@@ -220,7 +237,7 @@ __global__ void __launch_bounds__(kSortThreads)
     for (int k = 0; k < kSortItems; k++) {
         const int i = k * kSortThreads + tid;
         if (i < count) {
-            const uint64_t kk = s.keys[i];
+            const KeyT kk = s.keys[i];
             const uint32_t d = (uint32_t)(kk >> shift) & digit_mask;
             const int64_t g = s.bin_base[d] + i;
             keys_out[g] = kk;
@@ -230,8 +247,8 @@ __global__ void __launch_bounds__(kSortThreads)
 }
 
 struct SortTemp {
-    uint32_t* hist;        // [kMaxPasses][kRadix]
-    unsigned* tickets;     // [kMaxPasses]
+    uint32_t* hist;                // [kSortMaxPasses][kRadix]
+    unsigned* tickets;             // [kSortMaxPasses]
     unsigned long long* lookback;  // [tiles][kRadix]
     size_t bytes;
 };
@@ -240,64 +257,165 @@ SortTemp carve_sort_temp(void* temp, int n) {
     SortTemp t;
     char* p = reinterpret_cast<char*>(temp);
     t.hist = reinterpret_cast<uint32_t*>(p);
-    p += align_up(sizeof(uint32_t) * kMaxPasses * kRadix);
+    p += align_up(sizeof(uint32_t) * kSortMaxPasses * kRadix);
     t.tickets = reinterpret_cast<unsigned*>(p);
-    p += align_up(sizeof(unsigned) * kMaxPasses);
+    p += align_up(sizeof(unsigned) * kSortMaxPasses);
     t.lookback = reinterpret_cast<unsigned long long*>(p);
     const int tiles = cdiv(n > 0 ? n : 1, kSortTile);
     p += align_up(sizeof(unsigned long long) * (size_t)tiles * kRadix);
     t.bytes = (size_t)(p - reinterpret_cast<char*>(temp));
     return t;
 }
+
+template <typename KeyT>
+int configure_smem() {
+    static bool done = false;  // per instantiation; the attribute is per device function, idempotent
+    if (!done) {
+        HB_CUDA_OK(cudaFuncSetAttribute(radix_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(SortSmem<KeyT>)));
+        done = true;
+    }
+    return 0;
+}
+
+// Run the scatter passes of `plan` (histogram already in t.hist, raw counts).  Pairs ping-pong
+// between (k0,v0) and (k1,v1) starting from (k0,v0); v0 may be nullptr for "payload = index".
+template <typename KeyT>
+int run_passes(KeyT* k0, uint32_t* v0, KeyT* k1, uint32_t* v1, int n_cap, const uint32_t* n_dev,
+               const SortPassPlan& plan, const SortTemp& t, cudaStream_t stream, bool* result_in_first) {
+    int rc = configure_smem<KeyT>();
+    if (rc) return rc;
+    radix_offsets_kernel<<<plan.num_passes, kRadix, 0, stream>>>(t.hist);
+    HB_LAUNCH_OK("radix_offsets", stream, false);
+    const int tiles = cdiv(n_cap, kSortTile);
+    KeyT* kbuf[2] = {k0, k1};
+    uint32_t* vbuf[2] = {v0, v1};
+    int cur = 0;
+    for (int p = 0; p < plan.num_passes; p++) {
+        const uint32_t mask = (1u << plan.bits[p]) - 1u;
+        radix_onesweep_kernel<KeyT><<<tiles, kSortThreads, sizeof(SortSmem<KeyT>), stream>>>(
+            kbuf[cur], vbuf[cur], kbuf[cur ^ 1], vbuf[cur ^ 1], n_cap, n_dev, plan.shift[p], mask, p,
+            t.hist + p * kRadix, t.lookback, t.tickets);
+        HB_LAUNCH_OK("radix_onesweep", stream, false);
+        cur ^= 1;
+    }
+    const bool in_first = (cur == 0);
+    *result_in_first = in_first;
+    return 0;
+}
 }  // namespace
 
 size_t sort_temp_bytes(int n) { return carve_sort_temp(nullptr, n).bytes; }
 
-// Sorts on key bits [0, end_bit).  The pairs ping-pong between (keys_in, vals_in) and
-// (keys_out, vals_out); *result_in_input tells the caller where they ended up.
+SortPassPlan tile_pass_plan(int tile_bits) {
+    SortPassPlan sp;
+    memset(&sp, 0, sizeof(sp));
+    if (tile_bits <= 0) return sp;
+    const int n = cdiv(tile_bits, kRadixBits);
+    const int base = tile_bits / n, extra = tile_bits % n;
+    int shift = 32;
+    for (int p = 0; p < n; p++) {
+        sp.shift[p] = shift;
+        sp.bits[p] = base + (p < extra ? 1 : 0);
+        shift += sp.bits[p];
+    }
+    sp.num_passes = n;
+    return sp;
+}
+
+int sort_temp_clear(void* temp, size_t temp_bytes, int n_cap, cudaStream_t stream) {
+    const SortTemp t = carve_sort_temp(temp, n_cap);
+    if (temp == nullptr || temp_bytes < t.bytes) {
+        set_error("sort: temp storage too small (%zu < %zu)", temp_bytes, t.bytes);
+        return -1;
+    }
+    HB_CUDA_OK(cudaMemsetAsync(temp, 0, t.bytes, stream));
+    return 0;
+}
+
+uint32_t* sort_temp_histogram(void* temp) { return carve_sort_temp(temp, 1).hist; }
+
+// Stable argsort of the P depth keys (u32).  keys0 is read only; the sorted keys land in kC and the
+// permutation (original indices) in vC.  kB/vB are scratch.
+int launch_depth_argsort(const uint32_t* keys0, uint32_t* kB, uint32_t* vB, uint32_t* kC, uint32_t* vC, int P,
+                         void* temp, size_t temp_bytes, cudaStream_t stream) {
+    if (P <= 0) return 0;
+    int rc = sort_temp_clear(temp, temp_bytes, P, stream);
+    if (rc) return rc;
+    const SortTemp t = carve_sort_temp(temp, P);
+    SortPassPlan sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.num_passes = 4;
+    for (int p = 0; p < 4; p++) {
+        sp.shift[p] = 8 * p;
+        sp.bits[p] = 8;
+    }
+    int hist_blocks = cdiv(P, kHistThreads * 8);
+    if (hist_blocks > 148 * 2) hist_blocks = 148 * 2;
+    radix_histogram_kernel<uint32_t><<<hist_blocks, kHistThreads, 0, stream>>>(keys0, P, sp, t.hist);
+    HB_LAUNCH_OK("radix_histogram", stream, false);
+    rc = configure_smem<uint32_t>();
+    if (rc) return rc;
+    radix_offsets_kernel<<<4, kRadix, 0, stream>>>(t.hist);
+    HB_LAUNCH_OK("radix_offsets", stream, false);
+    const int tiles = cdiv(P, kSortTile);
+    const size_t sm = sizeof(SortSmem<uint32_t>);
+    // keys0 -> B -> C -> B -> C
+    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(keys0, nullptr, kB, vB, P, nullptr, 0, 255u, 0,
+                                                                         t.hist, t.lookback, t.tickets);
+    HB_LAUNCH_OK("radix_onesweep", stream, false);
+    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(kB, vB, kC, vC, P, nullptr, 8, 255u, 1,
+                                                                         t.hist + kRadix, t.lookback, t.tickets);
+    HB_LAUNCH_OK("radix_onesweep", stream, false);
+    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(kC, vC, kB, vB, P, nullptr, 16, 255u, 2,
+                                                                         t.hist + 2 * kRadix, t.lookback, t.tickets);
+    HB_LAUNCH_OK("radix_onesweep", stream, false);
+    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(kB, vB, kC, vC, P, nullptr, 24, 255u, 3,
+                                                                         t.hist + 3 * kRadix, t.lookback, t.tickets);
+    HB_LAUNCH_OK("radix_onesweep", stream, false);
+    return 0;
+}
+
+// Stable sort of the emitted pairs on the tile bits only.  The digit histograms were accumulated
+// by the duplicate kernel into sort_temp_histogram(temp) (cleared by sort_temp_clear before it).
+// The pairs start in (k0,v0); *result_in_first tells where they end up.
+int launch_tile_sort(uint64_t* k0, uint32_t* v0, uint64_t* k1, uint32_t* v1, int n_cap, const uint32_t* n_dev,
+                     const SortPassPlan& plan, void* temp, size_t temp_bytes, cudaStream_t stream,
+                     bool* result_in_first) {
+    *result_in_first = true;
+    if (n_cap <= 0 || plan.num_passes <= 0) return 0;
+    const SortTemp t = carve_sort_temp(temp, n_cap);
+    if (temp == nullptr || temp_bytes < t.bytes) {
+        set_error("tile_sort: temp storage too small (%zu < %zu)", temp_bytes, t.bytes);
+        return -1;
+    }
+    return run_passes<uint64_t>(k0, v0, k1, v1, n_cap, n_dev, plan, t, stream, result_in_first);
+}
+
+// Generic entry (C ABI hugs_b200_sort_pairs): sorts on key bits [0, end_bit) with 8-bit digits.
+// The pairs ping-pong between (keys_in, vals_in) and (keys_out, vals_out); *result_in_input tells
+// the caller where they ended up.
 int launch_sort_pairs_pingpong(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
                                int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream,
                                bool* result_in_input) {
     *result_in_input = true;
     if (n <= 0 || end_bit <= 0) return 0;
     if (end_bit > 64) end_bit = 64;
-    const int num_passes = cdiv(end_bit, kRadixBits);
+    int rc = sort_temp_clear(temp, temp_bytes, n, stream);
+    if (rc) return rc;
     const SortTemp t = carve_sort_temp(temp, n);
-    if (temp == nullptr || temp_bytes < t.bytes) {
-        set_error("sort_pairs: temp storage too small (%zu < %zu)", temp_bytes, t.bytes);
-        return -1;
+    SortPassPlan sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.num_passes = cdiv(end_bit, kRadixBits);
+    for (int p = 0; p < sp.num_passes; p++) {
+        sp.shift[p] = p * kRadixBits;
+        sp.bits[p] = (end_bit - sp.shift[p]) < kRadixBits ? (end_bit - sp.shift[p]) : kRadixBits;
     }
-    if ((reinterpret_cast<uintptr_t>(keys_in) & 15u) || (reinterpret_cast<uintptr_t>(keys_out) & 15u)) {
-        set_error("sort_pairs: key buffers must be 16-byte aligned");
-        return -1;
-    }
-    HB_CUDA_OK(cudaFuncSetAttribute(radix_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)sizeof(SortSmem)));
-    HB_CUDA_OK(cudaMemsetAsync(temp, 0, t.bytes, stream));
-    int hist_blocks = cdiv(n, kHistThreads * 2 * 8);
+    int hist_blocks = cdiv(n, kHistThreads * 8);
     if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;
-    if (hist_blocks < 1) hist_blocks = 1;
-    radix_histogram_kernel<<<hist_blocks, kHistThreads, 0, stream>>>(keys_in, n, num_passes, end_bit, t.hist);
+    radix_histogram_kernel<uint64_t><<<hist_blocks, kHistThreads, 0, stream>>>(keys_in, n, sp, t.hist);
     HB_LAUNCH_OK("radix_histogram", stream, false);
-    radix_offsets_kernel<<<num_passes, kRadix, 0, stream>>>(t.hist);
-    HB_LAUNCH_OK("radix_offsets", stream, false);
-    const int tiles = cdiv(n, kSortTile);
-    uint64_t* kin = keys_in;
-    uint32_t* vin = vals_in;
-    uint64_t* kout = keys_out;
-    uint32_t* vout = vals_out;
-    for (int p = 0; p < num_passes; p++) {
-        const int shift = p * kRadixBits;
-        const int bits = (end_bit - shift) < kRadixBits ? (end_bit - shift) : kRadixBits;
-        const uint32_t mask = (1u << bits) - 1u;
-        radix_onesweep_kernel<<<tiles, kSortThreads, sizeof(SortSmem), stream>>>(
-            kin, vin, kout, vout, n, shift, mask, p, t.hist + p * kRadix, t.lookback, t.tickets);
-        HB_LAUNCH_OK("radix_onesweep", stream, false);
-        uint64_t* tk = kin; kin = kout; kout = tk;
-        uint32_t* tv = vin; vin = vout; vout = tv;
-    }
-    *result_in_input = (kin == keys_in);
-    return 0;
+    return run_passes<uint64_t>(keys_in, vals_in, keys_out, vals_out, n, nullptr, sp, t, stream, result_in_input);
 }
 
 int launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,

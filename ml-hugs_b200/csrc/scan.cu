@@ -25,7 +25,10 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned l
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// `gather` (optional): scan in[gather[i]] instead of in[i] -- the rasterizer scans the per-Gaussian tile
+// counts in depth-sorted order without materialising the permuted array.
 __global__ void __launch_bounds__(kScanThreads) inclusive_scan_kernel(const uint32_t* __restrict__ in,
+                                                                      const uint32_t* __restrict__ gather,
                                                                       uint32_t* __restrict__ out, int n,
                                                                       unsigned long long* state,
                                                                       unsigned* ticket) {
@@ -40,7 +43,20 @@ __global__ void __launch_bounds__(kScanThreads) inclusive_scan_kernel(const uint
     const int base = tile * kScanTile + tid * kScanItems;
 
     uint32_t v[kScanItems];
-    if (base + kScanItems <= n) {
+    if (gather != nullptr) {
+        uint32_t g[kScanItems];
+        if (base + kScanItems <= n) {
+            const uint4 a = __ldg(reinterpret_cast<const uint4*>(gather + base));
+            const uint4 b = __ldg(reinterpret_cast<const uint4*>(gather + base) + 1);
+            g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w;
+            g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+#pragma unroll
+            for (int i = 0; i < kScanItems; i++) v[i] = __ldg(in + g[i]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < kScanItems; i++) v[i] = (base + i < n) ? __ldg(in + __ldg(gather + base + i)) : 0u;
+        }
+    } else if (base + kScanItems <= n) {
         const uint4 a = __ldg(reinterpret_cast<const uint4*>(in + base));
         const uint4 b = __ldg(reinterpret_cast<const uint4*>(in + base) + 1);
         v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
@@ -118,14 +134,15 @@ size_t scan_temp_bytes(int n) {
 }
 
 int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
-                          cudaStream_t stream) {
+                          cudaStream_t stream, const uint32_t* gather) {
     if (n <= 0) return 0;
     const size_t need = scan_temp_bytes(n);
     if (temp == nullptr || temp_bytes < need) {
         set_error("inclusive_scan: temp storage too small (%zu < %zu)", temp_bytes, need);
         return -1;
     }
-    if ((reinterpret_cast<uintptr_t>(in) & 15u) || (reinterpret_cast<uintptr_t>(out) & 15u)) {
+    if ((reinterpret_cast<uintptr_t>(in) & 15u) || (reinterpret_cast<uintptr_t>(out) & 15u) ||
+        (reinterpret_cast<uintptr_t>(gather) & 15u)) {
         set_error("inclusive_scan: in/out must be 16-byte aligned");
         return -1;
     }
@@ -133,7 +150,7 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, 
     HB_CUDA_OK(cudaMemsetAsync(temp, 0, need, stream));
     unsigned* ticket = reinterpret_cast<unsigned*>(temp);
     unsigned long long* state = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(temp) + 256);
-    inclusive_scan_kernel<<<tiles, kScanThreads, 0, stream>>>(in, out, n, state, ticket);
+    inclusive_scan_kernel<<<tiles, kScanThreads, 0, stream>>>(in, gather, out, n, state, ticket);
     HB_LAUNCH_OK("inclusive_scan", stream, false);
     return 0;
 }

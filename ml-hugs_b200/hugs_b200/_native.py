@@ -39,7 +39,7 @@ i32 = C.c_int
 class GeomLayout(C.Structure):
     _fields_ = [(n, C.c_size_t) for n in (
         "depths", "means2D", "conic_opacity", "rgb", "clamped", "tiles_touched", "point_offsets",
-        "scan_temp", "total")]
+        "scan_temp", "sorted_depths", "perm", "total")]
 
 
 class ImageLayout(C.Structure):
@@ -94,6 +94,10 @@ geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayou
 image_layout_of = _sig("hugs_b200_image_layout_of", i32, [i32, i32, C.POINTER(ImageLayout)])
 binning_layout_of = _sig("hugs_b200_binning_layout_of", i32, [i32, C.POINTER(BinningLayout)])
 
+binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_size_t])
+BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE = 0, 1, 2
+set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
+
 sort_bits = _sig("hugs_b200_sort_bits", i32, [i32, i32])
 sort_temp_bytes = _sig("hugs_b200_sort_temp_bytes", C.c_size_t, [i32])
 scan_temp_bytes = _sig("hugs_b200_scan_temp_bytes", C.c_size_t, [i32])
@@ -120,6 +124,7 @@ def read_stage_times(reset=True):
 
 
 EXPORTED_SYMBOLS = [
+    "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode",
     "hugs_b200_stage_timing_enable", "hugs_b200_stage_timing_read", "hugs_b200_stage_name",
     "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
     "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_mark_visible",

@@ -127,7 +127,8 @@ def decode_our_buffers(geom, binning, img, P, R, W, H):
     out = {}
     g, b, im = N.GeomLayout(), N.BinningLayout(), N.ImageLayout()
     N.geom_layout_of(P, g)
-    N.binning_layout_of(R, b)
+    # the binning workspace is laid out for a capacity >= R (recovered from the buffer size)
+    N.binning_layout_of(int(N.binning_capacity_of(binning.numel())), b)
     N.image_layout_of(W, H, im)
 
     def take(buf, off, count, dtype, itemsize):
@@ -141,6 +142,8 @@ def decode_our_buffers(geom, binning, img, P, R, W, H):
         out["clamped_bits"] = take(geom, g.clamped, P, torch.uint8, 1)
         out["tiles_touched"] = take(geom, g.tiles_touched, P, torch.int32, 4)
         out["point_offsets"] = take(geom, g.point_offsets, P, torch.int32, 4)
+        out["sorted_depths"] = take(geom, g.sorted_depths, P, torch.int32, 4)
+        out["perm"] = take(geom, g.perm, P, torch.int32, 4)
     Npix = W * H
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     out["accum_alpha"] = take(img, im.accum_alpha, Npix, torch.float32, 4)

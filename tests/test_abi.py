@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     missing = [s for s in declared_symbols() if not hasattr(lib, s)]
     assert not missing, "declared in include/hugs_b200.h but not exported: %s" % missing
     assert set(N.EXPORTED_SYMBOLS) <= set(declared_symbols())
-    assert N.abi_version() == 1
+    assert N.abi_version() == 2
 
 
 def test_sort_bits_match_reference_rule():
@@ -52,7 +52,15 @@ def test_layouts_are_aligned_and_disjoint():
     assert offs == sorted(offs) and all(o % 256 == 0 for o in offs) and g.total >= offs[-1]
     assert g.means2D - g.depths >= 4000 and g.conic_opacity - g.means2D >= 8000
     assert N.binning_layout_of(12345, b) > 0
-    assert b.point_list - b.point_list_keys >= 8 * 12345 and b.total > b.sort_temp
+    assert b.point_list == 0 and b.point_list_keys >= 4 * 12345 and b.total > b.sort_temp
+    # the capacity recovered from the buffer size describes the same layout (slices are 256-B aligned)
+    cap = N.binning_capacity_of(b.total)
+    b2 = N.BinningLayout()
+    N.binning_layout_of(cap, b2)
+    assert 12345 <= cap < 12345 + 64 and bytes(b2) == bytes(b)
+    assert N.binning_capacity_of(b.total + 100000) > cap
+    assert N.binning_capacity_of(0) == 0
+    assert N.set_binning_mode(7) == -1 and N.set_binning_mode(N.BINNING_ASYNC) == N.BINNING_ASYNC
     assert N.image_layout_of(1920, 1080, im) > 0
     assert im.n_contrib - im.accum_alpha >= 4 * 1920 * 1080 and im.total - im.ranges >= 8 * 8160
     assert N.geom_layout_of(-1, g) < 0
