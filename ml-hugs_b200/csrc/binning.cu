@@ -142,12 +142,18 @@ __global__ void __launch_bounds__(kDupThreads)
             const uint32_t tile = y * grid_x + x;
             keys[o] = ((uint64_t)tile << 32) | (uint64_t)s_depth[lo];
             vals[o] = s_idx[lo];
+            // Digit counts for the sort passes.  Lanes that share the first active lane's digit (the
+            // common case for the high tile bits) are counted with one atomic; the rest hit distinct
+            // counters mostly (low tile bits of neighbouring tiles) and add individually.
+            const int first_lane = __ffs(active) - 1;
 #pragma unroll
             for (int p = 0; p < 3; p++) {
                 if (p < plan.num_passes) {
                     const uint32_t d = (tile >> (plan.shift[p] - 32)) & ((1u << plan.bits[p]) - 1u);
-                    const unsigned peers = __match_any_sync(active, d);
-                    if (lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
+                    const uint32_t d0 = __shfl_sync(active, d, first_lane);
+                    const unsigned same = __ballot_sync(active, d == d0);
+                    if (d != d0) atomicAdd(&s_hist[p][d], 1u);
+                    else if ((int)lane == first_lane) atomicAdd(&s_hist[p][d0], (uint32_t)__popc(same));
                 }
             }
         }

@@ -120,6 +120,7 @@ __global__ void __launch_bounds__(kSortThreads)
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31, warp = tid >> 5;
     const unsigned lanemask_lt = (1u << lane) - 1u;
+    const int digit_bits = __popc(digit_mask);
 
     // n_host is the capacity the grid was sized for when the real count lives on the device
     int n = n_host;
@@ -149,16 +150,26 @@ __global__ void __launch_bounds__(kSortThreads)
         }
     }
 
-    // Stable warp-local ranks.
+    // Stable warp-local ranks.  Lanes holding the same digit are found with one ballot per digit
+    // bit (constant cost); match.any takes time proportional to the number of distinct digits in
+    // the warp and made the passes over the tile bits (32 distinct digits per warp) twice as slow
+    // as the passes over duplicated depth bytes (profiles/r01_b_sort_passes.txt).
     uint32_t rank[kSortItems];
 #pragma unroll
     for (int k = 0; k < kSortItems; k++) {
         const bool valid = full_tile || (warp_base + k * 32 + (int)lane < n);
-        const unsigned active = __ballot_sync(0xffffffffu, valid);
+        const uint32_t d = (uint32_t)(key[k] >> shift) & digit_mask;
+        unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < kRadixBits; b++) {
+            if (b < digit_bits) {
+                const bool bit = (d >> b) & 1u;
+                const unsigned m = __ballot_sync(0xffffffffu, valid && bit);
+                peers &= bit ? m : ~m;
+            }
+        }
         rank[k] = 0;
         if (valid) {
-            const uint32_t d = (uint32_t)(key[k] >> shift) & digit_mask;
-            const unsigned peers = __match_any_sync(active, d);
             const int leader = __ffs(peers) - 1;
             uint32_t old = 0;
             if ((int)lane == leader) {

@@ -1,0 +1,33 @@
+"""One profiled frame of the bench workload (GPU box, under ncu --profile-from-start off).
+usage: python tools/prof_frame.py [workload] [binning_mode]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+
+import bench
+from hugs_b200 import _native
+
+
+def main():
+    workload = sys.argv[1] if len(sys.argv) > 1 else "human_scene_1080p"
+    mode = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    _native.set_binning_mode(mode)
+    module, lbs_impl = bench.our_impl()
+    rep = bench.Replica(bench.make_workload(workload, 0, 1, dev), dev, module, lbs_impl)
+    for _ in range(3):
+        rep.step_resident()
+    torch.cuda.synchronize()
+    torch.cuda.cudart().cudaProfilerStart()
+    rep.step_resident()
+    torch.cuda.synchronize()
+    torch.cuda.cudart().cudaProfilerStop()
+    print("profiled one frame: P=%d R=%d mode=%d" % (rep.P, rep.last_node.num_rendered, mode))
+
+
+if __name__ == "__main__":
+    main()
