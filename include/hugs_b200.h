@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 2
+#define HUGS_B200_ABI_VERSION 3
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -122,6 +122,7 @@ int hugs_b200_rasterize_backward(
     const int* radii,
     char* geom_buffer,
     char* binning_buffer,
+    size_t binning_bytes,   /* size of the binning workspace as the forward resize callback was asked for */
     char* image_buffer,
     const float* dL_dpix,
     float* dL_dmean2D,
@@ -174,16 +175,19 @@ typedef struct hugs_b200_binning_layout {
     size_t point_list_keys_unsorted;  /* u64[R]                                        */
     size_t point_list_unsorted;       /* u32[R]                                        */
     size_t sort_temp;                 /* histograms + look-back state                  */
+    size_t hit_words;                 /* u32[(R+31)/32 + tiles + 1][8]: per 32 list positions of a tile and per
+                                         warp of the blend CTA, which Gaussians the forward pass blended     */
     size_t total;
 } hugs_b200_binning_layout;
 
 int hugs_b200_geom_layout_of(int P, hugs_b200_geom_layout* out);
 /* The binning workspace is laid out for a CAPACITY of pairs that may exceed the R of the call that
  * filled it (see hugs_b200_set_binning_mode); this recovers the capacity from the buffer size so that
- * hugs_b200_binning_layout_of(capacity) describes the buffer.  point_list always sits at offset 0. */
-size_t hugs_b200_binning_capacity_of(size_t nbytes);
+ * hugs_b200_binning_layout_of(capacity, width, height) describes the buffer.  point_list always sits at
+ * offset 0. */
+size_t hugs_b200_binning_capacity_of(size_t nbytes, int width, int height);
 int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out);
-int hugs_b200_binning_layout_of(int R, hugs_b200_binning_layout* out);
+int hugs_b200_binning_layout_of(int R, int width, int height, hugs_b200_binning_layout* out);
 
 /* ---------------------------------------------------------------------------------------------
  * How the forward pass bins (Gaussian, tile) pairs.  All three produce bit-identical keys, lists,

@@ -142,7 +142,7 @@ ImageView carve_image(char* base, int W, int H) {
     return v;
 }
 
-BinningView carve_binning(char* base, int R) {
+BinningView carve_binning(char* base, int R, int num_tiles) {
     BinningView b;
     char* p = base;
     const size_t n = (size_t)(R > 0 ? R : 0);
@@ -152,6 +152,8 @@ BinningView carve_binning(char* base, int R) {
     b.list_unsorted = take<uint32_t>(p, n);
     b.sort_temp_bytes = sort_temp_bytes(R);
     b.sort_temp = take<char>(p, b.sort_temp_bytes);
+    // last, so that no other offset depends on the tile count
+    b.hit_words = take<uint32_t>(p, ((n + 31) / 32 + (size_t)(num_tiles > 0 ? num_tiles : 0) + 1) * 8);
     b.total = (size_t)(p - base);
     return b;
 }
@@ -281,12 +283,15 @@ int hugs_b200_set_binning_mode(int mode) {
     return g_binning_mode.exchange(mode);
 }
 
-size_t hugs_b200_binning_capacity_of(size_t nbytes) {
+static int tiles_of(int width, int height) { return cdiv(width, HB_TILE_X) * cdiv(height, HB_TILE_Y); }
+
+size_t hugs_b200_binning_capacity_of(size_t nbytes, int width, int height) {
     // largest capacity whose layout fits in nbytes (the layout size is monotone in the capacity)
+    const int tiles = (width > 0 && height > 0) ? tiles_of(width, height) : 0;
     size_t lo = 0, hi = nbytes / 24 + 1;
     while (lo < hi) {
         const size_t mid = lo + (hi - lo + 1) / 2;
-        if (mid <= 0x7fffffffULL && carve_binning(nullptr, (int)mid).total <= nbytes) lo = mid;
+        if (mid <= 0x7fffffffULL && carve_binning(nullptr, (int)mid, tiles).total <= nbytes) lo = mid;
         else hi = mid - 1;
     }
     return lo;
@@ -348,16 +353,17 @@ int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out
     return 4;
 }
 
-int hugs_b200_binning_layout_of(int R, hugs_b200_binning_layout* out) {
-    if (!out || R < 0) return HUGS_B200_EINVAL;
-    const BinningView b = carve_binning(nullptr, R);
+int hugs_b200_binning_layout_of(int R, int width, int height, hugs_b200_binning_layout* out) {
+    if (!out || R < 0 || width <= 0 || height <= 0) return HUGS_B200_EINVAL;
+    const BinningView b = carve_binning(nullptr, R, tiles_of(width, height));
     out->point_list_keys = (size_t)reinterpret_cast<char*>(b.keys);
     out->point_list = (size_t)reinterpret_cast<char*>(b.list);
     out->point_list_keys_unsorted = (size_t)reinterpret_cast<char*>(b.keys_unsorted);
     out->point_list_unsorted = (size_t)reinterpret_cast<char*>(b.list_unsorted);
     out->sort_temp = (size_t)b.sort_temp;
+    out->hit_words = (size_t)reinterpret_cast<char*>(b.hit_words);
     out->total = b.total;
-    return 6;
+    return 7;
 }
 
 int hugs_b200_sort_bits(int width, int height) {
@@ -518,12 +524,12 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     const int stride = colors_precomp != nullptr ? 3 : 4;
     if (P == 0) feature_ptr = nullptr;
     for (;;) {
-        char* bin_base = binning_buffer(binning_user, carve_binning(nullptr, cap).total);
+        char* bin_base = binning_buffer(binning_user, carve_binning(nullptr, cap, num_tiles).total);
         if (!bin_base) {
             set_error("rasterize_forward: binning buffer callback returned NULL");
             return HUGS_B200_ENOMEM;
         }
-        bin = carve_binning(bin_base, cap);
+        bin = carve_binning(bin_base, cap, num_tiles);
         const uint32_t* n_dev = nullptr;
         if (cap > 0 && two_level) {
             n_dev = R_dev;
@@ -577,7 +583,7 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         HB_STAGE(launch_render_forward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y,
                                        P > 0 ? geom.means2D : nullptr, feature_ptr, stride,
                                        P > 0 ? geom.conic_opacity : nullptr, img.accum_alpha, img.n_contrib,
-                                       background, out_color, stream),
+                                       background, out_color, bin.hit_words, stream),
                  ST_RENDER_FWD);
         if (!R_known) {
             const int rc = wait_R();
@@ -596,7 +602,8 @@ int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* backgr
                                  const float* scales, float scale_modifier, const float* rotations,
                                  const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
                                  const float* cam_pos, float tan_fovx, float tan_fovy, const int* radii,
-                                 char* geom_buffer, char* binning_buffer, char* image_buffer, const float* dL_dpix,
+                                 char* geom_buffer, char* binning_buffer, size_t binning_bytes, char* image_buffer,
+                                 const float* dL_dpix,
                                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                                  float* dL_drot, int debug, hugs_b200_stream_t stream_) {
@@ -618,7 +625,13 @@ int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* backgr
     }
     const Camera cam = make_camera(viewmatrix, projmatrix, cam_pos, width, height, tan_fovx, tan_fovy);
     const GeomView geom = carve_geom(geom_buffer, P);
-    const BinningView bin = carve_binning(binning_buffer, R);
+    // The workspace was laid out for a capacity >= R (hugs_b200_set_binning_mode); recover it from the size.
+    const size_t cap = hugs_b200_binning_capacity_of(binning_bytes, width, height);
+    if ((size_t)R > cap) {
+        set_error("rasterize_backward: binning buffer of %zu bytes cannot hold %d pairs", binning_bytes, R);
+        return HUGS_B200_EINVAL;
+    }
+    const BinningView bin = carve_binning(binning_buffer, (int)cap, cam.grid_x * cam.grid_y);
     const ImageView img = carve_image(image_buffer, width, height);
 
     const float* color_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
@@ -633,7 +646,8 @@ int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* backgr
         if (R <= 0) return 0;
         return launch_render_backward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y, background,
                                       geom.means2D, geom.conic_opacity, color_ptr, stride, img.accum_alpha,
-                                      img.n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, stream);
+                                      img.n_contrib, bin.hit_words, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity,
+                                      dL_dcolor, stream);
     };
     HB_STAGE(blend_backward(), ST_RENDER_BWD);
     HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,

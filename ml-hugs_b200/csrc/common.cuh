@@ -76,11 +76,12 @@ struct BinningView {
     uint32_t* list_unsorted;
     char* sort_temp;
     size_t sort_temp_bytes;
+    uint32_t* hit_words;  // [(R+31)/32 + tiles + 1][8 warps]: what each warp of the forward blend actually blended
     size_t total;
 };
 GeomView carve_geom(char* base, int P);
 ImageView carve_image(char* base, int W, int H);
-BinningView carve_binning(char* base, int R);
+BinningView carve_binning(char* base, int R, int num_tiles);
 
 constexpr int kSortMaxPasses = 8;
 struct SortPassPlan {  // pass p sorts on `bits[p]` key bits starting at bit `shift[p]`
@@ -138,11 +139,12 @@ int launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, 
 int launch_render_forward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
                           const float2* means2D, const float* colors, int color_stride,
                           const float4* conic_opacity, float* final_T, uint32_t* n_contrib,
-                          const float* bg, float* out_color, cudaStream_t stream);
+                          const float* bg, float* out_color, uint32_t* hit_words, cudaStream_t stream);
 int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
                            const float* bg, const float2* means2D, const float4* conic_opacity,
                            const float* colors, int color_stride, const float* final_T,
-                           const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D /*[P,3]*/,
+                           const uint32_t* n_contrib, const uint32_t* hit_words, const float* dL_dpix,
+                           float* dL_dmean2D /*[P,3]*/,
                            float* dL_dconic /*[P,4]*/, float* dL_dopacity, float* dL_dcolor /*[P,3]*/,
                            cudaStream_t stream);
 int launch_preprocess_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,

@@ -5,11 +5,12 @@
 // Building blocks:
 //   * radix_histogram_kernel   one read of the keys builds the digit histogram of every pass;
 //   * radix_offsets_kernel     histogram -> exclusive bin offsets (one CTA per pass);
-//   * radix_onesweep_kernel    one scatter pass.  Each CTA owns a 4096-pair tile (atomic ticket
-//     order), ranks its keys stably with warp-level match_any + per-warp counters, obtains the
-//     tile's per-digit global offset by decoupled look-back over 64-bit (flag|count) words, stages
-//     the tile digit-sorted in shared memory and writes it out in coalesced runs.
-// Stability: a tile is loaded warp-striped (warp w owns 512 consecutive pairs, item k of lane l
+//   * radix_onesweep_kernel    one scatter pass.  Each CTA (512 threads x 8 pairs) owns a 4096-pair
+//     tile (atomic ticket order), ranks its keys stably with per-bit ballots + per-warp counters,
+//     obtains the tile's per-digit global offset by a WINDOWED decoupled look-back over 64-bit
+//     (flag|count) words, stages the tile digit-sorted in shared memory and writes it out in
+//     coalesced runs.
+// Stability: a tile is loaded warp-striped (warp w owns 256 consecutive pairs, item k of lane l
 // is pair 32k+l), items are ranked in k order and lanes in lane order, warps in warp order, tiles
 // in ticket == index order.
 //
@@ -24,6 +25,7 @@
 // of the R pairs on the tile bits only (2 passes at 1080p instead of 6).  See DESIGN.md.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace hb {
@@ -31,12 +33,8 @@ namespace hb {
 namespace {
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
-constexpr int kSortThreads = 256;
-constexpr int kSortWarps = kSortThreads / 32;
-constexpr int kSortItems = 16;
-constexpr int kSortTile = kSortThreads * kSortItems;  // 4096 pairs
+constexpr int kMinSortTile = 2048;  // smallest tile of any kernel variant: sizes the look-back array
 constexpr int kHistThreads = 512;
-static_assert(kSortThreads == kRadix, "one thread per digit in the look-back phase");
 static_assert(kSortMaxPasses == 8, "header constant");
 
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
@@ -96,27 +94,77 @@ __global__ void __launch_bounds__(kRadix) radix_offsets_kernel(uint32_t* __restr
 }
 
 // ---- 3. one scatter pass ---------------------------------------------------------------------
-template <typename KeyT>
+// 512 threads x 8 pairs: the same 4096-pair tile as 256 x 16, but half the registers per thread,
+// so keys AND payloads are loaded up front (one exposed DRAM round trip per tile instead of two)
+// and two to three CTAs (32-48 warps) stay resident per SM.
+template <typename KeyT, int THREADS, int ITEMS>
 struct SortSmem {
-    KeyT keys[kSortTile];                   // 32 KB (u64) / 16 KB (u32)
-    uint32_t vals[kSortTile];               // 16 KB
-    uint32_t warp_hist[kSortWarps][kRadix]; //  8 KB
+    KeyT keys[THREADS * ITEMS];                   // 32 KB (u64) / 16 KB (u32)
+    uint32_t vals[THREADS * ITEMS];               // 16 KB
+    uint32_t warp_hist[THREADS / 32][kRadix]; // 16 KB
     uint32_t local_start[kRadix];           //  1 KB  first staged slot of each digit
+    uint32_t count[kRadix];                 //  1 KB  pairs of each digit in this tile
     int64_t bin_base[kRadix];               //  2 KB  global index of staged slot 0 of each digit
-    uint32_t scan_warp[kSortWarps];
+    uint32_t scan_warp[kRadix / 32];
     unsigned tile;
 };
 
+// Decoupled look-back with a WINDOW.  The textbook walk (one thread per digit, one predecessor per
+// dependent L2 round trip) makes the time for an inclusive prefix to reach a tile grow like
+// sqrt(2 x tiles in flight) round trips; with ~300-450 tiles in flight on 148 SMs that chain, not
+// HBM, set the pass time (profiles/r01_d_sort_lookback.txt).  Here the `T` threads of a digit
+// fetch kLookWin x T predecessors per round trip, all loads in flight at once, and combine with
+// shuffles inside the digit's lane group.
+constexpr int kLookWin = 8;
+
+__device__ __forceinline__ uint32_t lookback_prefix(const unsigned long long* __restrict__ lookback, int tile, int d,
+                                                    int sub, int T, unsigned gmask, unsigned flag_agg,
+                                                    unsigned flag_inc) {
+    uint32_t prefix = 0;
+    const int kBig = 1 << 30;
+    for (int t0 = tile - 1; t0 >= 0; t0 -= T * kLookWin) {
+        unsigned long long w[kLookWin];
+#pragma unroll
+        for (int k = 0; k < kLookWin; k++) {
+            const int t = t0 - sub - T * k;
+            w[k] = (t >= 0) ? ld_relaxed_u64(lookback + (size_t)t * kRadix + d) : ((unsigned long long)flag_inc << 32);
+        }
+#pragma unroll
+        for (int k = 0; k < kLookWin; k++) {
+            const int t = t0 - sub - T * k;
+            if (t >= 0)
+                while ((unsigned)(w[k] >> 32) < flag_agg) w[k] = ld_relaxed_u64(lookback + (size_t)t * kRadix + d);
+        }
+        // distance (0-based) of the nearest predecessor that already holds an inclusive prefix
+        int best = kBig;
+#pragma unroll
+        for (int k = kLookWin - 1; k >= 0; k--)
+            if ((unsigned)(w[k] >> 32) == flag_inc) best = sub + T * k;
+        for (int o = T >> 1; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o));
+        uint32_t sum = 0;
+#pragma unroll
+        for (int k = 0; k < kLookWin; k++)
+            if (sub + T * k <= best) sum += (uint32_t)w[k];
+        for (int o = T >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(gmask, sum, o);
+        prefix += sum;
+        if (best != kBig) break;
+    }
+    return prefix;
+}
+
 // vals_in == nullptr means "the payload of item i is i" (first pass of an argsort).
-template <typename KeyT>
-__global__ void __launch_bounds__(kSortThreads)
+template <typename KeyT, int THREADS, int ITEMS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
     radix_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                           KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n_host,
                           const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask, int pass,
                           const uint32_t* __restrict__ pass_offsets, unsigned long long* lookback,
-                          unsigned* tickets) {
+                          unsigned* tickets, int dbg_no_lookback) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    SortSmem<KeyT>& s = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
+    constexpr int kSortThreads = THREADS, kSortItems = ITEMS, kSortWarps = THREADS / 32, kSortTile = THREADS * ITEMS;
+    static_assert(THREADS >= kRadix && THREADS % kRadix == 0, "digit phases use the first kRadix threads");
+    using Smem = SortSmem<KeyT, THREADS, ITEMS>;
+    Smem& s = *reinterpret_cast<Smem*>(smem_raw);
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31, warp = tid >> 5;
     const unsigned lanemask_lt = (1u << lane) - 1u;
@@ -127,8 +175,7 @@ __global__ void __launch_bounds__(kSortThreads)
     if (n_dev != nullptr) n = (int)min((uint32_t)n_host, __ldg(n_dev));
 
     if (tid == 0) s.tile = atomicAdd(tickets + pass, 1u);
-#pragma unroll
-    for (int w = 0; w < kSortWarps; w++) s.warp_hist[w][tid] = 0;
+    for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&s.warp_hist[0][0])[i] = 0;
     __syncthreads();
     const int tile = (int)s.tile;
     const long long tile_base_ll = (long long)tile * kSortTile;
@@ -137,23 +184,29 @@ __global__ void __launch_bounds__(kSortThreads)
     const int warp_base = tile_base + (int)warp * (32 * kSortItems);
     const bool full_tile = tile_base + kSortTile <= n;
 
-    // Load keys, warp-striped.
+    // Load keys and payloads, warp-striped; every load of the tile is in flight before the first use.
     KeyT key[kSortItems];
+    uint32_t val[kSortItems];
     if (full_tile) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) key[k] = __ldg(keys_in + warp_base + k * 32 + lane);
+#pragma unroll
+        for (int k = 0; k < kSortItems; k++) {
+            const int i = warp_base + k * 32 + (int)lane;
+            val[k] = (vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
+        }
     } else {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
             const int i = warp_base + k * 32 + (int)lane;
             key[k] = (i < n) ? __ldg(keys_in + i) : (KeyT)~(KeyT)0;
+            val[k] = (i < n && vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
         }
     }
 
     // Stable warp-local ranks.  Lanes holding the same digit are found with one ballot per digit
     // bit (constant cost); match.any takes time proportional to the number of distinct digits in
-    // the warp and made the passes over the tile bits (32 distinct digits per warp) twice as slow
-    // as the passes over duplicated depth bytes (profiles/r01_b_sort_passes.txt).
+    // the warp (profiles/r01_b_sort_passes.txt).
     uint32_t rank[kSortItems];
 #pragma unroll
     for (int k = 0; k < kSortItems; k++) {
@@ -183,49 +236,54 @@ __global__ void __launch_bounds__(kSortThreads)
     }
     __syncthreads();
 
-    // Per digit (thread tid == digit): exclusive scan over warps, tile count, look-back.
-    {
-        const int d = tid;
+    const unsigned flag_agg = (unsigned)(2 * pass + 1), flag_inc = (unsigned)(2 * pass + 2);
+    // Per digit (thread tid == digit): exclusive scan over warps, tile count, publish the aggregate.
+    uint32_t tile_count = 0, incl = 0;
+    if (tid < kRadix) {
         uint32_t sum = 0;
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++) {
-            const uint32_t t = s.warp_hist[w][d];
-            s.warp_hist[w][d] = sum;
+            const uint32_t t = s.warp_hist[w][tid];
+            s.warp_hist[w][tid] = sum;
             sum += t;
         }
-        const uint32_t tile_count = sum;
-        const unsigned long long flag_agg = (unsigned long long)(2 * pass + 1) << 32;
-        const unsigned long long flag_inc = (unsigned long long)(2 * pass + 2) << 32;
-        unsigned long long* my = lookback + (size_t)tile * kRadix + d;
-        st_relaxed_u64(my, (tile == 0 ? flag_inc : flag_agg) | tile_count);
-
-        // block exclusive scan of tile_count over digits -> local_start
-        uint32_t incl = tile_count;
+        tile_count = sum;
+        st_relaxed_u64(lookback + (size_t)tile * kRadix + tid,
+                       ((unsigned long long)(tile == 0 ? flag_inc : flag_agg) << 32) | tile_count);
+        s.count[tid] = tile_count;
+        // exclusive scan of tile_count over digits -> local_start
+        incl = tile_count;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= (unsigned)o) incl += t;
         }
         if (lane == 31) s.scan_warp[warp] = incl;
-        __syncthreads();
+    }
+    __syncthreads();
+    if (tid < kRadix) {
         uint32_t base = 0;
         for (unsigned w = 0; w < warp; w++) base += s.scan_warp[w];
-        const uint32_t local_start = base + incl - tile_count;
-        s.local_start[d] = local_start;
+        s.local_start[tid] = base + incl - tile_count;
+    }
 
-        // decoupled look-back: sum of this digit's counts over all previous tiles
-        uint32_t prefix = 0;
-        for (int t = tile - 1; t >= 0; --t) {
-            const unsigned long long* p = lookback + (size_t)t * kRadix + d;
-            unsigned long long w;
-            do {
-                w = ld_relaxed_u64(p);
-            } while ((w >> 32) < (flag_agg >> 32));
-            prefix += (uint32_t)w;
-            if ((w >> 32) == (flag_inc >> 32)) break;
+    // Windowed decoupled look-back: T = threads per digit (a power of two, at most one warp).
+    {
+        const int bins = 1 << digit_bits;
+        const int T = min(kSortThreads / bins, 32);
+        const int d = tid / T, sub = tid & (T - 1);
+        if (d < bins) {
+            const unsigned gmask = (T == 32) ? 0xffffffffu : (((1u << T) - 1u) << (lane & ~(unsigned)(T - 1)));
+            const uint32_t prefix =
+                dbg_no_lookback ? 0u : lookback_prefix(lookback, tile, d, sub, T, gmask, flag_agg, flag_inc);
+            if (sub == 0) {
+                const uint32_t cnt = s.count[d];
+                if (tile != 0)
+                    st_relaxed_u64(lookback + (size_t)tile * kRadix + d,
+                                   ((unsigned long long)flag_inc << 32) | (unsigned long long)(prefix + cnt));
+                s.bin_base[d] = (int64_t)__ldg(pass_offsets + d) + (int64_t)prefix;
+            }
         }
-        if (tile != 0) st_relaxed_u64(my, flag_inc | (unsigned long long)(prefix + tile_count));
-        s.bin_base[d] = (int64_t)__ldg(pass_offsets + d) + (int64_t)prefix - (int64_t)local_start;
     }
     __syncthreads();
 
@@ -237,7 +295,7 @@ __global__ void __launch_bounds__(kSortThreads)
             const uint32_t d = (uint32_t)(key[k] >> shift) & digit_mask;
             const uint32_t pos = s.local_start[d] + s.warp_hist[warp][d] + rank[k];
             s.keys[pos] = key[k];
-            s.vals[pos] = (vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
+            s.vals[pos] = val[k];
         }
     }
     __syncthreads();
@@ -250,7 +308,7 @@ __global__ void __launch_bounds__(kSortThreads)
         if (i < count) {
             const KeyT kk = s.keys[i];
             const uint32_t d = (uint32_t)(kk >> shift) & digit_mask;
-            const int64_t g = s.bin_base[d] + i;
+            const int64_t g = s.bin_base[d] + (int64_t)i - (int64_t)s.local_start[d];
             keys_out[g] = kk;
             vals_out[g] = s.vals[i];
         }
@@ -272,21 +330,54 @@ SortTemp carve_sort_temp(void* temp, int n) {
     t.tickets = reinterpret_cast<unsigned*>(p);
     p += align_up(sizeof(unsigned) * kSortMaxPasses);
     t.lookback = reinterpret_cast<unsigned long long*>(p);
-    const int tiles = cdiv(n > 0 ? n : 1, kSortTile);
+    const int tiles = cdiv(n > 0 ? n : 1, kMinSortTile);
     p += align_up(sizeof(unsigned long long) * (size_t)tiles * kRadix);
     t.bytes = (size_t)(p - reinterpret_cast<char*>(temp));
     return t;
 }
 
-template <typename KeyT>
-int configure_smem() {
-    static bool done = false;  // per instantiation; the attribute is per device function, idempotent
-    if (!done) {
-        HB_CUDA_OK(cudaFuncSetAttribute(radix_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)sizeof(SortSmem<KeyT>)));
-        done = true;
+// One scatter pass with a given CTA shape.
+template <typename KeyT, int THREADS, int ITEMS, int MINB>
+int launch_pass_shape(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout, int n_cap,
+                      const uint32_t* n_dev, int shift, uint32_t mask, int pass, const SortTemp& t,
+                      cudaStream_t stream) {
+    using Smem = SortSmem<KeyT, THREADS, ITEMS>;
+    auto kernel = radix_onesweep_kernel<KeyT, THREADS, ITEMS, MINB>;
+    static bool configured = false;  // per instantiation; the attribute is per device function, idempotent
+    if (!configured) {
+        HB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+        HB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        cudaSharedmemCarveoutMaxShared));
+        configured = true;
     }
+    const int tiles = cdiv(n_cap, THREADS * ITEMS);
+    kernel<<<tiles, THREADS, sizeof(Smem), stream>>>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass,
+                                                     t.hist + pass * kRadix, t.lookback, t.tickets,
+                                                     getenv("HB_SORT_NOLOOK") != nullptr);
+    HB_LAUNCH_OK("radix_onesweep", stream, false);
     return 0;
+}
+
+// CTA shape selection.  HB_SORT_SHAPE (tuning aid, read once): 0 = 512x8, 1 = 256x8, 2 = 256x16, 3 = 512x4.
+int sort_shape() {
+    static int shape = -1;
+    if (shape < 0) {
+        const char* e = getenv("HB_SORT_SHAPE");
+        shape = e ? atoi(e) : 0;
+        if (shape < 0 || shape > 3) shape = 0;
+    }
+    return shape;
+}
+
+template <typename KeyT>
+int launch_pass(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout, int n_cap, const uint32_t* n_dev,
+                int shift, uint32_t mask, int pass, const SortTemp& t, cudaStream_t stream) {
+    switch (sort_shape()) {
+        case 1: return launch_pass_shape<KeyT, 256, 8, 4>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
+        case 2: return launch_pass_shape<KeyT, 256, 16, 2>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
+        case 3: return launch_pass_shape<KeyT, 512, 4, 3>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
+        default: return launch_pass_shape<KeyT, 512, 8, 2>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
+    }
 }
 
 // Run the scatter passes of `plan` (histogram already in t.hist, raw counts).  Pairs ping-pong
@@ -294,20 +385,16 @@ int configure_smem() {
 template <typename KeyT>
 int run_passes(KeyT* k0, uint32_t* v0, KeyT* k1, uint32_t* v1, int n_cap, const uint32_t* n_dev,
                const SortPassPlan& plan, const SortTemp& t, cudaStream_t stream, bool* result_in_first) {
-    int rc = configure_smem<KeyT>();
-    if (rc) return rc;
     radix_offsets_kernel<<<plan.num_passes, kRadix, 0, stream>>>(t.hist);
     HB_LAUNCH_OK("radix_offsets", stream, false);
-    const int tiles = cdiv(n_cap, kSortTile);
     KeyT* kbuf[2] = {k0, k1};
     uint32_t* vbuf[2] = {v0, v1};
     int cur = 0;
     for (int p = 0; p < plan.num_passes; p++) {
         const uint32_t mask = (1u << plan.bits[p]) - 1u;
-        radix_onesweep_kernel<KeyT><<<tiles, kSortThreads, sizeof(SortSmem<KeyT>), stream>>>(
-            kbuf[cur], vbuf[cur], kbuf[cur ^ 1], vbuf[cur ^ 1], n_cap, n_dev, plan.shift[p], mask, p,
-            t.hist + p * kRadix, t.lookback, t.tickets);
-        HB_LAUNCH_OK("radix_onesweep", stream, false);
+        const int rc = launch_pass<KeyT>(kbuf[cur], vbuf[cur], kbuf[cur ^ 1], vbuf[cur ^ 1], n_cap, n_dev,
+                                         plan.shift[p], mask, p, t, stream);
+        if (rc) return rc;
         cur ^= 1;
     }
     const bool in_first = (cur == 0);
@@ -365,25 +452,17 @@ int launch_depth_argsort(const uint32_t* keys0, uint32_t* kB, uint32_t* vB, uint
     if (hist_blocks > 148 * 2) hist_blocks = 148 * 2;
     radix_histogram_kernel<uint32_t><<<hist_blocks, kHistThreads, 0, stream>>>(keys0, P, sp, t.hist);
     HB_LAUNCH_OK("radix_histogram", stream, false);
-    rc = configure_smem<uint32_t>();
-    if (rc) return rc;
     radix_offsets_kernel<<<4, kRadix, 0, stream>>>(t.hist);
     HB_LAUNCH_OK("radix_offsets", stream, false);
-    const int tiles = cdiv(P, kSortTile);
-    const size_t sm = sizeof(SortSmem<uint32_t>);
     // keys0 -> B -> C -> B -> C
-    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(keys0, nullptr, kB, vB, P, nullptr, 0, 255u, 0,
-                                                                         t.hist, t.lookback, t.tickets);
-    HB_LAUNCH_OK("radix_onesweep", stream, false);
-    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(kB, vB, kC, vC, P, nullptr, 8, 255u, 1,
-                                                                         t.hist + kRadix, t.lookback, t.tickets);
-    HB_LAUNCH_OK("radix_onesweep", stream, false);
-    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(kC, vC, kB, vB, P, nullptr, 16, 255u, 2,
-                                                                         t.hist + 2 * kRadix, t.lookback, t.tickets);
-    HB_LAUNCH_OK("radix_onesweep", stream, false);
-    radix_onesweep_kernel<uint32_t><<<tiles, kSortThreads, sm, stream>>>(kB, vB, kC, vC, P, nullptr, 24, 255u, 3,
-                                                                         t.hist + 3 * kRadix, t.lookback, t.tickets);
-    HB_LAUNCH_OK("radix_onesweep", stream, false);
+    const uint32_t* kin[4] = {keys0, kB, kC, kB};
+    const uint32_t* vin[4] = {nullptr, vB, vC, vB};
+    uint32_t* kout[4] = {kB, kC, kB, kC};
+    uint32_t* vout[4] = {vB, vC, vB, vC};
+    for (int p = 0; p < 4; p++) {
+        rc = launch_pass<uint32_t>(kin[p], vin[p], kout[p], vout[p], P, nullptr, 8 * p, 255u, p, t, stream);
+        if (rc) return rc;
+    }
     return 0;
 }
 

@@ -2,17 +2,25 @@
 // Replaces renderCUDA<3> backward (cuda_rasterizer/backward.cu:399-557).
 //
 // The reference issues 9 global float atomicAdds per (pixel, Gaussian) hit, all 256 pixels of a
-// tile hammering the same 9 addresses in lock step.  Here the 9 partial gradients
-// (colour 3, mean2D 2, conic 3, opacity 1) are
-//   1. reduced across the 32 pixels of a warp with shuffles (a halving butterfly: 14 SHFL
-//      instead of 45),
-//   2. accumulated across the 8 warps of the tile in shared memory (per-Gaussian slots of the
-//      staged batch, conflict-free [slot][9] layout),
-//   3. flushed once per (tile, Gaussian) pair with 9 global reductions -- 256x fewer global
-//      atomics than the reference.
-// Traversal starts at the tile's largest contributor count instead of the end of the tile's list
-// (entries past it were never blended by any pixel, backward.cu:486-488 skips them one by one),
-// and uses the same per-warp 8x4 sub-tile reject test as the forward pass.
+// tile hammering the same 9 addresses in lock step.  This kernel is issue-bound (not HBM-bound),
+// so everything below is about executing fewer warp instructions per blended Gaussian:
+//   * a warp owns an 8x4 sub-tile and walks ONLY the Gaussians it blended in the forward pass: the
+//     forward blend leaves one 32-bit mask per (32 list positions, warp) (render_forward.cu), so
+//     there is no cull test and no evaluation that ends in "no pixel of this warp was hit";
+//     positions behind the warp's own largest contributor count are never visited
+//     (backward.cu:486-488 skips them pixel by pixel);
+//   * the 9 partial gradients of a Gaussian are reduced over the warp's 32 pixels with a halving
+//     butterfly (12 SHFL instead of 45) and STORED -- not added -- to the warp's private slot of
+//     the staged batch: each warp meets each Gaussian once per batch, so the 8 warps of a tile
+//     need neither shared-memory atomics nor a zero fill; the flush sums the slots whose mask bit
+//     is set and issues one set of 9 global reductions per (tile, Gaussian) -- 256x fewer global
+//     atomics than the reference;
+//   * dL/dmean2D and dL/dconic are accumulated in a factored form (sums of X, Y, X dx, X dy, Y dy
+//     with X = dL/dG G dx, Y = dL/dG G dy) and multiplied by the conic once per (tile, Gaussian);
+//   * gradients need 1e-3, not bit-exactness: exp and the reciprocal of (1 - alpha) use the
+//     special-function unit (ex2.approx / rcp.approx) instead of the IEEE sequences the forward
+//     pass keeps for its contributor counts.
+// Batches are aligned to multiples of 128 list positions so that the forward masks line up.
 // Per-hit arithmetic follows backward.cu:490-554.
 #include "render_common.cuh"
 
@@ -20,18 +28,22 @@ namespace hb {
 
 namespace {
 
-// Sum 9 per-lane values over the warp.  On return every lane of quad q (lanes 4q..4q+3) holds the
-// total of v[q] in `r8` (q = 0..7) and every lane holds the total of v[8] in `r1`.
-__device__ __forceinline__ void warp_reduce9(const float (&v)[9], float& r8, float& r1) {
+constexpr int kBwdBatch = 128;                 // Gaussians staged per round
+constexpr int kBwdChunks = kBwdBatch / 32;     // forward-mask words per warp and round
+constexpr int kBwdWarps = kBlendThreads / 32;  // 8
+
+// Sum 9 per-lane values over the warp and store the totals to dst[0..8] (one predicated store).
+__device__ __forceinline__ void warp_reduce9_store(const float (&v)[9], float* dst) {
     const unsigned lane = threadIdx.x & 31u;
-    const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u;
-    float w[4];
+    const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u, b1 = lane & 2u;
+    float w[4], p8 = v[8];
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         const float send = b4 ? v[i] : v[i + 4];
         const float keep = b4 ? v[i + 4] : v[i];
         w[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
     }
+    p8 += __shfl_xor_sync(0xffffffffu, p8, 16);
     float x[2];
 #pragma unroll
     for (int i = 0; i < 2; i++) {
@@ -39,16 +51,25 @@ __device__ __forceinline__ void warp_reduce9(const float (&v)[9], float& r8, flo
         const float keep = b3 ? w[i + 2] : w[i];
         x[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
     }
+    p8 += __shfl_xor_sync(0xffffffffu, p8, 8);
+    float y;
     {
         const float send = b2 ? x[0] : x[1];
         const float keep = b2 ? x[1] : x[0];
-        r8 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        y = keep + __shfl_xor_sync(0xffffffffu, send, 4);
     }
-    r8 += __shfl_xor_sync(0xffffffffu, r8, 2);
-    r8 += __shfl_xor_sync(0xffffffffu, r8, 1);
-    r1 = v[8];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) r1 += __shfl_xor_sync(0xffffffffu, r1, d);
+    p8 += __shfl_xor_sync(0xffffffffu, p8, 4);
+    // y: value (lane >> 2) summed over the 8 lanes that share (lane & 3); p8: value 8, likewise.
+    // Lanes with bit 1 clear finish y, lanes with bit 1 set finish p8.
+    float r;
+    {
+        const float send = b1 ? y : p8;
+        const float keep = b1 ? p8 : y;
+        r = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    r += __shfl_xor_sync(0xffffffffu, r, 1);
+    if ((lane & 3u) == 0u) dst[lane >> 2] = r;
+    else if (lane == 2u) dst[8] = r;
 }
 
 __global__ void __launch_bounds__(kBlendThreads)
@@ -56,17 +77,21 @@ __global__ void __launch_bounds__(kBlendThreads)
                            int grid_x, const float* __restrict__ bg, const float2* __restrict__ means2D,
                            const float4* __restrict__ conic_opacity, const float* __restrict__ colors,
                            int color_stride, const float* __restrict__ final_T,
-                           const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
-                           float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic,
-                           float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolor) {
-    __shared__ uint32_t s_id[kBlendBatch];
-    __shared__ float2 s_xy[kBlendBatch];
-    __shared__ float4 s_co[kBlendBatch];
-    __shared__ float s_rgb[3][kBlendBatch];
-    __shared__ float s_grad[kBlendBatch][9];
-    __shared__ uint32_t s_max[kBlendThreads / 32];
+                           const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ hit_words,
+                           const float* __restrict__ dL_dpix, float* __restrict__ dL_dmean2D,
+                           float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
+                           float* __restrict__ dL_dcolor) {
+    __shared__ uint32_t s_id[kBwdBatch];
+    __shared__ float2 s_xy[kBwdBatch];
+    __shared__ float4 s_co[kBwdBatch];
+    __shared__ float s_rgb[3][kBwdBatch];
+    __shared__ float s_part[kBwdWarps][kBwdBatch][9];
+    __shared__ uint32_t s_hit[kBwdChunks][kBwdWarps];    // forward masks of this round
+    __shared__ uint32_t s_touch[kBwdWarps][kBwdChunks];  // what each warp actually wrote to s_part
+    __shared__ uint32_t s_max[kBwdWarps];
 
     const unsigned tile_x = blockIdx.x, tile_y = blockIdx.y;
+    const unsigned tile_id = tile_y * grid_x + tile_x;
     const PixelMap pm = pixel_map(tile_x, tile_y);
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const bool inside = pm.px < (unsigned)W && pm.py < (unsigned)H;
@@ -74,7 +99,7 @@ __global__ void __launch_bounds__(kBlendThreads)
     const size_t pix_id = (size_t)W * pm.py + pm.px;
     const size_t plane = (size_t)W * H;
 
-    const uint2 range = __ldg(ranges + tile_y * grid_x + tile_x);
+    const uint2 range = __ldg(ranges + tile_id);
 
     // In the forward, we stored the final value for T, the product of all (1 - alpha) factors,
     // and the (1-based) list position of the last contributing Gaussian of each pixel.
@@ -82,15 +107,13 @@ __global__ void __launch_bounds__(kBlendThreads)
     float T = T_final;
     const uint32_t last_contributor = inside ? __ldg(n_contrib + pix_id) : 0u;
 
-    // Largest contributor count of the tile: nothing behind it was blended by any pixel.
-    {
-        const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
-        if (lane == 0) s_max[warp] = wmax;
-    }
+    // Largest contributor count of this warp / of the tile: nothing behind it was blended.
+    const uint32_t warp_max = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0) s_max[warp] = warp_max;
     __syncthreads();
     uint32_t max_contrib = 0;
 #pragma unroll
-    for (int w = 0; w < kBlendThreads / 32; w++) max_contrib = max(max_contrib, s_max[w]);
+    for (int w = 0; w < kBwdWarps; w++) max_contrib = max(max_contrib, s_max[w]);
     const int todo = (int)min(max_contrib, range.y - range.x);
     if (todo == 0) return;
 
@@ -100,7 +123,8 @@ __global__ void __launch_bounds__(kBlendThreads)
         dLp1 = __ldg(dL_dpix + plane + pix_id);
         dLp2 = __ldg(dL_dpix + 2 * plane + pix_id);
     }
-    const float bg_dot_dpixel = __ldg(bg + 0) * dLp0 + __ldg(bg + 1) * dLp1 + __ldg(bg + 2) * dLp2;
+    // alpha also influences how much of the background colour is added (backward.cu:531-534)
+    const float bg_term = -T_final * (__ldg(bg + 0) * dLp0 + __ldg(bg + 1) * dLp1 + __ldg(bg + 2) * dLp2);
 
     float accum0 = 0.f, accum1 = 0.f, accum2 = 0.f;
     float last_alpha = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f;
@@ -108,13 +132,14 @@ __global__ void __launch_bounds__(kBlendThreads)
     // Gradient of pixel coordinate w.r.t. normalized screen-space viewport coordinates (-1 to 1).
     const float ddelx_dx = 0.5f * W;
     const float ddely_dy = 0.5f * H;
+    const uint32_t* const hit_base = hit_words + ((size_t)(range.x >> 5) + tile_id) * kBwdWarps;
 
-    for (int base = 0; base < todo; base += kBlendBatch) {
-        __syncthreads();
-        // Stage back to front: slot j holds list position todo-1-(base+j).
-        const int mine = base + (int)threadIdx.x;
-        if (mine < todo) {
-            const uint32_t id = __ldg(point_list + range.x + (uint32_t)(todo - 1 - mine));
+    for (int pb = ((todo - 1) / kBwdBatch) * kBwdBatch; pb >= 0; pb -= kBwdBatch) {
+        __syncthreads();  // the previous round's flush has read s_part / s_touch / s_id
+        const int nb = min(kBwdBatch, todo - pb);
+        // Stage list positions [pb, pb + nb): slot j holds position pb + j.
+        if ((int)threadIdx.x < nb) {
+            const uint32_t id = __ldg(point_list + range.x + (uint32_t)(pb + (int)threadIdx.x));
             s_id[threadIdx.x] = id;
             s_xy[threadIdx.x] = __ldg(means2D + id);
             s_co[threadIdx.x] = __ldg(conic_opacity + id);
@@ -128,106 +153,111 @@ __global__ void __launch_bounds__(kBlendThreads)
                 s_rgb[1][threadIdx.x] = __ldg(colors + (size_t)id * 3 + 1);
                 s_rgb[2][threadIdx.x] = __ldg(colors + (size_t)id * 3 + 2);
             }
+        } else if (threadIdx.x >= kBwdBatch && threadIdx.x < kBwdBatch + kBwdChunks * kBwdWarps) {
+            const int q = ((int)threadIdx.x - kBwdBatch) / kBwdWarps, w = ((int)threadIdx.x - kBwdBatch) % kBwdWarps;
+            uint32_t m = 0;
+            if (pb + 32 * q < todo) m = __ldg(hit_base + (size_t)((pb >> 5) + q) * kBwdWarps + w);
+            s_hit[q][w] = m;
         }
-#pragma unroll
-        for (int v = 0; v < 9; v++) s_grad[threadIdx.x][v] = 0.f;
         __syncthreads();
 
-        const int nb = min(kBlendBatch, todo - base);
-        for (int c = 0; c < nb; c += 32) {
-            const int jj = c + (int)lane;
-            bool keep = false;
-            if (jj < nb) {
-                const float2 g = s_xy[jj];
-                const float4 co = s_co[jj];
-                keep = gaussian_may_touch(g.x, g.y, co.x, co.y, co.z, co.w, pm.x0, pm.x1, pm.y0, pm.y1);
+        // This warp's masks, clipped to positions below its own largest contributor count (words
+        // beyond it were never written by the forward pass).
+        uint32_t mq = 0;
+        if (lane < (unsigned)kBwdChunks) {
+            const int p0 = pb + 32 * (int)lane;
+            if (p0 < (int)warp_max) {
+                mq = s_hit[lane][warp];
+                const int rem = (int)warp_max - p0;
+                if (rem < 32) mq &= (1u << rem) - 1u;
             }
-            unsigned m = __ballot_sync(0xffffffffu, keep);
+            s_touch[warp][lane] = mq;
+        }
+#pragma unroll 1
+        for (int q = kBwdChunks - 1; q >= 0; q--) {
+            unsigned m = __shfl_sync(0xffffffffu, mq, q);
             while (m) {
-                const int e = c + __ffs(m) - 1;
-                m &= m - 1;
-                const uint32_t pos = (uint32_t)(todo - 1 - (base + e));  // 0-based list position
+                const int bit = 31 - __clz(m);
+                m ^= 1u << bit;
+                const int e = 32 * q + bit;
+                const uint32_t pos = (uint32_t)(pb + e);  // 0-based list position
                 float g[9];
 #pragma unroll
                 for (int v = 0; v < 9; v++) g[v] = 0.f;
-                bool hit = false;
                 // Skip if this one is behind the last contributor of this pixel.
                 if (pos < last_contributor) {
                     const float2 xy = s_xy[e];
                     const float4 co = s_co[e];
-                    const float dx = __fadd_rn(xy.x, -pixfx);
-                    const float dy = __fadd_rn(xy.y, -pixfy);
-                    const float a = __fmaf_rn(dx, __fmul_rn(dx, co.x), __fmul_rn(dy, __fmul_rn(dy, co.z)));
-                    const float power = __fmaf_rn(a, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, co.y)));
+                    const float dx = xy.x - pixfx;
+                    const float dy = xy.y - pixfy;
+                    const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
                     if (!(power > 0.0f)) {
-                        const float G = expf(power);
-                        const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
+                        const float G = __expf(power);
+                        const float alpha = fminf(0.99f, co.w * G);
                         if (!(alpha < 1.0f / 255.0f)) {
-                            hit = true;
-                            T = T / (1.f - alpha);
+                            const float rcp = __fdividef(1.f, 1.f - alpha);
+                            T *= rcp;
                             const float dchannel_dcolor = alpha * T;
                             // Propagate gradients to per-Gaussian colours and keep gradients w.r.t.
                             // alpha (blending factor for a Gaussian/pixel pair).
                             const float c0 = s_rgb[0][e], c1 = s_rgb[1][e], c2 = s_rgb[2][e];
-                            accum0 = last_alpha * last_c0 + (1.f - last_alpha) * accum0;
-                            accum1 = last_alpha * last_c1 + (1.f - last_alpha) * accum1;
-                            accum2 = last_alpha * last_c2 + (1.f - last_alpha) * accum2;
+                            accum0 = fmaf(last_alpha, last_c0 - accum0, accum0);
+                            accum1 = fmaf(last_alpha, last_c1 - accum1, accum1);
+                            accum2 = fmaf(last_alpha, last_c2 - accum2, accum2);
                             last_c0 = c0;
                             last_c1 = c1;
                             last_c2 = c2;
+                            last_alpha = alpha;
                             float dL_dalpha = (c0 - accum0) * dLp0 + (c1 - accum1) * dLp1 + (c2 - accum2) * dLp2;
                             g[0] = dchannel_dcolor * dLp0;
                             g[1] = dchannel_dcolor * dLp1;
                             g[2] = dchannel_dcolor * dLp2;
-                            dL_dalpha *= T;
-                            last_alpha = alpha;
-                            // alpha also influences how much of the background colour is added.
-                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-
+                            dL_dalpha = fmaf(dL_dalpha, T, bg_term * rcp);
                             const float dL_dG = co.w * dL_dalpha;
-                            const float gdx = G * dx;
-                            const float gdy = G * dy;
-                            const float dG_ddelx = -gdx * co.x - gdy * co.y;
-                            const float dG_ddely = -gdy * co.z - gdx * co.y;
-                            g[3] = dL_dG * dG_ddelx * ddelx_dx;
-                            g[4] = dL_dG * dG_ddely * ddely_dy;
-                            g[5] = -0.5f * gdx * dx * dL_dG;
-                            g[6] = -0.5f * gdx * dy * dL_dG;
-                            g[7] = -0.5f * gdy * dy * dL_dG;
+                            const float X = dL_dG * (G * dx);
+                            const float Y = dL_dG * (G * dy);
+                            g[3] = X;
+                            g[4] = Y;
+                            g[5] = X * dx;
+                            g[6] = X * dy;
+                            g[7] = Y * dy;
                             g[8] = G * dL_dalpha;
                         }
                     }
                 }
-                if (__any_sync(0xffffffffu, hit)) {
-                    float r8, r1;
-                    warp_reduce9(g, r8, r1);
-                    if ((lane & 3u) == 0u) atomicAdd(&s_grad[e][lane >> 2], r8);
-                    if (lane == 1u) atomicAdd(&s_grad[e][8], r1);
-                }
+                warp_reduce9_store(g, &s_part[warp][e][0]);
             }
         }
         __syncthreads();
 
-        // One set of global reductions per (tile, Gaussian) pair.
+        // One set of global reductions per (tile, Gaussian) pair that some warp blended.
         if ((int)threadIdx.x < nb) {
-            float g[9];
+            const int e = (int)threadIdx.x;
+            float S[9];
+#pragma unroll
+            for (int v = 0; v < 9; v++) S[v] = 0.f;
             bool any = false;
 #pragma unroll
-            for (int v = 0; v < 9; v++) {
-                g[v] = s_grad[threadIdx.x][v];
-                any |= (g[v] != 0.f);
+            for (int w = 0; w < kBwdWarps; w++) {
+                if ((s_touch[w][e >> 5] >> (e & 31)) & 1u) {
+                    any = true;
+#pragma unroll
+                    for (int v = 0; v < 9; v++) S[v] += s_part[w][e][v];
+                }
             }
             if (any) {
-                const size_t id = s_id[threadIdx.x];
-                atomicAdd(dL_dcolor + id * 3 + 0, g[0]);
-                atomicAdd(dL_dcolor + id * 3 + 1, g[1]);
-                atomicAdd(dL_dcolor + id * 3 + 2, g[2]);
-                atomicAdd(dL_dmean2D + id * 3 + 0, g[3]);
-                atomicAdd(dL_dmean2D + id * 3 + 1, g[4]);
-                atomicAdd(dL_dconic + id * 4 + 0, g[5]);
-                atomicAdd(dL_dconic + id * 4 + 1, g[6]);
-                atomicAdd(dL_dconic + id * 4 + 3, g[7]);
-                atomicAdd(dL_dopacity + id, g[8]);
+                const size_t id = s_id[e];
+                const float4 co = s_co[e];
+                atomicAdd(dL_dcolor + id * 3 + 0, S[0]);
+                atomicAdd(dL_dcolor + id * 3 + 1, S[1]);
+                atomicAdd(dL_dcolor + id * 3 + 2, S[2]);
+                // dG/ddelx = -G dx A - G dy B, dG/ddely = -G dy C - G dx B (backward.cu:520-521)
+                atomicAdd(dL_dmean2D + id * 3 + 0, -(co.x * S[3] + co.y * S[4]) * ddelx_dx);
+                atomicAdd(dL_dmean2D + id * 3 + 1, -(co.z * S[4] + co.y * S[3]) * ddely_dy);
+                atomicAdd(dL_dconic + id * 4 + 0, -0.5f * S[5]);
+                atomicAdd(dL_dconic + id * 4 + 1, -0.5f * S[6]);
+                atomicAdd(dL_dconic + id * 4 + 3, -0.5f * S[7]);
+                atomicAdd(dL_dopacity + id, S[8]);
             }
         }
     }
@@ -236,13 +266,13 @@ __global__ void __launch_bounds__(kBlendThreads)
 
 int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
                            const float* bg, const float2* means2D, const float4* conic_opacity, const float* colors,
-                           int color_stride, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
-                           float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                           int color_stride, const float* final_T, const uint32_t* n_contrib,
+                           const uint32_t* hit_words, const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                            cudaStream_t stream) {
     const dim3 grid((unsigned)grid_x, (unsigned)grid_y, 1);
     render_backward_kernel<<<grid, kBlendThreads, 0, stream>>>(ranges, point_list, W, H, grid_x, bg, means2D,
                                                                conic_opacity, colors, color_stride, final_T, n_contrib,
-                                                               dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+                                                               hit_words, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
     HB_LAUNCH_OK("render_backward", stream, false);
     return 0;
 }

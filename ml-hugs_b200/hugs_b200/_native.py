@@ -49,7 +49,7 @@ class ImageLayout(C.Structure):
 class BinningLayout(C.Structure):
     _fields_ = [(n, C.c_size_t) for n in (
         "point_list_keys", "point_list", "point_list_keys_unsorted", "point_list_unsorted", "sort_temp",
-        "total")]
+        "hit_words", "total")]
 
 
 def _sig(name, restype, argtypes):
@@ -82,7 +82,7 @@ rasterize_backward = _sig("hugs_b200_rasterize_backward", i32, [
     fp, C.c_float, fp, fp,    # scales, scale_modifier, rotations, cov3D_precomp
     fp, fp, fp,               # viewmatrix, projmatrix, cam_pos
     C.c_float, C.c_float,     # tan_fovx, tan_fovy
-    fp, fp, fp, fp,           # radii, geom, binning, image
+    fp, fp, fp, C.c_size_t, fp,  # radii, geom, binning, binning_bytes, image
     fp,                       # dL_dpix
     fp, fp, fp, fp, fp, fp, fp, fp, fp,  # 9 gradient outputs
     i32, fp,                  # debug, stream
@@ -92,9 +92,9 @@ mark_visible = _sig("hugs_b200_mark_visible", i32, [i32, fp, fp, fp, fp, fp])
 
 geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayout)])
 image_layout_of = _sig("hugs_b200_image_layout_of", i32, [i32, i32, C.POINTER(ImageLayout)])
-binning_layout_of = _sig("hugs_b200_binning_layout_of", i32, [i32, C.POINTER(BinningLayout)])
+binning_layout_of = _sig("hugs_b200_binning_layout_of", i32, [i32, i32, i32, C.POINTER(BinningLayout)])
 
-binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_size_t])
+binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_size_t, i32, i32])
 BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE = 0, 1, 2
 set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
 

@@ -169,7 +169,8 @@ def rasterize_gaussians_backward(
                 N.ptr(scales), float(scale_modifier), N.ptr(rotations), N.ptr(cov3D_precomp),
                 N.ptr(viewmatrix), N.ptr(projmatrix), N.ptr(campos),
                 float(tan_fovx), float(tan_fovy),
-                radii.data_ptr(), N.ptr(geomBuffer), N.ptr(binningBuffer), N.ptr(imageBuffer),
+                radii.data_ptr(), N.ptr(geomBuffer), N.ptr(binningBuffer), int(binningBuffer.numel()),
+                N.ptr(imageBuffer),
                 dL_dout_color.data_ptr(),
                 dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), dL_dcolors.data_ptr(),
                 dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), N.ptr(dL_dsh), dL_dscales.data_ptr(),

@@ -128,7 +128,7 @@ def decode_our_buffers(geom, binning, img, P, R, W, H):
     g, b, im = N.GeomLayout(), N.BinningLayout(), N.ImageLayout()
     N.geom_layout_of(P, g)
     # the binning workspace is laid out for a capacity >= R (recovered from the buffer size)
-    N.binning_layout_of(int(N.binning_capacity_of(binning.numel())), b)
+    N.binning_layout_of(int(N.binning_capacity_of(binning.numel(), W, H)), W, H, b)
     N.image_layout_of(W, H, im)
 
     def take(buf, off, count, dtype, itemsize):

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     missing = [s for s in declared_symbols() if not hasattr(lib, s)]
     assert not missing, "declared in include/hugs_b200.h but not exported: %s" % missing
     assert set(N.EXPORTED_SYMBOLS) <= set(declared_symbols())
-    assert N.abi_version() == 2
+    assert N.abi_version() == 3
 
 
 def test_sort_bits_match_reference_rule():
@@ -51,15 +51,15 @@ def test_layouts_are_aligned_and_disjoint():
     offs = [g.depths, g.means2D, g.conic_opacity, g.rgb, g.clamped, g.tiles_touched, g.point_offsets, g.scan_temp]
     assert offs == sorted(offs) and all(o % 256 == 0 for o in offs) and g.total >= offs[-1]
     assert g.means2D - g.depths >= 4000 and g.conic_opacity - g.means2D >= 8000
-    assert N.binning_layout_of(12345, b) > 0
-    assert b.point_list == 0 and b.point_list_keys >= 4 * 12345 and b.total > b.sort_temp
+    assert N.binning_layout_of(12345, 1920, 1080, b) > 0
+    assert b.point_list == 0 and b.point_list_keys >= 4 * 12345 and b.total > b.hit_words > b.sort_temp
     # the capacity recovered from the buffer size describes the same layout (slices are 256-B aligned)
-    cap = N.binning_capacity_of(b.total)
+    cap = N.binning_capacity_of(b.total, 1920, 1080)
     b2 = N.BinningLayout()
-    N.binning_layout_of(cap, b2)
+    N.binning_layout_of(cap, 1920, 1080, b2)
     assert 12345 <= cap < 12345 + 64 and bytes(b2) == bytes(b)
-    assert N.binning_capacity_of(b.total + 100000) > cap
-    assert N.binning_capacity_of(0) == 0
+    assert N.binning_capacity_of(b.total + 100000, 1920, 1080) > cap
+    assert N.binning_capacity_of(0, 1920, 1080) == 0
     assert N.set_binning_mode(7) == -1 and N.set_binning_mode(N.BINNING_ASYNC) == N.BINNING_ASYNC
     assert N.image_layout_of(1920, 1080, im) > 0
     assert im.n_contrib - im.accum_alpha >= 4 * 1920 * 1080 and im.total - im.ranges >= 8 * 8160
@@ -83,7 +83,7 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert N.sort_pairs(None, None, None, None, 5, 45, None, 0, None) == -1
     assert N.inclusive_scan(None, None, 3, None, 0, None) == -1
     assert N.rasterize_backward(-1, 0, 0, 0, None, 16, 16, None, None, None, None, 1.0, None, None, None, None, None,
-                                1.0, 1.0, None, None, None, None, None, None, None, None, None, None, None, None,
+                                1.0, 1.0, None, None, None, 0, None, None, None, None, None, None, None, None, None,
                                 None, None, 0, None) == -1
     assert N.mark_visible(-3, None, None, None, None, None) == -1
     assert N.stage_name(0) == b"preprocess" and N.stage_name(99) is None
