@@ -224,6 +224,14 @@ size_t hugs_b200_sort_temp_bytes(int n);
 int hugs_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                          int n, int end_bit, void* temp, size_t temp_bytes, hugs_b200_stream_t stream);
 
+/* The same sort restricted to key bits [begin_bit, end_bit), split into equal digits of at most 8
+ * bits.  This is the second level of the rasterizer's binning: pairs emitted in (depth, index) order
+ * are sorted stably on the tile bits [32, 32+bit) only, which yields the order of the reference's
+ * single sort on [0, 32+bit) (CR/rasterizer_impl.cu:300-308). */
+int hugs_b200_sort_pairs_range(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                               int n, int begin_bit, int end_bit, void* temp, size_t temp_bytes,
+                               hugs_b200_stream_t stream);
+
 /* Bytes of temp storage hugs_b200_inclusive_scan needs for n items. */
 size_t hugs_b200_scan_temp_bytes(int n);
 

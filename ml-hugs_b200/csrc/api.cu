@@ -388,6 +388,28 @@ int hugs_b200_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_ou
                              static_cast<cudaStream_t>(stream));
 }
 
+int hugs_b200_sort_pairs_range(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
+                               int begin_bit, int end_bit, void* temp, size_t temp_bytes,
+                               hugs_b200_stream_t stream) {
+    if (n < 0 || begin_bit < 0 || end_bit < begin_bit || end_bit > 64) {
+        set_error("sort_pairs_range: bad n / bit range");
+        return HUGS_B200_EINVAL;
+    }
+    if (n > 0 && (!keys_in || !vals_in || !keys_out || !vals_out)) {
+        set_error("sort_pairs_range: null buffer");
+        return HUGS_B200_EINVAL;
+    }
+    if (end_bit == begin_bit && n > 0) {
+        HB_CUDA_OK(cudaMemcpyAsync(keys_out, keys_in, sizeof(uint64_t) * (size_t)n, cudaMemcpyDeviceToDevice,
+                                   static_cast<cudaStream_t>(stream)));
+        HB_CUDA_OK(cudaMemcpyAsync(vals_out, vals_in, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice,
+                                   static_cast<cudaStream_t>(stream)));
+        return 0;
+    }
+    return launch_sort_pairs(keys_in, vals_in, keys_out, vals_out, n, end_bit, temp, temp_bytes,
+                             static_cast<cudaStream_t>(stream), begin_bit);
+}
+
 int hugs_b200_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
                              hugs_b200_stream_t stream) {
     if (n < 0 || (n > 0 && (!in || !out))) {
@@ -534,28 +556,21 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         if (cap > 0 && two_level) {
             n_dev = R_dev;
             const SortPassPlan plan = tile_pass_plan(tile_bits);
-            // the last pass must land in (keys, list)
-            const bool even = (plan.num_passes % 2 == 0);
-            uint64_t* k0 = even ? bin.keys : bin.keys_unsorted;
-            uint32_t* v0 = even ? bin.list : bin.list_unsorted;
-            uint64_t* k1 = even ? bin.keys_unsorted : bin.keys;
-            uint32_t* v1 = even ? bin.list_unsorted : bin.list;
+            // Packed (tile << 32 | index) pairs ping-pong between the two 64-bit buffers; the last pass
+            // reads from keys_unsorted and writes (keys, list).
+            uint64_t* first_buf = (plan.num_passes % 2 == 0) ? bin.keys : bin.keys_unsorted;
             auto emit = [&]() -> int {
                 const int rc = sort_temp_clear(bin.sort_temp, bin.sort_temp_bytes, cap, stream);
                 if (rc) return rc;
-                return launch_duplicate_sorted(P, geom.perm, geom.sorted_depths, geom.point_offsets, geom.means2D, radii,
-                                               k0, v0, cam.grid_x, cam.grid_y, cap, plan,
-                                               sort_temp_histogram(bin.sort_temp), stream);
+                return launch_duplicate_sorted(P, geom.perm, geom.point_offsets, geom.means2D, radii, first_buf,
+                                               cam.grid_x, cam.grid_y, cap, plan, sort_temp_histogram(bin.sort_temp),
+                                               stream);
             };
             HB_STAGE(emit(), ST_DUPLICATE);
-            bool in_first = true;
-            HB_STAGE(launch_tile_sort(k0, v0, k1, v1, cap, n_dev, plan, bin.sort_temp, bin.sort_temp_bytes, stream,
-                                      &in_first),
+            HB_STAGE(launch_tile_sort(bin.keys, bin.keys_unsorted, bin.keys, bin.list,
+                                      reinterpret_cast<const uint32_t*>(geom.depths), cap, n_dev, plan, bin.sort_temp,
+                                      bin.sort_temp_bytes, stream),
                      ST_SORT);
-            if ((in_first ? k0 : k1) != bin.keys) {
-                set_error("rasterize_forward: internal error, sorted pairs landed in the wrong buffer");
-                return HUGS_B200_EINVAL;
-            }
         } else if (cap > 0) {
             // Reference structure: pairs emitted in Gaussian-index order, one sort on all 32+bit key bits.
             const int end_bit = 32 + tile_bits;

@@ -75,22 +75,24 @@ __global__ void __launch_bounds__(kDupThreads)
 }
 
 // Depth-sorted variant used by the rasterizer: CTA b owns the Gaussians at depth-sorted positions
-// [256 b, 256 b + 256) (`perm` = argsort of the depth bits, `sorted_depth` the sorted bits, `offsets`
-// the inclusive scan of tiles_touched in that order).  Pairs therefore leave this kernel ordered by
-// (depth bits, Gaussian index), and a stable sort on the tile bits alone reproduces the reference's
-// order on the full 32+bit key.  While emitting, the CTA also counts the tile digits of the
-// following sort passes (`plan`) into `hist`, so the sort needs no histogram pass of its own.
-// Emission is clamped to `cap` slots: the workspace is sized from the previous frames' pair count
-// before the real count has reached the host (api.cu); an overflow is detected there and redone.
+// [256 b, 256 b + 256) (`perm` = argsort of the depth bits, `offsets` the inclusive scan of
+// tiles_touched in that order).  Pairs therefore leave this kernel ordered by (depth bits, Gaussian
+// index), and a stable sort on the tile bits alone reproduces the reference's order on the full
+// 32+bit key.  Because the depth is implied by the position, a pair is emitted as ONE 64-bit word
+// (tile << 32 | Gaussian index): 8 B instead of the reference's 12 B (8 B key + 4 B value); the
+// last sort pass turns it back into (tile << 32 | depth bits, index).  While emitting, the CTA also
+// counts the tile digits of the following sort passes (`plan`) into `hist`, so the sort needs no
+// histogram pass of its own.  Emission is clamped to `cap` slots: the workspace is sized from the
+// previous frames' pair count before the real count has reached the host (api.cu); an overflow is
+// detected there and redone.
 __global__ void __launch_bounds__(kDupThreads)
-    duplicate_sorted_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ sorted_depth,
-                            const uint32_t* __restrict__ offsets, const float2* __restrict__ means2D,
-                            const int* __restrict__ radii, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
-                            unsigned grid_x, unsigned grid_y, uint32_t cap, const SortPassPlan plan,
-                            uint32_t* __restrict__ hist) {
+    duplicate_sorted_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets,
+                            const float2* __restrict__ means2D, const int* __restrict__ radii,
+                            uint64_t* __restrict__ pairs, unsigned grid_x, unsigned grid_y, uint32_t cap,
+                            const SortPassPlan plan, uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_off[kDupThreads + 1];
-    __shared__ uint32_t s_depth[kDupThreads];
     __shared__ uint32_t s_rect[kDupThreads];
+    __shared__ uint32_t s_inv[kDupThreads];  // ceil(2^32 / rect width): k / w == umulhi(k, inv) for k*w < 2^32
     __shared__ uint32_t s_idx[kDupThreads];
     __shared__ uint32_t s_hist[3][256];
     const int tid = threadIdx.x;
@@ -103,7 +105,7 @@ __global__ void __launch_bounds__(kDupThreads)
         end_off = __ldg(offsets + pos);
         const uint32_t idx = __ldg(perm + pos);
         const int r = __ldg(radii + idx);
-        uint32_t rect = 0;
+        uint32_t rect = 0, inv = 0;
         if (r > 0) {
             // getRect (auxiliary.h:46-56), same float sequence as preprocess.
             const float2 p = __ldg(means2D + idx);
@@ -112,10 +114,12 @@ __global__ void __launch_bounds__(kDupThreads)
             const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
             const unsigned max_x = min(
                 grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
-            rect = min_x | (min_y << 10) | ((max_x - min_x) << 20);
+            const unsigned w = max_x - min_x;
+            rect = min_x | (min_y << 10) | (w << 20);
+            inv = (w > 1u) ? (uint32_t)((0x100000000ull + w - 1u) / w) : 0u;
         }
         s_rect[tid] = rect;
-        s_depth[tid] = __ldg(sorted_depth + pos);
+        s_inv[tid] = inv;
         s_idx[tid] = idx;
     }
     if (tid == 0) s_off[0] = (first == 0) ? 0u : __ldg(offsets + first - 1);
@@ -124,6 +128,9 @@ __global__ void __launch_bounds__(kDupThreads)
     __syncthreads();
     const uint32_t begin = s_off[0];
     const uint32_t end = min(s_off[in_block], cap);
+    // digit layout of the first two sort passes relative to the tile id
+    const int sh0 = plan.shift[0] - 32, sh1 = plan.shift[1] - 32, sh2 = plan.shift[2] - 32;
+    const uint32_t mk0 = (1u << plan.bits[0]) - 1u, mk1 = (1u << plan.bits[1]) - 1u, mk2 = (1u << plan.bits[2]) - 1u;
     for (uint32_t ob = begin; ob < end; ob += kDupThreads) {
         const uint32_t o = ob + tid;
         const bool valid = o < end;
@@ -137,24 +144,29 @@ __global__ void __launch_bounds__(kDupThreads)
             const uint32_t rect = s_rect[lo];
             const uint32_t k = o - s_off[lo];
             const uint32_t w = rect >> 20;
-            const uint32_t y = ((rect >> 10) & 1023u) + k / w;
-            const uint32_t x = (rect & 1023u) + k % w;
+            const uint32_t q = (w > 1u) ? __umulhi(k, s_inv[lo]) : k;  // k / w
+            const uint32_t y = ((rect >> 10) & 1023u) + q;
+            const uint32_t x = (rect & 1023u) + (k - q * w);
             const uint32_t tile = y * grid_x + x;
-            keys[o] = ((uint64_t)tile << 32) | (uint64_t)s_depth[lo];
-            vals[o] = s_idx[lo];
-            // Digit counts for the sort passes.  Lanes that share the first active lane's digit (the
-            // common case for the high tile bits) are counted with one atomic; the rest hit distinct
-            // counters mostly (low tile bits of neighbouring tiles) and add individually.
+            pairs[o] = ((uint64_t)tile << 32) | (uint64_t)s_idx[lo];
+            // Digit counts for the sort passes.  Neighbouring slots are neighbouring tiles: their low
+            // digits differ (plain shared-memory atomics, no conflicts), their higher digits mostly
+            // coincide (lanes that share the first active lane's digit are counted with one atomic).
+            atomicAdd(&s_hist[0][(tile >> sh0) & mk0], 1u);
             const int first_lane = __ffs(active) - 1;
-#pragma unroll
-            for (int p = 0; p < 3; p++) {
-                if (p < plan.num_passes) {
-                    const uint32_t d = (tile >> (plan.shift[p] - 32)) & ((1u << plan.bits[p]) - 1u);
-                    const uint32_t d0 = __shfl_sync(active, d, first_lane);
-                    const unsigned same = __ballot_sync(active, d == d0);
-                    if (d != d0) atomicAdd(&s_hist[p][d], 1u);
-                    else if ((int)lane == first_lane) atomicAdd(&s_hist[p][d0], (uint32_t)__popc(same));
-                }
+            if (plan.num_passes > 1) {
+                const uint32_t d = (tile >> sh1) & mk1;
+                const uint32_t d0 = __shfl_sync(active, d, first_lane);
+                const unsigned same = __ballot_sync(active, d == d0);
+                if (d != d0) atomicAdd(&s_hist[1][d], 1u);
+                else if ((int)lane == first_lane) atomicAdd(&s_hist[1][d0], (uint32_t)__popc(same));
+            }
+            if (plan.num_passes > 2) {
+                const uint32_t d = (tile >> sh2) & mk2;
+                const uint32_t d0 = __shfl_sync(active, d, first_lane);
+                const unsigned same = __ballot_sync(active, d == d0);
+                if (d != d0) atomicAdd(&s_hist[2][d], 1u);
+                else if ((int)lane == first_lane) atomicAdd(&s_hist[2][d0], (uint32_t)__popc(same));
             }
         }
     }
@@ -249,17 +261,16 @@ int launch_duplicate(int P, const float2* means2D, const float* depths, const ui
     return 0;
 }
 
-int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* sorted_depth, const uint32_t* offsets,
-                            const float2* means2D, const int* radii, uint64_t* keys, uint32_t* vals, int grid_x,
-                            int grid_y, int cap, const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream) {
+int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* offsets, const float2* means2D,
+                            const int* radii, uint64_t* pairs, int grid_x, int grid_y, int cap,
+                            const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream) {
     if (P <= 0) return 0;
     if (grid_x > 1023 || grid_y > 1023 || plan.num_passes > 3) {
         set_error("duplicate_sorted: tile grid %dx%d too large", grid_x, grid_y);
         return HUGS_B200_EUNSUP_INTERNAL;
     }
     duplicate_sorted_kernel<<<cdiv(P, kDupThreads), kDupThreads, 0, stream>>>(
-        P, perm, sorted_depth, offsets, means2D, radii, keys, vals, (unsigned)grid_x, (unsigned)grid_y, (uint32_t)cap,
-        plan, hist);
+        P, perm, offsets, means2D, radii, pairs, (unsigned)grid_x, (unsigned)grid_y, (uint32_t)cap, plan, hist);
     HB_LAUNCH_OK("duplicate_with_keys", stream, false);
     return 0;
 }

@@ -114,9 +114,9 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, 
 int launch_duplicate(int P, const float2* means2D, const float* depths, const uint32_t* offsets,
                      const int* radii, uint64_t* keys, uint32_t* vals, int grid_x, int grid_y,
                      cudaStream_t stream);
-int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* sorted_depth, const uint32_t* offsets,
-                            const float2* means2D, const int* radii, uint64_t* keys, uint32_t* vals, int grid_x,
-                            int grid_y, int cap, const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream);
+int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* offsets, const float2* means2D,
+                            const int* radii, uint64_t* pairs, int grid_x, int grid_y, int cap,
+                            const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream);
 int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream,
                        const uint32_t* n_dev = nullptr);
 
@@ -127,14 +127,14 @@ int sort_temp_clear(void* temp, size_t temp_bytes, int n_cap, cudaStream_t strea
 uint32_t* sort_temp_histogram(void* temp);   // [kSortMaxPasses][256] digit counts, filled by the duplicate kernel
 int launch_depth_argsort(const uint32_t* keys0, uint32_t* kB, uint32_t* vB, uint32_t* kC, uint32_t* vC, int P,
                          void* temp, size_t temp_bytes, cudaStream_t stream);
-int launch_tile_sort(uint64_t* k0, uint32_t* v0, uint64_t* k1, uint32_t* v1, int n_cap, const uint32_t* n_dev,
-                     const SortPassPlan& plan, void* temp, size_t temp_bytes, cudaStream_t stream,
-                     bool* result_in_first);
+int launch_tile_sort(uint64_t* a, uint64_t* b, uint64_t* keys_out, uint32_t* list_out, const uint32_t* depth_bits,
+                     int n_cap, const uint32_t* n_dev, const SortPassPlan& plan, void* temp, size_t temp_bytes,
+                     cudaStream_t stream);
 int launch_sort_pairs_pingpong(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
                                int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream,
-                               bool* result_in_input);
+                               bool* result_in_input, int begin_bit = 0);
 int launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
-                      int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream);
+                      int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream, int begin_bit = 0);
 
 int launch_render_forward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
                           const float2* means2D, const float* colors, int color_stride,

@@ -33,7 +33,9 @@ namespace hb {
 namespace {
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
-constexpr int kMinSortTile = 2048;  // smallest tile of any kernel variant: sizes the look-back array
+constexpr int kSortThreads = 512;
+constexpr int kSortItems = 8;
+constexpr int kMinSortTile = kSortThreads * kSortItems;  // 4096 pairs per CTA: sizes the look-back array
 constexpr int kHistThreads = 512;
 static_assert(kSortMaxPasses == 8, "header constant");
 
@@ -94,81 +96,125 @@ __global__ void __launch_bounds__(kRadix) radix_offsets_kernel(uint32_t* __restr
 }
 
 // ---- 3. one scatter pass ---------------------------------------------------------------------
-// 512 threads x 8 pairs: the same 4096-pair tile as 256 x 16, but half the registers per thread,
-// so keys AND payloads are loaded up front (one exposed DRAM round trip per tile instead of two)
-// and two to three CTAs (32-48 warps) stay resident per SM.
-template <typename KeyT, int THREADS, int ITEMS>
+// The kernel is bound by instruction issue and shared-memory latency, not by HBM (ncu: 93 M warp
+// instructions per pass over 12.25 M pairs at 1.7 IPC/SM), so the three payload modes below exist to
+// execute fewer instructions per pair, and the CTA shape (512 threads x 8 pairs) to keep 32 warps
+// per SM resident with every global load of the tile in flight before its first use.
+//   kPairs     (key, u32 payload) pairs; vals_in == nullptr means "the payload of item i is i"
+//              (first pass of an argsort).  Generic stable pair sort.
+//   kKeysOnly  the payload rides in the low 32 bits of a u64 key (the sorted digit lies above them):
+//              one load / stage / store per pair instead of two.
+//   kSplit     last pass of a kKeysOnly sort: emits payload = low word to vals_out and
+//              key = (high word << 32) | low_table[payload] to keys_out.  The rasterizer sorts
+//              (tile << 32 | Gaussian index) and gets (tile << 32 | depth bits, index) out.
+enum SortMode { kPairs = 0, kKeysOnly = 1, kSplit = 2 };
+
+template <typename KeyT, int THREADS, int ITEMS, int MODE>
 struct SortSmem {
-    KeyT keys[THREADS * ITEMS];                   // 32 KB (u64) / 16 KB (u32)
-    uint32_t vals[THREADS * ITEMS];               // 16 KB
-    uint32_t warp_hist[THREADS / 32][kRadix]; // 16 KB
-    uint32_t local_start[kRadix];           //  1 KB  first staged slot of each digit
-    uint32_t count[kRadix];                 //  1 KB  pairs of each digit in this tile
-    int64_t bin_base[kRadix];               //  2 KB  global index of staged slot 0 of each digit
+    KeyT keys[THREADS * ITEMS];                              // 32 KB (u64) / 16 KB (u32)
+    uint32_t vals[MODE == kPairs ? THREADS * ITEMS : 1];     // 16 KB
+    uint32_t warp_hist[THREADS / 32][kRadix];                // 16 KB
+    uint32_t local_start[kRadix];  // first staged slot of each digit
+    uint32_t count[kRadix];        // pairs of each digit in this tile
+    uint32_t bin_off[kRadix];      // global index of staged slot 0 of each digit (mod 2^32)
     uint32_t scan_warp[kRadix / 32];
     unsigned tile;
 };
 
 // Decoupled look-back with a WINDOW.  The textbook walk (one thread per digit, one predecessor per
 // dependent L2 round trip) makes the time for an inclusive prefix to reach a tile grow like
-// sqrt(2 x tiles in flight) round trips; with ~300-450 tiles in flight on 148 SMs that chain, not
-// HBM, set the pass time (profiles/r01_d_sort_lookback.txt).  Here the `T` threads of a digit
-// fetch kLookWin x T predecessors per round trip, all loads in flight at once, and combine with
-// shuffles inside the digit's lane group.
-constexpr int kLookWin = 8;
+// sqrt(2 x tiles in flight) round trips; with ~300-450 tiles in flight on 148 SMs that chain cost
+// more than the HBM traffic of the pass.  Here the `T` threads of a digit fetch WIN x T predecessors
+// per round trip, all loads in flight at once, and combine with shuffles inside the digit's lane
+// group: a narrow first round (the nearest predecessors usually suffice), wide ones after it.
+template <int WIN>
+__device__ __forceinline__ bool lookback_round(const unsigned long long* __restrict__ lookback, int t0, int d,
+                                               int sub, int T, unsigned gmask, unsigned flag_agg, unsigned flag_inc,
+                                               uint32_t& prefix) {
+    const int kBig = 1 << 30;
+    unsigned long long w[WIN];
+#pragma unroll
+    for (int k = 0; k < WIN; k++) {
+        const int t = t0 - sub - T * k;
+        w[k] = (t >= 0) ? ld_relaxed_u64(lookback + (size_t)t * kRadix + d) : ((unsigned long long)flag_inc << 32);
+    }
+#pragma unroll
+    for (int k = 0; k < WIN; k++) {
+        const int t = t0 - sub - T * k;
+        if (t >= 0)
+            while ((unsigned)(w[k] >> 32) < flag_agg) w[k] = ld_relaxed_u64(lookback + (size_t)t * kRadix + d);
+    }
+    // distance (0-based) of the nearest predecessor that already holds an inclusive prefix
+    int best = kBig;
+#pragma unroll
+    for (int k = WIN - 1; k >= 0; k--)
+        if ((unsigned)(w[k] >> 32) == flag_inc) best = sub + T * k;
+    for (int o = T >> 1; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o));
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < WIN; k++)
+        if (sub + T * k <= best) sum += (uint32_t)w[k];
+    for (int o = T >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(gmask, sum, o);
+    prefix += sum;
+    return best != kBig;
+}
 
 __device__ __forceinline__ uint32_t lookback_prefix(const unsigned long long* __restrict__ lookback, int tile, int d,
                                                     int sub, int T, unsigned gmask, unsigned flag_agg,
                                                     unsigned flag_inc) {
     uint32_t prefix = 0;
-    const int kBig = 1 << 30;
-    for (int t0 = tile - 1; t0 >= 0; t0 -= T * kLookWin) {
-        unsigned long long w[kLookWin];
-#pragma unroll
-        for (int k = 0; k < kLookWin; k++) {
-            const int t = t0 - sub - T * k;
-            w[k] = (t >= 0) ? ld_relaxed_u64(lookback + (size_t)t * kRadix + d) : ((unsigned long long)flag_inc << 32);
-        }
-#pragma unroll
-        for (int k = 0; k < kLookWin; k++) {
-            const int t = t0 - sub - T * k;
-            if (t >= 0)
-                while ((unsigned)(w[k] >> 32) < flag_agg) w[k] = ld_relaxed_u64(lookback + (size_t)t * kRadix + d);
-        }
-        // distance (0-based) of the nearest predecessor that already holds an inclusive prefix
-        int best = kBig;
-#pragma unroll
-        for (int k = kLookWin - 1; k >= 0; k--)
-            if ((unsigned)(w[k] >> 32) == flag_inc) best = sub + T * k;
-        for (int o = T >> 1; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(gmask, best, o));
-        uint32_t sum = 0;
-#pragma unroll
-        for (int k = 0; k < kLookWin; k++)
-            if (sub + T * k <= best) sum += (uint32_t)w[k];
-        for (int o = T >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(gmask, sum, o);
-        prefix += sum;
-        if (best != kBig) break;
-    }
+    int t0 = tile - 1;
+    if (t0 < 0) return 0;
+    if (lookback_round<2>(lookback, t0, d, sub, T, gmask, flag_agg, flag_inc, prefix)) return prefix;
+    for (t0 -= 2 * T; t0 >= 0; t0 -= 8 * T)
+        if (lookback_round<8>(lookback, t0, d, sub, T, gmask, flag_agg, flag_inc, prefix)) break;
     return prefix;
 }
 
-// vals_in == nullptr means "the payload of item i is i" (first pass of an argsort).
-template <typename KeyT, int THREADS, int ITEMS, int MINB>
+// Stable warp-local rank of one item.  Lanes holding the same digit are found with one ballot per
+// digit bit (constant cost); match.any takes time proportional to the number of distinct digits in
+// the warp (profiles/r01_b_sort_passes.txt).  The leader bumps the warp's counter with one
+// shared-memory atomic (returns the old value).
+template <bool FULL, int BITS>
+__device__ __forceinline__ uint32_t warp_rank(uint32_t d, bool valid, int digit_bits, uint32_t* warp_hist,
+                                              unsigned lane, unsigned lanemask_lt) {
+    const int nbits = BITS ? BITS : digit_bits;  // BITS != 0: known at compile time, the loop below is straight-line
+    unsigned peers = FULL ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < kRadixBits; b++) {
+        if (b < nbits) {
+            const bool bit = (d >> b) & 1u;
+            const unsigned m = __ballot_sync(0xffffffffu, FULL ? bit : (valid && bit));
+            peers &= bit ? m : ~m;
+        }
+    }
+    // every lane takes part in the shuffle (a data-dependent member mask costs a match + reduction)
+    const int leader = (__ffs(peers) - 1) & 31;
+    uint32_t old = 0;
+    if ((FULL || valid) && (int)lane == leader) old = atomicAdd(warp_hist + d, (uint32_t)__popc(peers));
+    old = __shfl_sync(0xffffffffu, old, leader);
+    __syncwarp();
+    return (FULL || valid) ? old + __popc(peers & lanemask_lt) : 0u;
+}
+
+template <typename KeyT, int THREADS, int ITEMS, int MINB, int MODE, int BITS>
 __global__ void __launch_bounds__(THREADS, MINB)
     radix_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                           KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n_host,
                           const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask, int pass,
                           const uint32_t* __restrict__ pass_offsets, unsigned long long* lookback,
-                          unsigned* tickets, int dbg_no_lookback) {
+                          unsigned* tickets, const uint32_t* __restrict__ low_table, int dbg_no_lookback) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int kSortThreads = THREADS, kSortItems = ITEMS, kSortWarps = THREADS / 32, kSortTile = THREADS * ITEMS;
     static_assert(THREADS >= kRadix && THREADS % kRadix == 0, "digit phases use the first kRadix threads");
-    using Smem = SortSmem<KeyT, THREADS, ITEMS>;
+    static_assert(MODE == kPairs || sizeof(KeyT) == 8, "payload-in-key modes need 64-bit keys");
+    using Smem = SortSmem<KeyT, THREADS, ITEMS, MODE>;
     Smem& s = *reinterpret_cast<Smem*>(smem_raw);
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31, warp = tid >> 5;
     const unsigned lanemask_lt = (1u << lane) - 1u;
-    const int digit_bits = __popc(digit_mask);
+    const int digit_bits = BITS ? BITS : __popc(digit_mask);
+    if (BITS) digit_mask = (1u << BITS) - 1u;
 
     // n_host is the capacity the grid was sized for when the real count lives on the device
     int n = n_host;
@@ -184,55 +230,40 @@ __global__ void __launch_bounds__(THREADS, MINB)
     const int warp_base = tile_base + (int)warp * (32 * kSortItems);
     const bool full_tile = tile_base + kSortTile <= n;
 
-    // Load keys and payloads, warp-striped; every load of the tile is in flight before the first use.
+    // Load keys (and payloads), warp-striped; every load of the tile is in flight before the first use.
     KeyT key[kSortItems];
-    uint32_t val[kSortItems];
+    uint32_t val[MODE == kPairs ? kSortItems : 1];
     if (full_tile) {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) key[k] = __ldg(keys_in + warp_base + k * 32 + lane);
+        if (MODE == kPairs) {
 #pragma unroll
-        for (int k = 0; k < kSortItems; k++) {
-            const int i = warp_base + k * 32 + (int)lane;
-            val[k] = (vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
+            for (int k = 0; k < kSortItems; k++) {
+                const int i = warp_base + k * 32 + (int)lane;
+                val[MODE == kPairs ? k : 0] = (vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
+            }
         }
     } else {
 #pragma unroll
         for (int k = 0; k < kSortItems; k++) {
             const int i = warp_base + k * 32 + (int)lane;
             key[k] = (i < n) ? __ldg(keys_in + i) : (KeyT)~(KeyT)0;
-            val[k] = (i < n && vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
+            if (MODE == kPairs) val[MODE == kPairs ? k : 0] = (i < n && vals_in != nullptr) ? __ldg(vals_in + i) : (uint32_t)i;
         }
     }
 
-    // Stable warp-local ranks.  Lanes holding the same digit are found with one ballot per digit
-    // bit (constant cost); match.any takes time proportional to the number of distinct digits in
-    // the warp (profiles/r01_b_sort_passes.txt).
-    uint32_t rank[kSortItems];
+    uint32_t dig[kSortItems], rank[kSortItems];
 #pragma unroll
-    for (int k = 0; k < kSortItems; k++) {
-        const bool valid = full_tile || (warp_base + k * 32 + (int)lane < n);
-        const uint32_t d = (uint32_t)(key[k] >> shift) & digit_mask;
-        unsigned peers = __ballot_sync(0xffffffffu, valid);
+    for (int k = 0; k < kSortItems; k++) dig[k] = (uint32_t)(key[k] >> shift) & digit_mask;
+    if (full_tile) {
 #pragma unroll
-        for (int b = 0; b < kRadixBits; b++) {
-            if (b < digit_bits) {
-                const bool bit = (d >> b) & 1u;
-                const unsigned m = __ballot_sync(0xffffffffu, valid && bit);
-                peers &= bit ? m : ~m;
-            }
-        }
-        rank[k] = 0;
-        if (valid) {
-            const int leader = __ffs(peers) - 1;
-            uint32_t old = 0;
-            if ((int)lane == leader) {
-                old = s.warp_hist[warp][d];
-                s.warp_hist[warp][d] = old + __popc(peers);
-            }
-            old = __shfl_sync(peers, old, leader);
-            rank[k] = old + __popc(peers & lanemask_lt);
-        }
-        __syncwarp();
+        for (int k = 0; k < kSortItems; k++)
+            rank[k] = warp_rank<true, BITS>(dig[k], true, digit_bits, s.warp_hist[warp], lane, lanemask_lt);
+    } else {
+#pragma unroll
+        for (int k = 0; k < kSortItems; k++)
+            rank[k] = warp_rank<false, BITS>(dig[k], warp_base + k * 32 + (int)lane < n, digit_bits, s.warp_hist[warp], lane,
+                                       lanemask_lt);
     }
     __syncthreads();
 
@@ -266,6 +297,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
         for (unsigned w = 0; w < warp; w++) base += s.scan_warp[w];
         s.local_start[tid] = base + incl - tile_count;
     }
+    __syncthreads();
 
     // Windowed decoupled look-back: T = threads per digit (a power of two, at most one warp).
     {
@@ -281,21 +313,20 @@ __global__ void __launch_bounds__(THREADS, MINB)
                 if (tile != 0)
                     st_relaxed_u64(lookback + (size_t)tile * kRadix + d,
                                    ((unsigned long long)flag_inc << 32) | (unsigned long long)(prefix + cnt));
-                s.bin_base[d] = (int64_t)__ldg(pass_offsets + d) + (int64_t)prefix;
+                s.bin_off[d] = __ldg(pass_offsets + d) + prefix - s.local_start[d];
             }
         }
     }
-    __syncthreads();
 
-    // Stage the tile digit-sorted in shared memory.
+    // Stage the tile digit-sorted in shared memory (local_start / warp_hist were final before the
+    // barrier above; bin_off is not read until after the next one).
 #pragma unroll
     for (int k = 0; k < kSortItems; k++) {
         const int i = warp_base + k * 32 + (int)lane;
         if (full_tile || i < n) {
-            const uint32_t d = (uint32_t)(key[k] >> shift) & digit_mask;
-            const uint32_t pos = s.local_start[d] + s.warp_hist[warp][d] + rank[k];
+            const uint32_t pos = s.local_start[dig[k]] + s.warp_hist[warp][dig[k]] + rank[k];
             s.keys[pos] = key[k];
-            s.vals[pos] = val[k];
+            if (MODE == kPairs) s.vals[pos] = val[MODE == kPairs ? k : 0];
         }
     }
     __syncthreads();
@@ -308,9 +339,17 @@ __global__ void __launch_bounds__(THREADS, MINB)
         if (i < count) {
             const KeyT kk = s.keys[i];
             const uint32_t d = (uint32_t)(kk >> shift) & digit_mask;
-            const int64_t g = s.bin_base[d] + (int64_t)i - (int64_t)s.local_start[d];
-            keys_out[g] = kk;
-            vals_out[g] = s.vals[i];
+            const uint32_t g = s.bin_off[d] + (uint32_t)i;
+            if (MODE == kPairs) {
+                keys_out[g] = kk;
+                vals_out[g] = s.vals[i];
+            } else if (MODE == kKeysOnly) {
+                keys_out[g] = kk;
+            } else {
+                const uint32_t payload = (uint32_t)kk;
+                vals_out[g] = payload;
+                keys_out[g] = (KeyT)(((unsigned long long)kk & 0xffffffff00000000ull) | __ldg(low_table + payload));
+            }
         }
     }
 }
@@ -336,13 +375,15 @@ SortTemp carve_sort_temp(void* temp, int n) {
     return t;
 }
 
-// One scatter pass with a given CTA shape.
-template <typename KeyT, int THREADS, int ITEMS, int MINB>
-int launch_pass_shape(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout, int n_cap,
-                      const uint32_t* n_dev, int shift, uint32_t mask, int pass, const SortTemp& t,
-                      cudaStream_t stream) {
-    using Smem = SortSmem<KeyT, THREADS, ITEMS>;
-    auto kernel = radix_onesweep_kernel<KeyT, THREADS, ITEMS, MINB>;
+// One scatter pass.  CTA shape 512 x 8 (256x8, 256x16 and 512x4 measured within 3 % of it and are gone);
+// the common digit widths get a kernel with the width known at compile time.
+template <typename KeyT, int MODE, int BITS>
+int launch_pass_bits(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout, int n_cap,
+                     const uint32_t* n_dev, int shift, uint32_t mask, int pass, const SortTemp& t,
+                     const uint32_t* low_table, cudaStream_t stream) {
+    constexpr int THREADS = kSortThreads, ITEMS = kSortItems;
+    using Smem = SortSmem<KeyT, THREADS, ITEMS, MODE>;
+    auto kernel = radix_onesweep_kernel<KeyT, THREADS, ITEMS, 2, MODE, BITS>;
     static bool configured = false;  // per instantiation; the attribute is per device function, idempotent
     if (!configured) {
         HB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
@@ -350,34 +391,28 @@ int launch_pass_shape(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t
                                         cudaSharedmemCarveoutMaxShared));
         configured = true;
     }
+    static const bool no_lookback = getenv("HB_SORT_NOLOOK") != nullptr;  // timing experiments only: wrong output
     const int tiles = cdiv(n_cap, THREADS * ITEMS);
     kernel<<<tiles, THREADS, sizeof(Smem), stream>>>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass,
-                                                     t.hist + pass * kRadix, t.lookback, t.tickets,
-                                                     getenv("HB_SORT_NOLOOK") != nullptr);
+                                                     t.hist + pass * kRadix, t.lookback, t.tickets, low_table,
+                                                     no_lookback ? 1 : 0);
     HB_LAUNCH_OK("radix_onesweep", stream, false);
     return 0;
 }
 
-// CTA shape selection.  HB_SORT_SHAPE (tuning aid, read once): 0 = 512x8, 1 = 256x8, 2 = 256x16, 3 = 512x4.
-int sort_shape() {
-    static int shape = -1;
-    if (shape < 0) {
-        const char* e = getenv("HB_SORT_SHAPE");
-        shape = e ? atoi(e) : 0;
-        if (shape < 0 || shape > 3) shape = 0;
-    }
-    return shape;
-}
-
-template <typename KeyT>
+template <typename KeyT, int MODE>
 int launch_pass(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout, int n_cap, const uint32_t* n_dev,
-                int shift, uint32_t mask, int pass, const SortTemp& t, cudaStream_t stream) {
-    switch (sort_shape()) {
-        case 1: return launch_pass_shape<KeyT, 256, 8, 4>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
-        case 2: return launch_pass_shape<KeyT, 256, 16, 2>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
-        case 3: return launch_pass_shape<KeyT, 512, 4, 3>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
-        default: return launch_pass_shape<KeyT, 512, 8, 2>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, stream);
+                int shift, uint32_t mask, int pass, const SortTemp& t, cudaStream_t stream,
+                const uint32_t* low_table = nullptr) {
+#define HB_BITS(B) \
+    launch_pass_bits<KeyT, MODE, B>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, low_table, stream)
+    switch (__builtin_popcount(mask)) {
+        case 8: return HB_BITS(8);
+        case 7: return HB_BITS(7);
+        case 6: return HB_BITS(6);
+        default: return HB_BITS(0);
     }
+#undef HB_BITS
 }
 
 // Run the scatter passes of `plan` (histogram already in t.hist, raw counts).  Pairs ping-pong
@@ -392,8 +427,8 @@ int run_passes(KeyT* k0, uint32_t* v0, KeyT* k1, uint32_t* v1, int n_cap, const 
     int cur = 0;
     for (int p = 0; p < plan.num_passes; p++) {
         const uint32_t mask = (1u << plan.bits[p]) - 1u;
-        const int rc = launch_pass<KeyT>(kbuf[cur], vbuf[cur], kbuf[cur ^ 1], vbuf[cur ^ 1], n_cap, n_dev,
-                                         plan.shift[p], mask, p, t, stream);
+        const int rc = launch_pass<KeyT, kPairs>(kbuf[cur], vbuf[cur], kbuf[cur ^ 1], vbuf[cur ^ 1], n_cap, n_dev,
+                                                 plan.shift[p], mask, p, t, stream);
         if (rc) return rc;
         cur ^= 1;
     }
@@ -408,7 +443,7 @@ size_t sort_temp_bytes(int n) { return carve_sort_temp(nullptr, n).bytes; }
 SortPassPlan tile_pass_plan(int tile_bits) {
     SortPassPlan sp;
     memset(&sp, 0, sizeof(sp));
-    if (tile_bits <= 0) return sp;
+    if (tile_bits <= 0) tile_bits = 1;  // always at least one pass: the last pass is what unpacks the pairs
     const int n = cdiv(tile_bits, kRadixBits);
     const int base = tile_bits / n, extra = tile_bits % n;
     int shift = 32;
@@ -460,26 +495,44 @@ int launch_depth_argsort(const uint32_t* keys0, uint32_t* kB, uint32_t* vB, uint
     uint32_t* kout[4] = {kB, kC, kB, kC};
     uint32_t* vout[4] = {vB, vC, vB, vC};
     for (int p = 0; p < 4; p++) {
-        rc = launch_pass<uint32_t>(kin[p], vin[p], kout[p], vout[p], P, nullptr, 8 * p, 255u, p, t, stream);
+        rc = launch_pass<uint32_t, kPairs>(kin[p], vin[p], kout[p], vout[p], P, nullptr, 8 * p, 255u, p, t, stream);
         if (rc) return rc;
     }
     return 0;
 }
 
-// Stable sort of the emitted pairs on the tile bits only.  The digit histograms were accumulated
-// by the duplicate kernel into sort_temp_histogram(temp) (cleared by sort_temp_clear before it).
-// The pairs start in (k0,v0); *result_in_first tells where they end up.
-int launch_tile_sort(uint64_t* k0, uint32_t* v0, uint64_t* k1, uint32_t* v1, int n_cap, const uint32_t* n_dev,
-                     const SortPassPlan& plan, void* temp, size_t temp_bytes, cudaStream_t stream,
-                     bool* result_in_first) {
-    *result_in_first = true;
+// Stable sort of the emitted pairs on the tile bits only.  The pairs arrive packed as
+// (tile << 32 | Gaussian index) in depth order; the digit histograms were accumulated by the
+// duplicate kernel into sort_temp_histogram(temp) (cleared by sort_temp_clear before it).  All
+// passes but the last move 8 B per pair; the last one writes keys_out = (tile << 32 | depth bits of
+// that Gaussian, from depth_bits[index]) and list_out = index.  With an odd number of passes the
+// packed pairs must start in `b`, with an even number in `a` (the last pass reads from `b`).
+int launch_tile_sort(uint64_t* a, uint64_t* b, uint64_t* keys_out, uint32_t* list_out, const uint32_t* depth_bits,
+                     int n_cap, const uint32_t* n_dev, const SortPassPlan& plan, void* temp, size_t temp_bytes,
+                     cudaStream_t stream) {
     if (n_cap <= 0 || plan.num_passes <= 0) return 0;
     const SortTemp t = carve_sort_temp(temp, n_cap);
     if (temp == nullptr || temp_bytes < t.bytes) {
         set_error("tile_sort: temp storage too small (%zu < %zu)", temp_bytes, t.bytes);
         return -1;
     }
-    return run_passes<uint64_t>(k0, v0, k1, v1, n_cap, n_dev, plan, t, stream, result_in_first);
+    radix_offsets_kernel<<<plan.num_passes, kRadix, 0, stream>>>(t.hist);
+    HB_LAUNCH_OK("radix_offsets", stream, false);
+    uint64_t* buf[2] = {a, b};
+    int cur = (plan.num_passes % 2 == 0) ? 0 : 1;
+    for (int p = 0; p < plan.num_passes; p++) {
+        const uint32_t mask = (1u << plan.bits[p]) - 1u;
+        int rc;
+        if (p + 1 < plan.num_passes)
+            rc = launch_pass<uint64_t, kKeysOnly>(buf[cur], nullptr, buf[cur ^ 1], nullptr, n_cap, n_dev, plan.shift[p],
+                                                  mask, p, t, stream);
+        else
+            rc = launch_pass<uint64_t, kSplit>(buf[cur], nullptr, keys_out, list_out, n_cap, n_dev, plan.shift[p], mask,
+                                               p, t, stream, depth_bits);
+        if (rc) return rc;
+        cur ^= 1;
+    }
+    return 0;
 }
 
 // Generic entry (C ABI hugs_b200_sort_pairs): sorts on key bits [0, end_bit) with 8-bit digits.
@@ -487,19 +540,32 @@ int launch_tile_sort(uint64_t* k0, uint32_t* v0, uint64_t* k1, uint32_t* v1, int
 // the caller where they ended up.
 int launch_sort_pairs_pingpong(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
                                int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream,
-                               bool* result_in_input) {
+                               bool* result_in_input, int begin_bit) {
     *result_in_input = true;
-    if (n <= 0 || end_bit <= 0) return 0;
     if (end_bit > 64) end_bit = 64;
+    if (begin_bit < 0) begin_bit = 0;
+    if (n <= 0 || end_bit <= begin_bit) return 0;
     int rc = sort_temp_clear(temp, temp_bytes, n, stream);
     if (rc) return rc;
     const SortTemp t = carve_sort_temp(temp, n);
     SortPassPlan sp;
     memset(&sp, 0, sizeof(sp));
-    sp.num_passes = cdiv(end_bit, kRadixBits);
-    for (int p = 0; p < sp.num_passes; p++) {
-        sp.shift[p] = p * kRadixBits;
-        sp.bits[p] = (end_bit - sp.shift[p]) < kRadixBits ? (end_bit - sp.shift[p]) : kRadixBits;
+    if (begin_bit == 0) {
+        sp.num_passes = cdiv(end_bit, kRadixBits);
+        for (int p = 0; p < sp.num_passes; p++) {
+            sp.shift[p] = p * kRadixBits;
+            sp.bits[p] = (end_bit - sp.shift[p]) < kRadixBits ? (end_bit - sp.shift[p]) : kRadixBits;
+        }
+    } else {
+        // a bit range is split into equal digits (what the rasterizer does for the tile bits)
+        const int nbits = end_bit - begin_bit, np = cdiv(nbits, kRadixBits);
+        int shift = begin_bit;
+        for (int p = 0; p < np; p++) {
+            sp.shift[p] = shift;
+            sp.bits[p] = nbits / np + (p < nbits % np ? 1 : 0);
+            shift += sp.bits[p];
+        }
+        sp.num_passes = np;
     }
     int hist_blocks = cdiv(n, kHistThreads * 8);
     if (hist_blocks > 148 * 4) hist_blocks = 148 * 4;
@@ -509,10 +575,10 @@ int launch_sort_pairs_pingpong(uint64_t* keys_in, uint32_t* vals_in, uint64_t* k
 }
 
 int launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
-                      int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream) {
+                      int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream, int begin_bit) {
     bool in_input = false;
     const int rc = launch_sort_pairs_pingpong(keys_in, vals_in, keys_out, vals_out, n, end_bit, temp, temp_bytes,
-                                              stream, &in_input);
+                                              stream, &in_input, begin_bit);
     if (rc) return rc;
     if (in_input && n > 0) {
         HB_CUDA_OK(cudaMemcpyAsync(keys_out, keys_in, sizeof(uint64_t) * (size_t)n, cudaMemcpyDeviceToDevice, stream));

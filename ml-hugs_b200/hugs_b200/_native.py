@@ -102,6 +102,7 @@ sort_bits = _sig("hugs_b200_sort_bits", i32, [i32, i32])
 sort_temp_bytes = _sig("hugs_b200_sort_temp_bytes", C.c_size_t, [i32])
 scan_temp_bytes = _sig("hugs_b200_scan_temp_bytes", C.c_size_t, [i32])
 sort_pairs = _sig("hugs_b200_sort_pairs", i32, [fp, fp, fp, fp, i32, i32, fp, C.c_size_t, fp])
+sort_pairs_range = _sig("hugs_b200_sort_pairs_range", i32, [fp, fp, fp, fp, i32, i32, i32, fp, C.c_size_t, fp])
 inclusive_scan = _sig("hugs_b200_inclusive_scan", i32, [fp, fp, i32, fp, C.c_size_t, fp])
 
 lbs_forward = _sig("hugs_b200_lbs_forward", i32, [
@@ -129,7 +130,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
     "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_mark_visible",
     "hugs_b200_geom_layout_of", "hugs_b200_image_layout_of", "hugs_b200_binning_layout_of",
-    "hugs_b200_sort_bits", "hugs_b200_sort_temp_bytes", "hugs_b200_sort_pairs",
+    "hugs_b200_sort_bits", "hugs_b200_sort_temp_bytes", "hugs_b200_sort_pairs", "hugs_b200_sort_pairs_range",
     "hugs_b200_scan_temp_bytes", "hugs_b200_inclusive_scan",
     "hugs_b200_lbs_forward", "hugs_b200_lbs_backward",
 ]

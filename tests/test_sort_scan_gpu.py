@@ -87,3 +87,27 @@ def test_scan_rejects_small_temp():
     temp = torch.empty(8, dtype=torch.uint8, device="cuda")
     rc = N.inclusive_scan(x.data_ptr(), x.data_ptr(), 4096, temp.data_ptr(), 8, None)
     assert rc != 0 and b"temp storage too small" in N.last_error()
+
+
+@pytest.mark.parametrize("n,begin_bit,end_bit", [(100_003, 32, 45), (1_000_001, 32, 41), (4097, 32, 33), (50_000, 8, 27)])
+def test_sort_pairs_range_is_a_stable_sort_on_those_bits_only(n, begin_bit, end_bit):
+    """Second level of the rasterizer's binning: a stable sort on the tile bits alone of pairs that
+    arrive in (depth, index) order reproduces the full (tile | depth) key order."""
+    from hugs_b200 import _native as N
+
+    rng = np.random.default_rng(n + end_bit)
+    keys = rng.integers(0, 1 << 62, n).astype(np.uint64)
+    vals = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+    k_in = torch.from_numpy(keys.view(np.int64)).cuda()
+    v_in = torch.from_numpy(vals.view(np.int32)).cuda()
+    k_out, v_out = torch.empty_like(k_in), torch.empty_like(v_in)
+    tb = int(N.sort_temp_bytes(n))
+    temp = torch.empty(tb, dtype=torch.uint8, device="cuda")
+    rc = N.sort_pairs_range(N.ptr(k_in), N.ptr(v_in), N.ptr(k_out), N.ptr(v_out), n, begin_bit, end_bit,
+                            temp.data_ptr(), tb, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    N.check(rc, "sort_pairs_range")
+    torch.cuda.synchronize()
+    digit = (keys >> np.uint64(begin_bit)) & np.uint64((1 << (end_bit - begin_bit)) - 1)
+    order = np.argsort(digit, kind="stable")
+    assert (k_out.cpu().numpy().view(np.uint64) == keys[order]).all()
+    assert (v_out.cpu().numpy().view(np.uint32) == vals[order]).all()
