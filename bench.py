@@ -283,16 +283,24 @@ def stage_bytes(P, visible, R, W, H, n_human, sort_bits):
 
 
 def timed_loop(fn, steps, device, barrier):
-    """EXACTLY `steps` calls of fn between barrier+synchronize brackets, CUDA-event timed."""
-    barrier()
-    torch.cuda.synchronize(device)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        fn()
-    e1.record()
-    torch.cuda.synchronize(device)
-    barrier()
+    """EXACTLY `steps` calls of fn between barrier+synchronize brackets, CUDA-event timed.
+    The cyclic garbage collector is paused for the timed region (both arms): a generation-2 sweep of
+    the interpreter's ~10^6 live objects takes 20-30 ms, ten frames' worth, whenever it happens to fire."""
+    import gc
+    gc.collect()
+    gc.disable()
+    try:
+        barrier()
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(device)
+        barrier()
+    finally:
+        gc.enable()
     return e0.elapsed_time(e1)  # ms
 
 

@@ -170,9 +170,11 @@ typedef struct hugs_b200_image_layout {
 } hugs_b200_image_layout;
 
 typedef struct hugs_b200_binning_layout {
-    size_t point_list_keys;           /* u64[R] sorted keys  (tile<<32 | depth bits)   */
+    size_t point_list_keys;           /* u64[R] sorted keys  (tile<<32 | depth bits); two-level modes: after
+                                         hugs_b200_materialize_sorted_keys                                  */
     size_t point_list;                /* u32[R] sorted Gaussian indices                */
-    size_t point_list_keys_unsorted;  /* u64[R]                                        */
+    size_t point_list_keys_unsorted;  /* u64[R] scratch; two-level modes: tile id per list position (u16, or
+                                         u32 beyond 65536 tiles) once the forward call returns              */
     size_t point_list_unsorted;       /* u32[R]                                        */
     size_t sort_temp;                 /* histograms + look-back state                  */
     size_t hit_words;                 /* u32[(R+31)/32 + tiles + 1][8]: per 32 list positions of a tile and per
@@ -181,6 +183,14 @@ typedef struct hugs_b200_binning_layout {
 } hugs_b200_binning_layout;
 
 int hugs_b200_geom_layout_of(int P, hugs_b200_geom_layout* out);
+/* In the two-level binning modes nothing downstream reads the sorted 64-bit keys, so the forward pass
+ * does not write them (it keeps the sorted Gaussian list and a tile id per list position).  This
+ * fills point_list_keys[i] = tile(i) << 32 | depth bits of Gaussian point_list[i] for i < R -- the
+ * array cub::DeviceRadixSort::SortPairs leaves in the reference's binningState.point_list_keys
+ * (CR/rasterizer_impl.cu:303-308) -- from the buffers of the forward call (parity tests, debugging).
+ * No-op in HUGS_B200_BINNING_REFERENCE mode, where the keys are the sort's own output. */
+int hugs_b200_materialize_sorted_keys(int P, int R, int width, int height, char* geom_buffer,
+                                      char* binning_buffer, size_t binning_bytes, hugs_b200_stream_t stream);
 /* The binning workspace is laid out for a CAPACITY of pairs that may exceed the R of the call that
  * filled it (see hugs_b200_set_binning_mode); this recovers the capacity from the buffer size so that
  * hugs_b200_binning_layout_of(capacity, width, height) describes the buffer.  point_list always sits at

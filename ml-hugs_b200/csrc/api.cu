@@ -487,6 +487,7 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     // Two-level binning (depth argsort of the Gaussians + tile-bit sort of the pairs) needs the packed
     // rectangle format of the duplicate kernel; otherwise fall back to the reference's structure.
     const bool two_level = (mode != HUGS_B200_BINNING_REFERENCE) && cam.grid_x <= 1023 && cam.grid_y <= 1023;
+    const bool tile16 = num_tiles <= 65536;
     uint32_t* R_dev = nullptr;
     int* pinned = pinned_counter();
     cudaEvent_t ev = count_event();
@@ -556,9 +557,13 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         if (cap > 0 && two_level) {
             n_dev = R_dev;
             const SortPassPlan plan = tile_pass_plan(tile_bits);
-            // Packed (tile << 32 | index) pairs ping-pong between the two 64-bit buffers; the last pass
-            // reads from keys_unsorted and writes (keys, list).
-            uint64_t* first_buf = (plan.num_passes % 2 == 0) ? bin.keys : bin.keys_unsorted;
+            // Packed (tile << 32 | index) pairs ping-pong between the two 64-bit regions; the last pass
+            // reads from `keys` and leaves the sorted list plus the tile id of every list position
+            // (in the then dead `keys_unsorted` region).  The sorted 64-bit keys themselves are not
+            // needed by anything downstream; hugs_b200_materialize_sorted_keys writes them on demand.
+            uint64_t* const buf_a = bin.keys_unsorted;
+            uint64_t* const buf_b = bin.keys;
+            uint64_t* first_buf = (plan.num_passes % 2 == 0) ? buf_a : buf_b;
             auto emit = [&]() -> int {
                 const int rc = sort_temp_clear(bin.sort_temp, bin.sort_temp_bytes, cap, stream);
                 if (rc) return rc;
@@ -567,9 +572,8 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                                stream);
             };
             HB_STAGE(emit(), ST_DUPLICATE);
-            HB_STAGE(launch_tile_sort(bin.keys, bin.keys_unsorted, bin.keys, bin.list,
-                                      reinterpret_cast<const uint32_t*>(geom.depths), cap, n_dev, plan, bin.sort_temp,
-                                      bin.sort_temp_bytes, stream),
+            HB_STAGE(launch_tile_sort(buf_a, buf_b, bin.keys_unsorted, bin.list, tile16, cap, n_dev, plan,
+                                      bin.sort_temp, bin.sort_temp_bytes, stream),
                      ST_SORT);
         } else if (cap > 0) {
             // Reference structure: pairs emitted in Gaussian-index order, one sort on all 32+bit key bits.
@@ -594,7 +598,11 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                            cudaMemcpyDeviceToDevice, stream));
             }
         }
-        HB_STAGE(launch_tile_ranges(cap, bin.keys, img.ranges, num_tiles, stream, n_dev), ST_RANGES);
+        if (cap > 0 && two_level)
+            HB_STAGE(launch_tile_ranges_ids(cap, bin.keys_unsorted, tile16, img.ranges, num_tiles, stream, n_dev),
+                     ST_RANGES);
+        else
+            HB_STAGE(launch_tile_ranges(cap, bin.keys, img.ranges, num_tiles, stream, n_dev), ST_RANGES);
         HB_STAGE(launch_render_forward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y,
                                        P > 0 ? geom.means2D : nullptr, feature_ptr, stride,
                                        P > 0 ? geom.conic_opacity : nullptr, img.accum_alpha, img.n_contrib,
@@ -610,6 +618,28 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     if (P > 0) update_capacity_hint(P, width, height, R);
     *num_rendered = R;
     return 0;
+}
+
+int hugs_b200_materialize_sorted_keys(int P, int R, int width, int height, char* geom_buffer, char* binning_buffer,
+                                      size_t binning_bytes, hugs_b200_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (P < 0 || R < 0 || width <= 0 || height <= 0 || (R > 0 && (!geom_buffer || !binning_buffer))) {
+        set_error("materialize_sorted_keys: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    const int grid_x = cdiv(width, HB_TILE_X), grid_y = cdiv(height, HB_TILE_Y);
+    const bool two_level =
+        g_binning_mode.load(std::memory_order_relaxed) != HUGS_B200_BINNING_REFERENCE && grid_x <= 1023 && grid_y <= 1023;
+    if (!two_level || R == 0) return 0;  // the reference-structure sort leaves the keys in place
+    const size_t cap = hugs_b200_binning_capacity_of(binning_bytes, width, height);
+    if ((size_t)R > cap) {
+        set_error("materialize_sorted_keys: binning buffer of %zu bytes cannot hold %d pairs", binning_bytes, R);
+        return HUGS_B200_EINVAL;
+    }
+    const GeomView geom = carve_geom(geom_buffer, P);
+    const BinningView bin = carve_binning(binning_buffer, (int)cap, grid_x * grid_y);
+    return launch_materialize_keys(R, bin.keys_unsorted, grid_x * grid_y <= 65536, bin.list,
+                                   reinterpret_cast<const uint32_t*>(geom.depths), bin.keys, stream);
 }
 
 int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height,

@@ -245,7 +245,81 @@ __global__ void __launch_bounds__(256)
         ranges[t0].y = R;  // i0 == R-1
     }
 }
+// Tile ranges from the per-position tile ids (u16 / u32) that the two-level sort leaves behind: same
+// boundaries as identifyTileRanges finds in the high words of the sorted keys.  8 positions per thread.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    tile_ranges_ids_kernel(int R, const uint32_t* __restrict__ n_dev, const T* __restrict__ ids,
+                           uint2* __restrict__ ranges) {
+    if (n_dev != nullptr) R = (int)min((uint32_t)R, __ldg(n_dev));  // R was the capacity
+    constexpr int kPer = 8;
+    const int i0 = kPer * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (i0 >= R) return;
+    uint32_t t[kPer];
+    if (i0 + kPer <= R) {
+        if (sizeof(T) == 2) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(ids + i0));
+            t[0] = v.x & 0xffffu; t[1] = v.x >> 16; t[2] = v.y & 0xffffu; t[3] = v.y >> 16;
+            t[4] = v.z & 0xffffu; t[5] = v.z >> 16; t[6] = v.w & 0xffffu; t[7] = v.w >> 16;
+        } else {
+            const uint4 v0 = __ldg(reinterpret_cast<const uint4*>(ids + i0));
+            const uint4 v1 = __ldg(reinterpret_cast<const uint4*>(ids + i0) + 1);
+            t[0] = v0.x; t[1] = v0.y; t[2] = v0.z; t[3] = v0.w;
+            t[4] = v1.x; t[5] = v1.y; t[6] = v1.z; t[7] = v1.w;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kPer; k++) t[k] = (i0 + k < R) ? (uint32_t)__ldg(ids + i0 + k) : 0u;
+    }
+    uint32_t prev = (i0 == 0) ? 0xffffffffu : (uint32_t)__ldg(ids + i0 - 1);
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+        const int i = i0 + k;
+        if (i < R) {
+            if (t[k] != prev) {
+                if (i != 0) ranges[prev].y = (uint32_t)i;
+                ranges[t[k]].x = (uint32_t)i;
+            }
+            if (i == R - 1) ranges[t[k]].y = (uint32_t)R;
+            prev = t[k];
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    materialize_keys_kernel(int R, const T* __restrict__ ids, const uint32_t* __restrict__ list,
+                            const uint32_t* __restrict__ depth_bits, uint64_t* __restrict__ keys) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    keys[i] = ((uint64_t)__ldg(ids + i) << 32) | (uint64_t)__ldg(depth_bits + __ldg(list + i));
+}
 }  // namespace
+
+int launch_tile_ranges_ids(int R, const void* tile_ids, bool tile16, uint2* ranges, int num_tiles,
+                           cudaStream_t stream, const uint32_t* n_dev) {
+    HB_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
+    if (R <= 0) return 0;
+    const int blocks = cdiv(cdiv(R, 8), 256);
+    if (tile16)
+        tile_ranges_ids_kernel<uint16_t><<<blocks, 256, 0, stream>>>(R, n_dev, static_cast<const uint16_t*>(tile_ids), ranges);
+    else
+        tile_ranges_ids_kernel<uint32_t><<<blocks, 256, 0, stream>>>(R, n_dev, static_cast<const uint32_t*>(tile_ids), ranges);
+    HB_LAUNCH_OK("identify_tile_ranges", stream, false);
+    return 0;
+}
+
+int launch_materialize_keys(int R, const void* tile_ids, bool tile16, const uint32_t* list,
+                            const uint32_t* depth_bits, uint64_t* keys, cudaStream_t stream) {
+    if (R <= 0) return 0;
+    if (tile16)
+        materialize_keys_kernel<uint16_t><<<cdiv(R, 256), 256, 0, stream>>>(R, static_cast<const uint16_t*>(tile_ids), list, depth_bits, keys);
+    else
+        materialize_keys_kernel<uint32_t><<<cdiv(R, 256), 256, 0, stream>>>(R, static_cast<const uint32_t*>(tile_ids), list, depth_bits, keys);
+    HB_LAUNCH_OK("materialize_keys", stream, false);
+    return 0;
+}
+
 
 int launch_duplicate(int P, const float2* means2D, const float* depths, const uint32_t* offsets, const int* radii,
                      uint64_t* keys, uint32_t* vals, int grid_x, int grid_y, cudaStream_t stream) {

@@ -119,6 +119,12 @@ int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* offsets
                             const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream);
 int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream,
                        const uint32_t* n_dev = nullptr);
+// the same from the per-position tile ids the two-level sort leaves behind (u16 or u32)
+int launch_tile_ranges_ids(int R, const void* tile_ids, bool tile16, uint2* ranges, int num_tiles,
+                           cudaStream_t stream, const uint32_t* n_dev);
+// keys[i] = tile_ids[i] << 32 | depth_bits[list[i]]: the sorted 64-bit keys, on demand
+int launch_materialize_keys(int R, const void* tile_ids, bool tile16, const uint32_t* list,
+                            const uint32_t* depth_bits, uint64_t* keys, cudaStream_t stream);
 
 // ---- radix sort (radix_sort.cu) ------------------------------------------------------------------
 size_t sort_temp_bytes(int n);
@@ -127,8 +133,8 @@ int sort_temp_clear(void* temp, size_t temp_bytes, int n_cap, cudaStream_t strea
 uint32_t* sort_temp_histogram(void* temp);   // [kSortMaxPasses][256] digit counts, filled by the duplicate kernel
 int launch_depth_argsort(const uint32_t* keys0, uint32_t* kB, uint32_t* vB, uint32_t* kC, uint32_t* vC, int P,
                          void* temp, size_t temp_bytes, cudaStream_t stream);
-int launch_tile_sort(uint64_t* a, uint64_t* b, uint64_t* keys_out, uint32_t* list_out, const uint32_t* depth_bits,
-                     int n_cap, const uint32_t* n_dev, const SortPassPlan& plan, void* temp, size_t temp_bytes,
+int launch_tile_sort(uint64_t* a, uint64_t* b, void* tiles_out, uint32_t* list_out, bool tile16, int n_cap,
+                     const uint32_t* n_dev, const SortPassPlan& plan, void* temp, size_t temp_bytes,
                      cudaStream_t stream);
 int launch_sort_pairs_pingpong(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, int n,
                                int end_bit, void* temp, size_t temp_bytes, cudaStream_t stream,

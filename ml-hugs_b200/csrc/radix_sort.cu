@@ -104,9 +104,10 @@ __global__ void __launch_bounds__(kRadix) radix_offsets_kernel(uint32_t* __restr
 //              (first pass of an argsort).  Generic stable pair sort.
 //   kKeysOnly  the payload rides in the low 32 bits of a u64 key (the sorted digit lies above them):
 //              one load / stage / store per pair instead of two.
-//   kSplit     last pass of a kKeysOnly sort: emits payload = low word to vals_out and
-//              key = (high word << 32) | low_table[payload] to keys_out.  The rasterizer sorts
-//              (tile << 32 | Gaussian index) and gets (tile << 32 | depth bits, index) out.
+//   kSplit     last pass of a kKeysOnly sort: emits the low word (payload) to vals_out and the high
+//              word to a u16 / u32 array at keys_out.  The rasterizer sorts (tile << 32 | Gaussian
+//              index) and gets the sorted Gaussian list plus the tile id of every list position
+//              (6 B per pair written instead of 12).
 enum SortMode { kPairs = 0, kKeysOnly = 1, kSplit = 2 };
 
 template <typename KeyT, int THREADS, int ITEMS, int MODE>
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                           KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n_host,
                           const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask, int pass,
                           const uint32_t* __restrict__ pass_offsets, unsigned long long* lookback,
-                          unsigned* tickets, const uint32_t* __restrict__ low_table, int dbg_no_lookback) {
+                          unsigned* tickets, int tile16, int dbg_no_lookback) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int kSortThreads = THREADS, kSortItems = ITEMS, kSortWarps = THREADS / 32, kSortTile = THREADS * ITEMS;
     static_assert(THREADS >= kRadix && THREADS % kRadix == 0, "digit phases use the first kRadix threads");
@@ -332,23 +333,33 @@ __global__ void __launch_bounds__(THREADS, MINB)
     __syncthreads();
 
     // Coalesced write-out: consecutive staged slots of one digit are consecutive in global memory.
+    // Shared-memory reads are batched ahead of the stores (the compiler cannot move a load above a
+    // store to a possibly aliasing pointer on its own).
     const int count = full_tile ? kSortTile : (n - tile_base);
+    KeyT ko[kSortItems];
+    uint32_t go[kSortItems], vo[MODE == kPairs ? kSortItems : 1];
 #pragma unroll
     for (int k = 0; k < kSortItems; k++) {
         const int i = k * kSortThreads + tid;
         if (i < count) {
-            const KeyT kk = s.keys[i];
-            const uint32_t d = (uint32_t)(kk >> shift) & digit_mask;
-            const uint32_t g = s.bin_off[d] + (uint32_t)i;
+            ko[k] = s.keys[i];
+            if (MODE == kPairs) vo[MODE == kPairs ? k : 0] = s.vals[i];
+            go[k] = s.bin_off[(uint32_t)(ko[k] >> shift) & digit_mask] + (uint32_t)i;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < kSortItems; k++) {
+        if (k * kSortThreads + tid < count) {
             if (MODE == kPairs) {
-                keys_out[g] = kk;
-                vals_out[g] = s.vals[i];
+                keys_out[go[k]] = ko[k];
+                vals_out[go[k]] = vo[MODE == kPairs ? k : 0];
             } else if (MODE == kKeysOnly) {
-                keys_out[g] = kk;
+                keys_out[go[k]] = ko[k];
             } else {
-                const uint32_t payload = (uint32_t)kk;
-                vals_out[g] = payload;
-                keys_out[g] = (KeyT)(((unsigned long long)kk & 0xffffffff00000000ull) | __ldg(low_table + payload));
+                vals_out[go[k]] = (uint32_t)ko[k];
+                const uint32_t hi = (uint32_t)((unsigned long long)ko[k] >> 32);
+                if (tile16) reinterpret_cast<uint16_t*>(keys_out)[go[k]] = (uint16_t)hi;
+                else reinterpret_cast<uint32_t*>(keys_out)[go[k]] = hi;
             }
         }
     }
@@ -379,8 +390,8 @@ SortTemp carve_sort_temp(void* temp, int n) {
 // the common digit widths get a kernel with the width known at compile time.
 template <typename KeyT, int MODE, int BITS>
 int launch_pass_bits(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout, int n_cap,
-                     const uint32_t* n_dev, int shift, uint32_t mask, int pass, const SortTemp& t,
-                     const uint32_t* low_table, cudaStream_t stream) {
+                     const uint32_t* n_dev, int shift, uint32_t mask, int pass, const SortTemp& t, int tile16,
+                     cudaStream_t stream) {
     constexpr int THREADS = kSortThreads, ITEMS = kSortItems;
     using Smem = SortSmem<KeyT, THREADS, ITEMS, MODE>;
     auto kernel = radix_onesweep_kernel<KeyT, THREADS, ITEMS, 2, MODE, BITS>;
@@ -391,21 +402,20 @@ int launch_pass_bits(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t*
                                         cudaSharedmemCarveoutMaxShared));
         configured = true;
     }
-    static const bool no_lookback = getenv("HB_SORT_NOLOOK") != nullptr;  // timing experiments only: wrong output
+    static const int no_lookback = getenv("HB_SORT_NOLOOK") ? 1 : 0;  // timing experiments only: wrong output
     const int tiles = cdiv(n_cap, THREADS * ITEMS);
     kernel<<<tiles, THREADS, sizeof(Smem), stream>>>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass,
-                                                     t.hist + pass * kRadix, t.lookback, t.tickets, low_table,
-                                                     no_lookback ? 1 : 0);
+                                                     t.hist + pass * kRadix, t.lookback, t.tickets, tile16,
+                                                     no_lookback);
     HB_LAUNCH_OK("radix_onesweep", stream, false);
     return 0;
 }
 
 template <typename KeyT, int MODE>
 int launch_pass(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout, int n_cap, const uint32_t* n_dev,
-                int shift, uint32_t mask, int pass, const SortTemp& t, cudaStream_t stream,
-                const uint32_t* low_table = nullptr) {
+                int shift, uint32_t mask, int pass, const SortTemp& t, cudaStream_t stream, int tile16 = 0) {
 #define HB_BITS(B) \
-    launch_pass_bits<KeyT, MODE, B>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, low_table, stream)
+    launch_pass_bits<KeyT, MODE, B>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass, t, tile16, stream)
     switch (__builtin_popcount(mask)) {
         case 8: return HB_BITS(8);
         case 7: return HB_BITS(7);
@@ -504,11 +514,11 @@ int launch_depth_argsort(const uint32_t* keys0, uint32_t* kB, uint32_t* vB, uint
 // Stable sort of the emitted pairs on the tile bits only.  The pairs arrive packed as
 // (tile << 32 | Gaussian index) in depth order; the digit histograms were accumulated by the
 // duplicate kernel into sort_temp_histogram(temp) (cleared by sort_temp_clear before it).  All
-// passes but the last move 8 B per pair; the last one writes keys_out = (tile << 32 | depth bits of
-// that Gaussian, from depth_bits[index]) and list_out = index.  With an odd number of passes the
-// packed pairs must start in `b`, with an even number in `a` (the last pass reads from `b`).
-int launch_tile_sort(uint64_t* a, uint64_t* b, uint64_t* keys_out, uint32_t* list_out, const uint32_t* depth_bits,
-                     int n_cap, const uint32_t* n_dev, const SortPassPlan& plan, void* temp, size_t temp_bytes,
+// passes but the last move 8 B per pair; the last one reads from `b` and writes list_out = index
+// and tiles_out = tile id (u16 when tile16, else u32; tiles_out may alias `a`, which is dead by
+// then).  With an odd number of passes the packed pairs must start in `b`, with an even number in `a`.
+int launch_tile_sort(uint64_t* a, uint64_t* b, void* tiles_out, uint32_t* list_out, bool tile16, int n_cap,
+                     const uint32_t* n_dev, const SortPassPlan& plan, void* temp, size_t temp_bytes,
                      cudaStream_t stream) {
     if (n_cap <= 0 || plan.num_passes <= 0) return 0;
     const SortTemp t = carve_sort_temp(temp, n_cap);
@@ -527,8 +537,8 @@ int launch_tile_sort(uint64_t* a, uint64_t* b, uint64_t* keys_out, uint32_t* lis
             rc = launch_pass<uint64_t, kKeysOnly>(buf[cur], nullptr, buf[cur ^ 1], nullptr, n_cap, n_dev, plan.shift[p],
                                                   mask, p, t, stream);
         else
-            rc = launch_pass<uint64_t, kSplit>(buf[cur], nullptr, keys_out, list_out, n_cap, n_dev, plan.shift[p], mask,
-                                               p, t, stream, depth_bits);
+            rc = launch_pass<uint64_t, kSplit>(buf[cur], nullptr, reinterpret_cast<uint64_t*>(tiles_out), list_out, n_cap,
+                                               n_dev, plan.shift[p], mask, p, t, stream, tile16 ? 1 : 0);
         if (rc) return rc;
         cur ^= 1;
     }

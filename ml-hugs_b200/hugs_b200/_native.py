@@ -94,6 +94,8 @@ geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayou
 image_layout_of = _sig("hugs_b200_image_layout_of", i32, [i32, i32, C.POINTER(ImageLayout)])
 binning_layout_of = _sig("hugs_b200_binning_layout_of", i32, [i32, i32, i32, C.POINTER(BinningLayout)])
 
+materialize_sorted_keys = _sig("hugs_b200_materialize_sorted_keys", i32,
+                               [i32, i32, i32, i32, fp, fp, C.c_size_t, fp])
 binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_size_t, i32, i32])
 BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE = 0, 1, 2
 set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
@@ -125,7 +127,7 @@ def read_stage_times(reset=True):
 
 
 EXPORTED_SYMBOLS = [
-    "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode",
+    "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode", "hugs_b200_materialize_sorted_keys",
     "hugs_b200_stage_timing_enable", "hugs_b200_stage_timing_read", "hugs_b200_stage_name",
     "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
     "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_mark_visible",

@@ -2,6 +2,7 @@
 opaque buffers, decoding ours, and comparison metrics.  Test infrastructure only."""
 import importlib
 import importlib.util
+import ctypes
 import os
 import sys
 import types
@@ -150,6 +151,11 @@ def decode_our_buffers(geom, binning, img, P, R, W, H):
     out["n_contrib"] = take(img, im.n_contrib, Npix, torch.int32, 4)
     out["ranges"] = take(img, im.ranges, 2 * tiles, torch.int32, 4).reshape(tiles, 2)
     if R > 0:
+        # the two-level binning modes write the sorted 64-bit keys only on demand
+        N.check(N.materialize_sorted_keys(P, R, W, H, N.ptr(geom), N.ptr(binning), int(binning.numel()),
+                                          ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
+                "materialize_sorted_keys")
+        torch.cuda.synchronize()
         out["point_list_keys"] = take(binning, b.point_list_keys, R, torch.int64, 8)
         out["point_list"] = take(binning, b.point_list, R, torch.int32, 4)
     return out
