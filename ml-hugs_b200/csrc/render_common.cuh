@@ -30,6 +30,57 @@ __device__ __forceinline__ PixelMap pixel_map(unsigned tile_x, unsigned tile_y) 
     return m;
 }
 
+// ---- staged Gaussians --------------------------------------------------------------------------
+// One 48-byte record per staged Gaussian: (x, y, A, B) (C, opacity, r, g) (b, -, -, -).  The blend
+// loops read a record with three loads off ONE 32-bit shared-memory address (broadcast: every lane
+// reads the same record); separate arrays cost an address computation each, and with generic
+// addressing the compiler re-derives the shared window base inside the loop.
+constexpr int kStageBytes = 48;
+
+struct StagedGaussian {  // what a staging thread holds in registers between load and store
+    float2 xy;
+    float4 co;
+    float r, g, b;
+};
+
+__device__ __forceinline__ StagedGaussian load_gaussian(uint32_t id, const float2* __restrict__ means2D,
+                                                        const float4* __restrict__ conic_opacity,
+                                                        const float* __restrict__ colors, int color_stride) {
+    StagedGaussian s;
+    s.xy = __ldg(means2D + id);
+    s.co = __ldg(conic_opacity + id);
+    if (color_stride == 4) {
+        const float4 c = __ldg(reinterpret_cast<const float4*>(colors) + id);
+        s.r = c.x;
+        s.g = c.y;
+        s.b = c.z;
+    } else {
+        s.r = __ldg(colors + (size_t)id * 3 + 0);
+        s.g = __ldg(colors + (size_t)id * 3 + 1);
+        s.b = __ldg(colors + (size_t)id * 3 + 2);
+    }
+    return s;
+}
+
+__device__ __forceinline__ void sts_f4(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float lds_f1(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void store_gaussian(uint32_t slot_addr, const StagedGaussian& s) {
+    sts_f4(slot_addr, s.xy.x, s.xy.y, s.co.x, s.co.y);
+    sts_f4(slot_addr + 16, s.co.z, s.co.w, s.r, s.g);
+    sts_f4(slot_addr + 32, s.b, 0.f, 0.f, 0.f);
+}
+
 // Conservative reject test: returns false only when NO pixel centre inside the rectangle
 // [x0,x1]x[y0,y1] can reach alpha >= 1/255 for this Gaussian, i.e. when the reference's
 // per-pixel test `alpha < 1/255 -> continue` (forward.cu:343-345, backward.cu:499-501) would

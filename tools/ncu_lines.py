@@ -18,6 +18,7 @@ starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
 pick = next(i for i in starts if sub in rows[i][1])
 hdr = rows[pick + 1]
 iA, iS, iI, iN = hdr.index("Address"), hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("# Samples")
+iT = hdr.index("Predicated-On Thread Instructions Executed")
 body = []
 for r in rows[pick + 2:]:
     if r and r[0] == "Kernel Name":
@@ -34,12 +35,12 @@ for l in dis:
     if m: cur = (m.group(1).split("/")[-1], int(m.group(2))); continue
     m = re.match(r"\s+/\*([0-9a-f]{4,})\*/", l)
     if m and infn: line_of[int(m.group(1), 16)] = cur
-inst, samp = defaultdict(int), defaultdict(int)
+inst, samp, thr = defaultdict(int), defaultdict(int), defaultdict(int)
 for r in body:
     key = line_of.get(int(r[iA], 16) - base, ("?", 0))
-    inst[key] += int(r[iI]); samp[key] += int(r[iN])
+    inst[key] += int(r[iI]); samp[key] += int(r[iN]); thr[key] += int(r[iT])
 ti, ts = sum(inst.values()), sum(samp.values())
 print("total warp instructions %d, samples %d" % (ti, ts))
 for k in sorted(inst, key=lambda k: (k[0], k[1])):
     if 100 * inst[k] / ti >= min_pct or 100 * samp[k] / max(ts, 1) >= min_pct:
-        print("%-24s %5d  inst %5.2f%%  samples %5.2f%%" % (k[0], k[1], 100 * inst[k] / ti, 100 * samp[k] / max(ts, 1)))
+        print("%-24s %5d  inst %5.2f%%  samples %5.2f%%  lanes %4.1f" % (k[0], k[1], 100 * inst[k] / ti, 100 * samp[k] / max(ts, 1), thr[k] / max(inst[k], 1)))
