@@ -32,9 +32,8 @@ constexpr int kBwdBatch = 128;                 // Gaussians staged per round
 constexpr int kBwdChunks = kBwdBatch / 32;     // forward-mask words per warp and round
 constexpr int kBwdWarps = kBlendThreads / 32;  // 8
 
-// Sum 9 per-lane values over the warp and store the totals to dst[0..8] (one predicated store).
-__device__ __forceinline__ void warp_reduce9_store(const float (&v)[9], float* dst) {
-    const unsigned lane = threadIdx.x & 31u;
+// Sum 9 per-lane values over the warp and store the totals to the 9 floats at shared address `dst`.
+__device__ __forceinline__ void warp_reduce9_store(const float (&v)[9], uint32_t dst, unsigned lane) {
     const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u, b1 = lane & 2u;
     float w[4], p8 = v[8];
 #pragma unroll
@@ -68,8 +67,10 @@ __device__ __forceinline__ void warp_reduce9_store(const float (&v)[9], float* d
         r = keep + __shfl_xor_sync(0xffffffffu, send, 2);
     }
     r += __shfl_xor_sync(0xffffffffu, r, 1);
-    if ((lane & 3u) == 0u) dst[lane >> 2] = r;
-    else if (lane == 2u) dst[8] = r;
+    // lanes 0,4,..,28 hold values 0..7, lane 2 holds value 8: one predicated store
+    const unsigned slot = (lane == 2u) ? 8u : (lane >> 2);
+    if ((lane & 3u) == 0u || lane == 2u)
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst + 4u * slot), "f"(r) : "memory");
 }
 
 __global__ void __launch_bounds__(kBlendThreads)
@@ -82,18 +83,18 @@ __global__ void __launch_bounds__(kBlendThreads)
                            float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dcolor) {
     __shared__ uint32_t s_id[kBwdBatch];
-    __shared__ float2 s_xy[kBwdBatch];
-    __shared__ float4 s_co[kBwdBatch];
-    __shared__ float s_rgb[3][kBwdBatch];
+    __shared__ __align__(16) unsigned char s_stage[kBwdBatch * kStageBytes];
     __shared__ float s_part[kBwdWarps][kBwdBatch][9];
     __shared__ uint32_t s_hit[kBwdChunks][kBwdWarps];    // forward masks of this round
     __shared__ uint32_t s_touch[kBwdWarps][kBwdChunks];  // what each warp actually wrote to s_part
     __shared__ uint32_t s_max[kBwdWarps];
+    const uint32_t s_base = (uint32_t)__cvta_generic_to_shared(s_stage);
 
     const unsigned tile_x = blockIdx.x, tile_y = blockIdx.y;
     const unsigned tile_id = tile_y * grid_x + tile_x;
     const PixelMap pm = pixel_map(tile_x, tile_y);
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t part_base = (uint32_t)__cvta_generic_to_shared(&s_part[warp][0][0]);
     const bool inside = pm.px < (unsigned)W && pm.py < (unsigned)H;
     const float pixfx = (float)pm.px, pixfy = (float)pm.py;
     const size_t pix_id = (size_t)W * pm.py + pm.px;
@@ -134,31 +135,28 @@ __global__ void __launch_bounds__(kBlendThreads)
     const float ddely_dy = 0.5f * H;
     const uint32_t* const hit_base = hit_words + ((size_t)(range.x >> 5) + tile_id) * kBwdWarps;
 
-    for (int pb = ((todo - 1) / kBwdBatch) * kBwdBatch; pb >= 0; pb -= kBwdBatch) {
-        __syncthreads();  // the previous round's flush has read s_part / s_touch / s_id
+    // The list entries of the next round are fetched while this one is processed (first of the two
+    // dependent round trips of the gather).
+    const int pb0 = ((todo - 1) / kBwdBatch) * kBwdBatch;
+    uint32_t next_id = 0;
+    if ((int)threadIdx.x < todo - pb0) next_id = __ldg(point_list + range.x + (uint32_t)(pb0 + (int)threadIdx.x));
+
+    for (int pb = pb0; pb >= 0; pb -= kBwdBatch) {
+        __syncthreads();  // the previous round's flush has read s_part / s_touch / s_id / s_stage
         const int nb = min(kBwdBatch, todo - pb);
         // Stage list positions [pb, pb + nb): slot j holds position pb + j.
         if ((int)threadIdx.x < nb) {
-            const uint32_t id = __ldg(point_list + range.x + (uint32_t)(pb + (int)threadIdx.x));
-            s_id[threadIdx.x] = id;
-            s_xy[threadIdx.x] = __ldg(means2D + id);
-            s_co[threadIdx.x] = __ldg(conic_opacity + id);
-            if (color_stride == 4) {
-                const float4 c = __ldg(reinterpret_cast<const float4*>(colors) + id);
-                s_rgb[0][threadIdx.x] = c.x;
-                s_rgb[1][threadIdx.x] = c.y;
-                s_rgb[2][threadIdx.x] = c.z;
-            } else {
-                s_rgb[0][threadIdx.x] = __ldg(colors + (size_t)id * 3 + 0);
-                s_rgb[1][threadIdx.x] = __ldg(colors + (size_t)id * 3 + 1);
-                s_rgb[2][threadIdx.x] = __ldg(colors + (size_t)id * 3 + 2);
-            }
+            s_id[threadIdx.x] = next_id;
+            store_gaussian(s_base + threadIdx.x * kStageBytes,
+                           load_gaussian(next_id, means2D, conic_opacity, colors, color_stride));
         } else if (threadIdx.x >= kBwdBatch && threadIdx.x < kBwdBatch + kBwdChunks * kBwdWarps) {
             const int q = ((int)threadIdx.x - kBwdBatch) / kBwdWarps, w = ((int)threadIdx.x - kBwdBatch) % kBwdWarps;
             uint32_t m = 0;
             if (pb + 32 * q < todo) m = __ldg(hit_base + (size_t)((pb >> 5) + q) * kBwdWarps + w);
             s_hit[q][w] = m;
         }
+        if (pb >= kBwdBatch && threadIdx.x < kBwdBatch)  // the round after this one is always a full batch
+            next_id = __ldg(point_list + range.x + (uint32_t)(pb - kBwdBatch + (int)threadIdx.x));
         __syncthreads();
 
         // This warp's masks, clipped to positions below its own largest contributor count (words
@@ -180,52 +178,50 @@ __global__ void __launch_bounds__(kBlendThreads)
                 const int bit = 31 - __clz(m);
                 m ^= 1u << bit;
                 const int e = 32 * q + bit;
-                const uint32_t pos = (uint32_t)(pb + e);  // 0-based list position
-                float g[9];
-#pragma unroll
-                for (int v = 0; v < 9; v++) g[v] = 0.f;
-                // Skip if this one is behind the last contributor of this pixel.
-                if (pos < last_contributor) {
-                    const float2 xy = s_xy[e];
-                    const float4 co = s_co[e];
-                    const float dx = xy.x - pixfx;
-                    const float dy = xy.y - pixfy;
-                    const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-                    if (!(power > 0.0f)) {
-                        const float G = __expf(power);
-                        const float alpha = fminf(0.99f, co.w * G);
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            const float rcp = __fdividef(1.f, 1.f - alpha);
-                            T *= rcp;
-                            const float dchannel_dcolor = alpha * T;
-                            // Propagate gradients to per-Gaussian colours and keep gradients w.r.t.
-                            // alpha (blending factor for a Gaussian/pixel pair).
-                            const float c0 = s_rgb[0][e], c1 = s_rgb[1][e], c2 = s_rgb[2][e];
-                            accum0 = fmaf(last_alpha, last_c0 - accum0, accum0);
-                            accum1 = fmaf(last_alpha, last_c1 - accum1, accum1);
-                            accum2 = fmaf(last_alpha, last_c2 - accum2, accum2);
-                            last_c0 = c0;
-                            last_c1 = c1;
-                            last_c2 = c2;
-                            last_alpha = alpha;
-                            float dL_dalpha = (c0 - accum0) * dLp0 + (c1 - accum1) * dLp1 + (c2 - accum2) * dLp2;
-                            g[0] = dchannel_dcolor * dLp0;
-                            g[1] = dchannel_dcolor * dLp1;
-                            g[2] = dchannel_dcolor * dLp2;
-                            dL_dalpha = fmaf(dL_dalpha, T, bg_term * rcp);
-                            const float dL_dG = co.w * dL_dalpha;
-                            const float X = dL_dG * (G * dx);
-                            const float Y = dL_dG * (G * dy);
-                            g[3] = X;
-                            g[4] = Y;
-                            g[5] = X * dx;
-                            g[6] = X * dy;
-                            g[7] = Y * dy;
-                            g[8] = G * dL_dalpha;
-                        }
-                    }
+                const uint32_t addr = s_base + (uint32_t)e * kStageBytes;
+                const float4 g0 = lds_f4(addr);       // x, y, A, B
+                const float4 g1 = lds_f4(addr + 16);  // C, opacity, r, g
+                const float cb = lds_f1(addr + 32);   // b
+                // Straight-line: nearly every lane is hit by a Gaussian its warp blended (measured: 28
+                // of 32), so the state updates are predicated instead of branched around.
+                const float dx = g0.x - pixfx;
+                const float dy = g0.y - pixfy;
+                const float power = -0.5f * (g0.z * dx * dx + g1.x * dy * dy) - g0.w * dx * dy;
+                const float G = __expf(fminf(power, 0.f));  // clamp: a lane outside the footprint must not make inf
+                const float alpha = fminf(0.99f, g1.y * G);
+                // Skip if this one is behind the last contributor of this pixel, or was skipped by it
+                // in the forward pass (backward.cu:486-501).
+                const bool hit = ((uint32_t)(pb + e) < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                const float rcp = __fdividef(1.f, 1.f - alpha);
+                if (hit) {
+                    T *= rcp;
+                    accum0 = fmaf(last_alpha, last_c0 - accum0, accum0);
+                    accum1 = fmaf(last_alpha, last_c1 - accum1, accum1);
+                    accum2 = fmaf(last_alpha, last_c2 - accum2, accum2);
+                    last_c0 = g1.z;
+                    last_c1 = g1.w;
+                    last_c2 = cb;
+                    last_alpha = alpha;
                 }
-                warp_reduce9_store(g, &s_part[warp][e][0]);
+                // Propagate gradients to per-Gaussian colours and keep gradients w.r.t. alpha
+                // (blending factor for a Gaussian/pixel pair); both vanish for a lane that is not hit.
+                const float dchannel_dcolor = hit ? alpha * T : 0.f;
+                float dL_dalpha = (g1.z - accum0) * dLp0 + (g1.w - accum1) * dLp1 + (cb - accum2) * dLp2;
+                dL_dalpha = hit ? fmaf(dL_dalpha, T, bg_term * rcp) : 0.f;
+                const float dL_dG = g1.y * dL_dalpha;
+                const float X = dL_dG * (G * dx);
+                const float Y = dL_dG * (G * dy);
+                float g[9];
+                g[0] = dchannel_dcolor * dLp0;
+                g[1] = dchannel_dcolor * dLp1;
+                g[2] = dchannel_dcolor * dLp2;
+                g[3] = X;
+                g[4] = Y;
+                g[5] = X * dx;
+                g[6] = X * dy;
+                g[7] = Y * dy;
+                g[8] = G * dL_dalpha;
+                warp_reduce9_store(g, part_base + (uint32_t)e * 36u, lane);
             }
         }
         __syncthreads();
@@ -247,7 +243,9 @@ __global__ void __launch_bounds__(kBlendThreads)
             }
             if (any) {
                 const size_t id = s_id[e];
-                const float4 co = s_co[e];
+                const float4 r0 = lds_f4(s_base + (uint32_t)e * kStageBytes);       // x, y, A, B
+                const float cC = lds_f1(s_base + (uint32_t)e * kStageBytes + 16);   // C
+                const float4 co = make_float4(r0.z, r0.w, cC, 0.f);
                 atomicAdd(dL_dcolor + id * 3 + 0, S[0]);
                 atomicAdd(dL_dcolor + id * 3 + 1, S[1]);
                 atomicAdd(dL_dcolor + id * 3 + 2, S[2]);
