@@ -11,7 +11,10 @@ the job processes N frames per step ("scaling": "weak").
   value    frames/s with every input already resident in HBM, CUDA-event timed, max over ranks
   e2e      the same step through the public API with the per-frame inputs (camera, SMPL joint
            transforms, the image-space loss gradient that stands in for the training target)
-           copied from pinned host memory and the loss read back, inside the timed region
+           copied from pinned host memory and the loss read back, inside the timed region (the
+           25 MB target is uploaded on a copy stream under the forward pass; each step's loss is
+           copied to pinned memory and read by the host one step later, the last one before the
+           closing event)
   roofline the dominant kernel's algorithmic bytes / its CUDA-event time / measured HBM peak
   stages   the same for every stage (per-stage CUDA events recorded inside the library on the
            launching stream during a second pass of K steps)
@@ -182,6 +185,18 @@ class Replica:
         self.host["G"] = wl["G"].clone().pin_memory()
         self.dev = {k: v.to(device) for k, v in self.host.items()}
         self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host.values())
+        # e2e plumbing: the image-space loss gradient (the stand-in for the training target, 25 MB) is
+        # uploaded on a copy stream into one of two device buffers while the forward pass runs; the
+        # loss of every step is copied to pinned memory and read one step later, so the host never
+        # stalls the device (what a training loop's prefetcher / async logger does).
+        self.copy_stream = torch.cuda.Stream(device)
+        self.G_dev = [torch.empty_like(self.dev["G"]) for _ in range(2)]
+        self.G_ready = [torch.cuda.Event() for _ in range(2)]
+        self.step_done = [None, None]
+        self.loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+        self.loss_ready = [None, None]
+        self.e2e_step = 0
+        self.losses = []
 
     def leaves(self):
         names = ["h_xyz", "h_rotmat", "h_scales", "h_weights", "s_means", "s_scales", "s_rots", "opacity", "shs"]
@@ -209,7 +224,12 @@ class Replica:
         color, radii = self.module.GaussianRasterizer(settings)(
             means3D=means3D, means2D=self.means2D, opacities=self.opacity, shs=self.shs, scales=scales,
             rotations=rots)
+        if "G_ready" in inp:  # the upload of G runs on the copy stream; it is first needed here
+            torch.cuda.current_stream(self.device).wait_event(inp["G_ready"])
         loss = (color * inp["G"]).sum()
+        if "loss_out" in inp:
+            inp["loss_out"].copy_(loss.detach().reshape(1), non_blocking=True)
+            inp["loss_event"].record()
         loss.backward()
         self.last_radii = radii
         self.last_node = color.grad_fn
@@ -220,10 +240,38 @@ class Replica:
         return self.frame(dict(self.dev))
 
     def step_e2e(self):
+        """One frame with every per-frame input copied from pinned host memory (camera, joint
+        transforms on the compute stream; G on the copy stream) and the loss read back on the host."""
         self.zero_grad()
-        inp = {k: v.to(self.device, non_blocking=True) for k, v in self.host.items()}
-        loss = self.frame(inp)
-        return float(loss.item())  # device -> host read of the step's result (4 bytes, synchronises)
+        i = self.e2e_step % 2
+        main = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self.copy_stream):
+            if self.step_done[i] is not None:  # buffer i was last read by the step before the previous one
+                self.copy_stream.wait_event(self.step_done[i])
+            self.G_dev[i].copy_(self.host["G"], non_blocking=True)
+            self.G_ready[i].record(self.copy_stream)
+        inp = {k: v.to(self.device, non_blocking=True) for k, v in self.host.items() if k != "G"}
+        ev = torch.cuda.Event()
+        inp.update(G=self.G_dev[i], G_ready=self.G_ready[i], loss_out=self.loss_host[i], loss_event=ev)
+        self.frame(inp)
+        self.loss_ready[i] = ev
+        done = torch.cuda.Event()
+        done.record(main)
+        self.step_done[i] = done
+        self.e2e_step += 1
+        j = 1 - i  # read the previous step's loss (its copy has had a whole step to land)
+        if self.loss_ready[j] is not None:
+            self.loss_ready[j].synchronize()
+            self.loss_ready[j] = None
+            self.losses.append(float(self.loss_host[j][0]))
+
+    def drain_e2e(self):
+        """Read the last step's loss (called inside the timed region, after the last step)."""
+        i = (self.e2e_step - 1) % 2
+        if self.e2e_step and self.loss_ready[i] is not None:
+            self.loss_ready[i].synchronize()
+            self.loss_ready[i] = None
+            self.losses.append(float(self.loss_host[i][0]))
 
     def allreduce_grads(self):
         import torch.distributed as dist
@@ -282,7 +330,7 @@ def stage_bytes(P, visible, R, W, H, n_human, sort_bits):
     }
 
 
-def timed_loop(fn, steps, device, barrier):
+def timed_loop(fn, steps, device, barrier, finish=None):
     """EXACTLY `steps` calls of fn between barrier+synchronize brackets, CUDA-event timed.
     The cyclic garbage collector is paused for the timed region (both arms): a generation-2 sweep of
     the interpreter's ~10^6 live objects takes 20-30 ms, ten frames' worth, whenever it happens to fire."""
@@ -296,6 +344,8 @@ def timed_loop(fn, steps, device, barrier):
         e0.record()
         for _ in range(steps):
             fn()
+        if finish is not None:
+            finish()
         e1.record()
         torch.cuda.synchronize(device)
         barrier()
@@ -407,7 +457,10 @@ def main():
     launches = int(_native.launch_count(1))
     for _ in range(2):
         step_e2e()
-    ms_e2e = timed_loop(step_e2e, args.steps, device, barrier)
+    rep.drain_e2e()
+    rep.losses.clear()
+    ms_e2e = timed_loop(step_e2e, args.steps, device, barrier, finish=rep.drain_e2e)
+    assert len(rep.losses) == args.steps and all(math.isfinite(x) for x in rep.losses), "e2e: a loss was not read back"
     clocks = sampler.stop() if sampler else None
 
     # per-stage device times: same K steps again with the library's stage events switched on
@@ -493,7 +546,10 @@ def run_reference(args, config):
         ms = timed_loop(rep.step_resident, args.steps, device, lambda: None)
         for _ in range(2):
             rep.step_e2e()
-        ms_e2e = timed_loop(rep.step_e2e, args.steps, device, lambda: None)
+        rep.drain_e2e()
+        rep.losses.clear()
+        ms_e2e = timed_loop(rep.step_e2e, args.steps, device, lambda: None, finish=rep.drain_e2e)
+        assert len(rep.losses) == args.steps, "e2e: a loss was not read back"
         clocks = sampler.stop()
         v = args.steps / (ms * 1e-3)
         ve = args.steps / (ms_e2e * 1e-3)
