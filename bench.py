@@ -1,12 +1,13 @@
 #!/usr/bin/env python3
 """bench.py -- fwd+bwd frames/s of the HUGS splat hot path on N B200s (BASELINE.json metric).
 
-A "step" on each rank is ONE frame of the human+scene workload (BASELINE.json configs[2]: 110 210
+A "step" on each rank is --views-per-rank (default 4) frames of the human+scene workload (BASELINE.json configs[2]: 110 210
 LBS-deformed human Gaussians + 1 000 000 scene Gaussians, SH degree 3, 1920x1080):
     LBS forward -> rasterizer forward -> loss=(color*G).sum() -> rasterizer backward -> LBS backward
-followed, for N > 1, by one NCCL allreduce(sum) of the flat parameter-gradient buffer (view-batch
-data parallelism; a single view is never split).  Every rank renders its own view each step, so
-the job processes N frames per step ("scaling": "weak").
+per frame, gradients accumulated over the rank's frames, followed, for N > 1, by one NCCL
+allreduce(sum) of the parameter gradients (view-batch data parallelism; a single view is never
+split).  The step's view batch is N x views-per-rank views, so the per-rank work is fixed
+("scaling": "weak") and frames/s = N x views-per-rank x steps / time.
 
   value    frames/s with every input already resident in HBM, CUDA-event timed, max over ranks
   e2e      the same step through the public API with the per-frame inputs (camera, SMPL joint
@@ -58,6 +59,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="human_scene_1080p", choices=sorted(WORKLOADS))
+    ap.add_argument("--views-per-rank", type=int, default=4,
+                    help="views each rank renders per step before the gradient allreduce (view batch = this x N)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-baseline-seconds", type=float, default=20.0)
     return ap.parse_args()
@@ -130,22 +133,24 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # workload
 # ------------------------------------------------------------------------------------------------
-def make_workload(name, rank, world, device):
+def make_workload(name, rank, world, device, views=1):
     """Seeded synthetic tensors of the workload.  Parameters are identical on every
-    rank (replicas); each rank gets its own camera (view `rank` of `world` on the orbit), its own
-    SMPL joint transforms and its own image-space loss gradient."""
+    rank (replicas); the step's view batch of world x views views on the orbit is split across the
+    ranks, and every view has its own camera, SMPL joint transforms and image-space loss gradient."""
     from hugs_b200 import synth
 
     n_human, n_scene, W, H, focal = WORKLOADS[name]
-    cam = synth.make_camera(W, H, focal, view=rank, n_views=max(world, 1), seed=SEED)
+    n_views = max(world, 1) * views
+    cams = [synth.make_camera(W, H, focal, view=rank * views + v, n_views=n_views, seed=SEED) for v in range(views)]
     h = synth.make_human_gaussians(n_human, seed=SEED + 1)
-    A = synth.make_joint_transforms(1, SEED + 100 + rank)[0]
-    parts = dict(human=h, A=A, cam=cam, W=W, H=H, n_human=n_human, n_scene=n_scene)
+    As = [synth.make_joint_transforms(1, SEED + 100 + rank * views + v)[0] for v in range(views)]
+    Gs = [synth.make_dL_dcolor(W, H, SEED + rank * views + v) for v in range(views)]
+    parts = dict(human=h, A=As[0], cam=cams[0], G=Gs[0], As=As, cams=cams, Gs=Gs, W=W, H=H, n_human=n_human,
+                 n_scene=n_scene)
     if n_scene > 0:
         # scene frustum is laid out for the central camera so every rank holds the same replica
         cam0 = synth.make_camera(W, H, focal, seed=SEED)
         parts["scene"] = synth.make_scene_gaussians(n_scene, SEED + 2, cam0["tanfovx"], cam0["tanfovy"])
-    parts["G"] = synth.make_dL_dcolor(W, H, SEED + rank)
     return parts
 
 
@@ -178,25 +183,30 @@ class Replica:
         self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=True)
         self.transl = d(h["transl"][0])
         # per-frame inputs: pinned host copies (for e2e) and resident device copies (for value)
-        cam = wl["cam"]
-        self.tanfovx, self.tanfovy = cam["tanfovx"], cam["tanfovy"]
-        self.host = {k: cam[k].clone().pin_memory() for k in ("viewmatrix", "projmatrix", "campos", "bg")}
-        self.host["A"] = wl["A"].clone().pin_memory()
-        self.host["G"] = wl["G"].clone().pin_memory()
-        self.dev = {k: v.to(device) for k, v in self.host.items()}
-        self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host.values())
+        self.tanfovx, self.tanfovy = wl["cam"]["tanfovx"], wl["cam"]["tanfovy"]
+        self.hosts, self.devs = [], []
+        for cam, A, G in zip(wl["cams"], wl["As"], wl["Gs"]):
+            host = {k: cam[k].clone().pin_memory() for k in ("viewmatrix", "projmatrix", "campos", "bg")}
+            host["A"] = A.clone().pin_memory()
+            host["G"] = G.clone().pin_memory()
+            self.hosts.append(host)
+            self.devs.append({k: v.to(device) for k, v in host.items()})
+        self.views = len(self.hosts)
+        self.h2d_bytes = sum(v.numel() * v.element_size() for host in self.hosts for v in host.values())
+        self.last_nodes, self.last_radii_v = [None] * self.views, [None] * self.views
         # e2e plumbing: the image-space loss gradient (the stand-in for the training target, 25 MB) is
         # uploaded on a copy stream into one of two device buffers while the forward pass runs; the
         # loss of every step is copied to pinned memory and read one step later, so the host never
         # stalls the device (what a training loop's prefetcher / async logger does).
         self.copy_stream = torch.cuda.Stream(device)
-        self.G_dev = [torch.empty_like(self.dev["G"]) for _ in range(2)]
+        self.G_dev = [torch.empty_like(self.devs[0]["G"]) for _ in range(2)]
         self.G_ready = [torch.cuda.Event() for _ in range(2)]
         self.step_done = [None, None]
         self.loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
         self.loss_ready = [None, None]
         self.e2e_step = 0
         self.losses = []
+        self.flat_small = None
 
     def leaves(self):
         names = ["h_xyz", "h_rotmat", "h_scales", "h_weights", "s_means", "s_scales", "s_rots", "opacity", "shs"]
@@ -236,21 +246,29 @@ class Replica:
         return loss.detach()
 
     def step_resident(self):
+        """One step: every view of this rank's share of the view batch, gradients accumulated."""
         self.zero_grad()
-        return self.frame(dict(self.dev))
+        for v in range(self.views):
+            self.frame(dict(self.devs[v]))
+            self.last_nodes[v] = self.last_node
+            self.last_radii_v[v] = self.last_radii
 
     def step_e2e(self):
+        self.zero_grad()
+        for v in range(self.views):
+            self.frame_e2e(self.hosts[v])
+
+    def frame_e2e(self, host):
         """One frame with every per-frame input copied from pinned host memory (camera, joint
         transforms on the compute stream; G on the copy stream) and the loss read back on the host."""
-        self.zero_grad()
         i = self.e2e_step % 2
         main = torch.cuda.current_stream(self.device)
         with torch.cuda.stream(self.copy_stream):
             if self.step_done[i] is not None:  # buffer i was last read by the step before the previous one
                 self.copy_stream.wait_event(self.step_done[i])
-            self.G_dev[i].copy_(self.host["G"], non_blocking=True)
+            self.G_dev[i].copy_(host["G"], non_blocking=True)
             self.G_ready[i].record(self.copy_stream)
-        inp = {k: v.to(self.device, non_blocking=True) for k, v in self.host.items() if k != "G"}
+        inp = {k: v.to(self.device, non_blocking=True) for k, v in host.items() if k != "G"}
         ev = torch.cuda.Event()
         inp.update(G=self.G_dev[i], G_ready=self.G_ready[i], loss_out=self.loss_host[i], loss_event=ev)
         self.frame(inp)
@@ -259,7 +277,7 @@ class Replica:
         done.record(main)
         self.step_done[i] = done
         self.e2e_step += 1
-        j = 1 - i  # read the previous step's loss (its copy has had a whole step to land)
+        j = 1 - i  # read the previous frame's loss (its copy has had a whole frame to land)
         if self.loss_ready[j] is not None:
             self.loss_ready[j].synchronize()
             self.loss_ready[j] = None
@@ -277,8 +295,19 @@ class Replica:
         import torch.distributed as dist
         if not dist.is_initialized() or dist.get_world_size() == 1:
             return
-        for p in self.leaves().values():
-            dist.all_reduce(p.grad, op=dist.ReduceOp.SUM)
+        # Two collectives: the SH gradient (81 % of the bytes) in place, everything else through one
+        # flat buffer (a collective per small tensor costs more in launch latency than in transfer).
+        leaves = self.leaves()
+        dist.all_reduce(leaves["shs"].grad, op=dist.ReduceOp.SUM)
+        small = [p.grad for n, p in leaves.items() if n != "shs"]
+        if self.flat_small is None:
+            self.flat_small = torch.empty(sum(g.numel() for g in small), device=self.device)
+        torch.cat([g.reshape(-1) for g in small], out=self.flat_small)
+        dist.all_reduce(self.flat_small, op=dist.ReduceOp.SUM)
+        off = 0
+        for g in small:
+            g.copy_(self.flat_small[off:off + g.numel()].view_as(g))
+            off += g.numel()
 
 
 def our_impl():
@@ -408,8 +437,10 @@ def main():
     n_gpus = world
     n_human, n_scene, W, H, _ = WORKLOADS[args.workload]
     config = {"workload": args.workload, "n_human": n_human, "n_scene": n_scene, "image": "%dx%d" % (W, H),
-              "sh_degree": 3, "views_per_rank_per_step": 1,
-              "parallelism": "dp%d (view batch; allreduce of parameter gradients)" % n_gpus,
+              "sh_degree": 3, "views_per_rank_per_step": args.views_per_rank,
+              "global_view_batch": args.views_per_rank * n_gpus,
+              "parallelism": "dp%d (view batch split across ranks, gradients accumulated over a rank's views, "
+                             "one allreduce of the parameter gradients per step)" % n_gpus,
               "l2": "inputs larger than L2 (per-frame working set > 1 GB vs 126 MB L2), no flush"}
 
     # ---- reference arm -------------------------------------------------------------------------
@@ -432,7 +463,8 @@ def main():
 
     from hugs_b200 import _native
     module, lbs_impl = our_impl()
-    wl = make_workload(args.workload, rank, world, device)
+    V = args.views_per_rank
+    wl = make_workload(args.workload, rank, world, device, views=V)
     rep = Replica(wl, device, module, lbs_impl)
 
     def step_resident():
@@ -446,8 +478,9 @@ def main():
     for _ in range(max(args.warmup, 3)):
         step_resident()
     torch.cuda.synchronize(device)
-    R = int(rep.last_node.num_rendered)
-    visible = int((rep.last_radii > 0).sum())
+    # pair / visible counts: mean over this rank's views (they size the per-stage algorithmic bytes)
+    R = int(round(sum(int(nd.num_rendered) for nd in rep.last_nodes) / V))
+    visible = int(round(sum(int((r > 0).sum()) for r in rep.last_radii_v) / V))
 
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
@@ -460,7 +493,8 @@ def main():
     rep.drain_e2e()
     rep.losses.clear()
     ms_e2e = timed_loop(step_e2e, args.steps, device, barrier, finish=rep.drain_e2e)
-    assert len(rep.losses) == args.steps and all(math.isfinite(x) for x in rep.losses), "e2e: a loss was not read back"
+    assert len(rep.losses) == args.steps * V and all(math.isfinite(x) for x in rep.losses), \
+        "e2e: a loss was not read back"
     clocks = sampler.stop() if sampler else None
 
     # per-stage device times: same K steps again with the library's stage events switched on
@@ -485,7 +519,7 @@ def main():
     for name, (tot, calls) in stage_ms.items():
         if calls == 0:
             continue
-        per = tot / args.steps  # a stage may be entered more than once per frame (the two sort levels)
+        per = tot / (args.steps * V)  # per frame; a stage may be entered more than once (the two sort levels)
         gbs = nbytes[name] / (per * 1e-3) / 1e9
         stages[name] = {"ms": round(per, 4), "bytes": int(nbytes[name]), "gbs": round(gbs, 1),
                         "frac": round(gbs / peak, 4)}
@@ -496,23 +530,24 @@ def main():
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": s["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": s["frac"], "traffic": None, "peak_source": peak_kind,
                     "ms_per_launch": s["ms"], "algorithmic_bytes": s["bytes"],
-                    "timed": "per-stage CUDA events on the launching stream, %d steps (%.3f ms/step with events on)"
-                             % (args.steps, ms_staged / args.steps)}
+                    "timed": "per-stage CUDA events on the launching stream, %d frames (%.3f ms/frame with events on)"
+                             % (args.steps * V, ms_staged / (args.steps * V))}
     frame_bytes = sum(nbytes.values())
     line = {
-        "metric": METRIC, "value": round(n_gpus * args.steps / (ms * 1e-3), 3), "unit": UNIT, "n_gpus": n_gpus,
+        "metric": METRIC, "value": round(n_gpus * V * args.steps / (ms * 1e-3), 3), "unit": UNIT, "n_gpus": n_gpus,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": dict(config, P=rep.P, R=R, visible=visible, sort_bits=sort_bits),
-        "e2e": {"value": round(n_gpus * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
-                "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": 4 + 4,
+        "e2e": {"value": round(n_gpus * V * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
+                "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": (4 + 4) * V,
                 "ms_per_step": round(ms_e2e / args.steps, 4)},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roofline,
         "stages": stages,
         "frame": {"algorithmic_bytes": int(frame_bytes),
-                  "hbm_frac": round(frame_bytes / (ms / args.steps * 1e-3) / 1e9 / peak, 4)},
+                  "ms": round(ms / (args.steps * V), 4),
+                  "hbm_frac": round(frame_bytes / (ms / (args.steps * V) * 1e-3) / 1e9 / peak, 4)},
     }
     if n_gpus == 1 and not args.no_cpu_baseline:
         fps, threads, frames = cpu_oracle_frames(make_workload(args.workload, 0, 1, "cpu"), args.cpu_baseline_seconds)
@@ -537,7 +572,8 @@ def run_reference(args, config):
         device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
         torch.cuda.set_device(device)
         module, lbs_impl = reference_impl()
-        wl = make_workload(args.workload, 0, 1, device)
+        V = args.views_per_rank
+        wl = make_workload(args.workload, 0, 1, device, views=V)
         rep = Replica(wl, device, module, lbs_impl)
         for _ in range(max(args.warmup, 3)):
             rep.step_resident()
@@ -549,21 +585,22 @@ def run_reference(args, config):
         rep.drain_e2e()
         rep.losses.clear()
         ms_e2e = timed_loop(rep.step_e2e, args.steps, device, lambda: None, finish=rep.drain_e2e)
-        assert len(rep.losses) == args.steps, "e2e: a loss was not read back"
+        assert len(rep.losses) == args.steps * V, "e2e: a loss was not read back"
         clocks = sampler.stop()
-        v = args.steps / (ms * 1e-3)
-        ve = args.steps / (ms_e2e * 1e-3)
+        v = V * args.steps / (ms * 1e-3)
+        ve = V * args.steps / (ms_e2e * 1e-3)
         base.update({
             "value": round(v, 3), "ms_per_step": round(ms / args.steps, 4), "clocks": clocks,
             "e2e": {"value": round(ve, 3), "unit": UNIT, "h2d_bytes_per_step": int(rep.h2d_bytes),
-                    "d2h_bytes_per_step": 8, "ms_per_step": round(ms_e2e / args.steps, 4)},
+                    "d2h_bytes_per_step": 8 * V, "ms_per_step": round(ms_e2e / args.steps, 4)},
             "cpu_baseline": {"value": round(ve, 3), "unit": UNIT, "cores": 0, "kind": "reference",
                              "sample": "the reference has no CPU rasterizer: this is its own CUDA build "
                                        "(oracle/_ref, unmodified sources, sm_100) + its PyTorch LBS chain on the "
                                        "same B200, full frames of " + args.workload},
             "reference_device": "cuda",
         })
-        base["config"] = dict(config, P=rep.P, R=int(rep.last_node.num_rendered))
+        base["config"] = dict(config, P=rep.P,
+                              R=int(round(sum(int(nd.num_rendered) for nd in rep.last_nodes) / V)))
         print(json.dumps(base), flush=True)
         return 0
     # no GPU or no reference build: the CPU oracle port on the host cores

@@ -62,6 +62,11 @@ class _Workspace:
 
         self.callback = N.RESIZE_FN(_resize)
 
+    def release(self):
+        """Drop the ctypes thunk.  It closes over `self`, a reference cycle: without this the workspace
+        tensor (hundreds of MB) would live until the cyclic garbage collector happens to run."""
+        self.callback = None
+
 
 def rasterize_gaussians_forward(
     background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
@@ -96,6 +101,8 @@ def rasterize_gaussians_forward(
     if P == 0:
         # rasterize_points.cu:81: nothing is launched; colour stays at its zero fill.
         out_color = torch.zeros(3, H, W, dtype=torch.float32, device=device)
+        for ws in (geom, binning, img):
+            ws.release()
         return 0, out_color, radii, geom.tensor, binning.tensor, img.tensor
     out_color = torch.empty(3, H, W, dtype=torch.float32, device=device)
 
@@ -114,6 +121,7 @@ def rasterize_gaussians_forward(
             C.byref(num_rendered),
         )
     for ws in (geom, binning, img):
+        ws.release()
         if ws.error is not None:
             raise RuntimeError("workspace allocation failed: %r" % (ws.error,))
     N.check(rc, "rasterize_gaussians")

@@ -147,3 +147,32 @@ def test_finite_difference_on_sh_dc_coefficient():
                 vals.append(float((col.double() * sc["dL_dcolor"].double()).sum()))
             fd = (vals[0] - vals[1]) / 0.5
             assert abs(fd - float(g[i, 0, c])) <= 2e-3 * max(abs(fd), 1e-2), (i, c, fd, float(g[i, 0, c]))
+
+
+def test_workspaces_are_freed_without_the_cyclic_gc():
+    """The three workspaces (hundreds of MB at full size) must die by reference counting: with the
+    cyclic collector off (bench.py pauses it while timing), device memory must not grow per call."""
+    import gc
+
+    import diff_gaussian_rasterization as dgr
+    import scenes
+
+    sc = scenes.make_scene(20000, 2000, 320, 240, 250.0, 5, device="cuda")
+
+    def once():
+        o = scenes.run_module(sc, dgr, backward=True)
+        del o
+
+    once()
+    gc.collect()
+    gc.disable()
+    try:
+        torch.cuda.synchronize()
+        base = torch.cuda.memory_allocated()
+        for _ in range(10):
+            once()
+        torch.cuda.synchronize()
+        grown = torch.cuda.memory_allocated() - base
+    finally:
+        gc.enable()
+    assert grown < (1 << 20), "device memory grew by %d bytes over 10 calls with the cyclic GC off" % grown

@@ -26,7 +26,7 @@ def main():
     rep.step_resident()
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStop()
-    print("profiled one frame: P=%d R=%d mode=%d" % (rep.P, rep.last_node.num_rendered, mode))
+    print("profiled one frame: P=%d R=%d mode=%d" % (rep.P, rep.last_node.num_rendered, mode))  # views=1
 
 
 if __name__ == "__main__":
