@@ -122,7 +122,29 @@ __device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float s
     cov[5] = dot3_rn(M20, M20, M21, M21, M22, M22);
 }
 
-__global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessArgs a) {
+// SH rows staged in shared memory: 192 B per Gaussian padded to 208 B (52 words), so that the
+// 128-bit reads of a quarter warp (one row per lane) fall in disjoint banks.
+constexpr int kPreThreads = 256;
+constexpr int kShRowBytes = 208;
+constexpr int kPreSmemBytes = kPreThreads * kShRowBytes;
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+// One thread per Gaussian.  Memory behaviour (the stage is HBM bound, 311 B per visible Gaussian):
+//   * position, scale, quaternion and opacity are requested together, before anything is computed
+//     (one DRAM round trip, not three);
+//   * the 192-B SH rows -- 62 % of the bytes -- are fetched only for the Gaussians that survive the
+//     culls, by the whole warp: the 32 rows of a warp are one contiguous 6 KB block, lane l of copy j
+//     moves 16-byte word 32 j + l of it with cp.async (global -> shared, no registers, all twelve
+//     copies of a lane in flight at once), so every request is 512 contiguous bytes minus the rows of
+//     culled Gaussians, and each thread then reads its own row out of shared memory.
+__global__ void __launch_bounds__(kPreThreads, 3) preprocess_kernel(const PreprocessArgs a) {
+    extern __shared__ __align__(16) unsigned char s_rows[];  // [256][208 B] SH rows (vec4 path)
     __shared__ float s_cam[36];  // view[16], proj[16], campos[3]
     if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(a.view + threadIdx.x);
     else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(a.proj + threadIdx.x - 16);
@@ -131,172 +153,207 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessArgs a)
     const float* V = s_cam;
     const float* Pm = s_cam + 16;
 
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
+    const int idx = blockIdx.x * kPreThreads + threadIdx.x;
+    const bool valid = idx < a.P;
+    bool vis = false;
+    float px = 0.f, py = 0.f, pz = 0.f, depth = 0.f, pix_x = 0.f, pix_y = 0.f;
+    float conic_x = 0.f, conic_y = 0.f, conic_z = 0.f, opacity = 0.f;
+    int radius = 0;
+    unsigned tiles = 0;
 
-    const float px = __ldg(a.means3D + 3 * (size_t)idx + 0);
-    const float py = __ldg(a.means3D + 3 * (size_t)idx + 1);
-    const float pz = __ldg(a.means3D + 3 * (size_t)idx + 2);
-
-    // in_frustum (auxiliary.h:139-164): near-plane cull on view-space z only.
-    const float depth = RN_ADD(dot3_rn(V[2], px, V[6], py, V[10], pz), V[14]);
-    if (depth <= 0.2f) {
-        if (a.prefiltered) {
-            printf("Point is filtered although prefiltered is set. This shouldn't happen!");
-            __trap();
-        }
-        a.radii[idx] = 0;
-        a.tiles_touched[idx] = 0;
-        a.depths[idx] = __uint_as_float(0xFFFFFFFFu);  // depth-sort key of a culled Gaussian: last
-        return;
-    }
-
-    // Projection (forward.cu:197-200).
-    const float hx = RN_ADD(dot3_rn(Pm[0], px, Pm[4], py, Pm[8], pz), Pm[12]);
-    const float hy = RN_ADD(dot3_rn(Pm[1], px, Pm[5], py, Pm[9], pz), Pm[13]);
-    const float hw = RN_ADD(dot3_rn(Pm[3], px, Pm[7], py, Pm[11], pz), Pm[15]);
-    const float p_w = __frcp_rn(RN_ADD(hw, 0.0000001f));
-    const float proj_x = RN_MUL(hx, p_w);
-    const float proj_y = RN_MUL(hy, p_w);
-
-    // 3D covariance (forward.cu:204-213).
-    float cov3[6];
-    if (a.cov3D_precomp != nullptr) {
+    if (valid) do {
+        // ---- every per-Gaussian input except the SH row, requested up front -----------------
+        px = __ldg(a.means3D + 3 * (size_t)idx + 0);
+        py = __ldg(a.means3D + 3 * (size_t)idx + 1);
+        pz = __ldg(a.means3D + 3 * (size_t)idx + 2);
+        float cov3[6];
+        float sx = 0.f, sy = 0.f, sz = 0.f;
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool precomp = a.cov3D_precomp != nullptr;
+        if (precomp) {
 #pragma unroll
-        for (int i = 0; i < 6; i++) cov3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
-    } else {
-        const float sx = __ldg(a.scales + 3 * (size_t)idx + 0);
-        const float sy = __ldg(a.scales + 3 * (size_t)idx + 1);
-        const float sz = __ldg(a.scales + 3 * (size_t)idx + 2);
-        float4 q;
-        if (a.rot_vec4) {
-            q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+            for (int i = 0; i < 6; i++) cov3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
         } else {
-            q.x = __ldg(a.rotations + 4 * (size_t)idx + 0);
-            q.y = __ldg(a.rotations + 4 * (size_t)idx + 1);
-            q.z = __ldg(a.rotations + 4 * (size_t)idx + 2);
-            q.w = __ldg(a.rotations + 4 * (size_t)idx + 3);
+            sx = __ldg(a.scales + 3 * (size_t)idx + 0);
+            sy = __ldg(a.scales + 3 * (size_t)idx + 1);
+            sz = __ldg(a.scales + 3 * (size_t)idx + 2);
+            if (a.rot_vec4) {
+                q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+            } else {
+                q.x = __ldg(a.rotations + 4 * (size_t)idx + 0);
+                q.y = __ldg(a.rotations + 4 * (size_t)idx + 1);
+                q.z = __ldg(a.rotations + 4 * (size_t)idx + 2);
+                q.w = __ldg(a.rotations + 4 * (size_t)idx + 3);
+            }
         }
-        cov3d_from_scale_rot(sx, sy, sz, a.scale_modifier, q.x, q.y, q.z, q.w, cov3);
-    }
+        opacity = __ldg(a.opacities + idx);
 
-    // 2D covariance, EWA (forward.cu:74-113).
-    const float tz = depth;
-    float tx = RN_ADD(dot3_rn(V[0], px, V[4], py, V[8], pz), V[12]);
-    float ty = RN_ADD(dot3_rn(V[1], px, V[5], py, V[9], pz), V[13]);
-    const float limx = RN_MUL(a.tan_fovx, 1.3f);
-    const float limy = RN_MUL(a.tan_fovy, 1.3f);
-    const float txtz = RN_DIV(tx, tz);
-    const float tytz = RN_DIV(ty, tz);
-    tx = RN_MUL(fminf(limx, fmaxf(-limx, txtz)), tz);
-    ty = RN_MUL(fminf(limy, fmaxf(-limy, tytz)), tz);
-    const float tz2 = RN_MUL(tz, tz);
-    const float J00 = RN_DIV(a.focal_x, tz);
-    const float J02 = RN_DIV(-RN_MUL(a.focal_x, tx), tz2);
-    const float J11 = RN_DIV(a.focal_y, tz);
-    const float J12 = RN_DIV(-RN_MUL(a.focal_y, ty), tz2);
-    // T = W * J with W[c][r] = view[c + 4r]; only the two non-zero columns of J matter.
-    const float T00 = RN_FMA(V[2], J02, RN_MUL(V[0], J00));
-    const float T01 = RN_FMA(V[6], J02, RN_MUL(V[4], J00));
-    const float T02 = RN_FMA(V[10], J02, RN_MUL(V[8], J00));
-    const float T10 = RN_FMA(V[2], J12, RN_MUL(V[1], J11));
-    const float T11 = RN_FMA(V[6], J12, RN_MUL(V[5], J11));
-    const float T12 = RN_FMA(V[10], J12, RN_MUL(V[9], J11));
-    // X = T^T Vrk^T : X[c][r] = T[r][0]Vrk[0][c] + T[r][1]Vrk[1][c] + T[r][2]Vrk[2][c]
-    const float X00 = dot3_rn(T00, cov3[0], T01, cov3[1], T02, cov3[2]);
-    const float X10 = dot3_rn(T00, cov3[1], T01, cov3[3], T02, cov3[4]);
-    const float X20 = dot3_rn(T00, cov3[2], T01, cov3[4], T02, cov3[5]);
-    const float X01 = dot3_rn(T10, cov3[0], T11, cov3[1], T12, cov3[2]);
-    const float X11 = dot3_rn(T10, cov3[1], T11, cov3[3], T12, cov3[4]);
-    const float X21 = dot3_rn(T10, cov3[2], T11, cov3[4], T12, cov3[5]);
-    // cov = X T : cov[c][r] = X[0][r]T[c][0] + X[1][r]T[c][1] + X[2][r]T[c][2]; low-pass +0.3
-    const float cx = RN_ADD(dot3_rn(X00, T00, X10, T01, X20, T02), 0.3f);
-    const float cy = dot3_rn(X01, T00, X11, T01, X21, T02);
-    const float cz = RN_ADD(dot3_rn(X01, T10, X11, T11, X21, T12), 0.3f);
+        // in_frustum (auxiliary.h:139-164): near-plane cull on view-space z only.
+        depth = RN_ADD(dot3_rn(V[2], px, V[6], py, V[10], pz), V[14]);
+        if (depth <= 0.2f) {
+            if (a.prefiltered) {
+                printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+                __trap();
+            }
+            break;
+        }
 
-    // Invert (forward.cu:219-223).
-    const float det = RN_FMA(cx, cz, -RN_MUL(cy, cy));
-    if (det == 0.0f) {
+        // Projection (forward.cu:197-200).
+        const float hx = RN_ADD(dot3_rn(Pm[0], px, Pm[4], py, Pm[8], pz), Pm[12]);
+        const float hy = RN_ADD(dot3_rn(Pm[1], px, Pm[5], py, Pm[9], pz), Pm[13]);
+        const float hw = RN_ADD(dot3_rn(Pm[3], px, Pm[7], py, Pm[11], pz), Pm[15]);
+        const float p_w = __frcp_rn(RN_ADD(hw, 0.0000001f));
+        const float proj_x = RN_MUL(hx, p_w);
+        const float proj_y = RN_MUL(hy, p_w);
+
+        // 3D covariance (forward.cu:204-213).
+        if (!precomp) cov3d_from_scale_rot(sx, sy, sz, a.scale_modifier, q.x, q.y, q.z, q.w, cov3);
+
+        // 2D covariance, EWA (forward.cu:74-113).
+        const float tz = depth;
+        float tx = RN_ADD(dot3_rn(V[0], px, V[4], py, V[8], pz), V[12]);
+        float ty = RN_ADD(dot3_rn(V[1], px, V[5], py, V[9], pz), V[13]);
+        const float limx = RN_MUL(a.tan_fovx, 1.3f);
+        const float limy = RN_MUL(a.tan_fovy, 1.3f);
+        const float txtz = RN_DIV(tx, tz);
+        const float tytz = RN_DIV(ty, tz);
+        tx = RN_MUL(fminf(limx, fmaxf(-limx, txtz)), tz);
+        ty = RN_MUL(fminf(limy, fmaxf(-limy, tytz)), tz);
+        const float tz2 = RN_MUL(tz, tz);
+        const float J00 = RN_DIV(a.focal_x, tz);
+        const float J02 = RN_DIV(-RN_MUL(a.focal_x, tx), tz2);
+        const float J11 = RN_DIV(a.focal_y, tz);
+        const float J12 = RN_DIV(-RN_MUL(a.focal_y, ty), tz2);
+        // T = W * J with W[c][r] = view[c + 4r]; only the two non-zero columns of J matter.
+        const float T00 = RN_FMA(V[2], J02, RN_MUL(V[0], J00));
+        const float T01 = RN_FMA(V[6], J02, RN_MUL(V[4], J00));
+        const float T02 = RN_FMA(V[10], J02, RN_MUL(V[8], J00));
+        const float T10 = RN_FMA(V[2], J12, RN_MUL(V[1], J11));
+        const float T11 = RN_FMA(V[6], J12, RN_MUL(V[5], J11));
+        const float T12 = RN_FMA(V[10], J12, RN_MUL(V[9], J11));
+        // X = T^T Vrk^T : X[c][r] = T[r][0]Vrk[0][c] + T[r][1]Vrk[1][c] + T[r][2]Vrk[2][c]
+        const float X00 = dot3_rn(T00, cov3[0], T01, cov3[1], T02, cov3[2]);
+        const float X10 = dot3_rn(T00, cov3[1], T01, cov3[3], T02, cov3[4]);
+        const float X20 = dot3_rn(T00, cov3[2], T01, cov3[4], T02, cov3[5]);
+        const float X01 = dot3_rn(T10, cov3[0], T11, cov3[1], T12, cov3[2]);
+        const float X11 = dot3_rn(T10, cov3[1], T11, cov3[3], T12, cov3[4]);
+        const float X21 = dot3_rn(T10, cov3[2], T11, cov3[4], T12, cov3[5]);
+        // cov = X T : cov[c][r] = X[0][r]T[c][0] + X[1][r]T[c][1] + X[2][r]T[c][2]; low-pass +0.3
+        const float cx = RN_ADD(dot3_rn(X00, T00, X10, T01, X20, T02), 0.3f);
+        const float cy = dot3_rn(X01, T00, X11, T01, X21, T02);
+        const float cz = RN_ADD(dot3_rn(X01, T10, X11, T11, X21, T12), 0.3f);
+
+        // Invert (forward.cu:219-223).
+        const float det = RN_FMA(cx, cz, -RN_MUL(cy, cy));
+        if (det == 0.0f) break;
+        const float det_inv = __frcp_rn(det);
+        conic_x = RN_MUL(cz, det_inv);
+        conic_y = RN_MUL(cy, -det_inv);
+        conic_z = RN_MUL(cx, det_inv);
+
+        // Screen-space extent (forward.cu:229-237).
+        const float mid = RN_MUL(RN_ADD(cx, cz), 0.5f);
+        const float sq = __fsqrt_rn(fmaxf(0.1f, RN_FMA(mid, mid, -det)));
+        const float lambda1 = RN_ADD(mid, sq);
+        const float lambda2 = RN_ADD(mid, -sq);
+        const float radius_f = ceilf(RN_MUL(__fsqrt_rn(fmaxf(lambda1, lambda2)), 3.f));
+        radius = (int)radius_f;
+        // ndc2Pix is evaluated in double in the reference (auxiliary.h:41-44).
+        pix_x = (float)__dmul_rn(__fma_rn(__dadd_rn((double)proj_x, 1.0), (double)a.W, -1.0), 0.5);
+        pix_y = (float)__dmul_rn(__fma_rn(__dadd_rn((double)proj_y, 1.0), (double)a.H, -1.0), 0.5);
+        // getRect (auxiliary.h:46-56): float maths on an int radius, truncation, clamp to the grid.
+        const float rf = (float)radius;
+        const unsigned gx = (unsigned)a.grid_x, gy = (unsigned)a.grid_y;
+        const unsigned min_x = min(gx, (unsigned)max(0, (int)RN_MUL(RN_ADD(pix_x, -rf), 0.0625f)));
+        const unsigned min_y = min(gy, (unsigned)max(0, (int)RN_MUL(RN_ADD(pix_y, -rf), 0.0625f)));
+        const unsigned max_x =
+            min(gx, (unsigned)max(0, (int)RN_MUL(RN_ADD(RN_ADD(RN_ADD(pix_x, rf), 16.f), -1.f), 0.0625f)));
+        const unsigned max_y =
+            min(gy, (unsigned)max(0, (int)RN_MUL(RN_ADD(RN_ADD(RN_ADD(pix_y, rf), 16.f), -1.f), 0.0625f)));
+        tiles = (max_x - min_x) * (max_y - min_y);
+        if (tiles == 0) break;
+        vis = true;
+    } while (0);
+
+    if (valid && !vis) {
         a.radii[idx] = 0;
         a.tiles_touched[idx] = 0;
         a.depths[idx] = __uint_as_float(0xFFFFFFFFu);  // depth-sort key of a culled Gaussian: last
-        return;
-    }
-    const float det_inv = __frcp_rn(det);
-    const float conic_x = RN_MUL(cz, det_inv);
-    const float conic_y = RN_MUL(cy, -det_inv);
-    const float conic_z = RN_MUL(cx, det_inv);
-
-    // Screen-space extent (forward.cu:229-237).
-    const float mid = RN_MUL(RN_ADD(cx, cz), 0.5f);
-    const float sq = __fsqrt_rn(fmaxf(0.1f, RN_FMA(mid, mid, -det)));
-    const float lambda1 = RN_ADD(mid, sq);
-    const float lambda2 = RN_ADD(mid, -sq);
-    const float radius_f = ceilf(RN_MUL(__fsqrt_rn(fmaxf(lambda1, lambda2)), 3.f));
-    const int radius = (int)radius_f;
-    // ndc2Pix is evaluated in double in the reference (auxiliary.h:41-44).
-    const float pix_x = (float)__dmul_rn(__fma_rn(__dadd_rn((double)proj_x, 1.0), (double)a.W, -1.0), 0.5);
-    const float pix_y = (float)__dmul_rn(__fma_rn(__dadd_rn((double)proj_y, 1.0), (double)a.H, -1.0), 0.5);
-    // getRect (auxiliary.h:46-56): float maths on an int radius, truncation, clamp to the grid.
-    const float rf = (float)radius;
-    const unsigned gx = (unsigned)a.grid_x, gy = (unsigned)a.grid_y;
-    const unsigned min_x = min(gx, (unsigned)max(0, (int)RN_MUL(RN_ADD(pix_x, -rf), 0.0625f)));
-    const unsigned min_y = min(gy, (unsigned)max(0, (int)RN_MUL(RN_ADD(pix_y, -rf), 0.0625f)));
-    const unsigned max_x =
-        min(gx, (unsigned)max(0, (int)RN_MUL(RN_ADD(RN_ADD(RN_ADD(pix_x, rf), 16.f), -1.f), 0.0625f)));
-    const unsigned max_y =
-        min(gy, (unsigned)max(0, (int)RN_MUL(RN_ADD(RN_ADD(RN_ADD(pix_y, rf), 16.f), -1.f), 0.0625f)));
-    const unsigned tiles = (max_x - min_x) * (max_y - min_y);
-    if (tiles == 0) {
-        a.radii[idx] = 0;
-        a.tiles_touched[idx] = 0;
-        a.depths[idx] = __uint_as_float(0xFFFFFFFFu);  // depth-sort key of a culled Gaussian: last
-        return;
     }
 
     // Colour (forward.cu:241-247).
     if (a.colors_precomp == nullptr) {
-        float dx = px - V[32], dy = py - V[33], dz = pz - V[34];
-        const float len = sqrtf(dx * dx + dy * dy + dz * dz);
-        dx = dx / len;
-        dy = dy / len;
-        dz = dz / len;
         float sh[48];
         const int nf = 3 * (a.D + 1) * (a.D + 1);  // floats actually used
         if (a.sh_vec4) {
-            const float4* src = reinterpret_cast<const float4*>(a.shs) + 12 * (size_t)idx;
-            const int nv = (nf + 3) >> 2;
+            const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+            const unsigned alive = __ballot_sync(0xffffffffu, vis);
+            if (alive != 0u) {
+                const int nv = (nf + 3) >> 2;
+                const uint32_t s_warp = (uint32_t)__cvta_generic_to_shared(s_rows) + warp * 32u * kShRowBytes;
+                const float4* g_warp =
+                    reinterpret_cast<const float4*>(a.shs) + 12 * ((size_t)blockIdx.x * kPreThreads + warp * 32u);
+                unsigned row = lane / 12u, col = lane % 12u;  // 16-byte word 32 j + lane = (row, col)
 #pragma unroll
-            for (int i = 0; i < 12; i++) {
-                if (i < nv) {
-                    const float4 v = __ldg(src + i);
-                    sh[4 * i + 0] = v.x;
-                    sh[4 * i + 1] = v.y;
-                    sh[4 * i + 2] = v.z;
-                    sh[4 * i + 3] = v.w;
+                for (int j = 0; j < 12; j++) {
+                    if (((alive >> row) & 1u) && (int)col < nv)
+                        cp_async16(s_warp + row * kShRowBytes + col * 16u, g_warp + 32 * j + lane);
+                    col += 8u;
+                    row += 2u;
+                    if (col >= 12u) {
+                        col -= 12u;
+                        row += 1u;
+                    }
+                }
+                cp_async_wait_all();
+                __syncwarp();
+                if (vis) {
+                    const uint32_t mine = s_warp + lane * kShRowBytes;
+#pragma unroll
+                    for (int i = 0; i < 12; i++) {
+                        if (i < nv) {
+                            float4 v;
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                                         : "r"(mine + 16u * i));
+                            sh[4 * i + 0] = v.x;
+                            sh[4 * i + 1] = v.y;
+                            sh[4 * i + 2] = v.z;
+                            sh[4 * i + 3] = v.w;
+                        }
+                    }
                 }
             }
-        } else {
+        } else if (vis) {
             const float* src = a.shs + (size_t)idx * a.M * 3;
 #pragma unroll
             for (int i = 0; i < 48; i++)
                 if (i < nf) sh[i] = __ldg(src + i);
         }
-        float c[3];
-        eval_sh(a.D, sh, dx, dy, dz, c);
-        uint8_t mask = 0;
-        if (c[0] < 0.f) mask |= 1;
-        if (c[1] < 0.f) mask |= 2;
-        if (c[2] < 0.f) mask |= 4;
-        a.clamped[idx] = mask;
-        a.rgb[idx] = make_float4(fmaxf(c[0], 0.f), fmaxf(c[1], 0.f), fmaxf(c[2], 0.f), 0.f);
+        if (vis) {
+            float dx = px - V[32], dy = py - V[33], dz = pz - V[34];
+            const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+            dx = dx / len;
+            dy = dy / len;
+            dz = dz / len;
+            float c[3];
+            eval_sh(a.D, sh, dx, dy, dz, c);
+            uint8_t mask = 0;
+            if (c[0] < 0.f) mask |= 1;
+            if (c[1] < 0.f) mask |= 2;
+            if (c[2] < 0.f) mask |= 4;
+            a.clamped[idx] = mask;
+            a.rgb[idx] = make_float4(fmaxf(c[0], 0.f), fmaxf(c[1], 0.f), fmaxf(c[2], 0.f), 0.f);
+        }
     }
 
-    a.depths[idx] = depth;
-    a.radii[idx] = radius;
-    a.means2D[idx] = make_float2(pix_x, pix_y);
-    a.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, __ldg(a.opacities + idx));
-    a.tiles_touched[idx] = tiles;
+    if (vis) {
+        a.depths[idx] = depth;
+        a.radii[idx] = radius;
+        a.means2D[idx] = make_float2(pix_x, pix_y);
+        a.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opacity);
+        a.tiles_touched[idx] = tiles;
+    }
 }
 
 int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
@@ -336,7 +393,17 @@ int launch_preprocess(int P, int D, int M, const float* means3D, const float* sc
     a.prefiltered = prefiltered ? 1 : 0;
     a.sh_vec4 = (shs != nullptr && M == 16 && (reinterpret_cast<uintptr_t>(shs) & 15u) == 0) ? 1 : 0;
     a.rot_vec4 = (rotations != nullptr && (reinterpret_cast<uintptr_t>(rotations) & 15u) == 0) ? 1 : 0;
-    preprocess_kernel<<<cdiv(P, 256), 256, 0, stream>>>(a);
+    {  // opt in to > 48 KB of dynamic shared memory, once per device
+        static bool configured[64] = {false};
+        int dev = 0;
+        HB_CUDA_OK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !configured[dev]) {
+            HB_CUDA_OK(cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            kPreSmemBytes));
+            if (dev >= 0 && dev < 64) configured[dev] = true;
+        }
+    }
+    preprocess_kernel<<<cdiv(P, kPreThreads), kPreThreads, a.sh_vec4 ? kPreSmemBytes : 0, stream>>>(a);
     HB_LAUNCH_OK("preprocess", stream, false);
     return 0;
 }

@@ -55,282 +55,375 @@ __device__ __forceinline__ void store_sh_grad(const PreBwdArgs& a, int idx, cons
     }
 }
 
-__global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdArgs a) {
+// SH backward for one Gaussian (backward.cu:20-139): dL/dsh row `gsh` (bands above the active degree are
+// zero) and the view-direction path of dL/dmean (dnormvdv, auxiliary.h:107-117), added to dmean_*.
+__device__ __forceinline__ void sh_backward(int deg, const float* sh, float ox, float oy, float oz, const float* dRGB,
+                                            float* gsh, float& dmean_x, float& dmean_y, float& dmean_z) {
+    const float inv_len = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
+    const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
+    float w[16];  // dRGB/dsh_k
+#pragma unroll
+    for (int k = 0; k < 16; k++) w[k] = 0.f;
+    float ddir_x = 0.f, ddir_y = 0.f, ddir_z = 0.f;  // dL/ddir
+    w[0] = HB_SH_C0;
+    if (deg > 0) {
+        w[1] = -HB_SH_C1 * y;
+        w[2] = HB_SH_C1 * z;
+        w[3] = -HB_SH_C1 * x;
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        if (deg > 1) {
+            w[4] = HB_SH_C2_0 * xy;
+            w[5] = HB_SH_C2_1 * yz;
+            w[6] = HB_SH_C2_2 * (2.f * zz - xx - yy);
+            w[7] = HB_SH_C2_3 * xz;
+            w[8] = HB_SH_C2_4 * (xx - yy);
+            if (deg > 2) {
+                w[9] = HB_SH_C3_0 * y * (3.f * xx - yy);
+                w[10] = HB_SH_C3_1 * xy * z;
+                w[11] = HB_SH_C3_2 * y * (4.f * zz - xx - yy);
+                w[12] = HB_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+                w[13] = HB_SH_C3_4 * x * (4.f * zz - xx - yy);
+                w[14] = HB_SH_C3_5 * z * (xx - yy);
+                w[15] = HB_SH_C3_6 * x * (xx - 3.f * yy);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            float dx_ = -HB_SH_C1 * sh[3 * 3 + c];
+            float dy_ = -HB_SH_C1 * sh[1 * 3 + c];
+            float dz_ = HB_SH_C1 * sh[2 * 3 + c];
+            if (deg > 1) {
+                dx_ += HB_SH_C2_0 * y * sh[4 * 3 + c] + HB_SH_C2_2 * 2.f * -x * sh[6 * 3 + c] +
+                       HB_SH_C2_3 * z * sh[7 * 3 + c] + HB_SH_C2_4 * 2.f * x * sh[8 * 3 + c];
+                dy_ += HB_SH_C2_0 * x * sh[4 * 3 + c] + HB_SH_C2_1 * z * sh[5 * 3 + c] +
+                       HB_SH_C2_2 * 2.f * -y * sh[6 * 3 + c] + HB_SH_C2_4 * 2.f * -y * sh[8 * 3 + c];
+                dz_ += HB_SH_C2_1 * y * sh[5 * 3 + c] + HB_SH_C2_2 * 2.f * 2.f * z * sh[6 * 3 + c] +
+                       HB_SH_C2_3 * x * sh[7 * 3 + c];
+                if (deg > 2) {
+                    dx_ += HB_SH_C3_0 * sh[9 * 3 + c] * 3.f * 2.f * xy + HB_SH_C3_1 * sh[10 * 3 + c] * yz +
+                           HB_SH_C3_2 * sh[11 * 3 + c] * -2.f * xy + HB_SH_C3_3 * sh[12 * 3 + c] * -3.f * 2.f * xz +
+                           HB_SH_C3_4 * sh[13 * 3 + c] * (-3.f * xx + 4.f * zz - yy) +
+                           HB_SH_C3_5 * sh[14 * 3 + c] * 2.f * xz + HB_SH_C3_6 * sh[15 * 3 + c] * 3.f * (xx - yy);
+                    dy_ += HB_SH_C3_0 * sh[9 * 3 + c] * 3.f * (xx - yy) + HB_SH_C3_1 * sh[10 * 3 + c] * xz +
+                           HB_SH_C3_2 * sh[11 * 3 + c] * (-3.f * yy + 4.f * zz - xx) +
+                           HB_SH_C3_3 * sh[12 * 3 + c] * -3.f * 2.f * yz + HB_SH_C3_4 * sh[13 * 3 + c] * -2.f * xy +
+                           HB_SH_C3_5 * sh[14 * 3 + c] * -2.f * yz + HB_SH_C3_6 * sh[15 * 3 + c] * -3.f * 2.f * xy;
+                    dz_ += HB_SH_C3_1 * sh[10 * 3 + c] * xy + HB_SH_C3_2 * sh[11 * 3 + c] * 4.f * 2.f * yz +
+                           HB_SH_C3_3 * sh[12 * 3 + c] * 3.f * (2.f * zz - xx - yy) +
+                           HB_SH_C3_4 * sh[13 * 3 + c] * 4.f * 2.f * xz + HB_SH_C3_5 * sh[14 * 3 + c] * (xx - yy);
+                }
+            }
+            ddir_x += dx_ * dRGB[c];
+            ddir_y += dy_ * dRGB[c];
+            ddir_z += dz_ * dRGB[c];
+        }
+    }
+    // dL/dsh[k][c] = w[k] * dRGB[c]; bands above the active degree have w == 0.
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        gsh[3 * k + 0] = w[k] * dRGB[0];
+        gsh[3 * k + 1] = w[k] * dRGB[1];
+        gsh[3 * k + 2] = w[k] * dRGB[2];
+    }
+    // dnormvdv (auxiliary.h:107-117): through the normalisation of the view direction.
+    const float sum2 = ox * ox + oy * oy + oz * oz;
+    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    dmean_x += ((sum2 - ox * ox) * ddir_x - oy * ox * ddir_y - oz * ox * ddir_z) * invsum32;
+    dmean_y += (-ox * oy * ddir_x + (sum2 - oy * oy) * ddir_y - oz * oy * ddir_z) * invsum32;
+    dmean_z += (-ox * oz * ddir_x - oy * oz * ddir_y + (sum2 - oz * oz) * ddir_z) * invsum32;
+}
+
+constexpr int kPbThreads = 256;
+constexpr int kPbRowBytes = 208;  // 192-B SH row padded to 52 words: conflict-free 128-bit row access
+constexpr int kPbSmemBytes = kPbThreads * kPbRowBytes;
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// One thread per Gaussian.  Memory behaviour (the stage is HBM bound: ~303 B read + 256 B written
+// per visible Gaussian, three quarters of it the SH row and its gradient):
+//   * visibility is known from `radii` at once, so the SH rows of the visible Gaussians of a warp
+//     are requested first thing with cp.async (global -> shared; the 32 rows of a warp are one
+//     contiguous 6 KB block, copy j of lane l moves its 16-byte word 32 j + l) and arrive while the
+//     covariance chain is being differentiated;
+//   * every other input of the Gaussian is requested before the arithmetic starts;
+//   * dL/dsh is assembled row by row in the same shared-memory slots and written by the whole warp
+//     as twelve 512-byte contiguous stores (zero rows for culled Gaussians included), instead of
+//     twelve 16-byte stores per thread at a 192-byte stride.
+__global__ void __launch_bounds__(kPbThreads, 2) preprocess_backward_kernel(const PreBwdArgs a) {
+    extern __shared__ __align__(16) unsigned char s_rows[];  // [256][208 B] SH rows / dL_dsh rows (vec4 path)
     __shared__ float s_cam[36];
     if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(a.view + threadIdx.x);
     else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(a.proj + threadIdx.x - 16);
     else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(a.campos + threadIdx.x - 32);
-    __syncthreads();
+
+    const int idx = blockIdx.x * kPbThreads + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const bool valid = idx < a.P;
+    const bool vis = valid && (__ldg(a.radii + idx) > 0);
+    const bool sh_out = (a.dL_dsh != nullptr && a.M > 0);
+    const int deg = a.D;
+    const int nf = 3 * (deg + 1) * (deg + 1);
+    const int nv = (nf + 3) >> 2;
+    const uint32_t s_warp = (uint32_t)__cvta_generic_to_shared(s_rows) + warp * 32u * kPbRowBytes;
+    const size_t warp_row0 = (size_t)blockIdx.x * kPbThreads + warp * 32u;
+    const unsigned alive = __ballot_sync(0xffffffffu, vis);
+
+    // ---- SH rows of the visible Gaussians of this warp: in flight from here on ------------------
+    if (a.sh_vec4 && a.shs != nullptr && alive != 0u) {
+        const float4* g_warp = reinterpret_cast<const float4*>(a.shs) + 12 * warp_row0;
+        unsigned row = lane / 12u, col = lane % 12u;  // 16-byte word 32 j + lane = (row, col)
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            if (((alive >> row) & 1u) && (int)col < nv)
+                cp_async16(s_warp + row * kPbRowBytes + col * 16u, g_warp + 32 * j + lane);
+            col += 8u;
+            row += 2u;
+            if (col >= 12u) {
+                col -= 12u;
+                row += 1u;
+            }
+        }
+    }
+    __syncthreads();  // s_cam
     const float* V = s_cam;
     const float* Pm = s_cam + 16;
 
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
-
     float* out_mean = a.dL_dmean3D + 3 * (size_t)idx;
     float* out_cov = a.dL_dcov3D + 6 * (size_t)idx;
+    const bool has_scale = (a.cov3D_precomp == nullptr);
 
-    if (!(__ldg(a.radii + idx) > 0)) {
+    if (valid && !vis) {
         out_mean[0] = out_mean[1] = out_mean[2] = 0.f;
 #pragma unroll
         for (int i = 0; i < 6; i++) out_cov[i] = 0.f;
-        if (a.dL_dsh != nullptr && a.M > 0) {
-            float z[48];
-#pragma unroll
-            for (int i = 0; i < 48; i++) z[i] = 0.f;
-            store_sh_grad(a, idx, z);
-        }
         if (a.dL_dscale != nullptr) {
             a.dL_dscale[3 * (size_t)idx + 0] = 0.f;
             a.dL_dscale[3 * (size_t)idx + 1] = 0.f;
             a.dL_dscale[3 * (size_t)idx + 2] = 0.f;
         }
         if (a.dL_drot != nullptr) reinterpret_cast<float4*>(a.dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-        return;
     }
 
-    const float mx = __ldg(a.means3D + 3 * (size_t)idx + 0);
-    const float my = __ldg(a.means3D + 3 * (size_t)idx + 1);
-    const float mz = __ldg(a.means3D + 3 * (size_t)idx + 2);
-
-    // ---- scale / rotation -> M, Sigma (forward.cu:118-152) ----------------------------------
-    const bool has_scale = (a.cov3D_precomp == nullptr);
-    float cov3[6];
+    // state that crosses the cooperative SH phase
+    float mx = 0.f, my = 0.f, mz = 0.f;
+    float dmean_x = 0.f, dmean_y = 0.f, dmean_z = 0.f;
+    float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float sx = 0.f, sy = 0.f, sz = 0.f, qr = 0.f, qx = 0.f, qy = 0.f, qz = 0.f;
-    float R[3][3];  // R[c][r], glm column-major
-    if (has_scale) {
-        sx = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 0);
-        sy = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 1);
-        sz = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 2);
-        qr = __ldg(a.rotations + 4 * (size_t)idx + 0);
-        qx = __ldg(a.rotations + 4 * (size_t)idx + 1);
-        qy = __ldg(a.rotations + 4 * (size_t)idx + 2);
-        qz = __ldg(a.rotations + 4 * (size_t)idx + 3);
-        R[0][0] = 1.f - 2.f * (qy * qy + qz * qz);
-        R[0][1] = 2.f * (qx * qy - qr * qz);
-        R[0][2] = 2.f * (qx * qz + qr * qy);
-        R[1][0] = 2.f * (qx * qy + qr * qz);
-        R[1][1] = 1.f - 2.f * (qx * qx + qz * qz);
-        R[1][2] = 2.f * (qy * qz - qr * qx);
-        R[2][0] = 2.f * (qx * qz - qr * qy);
-        R[2][1] = 2.f * (qy * qz + qr * qx);
-        R[2][2] = 1.f - 2.f * (qx * qx + qy * qy);
-        const float s[3] = {sx, sy, sz};
-        float Mm[3][3];
-#pragma unroll
-        for (int c = 0; c < 3; c++)
-#pragma unroll
-            for (int r = 0; r < 3; r++) Mm[c][r] = s[r] * R[c][r];
-        cov3[0] = Mm[0][0] * Mm[0][0] + Mm[0][1] * Mm[0][1] + Mm[0][2] * Mm[0][2];
-        cov3[1] = Mm[0][0] * Mm[1][0] + Mm[0][1] * Mm[1][1] + Mm[0][2] * Mm[1][2];
-        cov3[2] = Mm[0][0] * Mm[2][0] + Mm[0][1] * Mm[2][1] + Mm[0][2] * Mm[2][2];
-        cov3[3] = Mm[1][0] * Mm[1][0] + Mm[1][1] * Mm[1][1] + Mm[1][2] * Mm[1][2];
-        cov3[4] = Mm[1][0] * Mm[2][0] + Mm[1][1] * Mm[2][1] + Mm[1][2] * Mm[2][2];
-        cov3[5] = Mm[2][0] * Mm[2][0] + Mm[2][1] * Mm[2][1] + Mm[2][2] * Mm[2][2];
-    } else {
-#pragma unroll
-        for (int i = 0; i < 6; i++) cov3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
-    }
+    float R[3][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};  // R[c][r], glm column-major
+    float dRGB[3] = {0.f, 0.f, 0.f};
 
-    // ---- cov2D backward (backward.cu:144-274) -------------------------------------------------
-    const float4 dconic4 = __ldg(reinterpret_cast<const float4*>(a.dL_dconic) + idx);
-    const float dcon_x = dconic4.x, dcon_y = dconic4.y, dcon_z = dconic4.w;
-    float tx = V[0] * mx + V[4] * my + V[8] * mz + V[12];
-    float ty = V[1] * mx + V[5] * my + V[9] * mz + V[13];
-    const float tz = V[2] * mx + V[6] * my + V[10] * mz + V[14];
-    const float limx = 1.3f * a.tan_fovx;
-    const float limy = 1.3f * a.tan_fovy;
-    const float txtz = tx / tz;
-    const float tytz = ty / tz;
-    tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
-    ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
-    const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
-    const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
-    const float hx = a.focal_x, hy = a.focal_y;
-    const float J00 = hx / tz, J02 = -(hx * tx) / (tz * tz);
-    const float J11 = hy / tz, J12 = -(hy * ty) / (tz * tz);
-    // T = W J, T[c][r]; third column is zero.
-    const float T00 = V[0] * J00 + V[2] * J02, T01 = V[4] * J00 + V[6] * J02, T02 = V[8] * J00 + V[10] * J02;
-    const float T10 = V[1] * J11 + V[2] * J12, T11 = V[5] * J11 + V[6] * J12, T12 = V[9] * J11 + V[10] * J12;
-    const float V00 = cov3[0], V01 = cov3[1], V02 = cov3[2], V11 = cov3[3], V12 = cov3[4], V22 = cov3[5];
-    // rows of T times Vrk (used by both cov2D and dL/dT)
-    const float TV00 = T00 * V00 + T01 * V01 + T02 * V02;
-    const float TV01 = T00 * V01 + T01 * V11 + T02 * V12;
-    const float TV02 = T00 * V02 + T01 * V12 + T02 * V22;
-    const float TV10 = T10 * V00 + T11 * V01 + T12 * V02;
-    const float TV11 = T10 * V01 + T11 * V11 + T12 * V12;
-    const float TV12 = T10 * V02 + T11 * V12 + T12 * V22;
-    const float ca = TV00 * T00 + TV01 * T01 + TV02 * T02 + 0.3f;
-    const float cb = TV10 * T00 + TV11 * T01 + TV12 * T02;
-    const float cc = TV10 * T10 + TV11 * T11 + TV12 * T12 + 0.3f;
-
-    const float denom = ca * cc - cb * cb;
-    float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
-    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-    float dcov[6];
-    if (denom2inv != 0.f) {
-        dL_da = denom2inv * (-cc * cc * dcon_x + 2.f * cb * cc * dcon_y + (denom - ca * cc) * dcon_z);
-        dL_dc = denom2inv * (-ca * ca * dcon_z + 2.f * ca * cb * dcon_y + (denom - ca * cc) * dcon_x);
-        dL_db = denom2inv * 2.f * (cb * cc * dcon_x - (denom + 2.f * cb * cb) * dcon_y + ca * cb * dcon_z);
-        dcov[0] = T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc;
-        dcov[3] = T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc;
-        dcov[5] = T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc;
-        dcov[1] = 2.f * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2.f * T10 * T11 * dL_dc;
-        dcov[2] = 2.f * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2.f * T10 * T12 * dL_dc;
-        dcov[4] = 2.f * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2.f * T11 * T12 * dL_dc;
-    } else {
-#pragma unroll
-        for (int i = 0; i < 6; i++) dcov[i] = 0.f;
-    }
-#pragma unroll
-    for (int i = 0; i < 6; i++) out_cov[i] = dcov[i];
-
-    const float dL_dT00 = 2.f * TV00 * dL_da + TV10 * dL_db;
-    const float dL_dT01 = 2.f * TV01 * dL_da + TV11 * dL_db;
-    const float dL_dT02 = 2.f * TV02 * dL_da + TV12 * dL_db;
-    const float dL_dT10 = 2.f * TV10 * dL_dc + TV00 * dL_db;
-    const float dL_dT11 = 2.f * TV11 * dL_dc + TV01 * dL_db;
-    const float dL_dT12 = 2.f * TV12 * dL_dc + TV02 * dL_db;
-    const float dL_dJ00 = V[0] * dL_dT00 + V[4] * dL_dT01 + V[8] * dL_dT02;
-    const float dL_dJ02 = V[2] * dL_dT00 + V[6] * dL_dT01 + V[10] * dL_dT02;
-    const float dL_dJ11 = V[1] * dL_dT10 + V[5] * dL_dT11 + V[9] * dL_dT12;
-    const float dL_dJ12 = V[2] * dL_dT10 + V[6] * dL_dT11 + V[10] * dL_dT12;
-    const float itz = 1.f / tz;
-    const float itz2 = itz * itz;
-    const float itz3 = itz2 * itz;
-    const float dL_dtx = x_grad_mul * -hx * itz2 * dL_dJ02;
-    const float dL_dty = y_grad_mul * -hy * itz2 * dL_dJ12;
-    const float dL_dtz = -hx * itz2 * dL_dJ00 - hy * itz2 * dL_dJ11 + (2.f * hx * tx) * itz3 * dL_dJ02 +
-                         (2.f * hy * ty) * itz3 * dL_dJ12;
-    // transformVec4x3Transpose
-    float dmean_x = V[0] * dL_dtx + V[1] * dL_dty + V[2] * dL_dtz;
-    float dmean_y = V[4] * dL_dtx + V[5] * dL_dty + V[6] * dL_dtz;
-    float dmean_z = V[8] * dL_dtx + V[9] * dL_dty + V[10] * dL_dtz;
-
-    // ---- projection path (backward.cu:370-387) ---------------------------------------------
-    {
-        const float m_hw = Pm[3] * mx + Pm[7] * my + Pm[11] * mz + Pm[15];
-        const float m_w = 1.0f / (m_hw + 0.0000001f);
-        const float mul1 = (Pm[0] * mx + Pm[4] * my + Pm[8] * mz + Pm[12]) * m_w * m_w;
-        const float mul2 = (Pm[1] * mx + Pm[5] * my + Pm[9] * mz + Pm[13]) * m_w * m_w;
+    if (vis) {
+        // ---- every other per-Gaussian input, requested before the arithmetic ------------------
+        mx = __ldg(a.means3D + 3 * (size_t)idx + 0);
+        my = __ldg(a.means3D + 3 * (size_t)idx + 1);
+        mz = __ldg(a.means3D + 3 * (size_t)idx + 2);
+        const float4 dconic4 = __ldg(reinterpret_cast<const float4*>(a.dL_dconic) + idx);
         const float g2x = __ldg(a.dL_dmean2D + 3 * (size_t)idx + 0);
         const float g2y = __ldg(a.dL_dmean2D + 3 * (size_t)idx + 1);
-        dmean_x += (Pm[0] * m_w - Pm[3] * mul1) * g2x + (Pm[1] * m_w - Pm[3] * mul2) * g2y;
-        dmean_y += (Pm[4] * m_w - Pm[7] * mul1) * g2x + (Pm[5] * m_w - Pm[7] * mul2) * g2y;
-        dmean_z += (Pm[8] * m_w - Pm[11] * mul1) * g2x + (Pm[9] * m_w - Pm[11] * mul2) * g2y;
+        if (a.shs != nullptr) {
+            const uint8_t cl = __ldg(a.clamped + idx);
+            const float c0 = __ldg(a.dL_dcolor + 3 * (size_t)idx + 0);
+            const float c1 = __ldg(a.dL_dcolor + 3 * (size_t)idx + 1);
+            const float c2 = __ldg(a.dL_dcolor + 3 * (size_t)idx + 2);
+            dRGB[0] = (cl & 1) ? 0.f : c0;
+            dRGB[1] = (cl & 2) ? 0.f : c1;
+            dRGB[2] = (cl & 4) ? 0.f : c2;
+        }
+        float cov3[6];
+        if (has_scale) {
+            sx = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 0);
+            sy = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 1);
+            sz = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 2);
+            qr = __ldg(a.rotations + 4 * (size_t)idx + 0);
+            qx = __ldg(a.rotations + 4 * (size_t)idx + 1);
+            qy = __ldg(a.rotations + 4 * (size_t)idx + 2);
+            qz = __ldg(a.rotations + 4 * (size_t)idx + 3);
+            R[0][0] = 1.f - 2.f * (qy * qy + qz * qz);
+            R[0][1] = 2.f * (qx * qy - qr * qz);
+            R[0][2] = 2.f * (qx * qz + qr * qy);
+            R[1][0] = 2.f * (qx * qy + qr * qz);
+            R[1][1] = 1.f - 2.f * (qx * qx + qz * qz);
+            R[1][2] = 2.f * (qy * qz - qr * qx);
+            R[2][0] = 2.f * (qx * qz - qr * qy);
+            R[2][1] = 2.f * (qy * qz + qr * qx);
+            R[2][2] = 1.f - 2.f * (qx * qx + qy * qy);
+            const float s[3] = {sx, sy, sz};
+            float Mm[3][3];
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+#pragma unroll
+                for (int r = 0; r < 3; r++) Mm[c][r] = s[r] * R[c][r];
+            cov3[0] = Mm[0][0] * Mm[0][0] + Mm[0][1] * Mm[0][1] + Mm[0][2] * Mm[0][2];
+            cov3[1] = Mm[0][0] * Mm[1][0] + Mm[0][1] * Mm[1][1] + Mm[0][2] * Mm[1][2];
+            cov3[2] = Mm[0][0] * Mm[2][0] + Mm[0][1] * Mm[2][1] + Mm[0][2] * Mm[2][2];
+            cov3[3] = Mm[1][0] * Mm[1][0] + Mm[1][1] * Mm[1][1] + Mm[1][2] * Mm[1][2];
+            cov3[4] = Mm[1][0] * Mm[2][0] + Mm[1][1] * Mm[2][1] + Mm[1][2] * Mm[2][2];
+            cov3[5] = Mm[2][0] * Mm[2][0] + Mm[2][1] * Mm[2][1] + Mm[2][2] * Mm[2][2];
+        } else {
+#pragma unroll
+            for (int i = 0; i < 6; i++) cov3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
+        }
+
+        // ---- cov2D backward (backward.cu:144-274) -------------------------------------------------
+        const float dcon_x = dconic4.x, dcon_y = dconic4.y, dcon_z = dconic4.w;
+        float tx = V[0] * mx + V[4] * my + V[8] * mz + V[12];
+        float ty = V[1] * mx + V[5] * my + V[9] * mz + V[13];
+        const float tz = V[2] * mx + V[6] * my + V[10] * mz + V[14];
+        const float limx = 1.3f * a.tan_fovx;
+        const float limy = 1.3f * a.tan_fovy;
+        const float txtz = tx / tz;
+        const float tytz = ty / tz;
+        tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+        ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+        const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+        const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+        const float hx = a.focal_x, hy = a.focal_y;
+        const float J00 = hx / tz, J02 = -(hx * tx) / (tz * tz);
+        const float J11 = hy / tz, J12 = -(hy * ty) / (tz * tz);
+        // T = W J, T[c][r]; third column is zero.
+        const float T00 = V[0] * J00 + V[2] * J02, T01 = V[4] * J00 + V[6] * J02, T02 = V[8] * J00 + V[10] * J02;
+        const float T10 = V[1] * J11 + V[2] * J12, T11 = V[5] * J11 + V[6] * J12, T12 = V[9] * J11 + V[10] * J12;
+        const float V00 = cov3[0], V01 = cov3[1], V02 = cov3[2], V11 = cov3[3], V12 = cov3[4], V22 = cov3[5];
+        // rows of T times Vrk (used by both cov2D and dL/dT)
+        const float TV00 = T00 * V00 + T01 * V01 + T02 * V02;
+        const float TV01 = T00 * V01 + T01 * V11 + T02 * V12;
+        const float TV02 = T00 * V02 + T01 * V12 + T02 * V22;
+        const float TV10 = T10 * V00 + T11 * V01 + T12 * V02;
+        const float TV11 = T10 * V01 + T11 * V11 + T12 * V12;
+        const float TV12 = T10 * V02 + T11 * V12 + T12 * V22;
+        const float ca = TV00 * T00 + TV01 * T01 + TV02 * T02 + 0.3f;
+        const float cb = TV10 * T00 + TV11 * T01 + TV12 * T02;
+        const float cc = TV10 * T10 + TV11 * T11 + TV12 * T12 + 0.3f;
+
+        const float denom = ca * cc - cb * cb;
+        float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        if (denom2inv != 0.f) {
+            dL_da = denom2inv * (-cc * cc * dcon_x + 2.f * cb * cc * dcon_y + (denom - ca * cc) * dcon_z);
+            dL_dc = denom2inv * (-ca * ca * dcon_z + 2.f * ca * cb * dcon_y + (denom - ca * cc) * dcon_x);
+            dL_db = denom2inv * 2.f * (cb * cc * dcon_x - (denom + 2.f * cb * cb) * dcon_y + ca * cb * dcon_z);
+            dcov[0] = T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc;
+            dcov[3] = T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc;
+            dcov[5] = T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc;
+            dcov[1] = 2.f * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2.f * T10 * T11 * dL_dc;
+            dcov[2] = 2.f * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2.f * T10 * T12 * dL_dc;
+            dcov[4] = 2.f * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2.f * T11 * T12 * dL_dc;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 6; i++) dcov[i] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 6; i++) out_cov[i] = dcov[i];
+
+        const float dL_dT00 = 2.f * TV00 * dL_da + TV10 * dL_db;
+        const float dL_dT01 = 2.f * TV01 * dL_da + TV11 * dL_db;
+        const float dL_dT02 = 2.f * TV02 * dL_da + TV12 * dL_db;
+        const float dL_dT10 = 2.f * TV10 * dL_dc + TV00 * dL_db;
+        const float dL_dT11 = 2.f * TV11 * dL_dc + TV01 * dL_db;
+        const float dL_dT12 = 2.f * TV12 * dL_dc + TV02 * dL_db;
+        const float dL_dJ00 = V[0] * dL_dT00 + V[4] * dL_dT01 + V[8] * dL_dT02;
+        const float dL_dJ02 = V[2] * dL_dT00 + V[6] * dL_dT01 + V[10] * dL_dT02;
+        const float dL_dJ11 = V[1] * dL_dT10 + V[5] * dL_dT11 + V[9] * dL_dT12;
+        const float dL_dJ12 = V[2] * dL_dT10 + V[6] * dL_dT11 + V[10] * dL_dT12;
+        const float itz = 1.f / tz;
+        const float itz2 = itz * itz;
+        const float itz3 = itz2 * itz;
+        const float dL_dtx = x_grad_mul * -hx * itz2 * dL_dJ02;
+        const float dL_dty = y_grad_mul * -hy * itz2 * dL_dJ12;
+        const float dL_dtz = -hx * itz2 * dL_dJ00 - hy * itz2 * dL_dJ11 + (2.f * hx * tx) * itz3 * dL_dJ02 +
+                             (2.f * hy * ty) * itz3 * dL_dJ12;
+        // transformVec4x3Transpose
+        dmean_x = V[0] * dL_dtx + V[1] * dL_dty + V[2] * dL_dtz;
+        dmean_y = V[4] * dL_dtx + V[5] * dL_dty + V[6] * dL_dtz;
+        dmean_z = V[8] * dL_dtx + V[9] * dL_dty + V[10] * dL_dtz;
+
+        // ---- projection path (backward.cu:370-387) ---------------------------------------------
+        {
+            const float m_hw = Pm[3] * mx + Pm[7] * my + Pm[11] * mz + Pm[15];
+            const float m_w = 1.0f / (m_hw + 0.0000001f);
+            const float mul1 = (Pm[0] * mx + Pm[4] * my + Pm[8] * mz + Pm[12]) * m_w * m_w;
+            const float mul2 = (Pm[1] * mx + Pm[5] * my + Pm[9] * mz + Pm[13]) * m_w * m_w;
+            dmean_x += (Pm[0] * m_w - Pm[3] * mul1) * g2x + (Pm[1] * m_w - Pm[3] * mul2) * g2y;
+            dmean_y += (Pm[4] * m_w - Pm[7] * mul1) * g2x + (Pm[5] * m_w - Pm[7] * mul2) * g2y;
+            dmean_z += (Pm[8] * m_w - Pm[11] * mul1) * g2x + (Pm[9] * m_w - Pm[11] * mul2) * g2y;
+        }
     }
 
     // ---- SH backward (backward.cu:20-139) ------------------------------------------------------
-    if (a.shs != nullptr) {
-        const float ox = mx - V[32], oy = my - V[33], oz = mz - V[34];
-        const float inv_len = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
-        const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
-        const int deg = a.D;
-        const int nf = 3 * (deg + 1) * (deg + 1);
-        float sh[48];
-        if (a.sh_vec4) {
-            const float4* src = reinterpret_cast<const float4*>(a.shs) + 12 * (size_t)idx;
-            const int nv = (nf + 3) >> 2;
+    float gsh[48];
+    bool have_gsh = false;  // gsh holds this Gaussian's dL/dsh row (non-vec4 path stores it itself)
+    if (a.sh_vec4 && sh_out) {
+        // cooperative path: rows in shared memory
+        if (a.shs != nullptr) cp_async_wait_all();
+        __syncwarp();
+        const uint32_t mine = s_warp + lane * kPbRowBytes;
+        if (vis && a.shs != nullptr) {
+            float sh[48];
 #pragma unroll
             for (int i = 0; i < 12; i++) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (i < nv) v = __ldg(src + i);
+                if (i < nv) v = lds128(mine + 16u * i);
                 sh[4 * i + 0] = v.x;
                 sh[4 * i + 1] = v.y;
                 sh[4 * i + 2] = v.z;
                 sh[4 * i + 3] = v.w;
             }
+            sh_backward(deg, sh, mx - V[32], my - V[33], mz - V[34], dRGB, gsh, dmean_x, dmean_y, dmean_z);
+#pragma unroll
+            for (int i = 0; i < 12; i++) sts128(mine + 16u * i, gsh[4 * i], gsh[4 * i + 1], gsh[4 * i + 2], gsh[4 * i + 3]);
         } else {
+#pragma unroll
+            for (int i = 0; i < 12; i++) sts128(mine + 16u * i, 0.f, 0.f, 0.f, 0.f);
+        }
+        __syncwarp();
+        float4* g_out = reinterpret_cast<float4*>(a.dL_dsh) + 12 * warp_row0;
+        const long long rows_left = (long long)a.P - (long long)warp_row0;  // rows of this warp inside [0, P)
+        unsigned row = lane / 12u, col = lane % 12u;
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            if ((long long)row < rows_left) {
+                const float4 v = lds128(s_warp + row * kPbRowBytes + col * 16u);
+                g_out[32 * j + lane] = v;
+            }
+            col += 8u;
+            row += 2u;
+            if (col >= 12u) {
+                col -= 12u;
+                row += 1u;
+            }
+        }
+    } else if (valid) {
+        if (vis && a.shs != nullptr) {
+            float sh[48];
             const float* src = a.shs + (size_t)idx * a.M * 3;
 #pragma unroll
             for (int i = 0; i < 48; i++) sh[i] = (i < nf) ? __ldg(src + i) : 0.f;
+            sh_backward(deg, sh, mx - V[32], my - V[33], mz - V[34], dRGB, gsh, dmean_x, dmean_y, dmean_z);
+            have_gsh = true;
         }
-        const uint8_t cl = __ldg(a.clamped + idx);
-        float dRGB[3];
-        dRGB[0] = (cl & 1) ? 0.f : __ldg(a.dL_dcolor + 3 * (size_t)idx + 0);
-        dRGB[1] = (cl & 2) ? 0.f : __ldg(a.dL_dcolor + 3 * (size_t)idx + 1);
-        dRGB[2] = (cl & 4) ? 0.f : __ldg(a.dL_dcolor + 3 * (size_t)idx + 2);
-
-        float w[16];  // dRGB/dsh_k
+        if (sh_out) {
+            if (!have_gsh) {
 #pragma unroll
-        for (int k = 0; k < 16; k++) w[k] = 0.f;
-        float ddir_x = 0.f, ddir_y = 0.f, ddir_z = 0.f;  // dL/ddir
-        w[0] = HB_SH_C0;
-        if (deg > 0) {
-            w[1] = -HB_SH_C1 * y;
-            w[2] = HB_SH_C1 * z;
-            w[3] = -HB_SH_C1 * x;
-            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-            if (deg > 1) {
-                w[4] = HB_SH_C2_0 * xy;
-                w[5] = HB_SH_C2_1 * yz;
-                w[6] = HB_SH_C2_2 * (2.f * zz - xx - yy);
-                w[7] = HB_SH_C2_3 * xz;
-                w[8] = HB_SH_C2_4 * (xx - yy);
-                if (deg > 2) {
-                    w[9] = HB_SH_C3_0 * y * (3.f * xx - yy);
-                    w[10] = HB_SH_C3_1 * xy * z;
-                    w[11] = HB_SH_C3_2 * y * (4.f * zz - xx - yy);
-                    w[12] = HB_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
-                    w[13] = HB_SH_C3_4 * x * (4.f * zz - xx - yy);
-                    w[14] = HB_SH_C3_5 * z * (xx - yy);
-                    w[15] = HB_SH_C3_6 * x * (xx - 3.f * yy);
-                }
+                for (int i = 0; i < 48; i++) gsh[i] = 0.f;
             }
-#pragma unroll
-            for (int c = 0; c < 3; c++) {
-                float dx_ = -HB_SH_C1 * sh[3 * 3 + c];
-                float dy_ = -HB_SH_C1 * sh[1 * 3 + c];
-                float dz_ = HB_SH_C1 * sh[2 * 3 + c];
-                if (deg > 1) {
-                    dx_ += HB_SH_C2_0 * y * sh[4 * 3 + c] + HB_SH_C2_2 * 2.f * -x * sh[6 * 3 + c] +
-                           HB_SH_C2_3 * z * sh[7 * 3 + c] + HB_SH_C2_4 * 2.f * x * sh[8 * 3 + c];
-                    dy_ += HB_SH_C2_0 * x * sh[4 * 3 + c] + HB_SH_C2_1 * z * sh[5 * 3 + c] +
-                           HB_SH_C2_2 * 2.f * -y * sh[6 * 3 + c] + HB_SH_C2_4 * 2.f * -y * sh[8 * 3 + c];
-                    dz_ += HB_SH_C2_1 * y * sh[5 * 3 + c] + HB_SH_C2_2 * 2.f * 2.f * z * sh[6 * 3 + c] +
-                           HB_SH_C2_3 * x * sh[7 * 3 + c];
-                    if (deg > 2) {
-                        dx_ += HB_SH_C3_0 * sh[9 * 3 + c] * 3.f * 2.f * xy + HB_SH_C3_1 * sh[10 * 3 + c] * yz +
-                               HB_SH_C3_2 * sh[11 * 3 + c] * -2.f * xy + HB_SH_C3_3 * sh[12 * 3 + c] * -3.f * 2.f * xz +
-                               HB_SH_C3_4 * sh[13 * 3 + c] * (-3.f * xx + 4.f * zz - yy) +
-                               HB_SH_C3_5 * sh[14 * 3 + c] * 2.f * xz + HB_SH_C3_6 * sh[15 * 3 + c] * 3.f * (xx - yy);
-                        dy_ += HB_SH_C3_0 * sh[9 * 3 + c] * 3.f * (xx - yy) + HB_SH_C3_1 * sh[10 * 3 + c] * xz +
-                               HB_SH_C3_2 * sh[11 * 3 + c] * (-3.f * yy + 4.f * zz - xx) +
-                               HB_SH_C3_3 * sh[12 * 3 + c] * -3.f * 2.f * yz + HB_SH_C3_4 * sh[13 * 3 + c] * -2.f * xy +
-                               HB_SH_C3_5 * sh[14 * 3 + c] * -2.f * yz + HB_SH_C3_6 * sh[15 * 3 + c] * -3.f * 2.f * xy;
-                        dz_ += HB_SH_C3_1 * sh[10 * 3 + c] * xy + HB_SH_C3_2 * sh[11 * 3 + c] * 4.f * 2.f * yz +
-                               HB_SH_C3_3 * sh[12 * 3 + c] * 3.f * (2.f * zz - xx - yy) +
-                               HB_SH_C3_4 * sh[13 * 3 + c] * 4.f * 2.f * xz + HB_SH_C3_5 * sh[14 * 3 + c] * (xx - yy);
-                    }
-                }
-                ddir_x += dx_ * dRGB[c];
-                ddir_y += dy_ * dRGB[c];
-                ddir_z += dz_ * dRGB[c];
-            }
+            store_sh_grad(a, idx, gsh);
         }
-        // dL/dsh[k][c] = w[k] * dRGB[c]; bands above the active degree have w == 0.
-        float gsh[48];
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            gsh[3 * k + 0] = w[k] * dRGB[0];
-            gsh[3 * k + 1] = w[k] * dRGB[1];
-            gsh[3 * k + 2] = w[k] * dRGB[2];
-        }
-        store_sh_grad(a, idx, gsh);
-
-        // dnormvdv (auxiliary.h:107-117): through the normalisation of the view direction.
-        const float sum2 = ox * ox + oy * oy + oz * oz;
-        const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
-        dmean_x += ((sum2 - ox * ox) * ddir_x - oy * ox * ddir_y - oz * ox * ddir_z) * invsum32;
-        dmean_y += (-ox * oy * ddir_x + (sum2 - oy * oy) * ddir_y - oz * oy * ddir_z) * invsum32;
-        dmean_z += (-ox * oz * ddir_x - oy * oz * ddir_y + (sum2 - oz * oz) * ddir_z) * invsum32;
-    } else if (a.dL_dsh != nullptr && a.M > 0) {
-        float z[48];
-#pragma unroll
-        for (int i = 0; i < 48; i++) z[i] = 0.f;
-        store_sh_grad(a, idx, z);
     }
 
+    if (!vis) return;
     out_mean[0] = dmean_x;
     out_mean[1] = dmean_y;
     out_mean[2] = dmean_z;
@@ -433,7 +526,17 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
         set_error("preprocess_backward: need scales+rotations or cov3D_precomp");
         return -1;
     }
-    preprocess_backward_kernel<<<cdiv(P, 256), 256, 0, stream>>>(a);
+    {  // opt in to > 48 KB of dynamic shared memory, once per device
+        static bool configured[64] = {false};
+        int dev = 0;
+        HB_CUDA_OK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !configured[dev]) {
+            HB_CUDA_OK(cudaFuncSetAttribute(preprocess_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            kPbSmemBytes));
+            if (dev >= 0 && dev < 64) configured[dev] = true;
+        }
+    }
+    preprocess_backward_kernel<<<cdiv(P, kPbThreads), kPbThreads, a.sh_vec4 ? kPbSmemBytes : 0, stream>>>(a);
     HB_LAUNCH_OK("preprocess_backward", stream, false);
     return 0;
 }

@@ -73,7 +73,18 @@ __device__ __forceinline__ void warp_reduce9_store(const float (&v)[9], uint32_t
         asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst + 4u * slot), "f"(r) : "memory");
 }
 
-__global__ void __launch_bounds__(kBlendThreads)
+__device__ __forceinline__ float ex2_ftz(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_ftz(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__global__ void __launch_bounds__(kBlendThreads, 5)
     render_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                            int grid_x, const float* __restrict__ bg, const float2* __restrict__ means2D,
                            const float4* __restrict__ conic_opacity, const float* __restrict__ colors,
@@ -187,12 +198,15 @@ __global__ void __launch_bounds__(kBlendThreads)
                 const float dx = g0.x - pixfx;
                 const float dy = g0.y - pixfy;
                 const float power = -0.5f * (g0.z * dx * dx + g1.x * dy * dy) - g0.w * dx * dy;
-                const float G = __expf(fminf(power, 0.f));  // clamp: a lane outside the footprint must not make inf
+                // clamp: a lane outside the footprint must not make inf.  ex2 / rcp are the bare
+                // special-function instructions (flush-to-zero forms: no denormal fix-up code; 1 - alpha
+                // >= 0.01 and a G that underflows belongs to a lane that is not hit).
+                const float G = ex2_ftz(fminf(power, 0.f) * 1.4426950408889634f);
                 const float alpha = fminf(0.99f, g1.y * G);
                 // Skip if this one is behind the last contributor of this pixel, or was skipped by it
                 // in the forward pass (backward.cu:486-501).
                 const bool hit = ((uint32_t)(pb + e) < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                const float rcp = __fdividef(1.f, 1.f - alpha);
+                const float rcp = rcp_ftz(1.f - alpha);
                 if (hit) {
                     T *= rcp;
                     accum0 = fmaf(last_alpha, last_c0 - accum0, accum0);
