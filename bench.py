@@ -141,10 +141,13 @@ def make_workload(name, rank, world, device, views=1):
 
     n_human, n_scene, W, H, focal = WORKLOADS[name]
     n_views = max(world, 1) * views
-    cams = [synth.make_camera(W, H, focal, view=rank * views + v, n_views=n_views, seed=SEED) for v in range(views)]
+    # round-robin split of the step's view batch (hugs_b200.dp.shard_views): every rank gets the same
+    # mix of orbit positions, so the ranks' pair counts -- and step times -- stay balanced
+    mine = [v * max(world, 1) + rank for v in range(views)]
+    cams = [synth.make_camera(W, H, focal, view=i, n_views=n_views, seed=SEED) for i in mine]
     h = synth.make_human_gaussians(n_human, seed=SEED + 1)
-    As = [synth.make_joint_transforms(1, SEED + 100 + rank * views + v)[0] for v in range(views)]
-    Gs = [synth.make_dL_dcolor(W, H, SEED + rank * views + v) for v in range(views)]
+    As = [synth.make_joint_transforms(1, SEED + 100 + i)[0] for i in mine]
+    Gs = [synth.make_dL_dcolor(W, H, SEED + i) for i in mine]
     parts = dict(human=h, A=As[0], cam=cams[0], G=Gs[0], As=As, cams=cams, Gs=Gs, W=W, H=H, n_human=n_human,
                  n_scene=n_scene)
     if n_scene > 0:
@@ -157,7 +160,7 @@ def make_workload(name, rank, world, device, views=1):
 class Replica:
     """Device-resident parameter replica + the per-frame inputs, and the frame step itself."""
 
-    def __init__(self, wl, device, module, lbs_impl):
+    def __init__(self, wl, device, module, lbs_impl, sh_sink=False):
         self.device = device
         self.module = module      # a diff_gaussian_rasterization-shaped module (ours or the reference)
         self.lbs_impl = lbs_impl  # callable(A, xyz, w, rotmat, scales, transl) -> (xyz', rotq, scales')
@@ -180,6 +183,13 @@ class Replica:
         self.opacity = leaf(torch.cat(opac))
         self.shs = leaf(torch.cat(shs))
         self.P = self.opacity.shape[0]
+        # our arm: every view's SH gradient (81 % of the gradient bytes) is accumulated by the backward
+        # kernel itself, in the buffer the allreduce then works on (hugs_b200.ShGradSink)
+        self.sh_sink = None
+        if sh_sink:
+            import hugs_b200
+            self.sh_sink = hugs_b200.attach_sh_grad_sink(self.shs)
+        self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
         self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=True)
         self.transl = d(h["transl"][0])
         # per-frame inputs: pinned host copies (for e2e) and resident device copies (for value)
@@ -213,8 +223,11 @@ class Replica:
         return {n: getattr(self, n) for n in names if getattr(self, n) is not None}
 
     def zero_grad(self):
-        for p in self.leaves().values():
-            p.grad = None
+        for n, p in self.leaves().items():
+            if n == "shs" and self.sh_sink is not None:
+                self.sh_sink.reset()  # the next backward pass overwrites the sink buffer
+            else:
+                p.grad = None
         self.means2D.grad = None
 
     def frame(self, inp):
@@ -298,6 +311,9 @@ class Replica:
         # Two collectives: the SH gradient (81 % of the bytes) in place, everything else through one
         # flat buffer (a collective per small tensor costs more in launch latency than in transfer).
         leaves = self.leaves()
+        if self.comm_events is not None:
+            ev0 = torch.cuda.Event(enable_timing=True)
+            ev0.record()
         dist.all_reduce(leaves["shs"].grad, op=dist.ReduceOp.SUM)
         small = [p.grad for n, p in leaves.items() if n != "shs"]
         if self.flat_small is None:
@@ -308,6 +324,10 @@ class Replica:
         for g in small:
             g.copy_(self.flat_small[off:off + g.numel()].view_as(g))
             off += g.numel()
+        if self.comm_events is not None:
+            ev1 = torch.cuda.Event(enable_timing=True)
+            ev1.record()
+            self.comm_events.append((ev0, ev1))
 
 
 def our_impl():
@@ -341,7 +361,7 @@ def reference_impl():
 # ------------------------------------------------------------------------------------------------
 # roofline accounting (algorithmic bytes: SURVEY.md 8(d) / DESIGN.md "Algorithmic bytes")
 # ------------------------------------------------------------------------------------------------
-def stage_bytes(P, visible, R, W, H, n_human, sort_bits):
+def stage_bytes(P, visible, R, W, H, n_human, sort_bits, views=1, sh_sink=False):
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     culled = P - visible
     passes = (sort_bits + 7) // 8
@@ -354,7 +374,11 @@ def stage_bytes(P, visible, R, W, H, n_human, sort_bits):
         "identify_tile_ranges": 8 * R + 8 * tiles,
         "render_forward": 40 * R + 20 * W * H + 8 * tiles,
         "render_backward": 76 * R + 20 * W * H,
-        "preprocess_backward": 559 * visible + 260 * culled,
+        # per view.  With the SH gradient sink, views 2..V of a step ADD their 192-B SH gradient row to the
+        # sink (read + write, visible Gaussians only) instead of writing it: 559 + 192 B per visible
+        # Gaussian, 68 B (the zero rows of the other outputs) per culled one.
+        "preprocess_backward": (559 * visible + 260 * culled if not sh_sink else
+                                ((559 * visible + 260 * culled) + (views - 1) * (751 * visible + 68 * culled)) // views),
         "lbs_backward": 352 * n_human,
     }
 
@@ -439,8 +463,8 @@ def main():
     config = {"workload": args.workload, "n_human": n_human, "n_scene": n_scene, "image": "%dx%d" % (W, H),
               "sh_degree": 3, "views_per_rank_per_step": args.views_per_rank,
               "global_view_batch": args.views_per_rank * n_gpus,
-              "parallelism": "dp%d (view batch split across ranks, gradients accumulated over a rank's views, "
-                             "one allreduce of the parameter gradients per step)" % n_gpus,
+              "parallelism": "dp%d (view batch split round-robin across ranks, gradients accumulated over a rank's "
+                             "views, one allreduce of the parameter gradients per step)" % n_gpus,
               "l2": "inputs larger than L2 (per-frame working set > 1 GB vs 126 MB L2), no flush"}
 
     # ---- reference arm -------------------------------------------------------------------------
@@ -465,7 +489,7 @@ def main():
     module, lbs_impl = our_impl()
     V = args.views_per_rank
     wl = make_workload(args.workload, rank, world, device, views=V)
-    rep = Replica(wl, device, module, lbs_impl)
+    rep = Replica(wl, device, module, lbs_impl, sh_sink=True)
 
     def step_resident():
         rep.step_resident()
@@ -500,9 +524,25 @@ def main():
     # per-stage device times: same K steps again with the library's stage events switched on
     _native.read_stage_times(reset=True)
     _native.stage_timing_enable(1)
+    rep.comm_events = []
     ms_staged = timed_loop(step_resident, args.steps, device, barrier)
     _native.stage_timing_enable(0)
     stage_ms = _native.read_stage_times(reset=True)
+    # data-parallel accounting (this pass only): time inside the gradient exchange per step -- waiting for
+    # the slowest rank included -- on every rank
+    comm_ms = sum(a.elapsed_time(b) for a, b in rep.comm_events) / max(len(rep.comm_events), 1)
+    rep.comm_events = None
+    dp_info = None
+    if world > 1:
+        t = torch.tensor([comm_ms, ms_staged / args.steps], dtype=torch.float64, device=device)
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        dp_info = {"exchange_ms_per_step_by_rank": [round(float(x[0]), 3) for x in allt],
+                   "exchange_ms_min": round(min(float(x[0]) for x in allt), 3),
+                   "gradient_bytes": int(sum(p.numel() * 4 for p in rep.leaves().values())),
+                   "collectives_per_step": 2,
+                   "note": "min over ranks ~ pure transfer (the last rank to arrive does not wait); the rest is "
+                           "waiting for the slowest rank's views"}
 
     from hugs_b200 import dp
     ms = dp.max_over_ranks(ms, device)
@@ -514,7 +554,7 @@ def main():
 
     peak, peak_kind = peaks()
     sort_bits = int(_native.sort_bits(W, H))
-    nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits)
+    nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits, views=V, sh_sink=rep.sh_sink is not None)
     stages = {}
     for name, (tot, calls) in stage_ms.items():
         if calls == 0:
@@ -542,6 +582,7 @@ def main():
                 "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": (4 + 4) * V,
                 "ms_per_step": round(ms_e2e / args.steps, 4)},
         "gpu_launches": launches,
+        "dp": dp_info,
         "clocks": clocks,
         "roofline": roofline,
         "stages": stages,

@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 3
+#define HUGS_B200_ABI_VERSION 4
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -136,6 +136,47 @@ int hugs_b200_rasterize_backward(
     float* dL_drot,
     int debug,
     hugs_b200_stream_t stream);
+
+/* The same backward pass for view-batched training (gradient accumulation over the views a rank
+ * renders before the data-parallel allreduce; the reference renders one view per optimiser step and
+ * leaves accumulation to torch's AccumulateGrad: read old + read new + write, for all P rows).
+ * dL_dsh_accumulate == 0: identical to hugs_b200_rasterize_backward (every row of dL_dsh written,
+ * zero rows for culled Gaussians).  dL_dsh_accumulate != 0: dL_dsh must hold valid data; the SH
+ * gradient of every VISIBLE Gaussian is ADDED to its row, rows of culled Gaussians are not touched.
+ * All other outputs are overwritten as before. */
+int hugs_b200_rasterize_backward_acc(
+    int P, int D, int M, int R,
+    const float* background,
+    int width, int height,
+    const float* means3D,
+    const float* shs,
+    const float* colors_precomp,
+    const float* scales,
+    float scale_modifier,
+    const float* rotations,
+    const float* cov3D_precomp,
+    const float* viewmatrix,
+    const float* projmatrix,
+    const float* cam_pos,
+    float tan_fovx, float tan_fovy,
+    const int* radii,
+    char* geom_buffer,
+    char* binning_buffer,
+    size_t binning_bytes,
+    char* image_buffer,
+    const float* dL_dpix,
+    float* dL_dmean2D,
+    float* dL_dconic,
+    float* dL_dopacity,
+    float* dL_dcolor,
+    float* dL_dmean3D,
+    float* dL_dcov3D,
+    float* dL_dsh,
+    float* dL_dscale,
+    float* dL_drot,
+    int debug,
+    hugs_b200_stream_t stream,
+    int dL_dsh_accumulate);
 
 /* Replaces CudaRasterizer::Rasterizer::markVisible (CR/rasterizer.h:23-29,
  * CR/rasterizer_impl.cu:141-153; kernel checkFrustum :54-66).  present is uint8/bool [P]. */

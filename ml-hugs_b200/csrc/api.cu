@@ -642,7 +642,7 @@ int hugs_b200_materialize_sorted_keys(int P, int R, int width, int height, char*
                                    reinterpret_cast<const uint32_t*>(geom.depths), bin.keys, stream);
 }
 
-int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height,
+int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* background, int width, int height,
                                  const float* means3D, const float* shs, const float* colors_precomp,
                                  const float* scales, float scale_modifier, const float* rotations,
                                  const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
@@ -651,7 +651,7 @@ int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* backgr
                                  const float* dL_dpix,
                                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
-                                 float* dL_drot, int debug, hugs_b200_stream_t stream_) {
+                                 float* dL_drot, int debug, hugs_b200_stream_t stream_, int dL_dsh_accumulate) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (P < 0 || R < 0 || width <= 0 || height <= 0) {
         set_error("rasterize_backward: bad sizes");
@@ -697,9 +697,27 @@ int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* backgr
     HB_STAGE(blend_backward(), ST_RENDER_BWD);
     HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,
                                         rotations, scale_modifier, cov3D_precomp, cam, dL_dmean2D, dL_dconic,
-                                        dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, stream),
+                                        dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
+                                        dL_dsh_accumulate != 0, stream),
              ST_PREPROCESS_BWD);
     return 0;
+}
+
+int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height,
+                                 const float* means3D, const float* shs, const float* colors_precomp,
+                                 const float* scales, float scale_modifier, const float* rotations,
+                                 const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                 const float* cam_pos, float tan_fovx, float tan_fovy, const int* radii,
+                                 char* geom_buffer, char* binning_buffer, size_t binning_bytes, char* image_buffer,
+                                 const float* dL_dpix,
+                                 float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                                 float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
+                                 float* dL_drot, int debug, hugs_b200_stream_t stream) {
+    return hugs_b200_rasterize_backward_acc(P, D, M, R, background, width, height, means3D, shs, colors_precomp, scales,
+                                            scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, cam_pos,
+                                            tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer, binning_bytes,
+                                            image_buffer, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor,
+                                            dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, debug, stream, 0);
 }
 
 int hugs_b200_lbs_forward(int F, int N, int J, const float* A, const float* xyz, const float* weights,

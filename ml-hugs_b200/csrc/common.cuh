@@ -158,7 +158,7 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                float scale_modifier, const float* cov3D_precomp, const Camera& cam,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
-                               float* dL_drot, cudaStream_t stream);
+                               float* dL_drot, bool sh_accumulate, cudaStream_t stream);
 
 int launch_lbs_forward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
                        const float* rotmat, const float* scales, const float* transl, float smpl_scale,

@@ -38,6 +38,7 @@ struct PreBwdArgs {
     float* dL_dscale;         // [P,3]
     float* dL_drot;           // [P,4]
     int sh_vec4;
+    int sh_accumulate;  // add visible rows of dL_dsh into the existing contents, leave culled rows alone
 };
 
 __device__ __forceinline__ void store_sh_grad(const PreBwdArgs& a, int idx, const float* g /*48*/) {
@@ -395,8 +396,16 @@ __global__ void __launch_bounds__(kPbThreads, 2) preprocess_backward_kernel(cons
 #pragma unroll
         for (int j = 0; j < 12; j++) {
             if ((long long)row < rows_left) {
-                const float4 v = lds128(s_warp + row * kPbRowBytes + col * 16u);
-                g_out[32 * j + lane] = v;
+                if (!a.sh_accumulate) {
+                    g_out[32 * j + lane] = lds128(s_warp + row * kPbRowBytes + col * 16u);
+                } else if ((alive >> row) & 1u) {
+                    // view-batch accumulation: fire-and-forget 16-byte reductions at the L2, still
+                    // 512 contiguous bytes per warp instruction; culled rows cost nothing
+                    const float4 v = lds128(s_warp + row * kPbRowBytes + col * 16u);
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(g_out + 32 * j + lane),
+                                 "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                                 : "memory");
+                }
             }
             col += 8u;
             row += 2u;
@@ -414,7 +423,14 @@ __global__ void __launch_bounds__(kPbThreads, 2) preprocess_backward_kernel(cons
             sh_backward(deg, sh, mx - V[32], my - V[33], mz - V[34], dRGB, gsh, dmean_x, dmean_y, dmean_z);
             have_gsh = true;
         }
-        if (sh_out) {
+        if (sh_out && a.sh_accumulate) {
+            if (have_gsh) {
+                float* dst = a.dL_dsh + (size_t)idx * a.M * 3;
+#pragma unroll
+                for (int i = 0; i < 48; i++)
+                    if (i < a.M * 3) dst[i] += gsh[i];
+            }
+        } else if (sh_out) {
             if (!have_gsh) {
 #pragma unroll
                 for (int i = 0; i < 48; i++) gsh[i] = 0.f;
@@ -490,7 +506,7 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                float scale_modifier, const float* cov3D_precomp, const Camera& cam,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcolor,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                               cudaStream_t stream) {
+                               bool sh_accumulate, cudaStream_t stream) {
     PreBwdArgs a;
     a.P = P;
     a.D = D;
@@ -518,6 +534,7 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
     a.dL_dsh = dL_dsh;
     a.dL_dscale = dL_dscale;
     a.dL_drot = dL_drot;
+    a.sh_accumulate = sh_accumulate ? 1 : 0;
     a.sh_vec4 = (M == 16 && (shs == nullptr || (reinterpret_cast<uintptr_t>(shs) & 15u) == 0) &&
                  (reinterpret_cast<uintptr_t>(dL_dsh) & 15u) == 0)
                     ? 1

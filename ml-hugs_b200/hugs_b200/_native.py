@@ -88,6 +88,20 @@ rasterize_backward = _sig("hugs_b200_rasterize_backward", i32, [
     i32, fp,                  # debug, stream
 ])
 
+rasterize_backward_acc = _sig("hugs_b200_rasterize_backward_acc", i32, [
+    i32, i32, i32, i32,       # P, D, M, R
+    fp, i32, i32,             # background, width, height
+    fp, fp, fp,               # means3D, shs, colors_precomp
+    fp, C.c_float, fp, fp,    # scales, scale_modifier, rotations, cov3D_precomp
+    fp, fp, fp,               # viewmatrix, projmatrix, cam_pos
+    C.c_float, C.c_float,     # tan_fovx, tan_fovy
+    fp, fp, fp, C.c_size_t, fp,  # radii, geom, binning, binning_bytes, image
+    fp,                       # dL_dpix
+    fp, fp, fp, fp, fp, fp, fp, fp, fp,  # 9 gradient outputs
+    i32, fp,                  # debug, stream
+    i32,                      # dL_dsh_accumulate
+])
+
 mark_visible = _sig("hugs_b200_mark_visible", i32, [i32, fp, fp, fp, fp, fp])
 
 geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayout)])
@@ -130,7 +144,8 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode", "hugs_b200_materialize_sorted_keys",
     "hugs_b200_stage_timing_enable", "hugs_b200_stage_timing_read", "hugs_b200_stage_name",
     "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
-    "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_mark_visible",
+    "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_rasterize_backward_acc",
+    "hugs_b200_mark_visible",
     "hugs_b200_geom_layout_of", "hugs_b200_image_layout_of", "hugs_b200_binning_layout_of",
     "hugs_b200_sort_bits", "hugs_b200_sort_temp_bytes", "hugs_b200_sort_pairs", "hugs_b200_sort_pairs_range",
     "hugs_b200_scan_temp_bytes", "hugs_b200_inclusive_scan",

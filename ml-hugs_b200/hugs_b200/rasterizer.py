@@ -131,11 +131,15 @@ def rasterize_gaussians_forward(
 def rasterize_gaussians_backward(
     background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
     projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
-    imageBuffer, debug,
+    imageBuffer, debug, sh_grad_out=None, sh_grad_accumulate=False,
 ):
     """Same 21 arguments and 8 return values as the reference's ``_C.rasterize_gaussians_backward``
     (rasterize_points.h:40-62): (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
-    dL_dsh, dL_dscales, dL_drotations)."""
+    dL_dsh, dL_dscales, dL_drotations).
+
+    ``sh_grad_out`` / ``sh_grad_accumulate`` (not in the reference) serve view-batched training: the SH
+    gradient is written (or, with ``sh_grad_accumulate``, added for the visible Gaussians) straight into
+    the caller's [P,M,3] buffer, which is also what is returned as dL_dsh."""
     device = means3D.device
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
@@ -164,13 +168,21 @@ def rasterize_gaussians_backward(
     dL_dconic = alloc((P, 2, 2), **opts)
     dL_dopacity = alloc((P, 1), **opts)
     dL_dcov3D = alloc((P, 6), **opts)
-    dL_dsh = alloc((P, M, 3), **opts)
+    if sh_grad_out is not None:
+        if (sh_grad_out.dtype != torch.float32 or sh_grad_out.device != device or not sh_grad_out.is_contiguous()
+                or tuple(sh_grad_out.shape) != (P, M, 3)):
+            raise ValueError("sh_grad_out must be a contiguous float32 [P,M,3] tensor on the inputs' device")
+        dL_dsh = sh_grad_out
+    else:
+        if sh_grad_accumulate:
+            raise ValueError("sh_grad_accumulate needs sh_grad_out")
+        dL_dsh = alloc((P, M, 3), **opts)
     dL_dscales = alloc((P, 3), **opts)
     dL_drotations = alloc((P, 4), **opts)
 
     if P != 0:
         with torch.cuda.device(device):
-            rc = N.rasterize_backward(
+            rc = N.rasterize_backward_acc(
                 P, int(degree), M, int(R),
                 N.ptr(background), W, H,
                 N.ptr(means3D), N.ptr(sh), N.ptr(colors),
@@ -183,7 +195,7 @@ def rasterize_gaussians_backward(
                 dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), dL_dcolors.data_ptr(),
                 dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), N.ptr(dL_dsh), dL_dscales.data_ptr(),
                 dL_drotations.data_ptr(),
-                int(bool(debug)), _stream_ptr(device),
+                int(bool(debug)), _stream_ptr(device), int(bool(sh_grad_accumulate)),
             )
         N.check(rc, "rasterize_gaussians_backward")
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
@@ -211,6 +223,53 @@ _C = SimpleNamespace(
     rasterize_gaussians_backward=rasterize_gaussians_backward,
     mark_visible=mark_visible,
 )
+
+
+class ShGradSink:
+    """Where the SH gradient of a parameter tensor goes during view-batched training.
+
+    The reference renders one view per optimiser step.  When a data-parallel rank renders several
+    views per step (``hugs_b200.dp``), torch's AccumulateGrad adds every view's [P,16,3] gradient to
+    ``param.grad`` with a separate elementwise kernel (768 B of traffic per Gaussian and view on top
+    of the 192 B the backward pass wrote).  With a sink attached, the backward pass of every render
+    whose ``shs`` argument IS ``param`` writes (first view after ``reset()``) or adds (later views;
+    visible Gaussians only) its SH gradient directly into ``buffer``; autograd sees no gradient for
+    ``shs``.  ``param.grad`` is pointed at ``buffer``."""
+
+    def __init__(self, param, buffer=None):
+        if not (param.is_leaf and param.dtype == torch.float32 and param.dim() == 3 and param.is_contiguous()):
+            raise ValueError("an SH gradient sink needs a contiguous float32 [P,M,3] leaf tensor")
+        self.param = param
+        self.buffer = torch.zeros_like(param) if buffer is None else buffer
+        if tuple(self.buffer.shape) != tuple(param.shape) or self.buffer.dtype != torch.float32 \
+                or self.buffer.device != param.device or not self.buffer.is_contiguous():
+            raise ValueError("sink buffer must match the parameter (contiguous float32, same shape and device)")
+        self.fresh = True  # the next backward pass overwrites the buffer instead of adding to it
+        param.grad = self.buffer
+
+    def reset(self):
+        """Start of a step: the next backward pass overwrites the buffer (no zero fill needed)."""
+        self.fresh = True
+        if self.param.grad is not self.buffer:
+            self.param.grad = self.buffer
+
+
+_sh_sinks = {}
+
+
+def attach_sh_grad_sink(param, buffer=None):
+    sink = ShGradSink(param, buffer)
+    _sh_sinks[id(param)] = sink
+    return sink
+
+
+def detach_sh_grad_sink(param):
+    _sh_sinks.pop(id(param), None)
+
+
+def _sink_of(sh):
+    sink = _sh_sinks.get(id(sh))
+    return sink if (sink is not None and sink.param is sh) else None
 
 
 def rasterize_gaussians(
@@ -288,6 +347,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         # Keep relevant tensors for backward
         ctx.raster_settings = raster_settings
         ctx.num_rendered = num_rendered
+        ctx.sh_sink = _sink_of(sh)
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               geomBuffer, binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
@@ -322,18 +382,24 @@ class _RasterizeGaussians(torch.autograd.Function):
                 imgBuffer,
                 raster_settings.debug)
 
+        # view-batched training: the SH gradient goes straight into the attached sink (ShGradSink)
+        sink = ctx.sh_sink
+        kw = {} if sink is None else dict(sh_grad_out=sink.buffer, sh_grad_accumulate=not sink.fresh)
         if raster_settings.debug:
             cpu_args = cpu_deep_copy_tuple(args)  # Copy them before they can be corrupted
             try:
                 (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp,
-                 grad_sh, grad_scales, grad_rotations) = _C.rasterize_gaussians_backward(*args)
+                 grad_sh, grad_scales, grad_rotations) = rasterize_gaussians_backward(*args, **kw)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
             (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp,
-             grad_sh, grad_scales, grad_rotations) = _C.rasterize_gaussians_backward(*args)
+             grad_sh, grad_scales, grad_rotations) = rasterize_gaussians_backward(*args, **kw)
+        if sink is not None:
+            sink.fresh = False
+            grad_sh = None  # delivered through the sink
 
         def present(inp, g):
             # the reference hands back [P,...] zero tensors even for inputs that were passed as the
@@ -343,7 +409,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         grads = (
             grad_means3D,
             grad_means2D,
-            present(sh, grad_sh),
+            present(sh, grad_sh) if grad_sh is not None else None,
             present(colors_precomp, grad_colors_precomp),
             grad_opacities,
             present(scales, grad_scales),
