@@ -4,7 +4,7 @@ TAG=${1:-rXX}
 O=gpurun_out
 mkdir -p $O
 nvidia-smi topo -m > $O/${TAG}_topo.txt 2>&1
-for N in 1 2 4 8; do
+for N in ${NS:-1 2 4 8}; do
   if [ $N = 1 ]; then
     timeout 600 python bench.py --gpus 1 --steps 30 --warmup 5 --no-cpu-baseline > $O/${TAG}_scale_$N.json 2> $O/${TAG}_scale_$N.err
   else
@@ -16,3 +16,9 @@ for N in 1 2 4 8; do
   echo "N=$N rc=$?"; python -c "
 import json;d=json.load(open('$O/${TAG}_scale_$N.json'));print($N,d['value'],d['e2e']['value'],d['ms_per_step'])"
 done
+python - <<PY
+import json
+for n in "${NS:-1 2 4 8}".split():
+    d=json.load(open("$O/${TAG}_scale_%s.json" % n))
+    print(n, "dp:", d.get("dp"))
+PY
