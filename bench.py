@@ -565,10 +565,28 @@ def main():
                         "frac": round(gbs / peak, 4)}
     dominant = max(stages, key=lambda k: stages[k]["ms"]) if stages else None
     roofline = None
+    # DRAM bytes per launch from the committed ncu --set full capture of this workload (null for others)
+    traffic, traffic_src = None, None
+    try:
+        if args.workload == "human_scene_1080p":
+            with open(os.path.join(ROOT, "profiles", "ncu_dram_traffic.json")) as f:
+                tj = json.load(f)
+            traffic, traffic_src = tj["bytes_per_frame"], tj["source"]
+            for name in stages:
+                if name in traffic:
+                    stages[name]["dram_traffic"] = int(traffic[name])
+    except Exception:
+        traffic = None
     if dominant:
         s = stages[dominant]
+        issue_bound = dominant in ("render_forward", "render_backward")
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": s["gbs"], "peak": peak, "unit": "GB/s",
-                    "frac": s["frac"], "traffic": None, "peak_source": peak_kind,
+                    "frac": s["frac"], "traffic": int(traffic[dominant]) if traffic and dominant in traffic else None,
+                    "traffic_source": traffic_src,
+                    "limiter": ("instruction issue (ncu: 86-92 % issue-slot active, DRAM traffic far below the "
+                                "algorithmic gather bytes because a tile's Gaussians are served by L2): see "
+                                "DESIGN.md section 5; the HBM-bound stages are in `stages`") if issue_bound else "hbm",
+                    "peak_source": peak_kind,
                     "ms_per_launch": s["ms"], "algorithmic_bytes": s["bytes"],
                     "timed": "per-stage CUDA events on the launching stream, %d frames (%.3f ms/frame with events on)"
                              % (args.steps * V, ms_staged / (args.steps * V))}
