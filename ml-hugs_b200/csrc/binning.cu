@@ -95,9 +95,12 @@ __global__ void __launch_bounds__(kDupThreads)
     __shared__ uint32_t s_inv[kDupThreads];  // ceil(2^32 / rect width): k / w == umulhi(k, inv) for k*w < 2^32
     __shared__ uint32_t s_idx[kDupThreads];
     __shared__ uint32_t s_hist[3][256];
+    __shared__ uint32_t s_head[kDupThreads];       // first-slot markers of the current output chunk
+    __shared__ uint32_t s_wmax[kDupThreads / 32];
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31u;
     const int first = blockIdx.x * kDupThreads;
+    s_head[tid] = 0;
     const int pos = first + tid;
     for (int i = tid; i < plan.num_passes * 256; i += kDupThreads) s_hist[i >> 8][i & 255] = 0;
     uint32_t end_off = 0;
@@ -131,16 +134,43 @@ __global__ void __launch_bounds__(kDupThreads)
     // digit layout of the first two sort passes relative to the tile id
     const int sh0 = plan.shift[0] - 32, sh1 = plan.shift[1] - 32, sh2 = plan.shift[2] - 32;
     const uint32_t mk0 = (1u << plan.bits[0]) - 1u, mk1 = (1u << plan.bits[1]) - 1u, mk2 = (1u << plan.bits[2]) - 1u;
+    const uint32_t my_start = (tid < in_block) ? s_off[tid] : 0u;
+    const uint32_t my_len = (tid < in_block) ? s_off[tid + 1] - my_start : 0u;
+    uint32_t carry = 0;  // owner of the slot before the current chunk (same value in every thread)
     for (uint32_t ob = begin; ob < end; ob += kDupThreads) {
         const uint32_t o = ob + tid;
         const bool valid = o < end;
         const unsigned active = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            int lo = 0, hi = in_block;  // invariant: s_off[lo] <= o < s_off[hi]
-            while (hi - lo > 1) {
-                const int mid = (lo + hi) >> 1;
-                if (s_off[mid] <= o) lo = mid; else hi = mid;
+        // Owner of every slot of this 256-slot chunk without a search: each non-empty Gaussian whose
+        // first slot lies in the chunk drops its index there, an inclusive max-scan spreads it to the
+        // slots behind it, `carry` (the owner of the slot before the chunk) covers the chunk's head.
+        // (A binary search over s_off per slot was 47 % of this kernel's instructions.)
+        if (my_len != 0u && my_start - ob < (uint32_t)kDupThreads) s_head[my_start - ob] = (uint32_t)tid;
+        __syncthreads();
+        uint32_t own = s_head[tid];
+        s_head[tid] = 0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, own, d);
+            if (lane >= (unsigned)d) own = max(own, t);
+        }
+        if (lane == 31) s_wmax[tid >> 5] = own;
+        __syncthreads();
+        {
+            uint32_t wv = (lane < (unsigned)(kDupThreads / 32)) ? s_wmax[lane] : 0u;
+#pragma unroll
+            for (int d = 1; d < kDupThreads / 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, wv, d);
+                if (lane >= (unsigned)d) wv = max(wv, t);
             }
+            const uint32_t prev = __shfl_sync(0xffffffffu, wv, (int)((tid >> 5) + 31) & 31);  // warp 0 reads lane 31: 0
+            const uint32_t total = __shfl_sync(0xffffffffu, wv, kDupThreads / 32 - 1);
+            own = max(own, carry);
+            if ((tid >> 5) != 0) own = max(own, prev);
+            carry = max(carry, total);
+        }
+        if (valid) {
+            const int lo = (int)own;
             const uint32_t rect = s_rect[lo];
             const uint32_t k = o - s_off[lo];
             const uint32_t w = rect >> 20;
