@@ -329,6 +329,24 @@ int hugs_b200_lbs_backward(int F, int N, int J,
                            float* d_scales, float* d_transl, float* d_smpl_scale,
                            hugs_b200_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Image-space losses, the step right after the rasterizer in the reference's training loop
+ * (SURVEY.md 8(f) N3).  Replaces l1_loss + ssim/_ssim (hugs/losses/utils.py:52-55, 63-103: window 11,
+ * sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2) as called by hugs/losses/loss.py:87-107, and
+ * their autograd backward.  Images are float32 [C,H,W] (a batch is folded into C: the reference's
+ * conv2d is depthwise).
+ *   forward : sums[0] = sum |img1 - img2|, sums[1] = sum of the SSIM map (double[2], device; divide
+ *             by C*H*W for the means the reference returns); dmap float32 [3][C][H][W] receives the
+ *             per-pixel derivative planes the backward needs (NULL: forward only).
+ *   backward: dL_dimg1 [C,H,W] = g[0] * d(l1 mean)/d img1 + g[1] * d(ssim mean)/d img1, with
+ *             g = float32[2] on the device (the autograd gradients of the two scalars).
+ * ------------------------------------------------------------------------------------------- */
+int hugs_b200_l1_ssim_forward(int C, int H, int W, const float* img1, const float* img2,
+                              float* dmap, double* sums, hugs_b200_stream_t stream);
+int hugs_b200_l1_ssim_backward(int C, int H, int W, const float* img1, const float* img2,
+                               const float* dmap, const float* g, float* dL_dimg1,
+                               hugs_b200_stream_t stream);
+
 /* Number of kernel launches issued by this library (all host threads) since the last reset
  * (bench.py reports it as gpu_launches). */
 long long hugs_b200_launch_count(int reset);

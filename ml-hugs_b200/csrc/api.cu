@@ -748,4 +748,22 @@ int hugs_b200_lbs_backward(int F, int N, int J, const float* A, const float* xyz
                                static_cast<cudaStream_t>(stream));
 }
 
+int hugs_b200_l1_ssim_forward(int C, int H, int W, const float* img1, const float* img2, float* dmap, double* sums,
+                              hugs_b200_stream_t stream) {
+    if (C < 0 || H < 0 || W < 0 || !sums || ((size_t)C * H * W > 0 && (!img1 || !img2))) {
+        set_error("l1_ssim_forward: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_l1_ssim_forward(C, H, W, img1, img2, dmap, sums, static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_l1_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* dmap,
+                               const float* g, float* dL_dimg1, hugs_b200_stream_t stream) {
+    if (C < 0 || H < 0 || W < 0 || ((size_t)C * H * W > 0 && (!img1 || !img2 || !dmap || !g || !dL_dimg1))) {
+        set_error("l1_ssim_backward: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_l1_ssim_backward(C, H, W, img1, img2, dmap, g, dL_dimg1, static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

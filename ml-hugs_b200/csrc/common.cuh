@@ -169,6 +169,12 @@ int launch_lbs_backward(int F, int N, int J, const float* A, const float* xyz, c
                         float* d_xyz, float* d_weights, float* d_rotmat, float* d_scales, float* d_transl,
                         float* d_smpl_scale, cudaStream_t stream);
 
+// ---- image-space losses (image_loss.cu) -------------------------------------------------------
+int launch_l1_ssim_forward(int C, int H, int W, const float* img1, const float* img2, float* dmap, double* sums,
+                           cudaStream_t stream);
+int launch_l1_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* dmap,
+                            const float* g, float* dL_dimg1, cudaStream_t stream);
+
 // ---- device helpers ------------------------------------------------------------------------
 #ifdef __CUDACC__
 __device__ __forceinline__ float4 ldg_f4(const float4* p) { return __ldg(p); }

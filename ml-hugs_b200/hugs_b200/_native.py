@@ -102,6 +102,9 @@ rasterize_backward_acc = _sig("hugs_b200_rasterize_backward_acc", i32, [
     i32,                      # dL_dsh_accumulate
 ])
 
+l1_ssim_forward = _sig("hugs_b200_l1_ssim_forward", i32, [i32, i32, i32, fp, fp, fp, fp, fp])
+l1_ssim_backward = _sig("hugs_b200_l1_ssim_backward", i32, [i32, i32, i32, fp, fp, fp, fp, fp, fp])
+
 mark_visible = _sig("hugs_b200_mark_visible", i32, [i32, fp, fp, fp, fp, fp])
 
 geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayout)])
@@ -150,6 +153,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_sort_bits", "hugs_b200_sort_temp_bytes", "hugs_b200_sort_pairs", "hugs_b200_sort_pairs_range",
     "hugs_b200_scan_temp_bytes", "hugs_b200_inclusive_scan",
     "hugs_b200_lbs_forward", "hugs_b200_lbs_backward",
+    "hugs_b200_l1_ssim_forward", "hugs_b200_l1_ssim_backward",
 ]
 
 
