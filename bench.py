@@ -190,6 +190,10 @@ class Replica:
             import hugs_b200
             self.sh_sink = hugs_b200.attach_sh_grad_sink(self.shs)
         self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
+        # views of a step alternate between `n_streams` CUDA streams: the issue-bound blend kernels of one
+        # view overlap the latency- and HBM-bound binning / per-Gaussian kernels of the next
+        self.n_streams = max(1, int(os.environ.get("HB_STREAMS", "2"))) if sh_sink else 1
+        self.streams = [torch.cuda.Stream(device) for _ in range(self.n_streams)] if self.n_streams > 1 else []
         self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=True)
         self.transl = d(h["transl"][0])
         # per-frame inputs: pinned host copies (for e2e) and resident device copies (for value)
@@ -225,7 +229,10 @@ class Replica:
     def zero_grad(self):
         for n, p in self.leaves().items():
             if n == "shs" and self.sh_sink is not None:
-                self.sh_sink.reset()  # the next backward pass overwrites the sink buffer
+                if self.n_streams > 1:
+                    self.sh_sink.zero_()  # every view adds (views run concurrently on several streams)
+                else:
+                    self.sh_sink.reset()  # the next backward pass overwrites the sink buffer
             else:
                 p.grad = None
         self.means2D.grad = None
@@ -261,6 +268,18 @@ class Replica:
     def step_resident(self):
         """One step: every view of this rank's share of the view batch, gradients accumulated."""
         self.zero_grad()
+        if self.n_streams > 1:
+            main = torch.cuda.current_stream(self.device)
+            for s in self.streams:
+                s.wait_stream(main)
+            for v in range(self.views):
+                with torch.cuda.stream(self.streams[v % self.n_streams]):
+                    self.frame(dict(self.devs[v]))
+                self.last_nodes[v] = self.last_node
+                self.last_radii_v[v] = self.last_radii
+            for s in self.streams:
+                main.wait_stream(s)
+            return
         for v in range(self.views):
             self.frame(dict(self.devs[v]))
             self.last_nodes[v] = self.last_node
@@ -268,6 +287,16 @@ class Replica:
 
     def step_e2e(self):
         self.zero_grad()
+        if self.n_streams > 1:
+            main = torch.cuda.current_stream(self.device)
+            for s in self.streams:
+                s.wait_stream(main)
+            for v in range(self.views):
+                with torch.cuda.stream(self.streams[v % self.n_streams]):
+                    self.frame_e2e(self.hosts[v])
+            for s in self.streams:
+                main.wait_stream(s)
+            return
         for v in range(self.views):
             self.frame_e2e(self.hosts[v])
 
@@ -463,6 +492,7 @@ def main():
     config = {"workload": args.workload, "n_human": n_human, "n_scene": n_scene, "image": "%dx%d" % (W, H),
               "sh_degree": 3, "views_per_rank_per_step": args.views_per_rank,
               "global_view_batch": args.views_per_rank * n_gpus,
+              "cuda_streams_per_rank": max(1, int(os.environ.get("HB_STREAMS", "2"))) if args.impl == "ours" else 1,
               "parallelism": "dp%d (view batch split round-robin across ranks, gradients accumulated over a rank's "
                              "views, one allreduce of the parameter gradients per step)" % n_gpus,
               "l2": "inputs larger than L2 (per-frame working set > 1 GB vs 126 MB L2), no flush"}
@@ -523,9 +553,12 @@ def main():
 
     # per-stage device times: same K steps again with the library's stage events switched on
     _native.read_stage_times(reset=True)
+    # (one stream in this pass: a stage's events must not span the other stream's kernels)
     _native.stage_timing_enable(1)
     rep.comm_events = []
+    n_streams, rep.n_streams = rep.n_streams, 1
     ms_staged = timed_loop(step_resident, args.steps, device, barrier)
+    rep.n_streams = n_streams
     _native.stage_timing_enable(0)
     stage_ms = _native.read_stage_times(reset=True)
     # data-parallel accounting (this pass only): time inside the gradient exchange per step -- waiting for
@@ -588,8 +621,9 @@ def main():
                                 "DESIGN.md section 5; the HBM-bound stages are in `stages`") if issue_bound else "hbm",
                     "peak_source": peak_kind,
                     "ms_per_launch": s["ms"], "algorithmic_bytes": s["bytes"],
-                    "timed": "per-stage CUDA events on the launching stream, %d frames (%.3f ms/frame with events on)"
-                             % (args.steps * V, ms_staged / (args.steps * V))}
+                    "timed": "per-stage CUDA events on the launching stream, %d frames on ONE stream (%.3f ms/frame "
+                             "with events on; the timed region above alternates views over %d streams)"
+                             % (args.steps * V, ms_staged / (args.steps * V), rep.n_streams)}
     frame_bytes = sum(nbytes.values())
     line = {
         "metric": METRIC, "value": round(n_gpus * V * args.steps / (ms * 1e-3), 3), "unit": UNIT, "n_gpus": n_gpus,

@@ -67,19 +67,39 @@ class FlatGradBuffer:
 
 
 def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, world_size: int,
-            group=None) -> float:
+            group=None, streams: Sequence = ()) -> float:
     """One data-parallel step: ``render_view(v)`` must return the scalar loss tensor of view ``v``
     (forward through LBS + rasterizer); this rank handles ``shard_views`` of ``views``, calls
     backward on each loss (gradients accumulate in ``buf``), then allreduces.  Returns the local
-    loss sum."""
+    loss sum.
+
+    ``streams`` (CUDA only): the rank's views alternate between these streams, so the issue-bound
+    blend kernels of one view overlap the latency- and HBM-bound binning / per-Gaussian kernels of
+    the next (measured +5 % frames/s with two streams on B200); autograd orders the gradient
+    accumulation.  The losses are summed on the device and read once, after the last view."""
     buf.zero_()
-    total = 0.0
-    for i in shard_views(len(views), rank, world_size):
-        loss = render_view(views[i])
-        loss.backward()
-        total += float(loss.detach())
+    mine = shard_views(len(views), rank, world_size)
+    if not streams:
+        total = 0.0
+        for i in mine:
+            loss = render_view(views[i])
+            loss.backward()
+            total += float(loss.detach())
+        buf.allreduce(group)
+        return total
+    main = torch.cuda.current_stream()
+    for s in streams:
+        s.wait_stream(main)
+    losses = []
+    for k, i in enumerate(mine):
+        with torch.cuda.stream(streams[k % len(streams)]):
+            loss = render_view(views[i])
+            loss.backward()
+            losses.append(loss.detach())
+    for s in streams:
+        main.wait_stream(s)
     buf.allreduce(group)
-    return total
+    return float(torch.stack(losses).sum()) if losses else 0.0
 
 
 def init_from_env(backend: str = None):

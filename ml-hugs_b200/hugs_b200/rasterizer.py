@@ -254,6 +254,16 @@ class ShGradSink:
             self.param.grad = self.buffer
 
 
+    def zero_(self):
+        """Start of a step whose views run on several CUDA streams: clear the buffer and let EVERY
+        backward pass add into it (additions commute; an overwriting first pass would have to be
+        ordered before the others)."""
+        self.buffer.zero_()
+        self.fresh = False
+        if self.param.grad is not self.buffer:
+            self.param.grad = self.buffer
+
+
 _sh_sinks = {}
 
 
