@@ -188,7 +188,14 @@ class Replica:
         self.sh_sink = None
         if sh_sink:
             import hugs_b200
-            self.sh_sink = hugs_b200.attach_sh_grad_sink(self.shs)
+            # one flat gradient buffer: [SH gradient (the sink) | every other gradient], so the exchange is
+            # ONE collective over 275 MB
+            n_sh = self.shs.numel()
+            n_small = sum(t.numel() for t in (h["xyz"], h["rotmat"], h["scales"], h["lbs_weights"])) + self.opacity.numel()
+            if self.n_scene > 0:
+                n_small += sum(wl["scene"][k].numel() for k in ("means3D", "scales", "rotations"))
+            self.flat_all = torch.zeros(n_sh + n_small, device=device)
+            self.sh_sink = hugs_b200.attach_sh_grad_sink(self.shs, self.flat_all[:n_sh].view_as(self.shs))
         self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
         # views of a step alternate between `n_streams` CUDA streams: the issue-bound blend kernels of one
         # view overlap the latency- and HBM-bound binning / per-Gaussian kernels of the next
@@ -343,12 +350,18 @@ class Replica:
         if self.comm_events is not None:
             ev0 = torch.cuda.Event(enable_timing=True)
             ev0.record()
-        dist.all_reduce(leaves["shs"].grad, op=dist.ReduceOp.SUM)
         small = [p.grad for n, p in leaves.items() if n != "shs"]
-        if self.flat_small is None:
-            self.flat_small = torch.empty(sum(g.numel() for g in small), device=self.device)
-        torch.cat([g.reshape(-1) for g in small], out=self.flat_small)
-        dist.all_reduce(self.flat_small, op=dist.ReduceOp.SUM)
+        if self.sh_sink is not None:
+            n_sh = self.shs.numel()
+            self.flat_small = self.flat_all[n_sh:]
+            torch.cat([g.reshape(-1) for g in small], out=self.flat_small)
+            dist.all_reduce(self.flat_all, op=dist.ReduceOp.SUM)
+        else:
+            dist.all_reduce(leaves["shs"].grad, op=dist.ReduceOp.SUM)
+            if self.flat_small is None:
+                self.flat_small = torch.empty(sum(g.numel() for g in small), device=self.device)
+            torch.cat([g.reshape(-1) for g in small], out=self.flat_small)
+            dist.all_reduce(self.flat_small, op=dist.ReduceOp.SUM)
         off = 0
         for g in small:
             g.copy_(self.flat_small[off:off + g.numel()].view_as(g))
@@ -573,7 +586,7 @@ def main():
         dp_info = {"exchange_ms_per_step_by_rank": [round(float(x[0]), 3) for x in allt],
                    "exchange_ms_min": round(min(float(x[0]) for x in allt), 3),
                    "gradient_bytes": int(sum(p.numel() * 4 for p in rep.leaves().values())),
-                   "collectives_per_step": 2,
+                   "collectives_per_step": 1,
                    "note": "min over ranks ~ pure transfer (the last rank to arrive does not wait); the rest is "
                            "waiting for the slowest rank's views"}
 
