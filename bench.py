@@ -13,9 +13,9 @@ split).  The step's view batch is N x views-per-rank views, so the per-rank work
   e2e      the same step through the public API with the per-frame inputs (camera, SMPL joint
            transforms, the image-space loss gradient that stands in for the training target)
            copied from pinned host memory and the loss read back, inside the timed region (the
-           25 MB target is uploaded on a copy stream under the forward pass; each step's loss is
-           copied to pinned memory and read by the host one step later, the last one before the
-           closing event)
+           25 MB target is uploaded on a copy stream under the forward pass; every frame's loss is
+           copied to a pinned slot and read by the host four frames later, the pending ones before
+           the closing event); the views of a step alternate between two CUDA streams
   roofline the dominant kernel's algorithmic bytes / its CUDA-event time / measured HBM peak
   stages   the same for every stage (per-stage CUDA events recorded inside the library on the
            launching stream during a second pass of K steps)
@@ -223,8 +223,8 @@ class Replica:
         self.G_dev = [torch.empty_like(self.devs[0]["G"]) for _ in range(2)]
         self.G_ready = [torch.cuda.Event() for _ in range(2)]
         self.step_done = [None, None]
-        self.loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
-        self.loss_ready = [None, None]
+        self.loss_host = [torch.zeros(1).pin_memory() for _ in range(4)]
+        self.loss_ready = [None] * 4
         self.e2e_step = 0
         self.losses = []
         self.flat_small = None
@@ -317,28 +317,38 @@ class Replica:
                 self.copy_stream.wait_event(self.step_done[i])
             self.G_dev[i].copy_(host["G"], non_blocking=True)
             self.G_ready[i].record(self.copy_stream)
-        inp = {k: v.to(self.device, non_blocking=True) for k, v in host.items() if k != "G"}
+        # camera + joint transforms travel as ONE pinned record (one async copy instead of five)
+        small = [(k, v) for k, v in host.items() if k != "G" and k != "_packed"]
+        if "_packed" not in host:
+            host["_packed"] = torch.cat([v.reshape(-1) for _, v in small]).pin_memory()
+        rec = host["_packed"].to(self.device, non_blocking=True)
+        inp, off = {}, 0
+        for k, v in small:
+            inp[k] = rec[off:off + v.numel()].view(v.shape)
+            off += v.numel()
+        # Loss read-back: every frame's loss is copied to a pinned slot of a small ring and read by the
+        # host when the slot comes round again (4 frames later: the copy has long landed, the host never
+        # stalls the device); drain_e2e reads what is still pending before the closing event.
+        s = self.e2e_step % len(self.loss_host)
+        if self.loss_ready[s] is not None:
+            self.loss_ready[s].synchronize()
+            self.losses.append(float(self.loss_host[s][0]))
         ev = torch.cuda.Event()
-        inp.update(G=self.G_dev[i], G_ready=self.G_ready[i], loss_out=self.loss_host[i], loss_event=ev)
+        inp.update(G=self.G_dev[i], G_ready=self.G_ready[i], loss_out=self.loss_host[s], loss_event=ev)
         self.frame(inp)
-        self.loss_ready[i] = ev
+        self.loss_ready[s] = ev
         done = torch.cuda.Event()
         done.record(main)
         self.step_done[i] = done
         self.e2e_step += 1
-        j = 1 - i  # read the previous frame's loss (its copy has had a whole frame to land)
-        if self.loss_ready[j] is not None:
-            self.loss_ready[j].synchronize()
-            self.loss_ready[j] = None
-            self.losses.append(float(self.loss_host[j][0]))
 
     def drain_e2e(self):
-        """Read the last step's loss (called inside the timed region, after the last step)."""
-        i = (self.e2e_step - 1) % 2
-        if self.e2e_step and self.loss_ready[i] is not None:
-            self.loss_ready[i].synchronize()
-            self.loss_ready[i] = None
-            self.losses.append(float(self.loss_host[i][0]))
+        """Read the losses still pending (called inside the timed region, after the last step)."""
+        for s in range(len(self.loss_host)):
+            if self.loss_ready[s] is not None:
+                self.loss_ready[s].synchronize()
+                self.loss_ready[s] = None
+                self.losses.append(float(self.loss_host[s][0]))
 
     def allreduce_grads(self):
         import torch.distributed as dist
