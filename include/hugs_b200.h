@@ -347,6 +347,17 @@ int hugs_b200_l1_ssim_backward(int C, int H, int W, const float* img1, const flo
                                const float* dmap, const float* g, float* dL_dimg1,
                                hugs_b200_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Mean SQUARED distance of every point to its 3 nearest neighbours (exact).  Replaces simple-knn's
+ * distCUDA2 (submodules/simple-knn/simple_knn.cu:185-221, spatial.cu), which hugs/models/scene.py:181
+ * uses to initialise the scene Gaussians' scales.  points float32 [P,3],
+ * mean_dist2 float32 [P]; temp: hugs_b200_knn_temp_bytes(P) bytes of device scratch.  Fewer than 4
+ * points: the missing neighbours count as FLT_MAX, as in the reference (huge or inf results).
+ * ------------------------------------------------------------------------------------------- */
+size_t hugs_b200_knn_temp_bytes(int P);
+int hugs_b200_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* temp, size_t temp_bytes,
+                             hugs_b200_stream_t stream);
+
 /* Number of kernel launches issued by this library (all host threads) since the last reset
  * (bench.py reports it as gpu_launches). */
 long long hugs_b200_launch_count(int reset);

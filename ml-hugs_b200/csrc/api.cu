@@ -766,4 +766,15 @@ int hugs_b200_l1_ssim_backward(int C, int H, int W, const float* img1, const flo
     return launch_l1_ssim_backward(C, H, W, img1, img2, dmap, g, dL_dimg1, static_cast<cudaStream_t>(stream));
 }
 
+size_t hugs_b200_knn_temp_bytes(int P) { return knn_temp_bytes(P); }
+
+int hugs_b200_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* temp, size_t temp_bytes,
+                             hugs_b200_stream_t stream) {
+    if (P < 0 || (P > 0 && (!points || !mean_dist2))) {
+        set_error("knn_mean_dist2: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_knn_mean_dist2(P, points, mean_dist2, temp, temp_bytes, static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

@@ -175,6 +175,11 @@ int launch_l1_ssim_forward(int C, int H, int W, const float* img1, const float* 
 int launch_l1_ssim_backward(int C, int H, int W, const float* img1, const float* img2, const float* dmap,
                             const float* g, float* dL_dimg1, cudaStream_t stream);
 
+// ---- 3-nearest-neighbour mean squared distance (knn.cu) -----------------------------------------
+size_t knn_temp_bytes(int P);
+int launch_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* temp, size_t temp_bytes,
+                          cudaStream_t stream);
+
 // ---- device helpers ------------------------------------------------------------------------
 #ifdef __CUDACC__
 __device__ __forceinline__ float4 ldg_f4(const float4* p) { return __ldg(p); }

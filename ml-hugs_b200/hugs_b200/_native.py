@@ -105,6 +105,9 @@ rasterize_backward_acc = _sig("hugs_b200_rasterize_backward_acc", i32, [
 l1_ssim_forward = _sig("hugs_b200_l1_ssim_forward", i32, [i32, i32, i32, fp, fp, fp, fp, fp])
 l1_ssim_backward = _sig("hugs_b200_l1_ssim_backward", i32, [i32, i32, i32, fp, fp, fp, fp, fp, fp])
 
+knn_temp_bytes = _sig("hugs_b200_knn_temp_bytes", C.c_size_t, [i32])
+knn_mean_dist2 = _sig("hugs_b200_knn_mean_dist2", i32, [i32, fp, fp, fp, C.c_size_t, fp])
+
 mark_visible = _sig("hugs_b200_mark_visible", i32, [i32, fp, fp, fp, fp, fp])
 
 geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayout)])
@@ -154,6 +157,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_scan_temp_bytes", "hugs_b200_inclusive_scan",
     "hugs_b200_lbs_forward", "hugs_b200_lbs_backward",
     "hugs_b200_l1_ssim_forward", "hugs_b200_l1_ssim_backward",
+    "hugs_b200_knn_temp_bytes", "hugs_b200_knn_mean_dist2",
 ]
 
 

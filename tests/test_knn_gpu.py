@@ -1,0 +1,64 @@
+"""distCUDA2 on the GPU against the brute-force oracle: uniform, clustered and
+degenerate clouds, sizes around the 256-point box, and 300 k points.  Tolerance 1e-6 relative (the
+three neighbours are the same; the oracle sums squares in float64)."""
+import numpy as np
+import pytest
+import torch
+
+import refutil  # noqa: F401
+from oracle import knn_oracle as KO
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(p):
+    from hugs_b200.knn import distCUDA2
+    got = distCUDA2(torch.from_numpy(p).cuda()).cpu().numpy()
+    want = KO.dist2_mean3(p)
+    fin = np.isfinite(want)
+    assert (np.isfinite(got) == fin).all()
+    assert np.abs(got[fin] - want[fin]).max() <= 1e-6 * max(float(want[fin].max()), 1e-30) if fin.any() else True
+    rel = np.abs(got[fin] - want[fin]) / np.maximum(want[fin], 1e-20)
+    assert (rel <= 1e-5).all() if fin.any() else True
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 5, 255, 256, 257, 1000, 5000])
+def test_uniform_cloud_sizes(P):
+    _check(np.random.default_rng(P).random((P, 3), dtype=np.float32) * 10 - 5)
+
+
+def test_clustered_duplicates_and_degenerate_axes():
+    rng = np.random.default_rng(7)
+    centers = rng.random((20, 3), dtype=np.float32) * 100
+    p = (centers[rng.integers(0, 20, 20000)] + rng.normal(0, 0.05, (20000, 3))).astype(np.float32)
+    p[:500] = p[500:1000]                      # exact duplicates
+    _check(p)
+    flat = rng.random((3000, 3), dtype=np.float32)
+    flat[:, 2] = 1.5                           # a plane: zero extent along z
+    _check(flat)
+    _check(np.zeros((600, 3), np.float32))     # every point identical
+
+
+def test_large_cloud_matches_oracle_on_a_sample_and_is_permutation_equivariant():
+    from hugs_b200.knn import distCUDA2
+    rng = np.random.default_rng(11)
+    P = 300_000
+    p = rng.random((P, 3), dtype=np.float32) * np.array([40, 25, 8], np.float32)
+    got = distCUDA2(torch.from_numpy(p).cuda()).cpu().numpy()
+    idx = rng.integers(0, P, 2000)
+    d = ((p[idx, None, :].astype(np.float64) - p[None, :, :].astype(np.float64)) ** 2).sum(-1)
+    d[np.arange(len(idx)), idx] = np.inf
+    want = np.sort(np.partition(d, 2, axis=1)[:, :3], axis=1).astype(np.float32).sum(1) / np.float32(3)
+    assert (np.abs(got[idx] - want) <= 1e-5 * want).all()
+    perm = rng.permutation(P)
+    got2 = distCUDA2(torch.from_numpy(p[perm]).cuda()).cpu().numpy()
+    assert np.array_equal(got2, got[perm])
+
+
+def test_signature_matches_reference_use():
+    from hugs_b200.knn import distCUDA2
+    pts = torch.rand(1234, 3, device="cuda")
+    d2 = torch.clamp_min(distCUDA2(pts), 0.0000001)    # hugs/models/scene.py:181
+    assert d2.shape == (1234,) and d2.dtype == torch.float32 and bool((d2 > 0).all())
+    with pytest.raises(RuntimeError):
+        distCUDA2(pts.cpu())
