@@ -47,6 +47,51 @@ def run(cmd):
     subprocess.check_call(cmd)
 
 
+def build_simple_knn():
+    """The reference's simple-knn extension (distCUDA2), same recipe: its own sources where they lie,
+    plain nvcc / g++, output under oracle/_ref/simple_knn/.  `-include cfloat`: simple_knn.cu uses
+    FLT_MAX without including <cfloat>."""
+    from torch.utils import cpp_extension as ce
+    knn = os.path.join(REF, "submodules", "simple-knn")
+    if not os.path.isdir(knn):
+        return
+    pkg = os.path.join(OUT, "simple_knn")
+    os.makedirs(pkg, exist_ok=True)
+    os.makedirs(OBJ, exist_ok=True)
+    target = os.path.join(pkg, "_C" + sysconfig.get_config_var("EXT_SUFFIX"))
+    srcs = [os.path.join(knn, f) for f in ("simple_knn.cu", "spatial.cu", "ext.cpp")]
+    if os.path.exists(target) and os.path.getmtime(target) > max(os.path.getmtime(f) for f in srcs) \
+            and "--force" not in sys.argv:
+        print(f"{target} is up to date")
+        return
+    incs = ["-I" + q for q in ce.include_paths()] + ["-I" + sysconfig.get_paths()["include"], "-I" + knn]
+    defs = ["-DTORCH_EXTENSION_NAME=_C", "-DTORCH_API_INCLUDE_EXTENSION_H", "-D_GLIBCXX_USE_CXX11_ABI=1"]
+    cuda_home = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    nvcc = os.path.join(cuda_home, "bin", "nvcc")
+    objs, jobs = [], []
+    for f in ("simple_knn.cu", "spatial.cu"):
+        o = os.path.join(OBJ, "knn_" + f + ".o")
+        objs.append(o)
+        jobs.append([nvcc, "-c", os.path.join(knn, f), "-o", o, "-std=c++17", "-O3", "-gencode",
+                     "arch=compute_100,code=sm_100", "--expt-relaxed-constexpr", "-include", "cfloat",
+                     "--compiler-options", "-fPIC", "-w"] + incs + defs)
+    o = os.path.join(OBJ, "knn_ext.cpp.o")
+    objs.append(o)
+    jobs.append(["g++", "-c", os.path.join(knn, "ext.cpp"), "-o", o, "-std=c++17", "-O2", "-fPIC", "-w",
+                 "-I" + os.path.join(cuda_home, "include")] + incs + defs)
+    with ThreadPoolExecutor(max_workers=3) as ex:
+        list(ex.map(run, jobs))
+    link = ["g++", "-shared", "-o", target] + objs
+    for d in ce.library_paths():
+        link += ["-L" + d, "-Wl,-rpath," + d]
+    link += ["-L" + os.path.join(cuda_home, "lib64"), "-lc10", "-ltorch", "-ltorch_cpu", "-ltorch_python",
+             "-lc10_cuda", "-ltorch_cuda", "-lcudart"]
+    run(link)
+    with open(os.path.join(pkg, "__init__.py"), "w") as f:
+        f.write("")
+    print("oracle/_ref ready:", target)
+
+
 def main():
     if not os.path.isdir(DGR):
         print(f"reference not present at {DGR}; keeping any prebuilt oracle/_ref", file=sys.stderr)
@@ -117,6 +162,10 @@ def main():
     ]:
         shutil.copyfile(os.path.join(REF, rel), os.path.join(HUGS, name))
     print("oracle/_ref ready:", target)
+    try:
+        build_simple_knn()
+    except Exception as e:  # noqa: BLE001  (the rasterizer build above is what the parity suite needs)
+        print("simple-knn reference build failed (distCUDA2 parity stays unpinned):", e, file=sys.stderr)
     return 0
 
 

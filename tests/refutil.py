@@ -33,6 +33,24 @@ def load_ref_rasterizer():
     return mod
 
 
+def ref_knn_available():
+    pkg = os.path.join(REF_DIR, "simple_knn")
+    return os.path.isdir(pkg) and any(f.startswith("_C") and f.endswith(".so") for f in os.listdir(pkg))
+
+
+def load_ref_knn():
+    """The unmodified reference simple-knn extension (oracle/_ref/simple_knn/_C*.so) -> its distCUDA2."""
+    if "ref_simple_knn_C" not in sys.modules:
+        import torch  # noqa: F401  (the extension links against libtorch)
+        pkg = os.path.join(REF_DIR, "simple_knn")
+        so = [f for f in os.listdir(pkg) if f.startswith("_C") and f.endswith(".so")][0]
+        spec = importlib.util.spec_from_file_location("_C", os.path.join(pkg, so))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        sys.modules["ref_simple_knn_C"] = mod
+    return sys.modules["ref_simple_knn_C"].distCUDA2
+
+
 def load_ref_lbs(ref_root=None):
     """The reference's lbs.py + rotations.py, with `smplx.lbs` shimmed by the reference's own
     vendored copy (hugs/datasets/neuman_utils/smpl.py:363-505) because smplx is not installable."""

@@ -62,3 +62,27 @@ def test_signature_matches_reference_use():
     assert d2.shape == (1234,) and d2.dtype == torch.float32 and bool((d2 > 0).all())
     with pytest.raises(RuntimeError):
         distCUDA2(pts.cpu())
+
+
+@pytest.mark.skipif(not refutil.ref_knn_available(), reason="oracle/_ref/simple_knn (reference build) not present")
+@pytest.mark.parametrize("P,kind", [(1000, "uniform"), (50_000, "clustered"), (1_000_000, "scene")])
+def test_live_parity_with_reference_simple_knn(P, kind):
+    """Against the unmodified reference extension on the same GPU.  The three neighbours are the same
+    set; the squared distances use the same FMA contraction, so the results are expected to be
+    bit-identical (asserted to 1e-6 relative, the count of bit differences is reported)."""
+    from hugs_b200.knn import distCUDA2
+    ref = refutil.load_ref_knn()
+    rng = np.random.default_rng(P)
+    if kind == "uniform":
+        p = rng.random((P, 3), dtype=np.float32) * 10 - 5
+    elif kind == "clustered":
+        c = rng.random((50, 3), dtype=np.float32) * 50
+        p = (c[rng.integers(0, 50, P)] + rng.normal(0, 0.1, (P, 3))).astype(np.float32)
+    else:  # the bench's scene recipe: a frustum-shaped cloud, z in (2, 30)
+        z = rng.random(P, dtype=np.float32) * 28 + 2
+        p = np.stack([z * 0.8 * (rng.random(P, dtype=np.float32) * 2 - 1), z * 0.45 * (rng.random(P, dtype=np.float32) * 2 - 1), z], 1)
+    t = torch.from_numpy(np.ascontiguousarray(p)).cuda()
+    got, want = distCUDA2(t), ref(t)
+    torch.cuda.synchronize()
+    assert float(((got - want).abs() / want.clamp_min(1e-20)).max()) <= 1e-6
+    print("bit-different results: %d of %d" % (int((got.view(torch.int32) != want.view(torch.int32)).sum()), P))
