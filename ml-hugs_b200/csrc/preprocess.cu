@@ -124,7 +124,7 @@ __device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float s
 
 // SH rows staged in shared memory: 192 B per Gaussian padded to 208 B (52 words), so that the
 // 128-bit reads of a quarter warp (one row per lane) fall in disjoint banks.
-constexpr int kPreThreads = 256;
+constexpr int kPreThreads = 128;
 constexpr int kShRowBytes = 208;
 constexpr int kPreSmemBytes = kPreThreads * kShRowBytes;
 
@@ -143,7 +143,7 @@ __device__ __forceinline__ void cp_async_wait_all() {
 //     moves 16-byte word 32 j + l of it with cp.async (global -> shared, no registers, all twelve
 //     copies of a lane in flight at once), so every request is 512 contiguous bytes minus the rows of
 //     culled Gaussians, and each thread then reads its own row out of shared memory.
-__global__ void __launch_bounds__(kPreThreads, 3) preprocess_kernel(const PreprocessArgs a) {
+__global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const PreprocessArgs a) {
     extern __shared__ __align__(16) unsigned char s_rows[];  // [256][208 B] SH rows (vec4 path)
     __shared__ float s_cam[36];  // view[16], proj[16], campos[3]
     if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(a.view + threadIdx.x);

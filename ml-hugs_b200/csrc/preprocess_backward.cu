@@ -134,7 +134,7 @@ __device__ __forceinline__ void sh_backward(int deg, const float* sh, float ox, 
     dmean_z += (-ox * oz * ddir_x - oy * oz * ddir_y + (sum2 - oz * oz) * ddir_z) * invsum32;
 }
 
-constexpr int kPbThreads = 256;
+constexpr int kPbThreads = 128;
 constexpr int kPbRowBytes = 208;  // 192-B SH row padded to 52 words: conflict-free 128-bit row access
 constexpr int kPbSmemBytes = kPbThreads * kPbRowBytes;
 
@@ -163,7 +163,7 @@ __device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c,
 //   * dL/dsh is assembled row by row in the same shared-memory slots and written by the whole warp
 //     as twelve 512-byte contiguous stores (zero rows for culled Gaussians included), instead of
 //     twelve 16-byte stores per thread at a 192-byte stride.
-__global__ void __launch_bounds__(kPbThreads, 2) preprocess_backward_kernel(const PreBwdArgs a) {
+__global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(const PreBwdArgs a) {
     extern __shared__ __align__(16) unsigned char s_rows[];  // [256][208 B] SH rows / dL_dsh rows (vec4 path)
     __shared__ float s_cam[36];
     if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(a.view + threadIdx.x);
