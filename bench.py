@@ -622,12 +622,13 @@ def main():
     dominant = max(stages, key=lambda k: stages[k]["ms"]) if stages else None
     roofline = None
     # DRAM bytes per launch from the committed ncu --set full capture of this workload (null for others)
-    traffic, traffic_src = None, None
+    traffic, traffic_src, issue_pct = None, None, {}
     try:
         if args.workload == "human_scene_1080p":
             with open(os.path.join(ROOT, "profiles", "ncu_dram_traffic.json")) as f:
                 tj = json.load(f)
             traffic, traffic_src = tj["bytes_per_frame"], tj["source"]
+            issue_pct = tj.get("issue_active_pct", {})
             for name in stages:
                 if name in traffic:
                     stages[name]["dram_traffic"] = int(traffic[name])
@@ -639,6 +640,7 @@ def main():
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": s["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": s["frac"], "traffic": int(traffic[dominant]) if traffic and dominant in traffic else None,
                     "traffic_source": traffic_src,
+                    "issue_active_pct_ncu": issue_pct.get(dominant),
                     "limiter": ("instruction issue (ncu: 86-92 % issue-slot active, DRAM traffic far below the "
                                 "algorithmic gather bytes because a tile's Gaussians are served by L2): see "
                                 "DESIGN.md section 5; the HBM-bound stages are in `stages`") if issue_bound else "hbm",
