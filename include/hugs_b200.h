@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 4
+#define HUGS_B200_ABI_VERSION 5
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -357,6 +357,42 @@ int hugs_b200_l1_ssim_backward(int C, int H, int W, const float* img1, const flo
 size_t hugs_b200_knn_temp_bytes(int P);
 int hugs_b200_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* temp, size_t temp_bytes,
                              hugs_b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Densification statistics after a backward pass, one launch, no host sync.
+ * For every i < n with radii[i] > 0 (the reference's visibility_filter, gs_renderer.py:156):
+ *   max_radii2D[i]        = max(max_radii2D[i], radii[i])          gs_trainer.py:406-411, :429-435
+ *   xyz_gradient_accum[i] += ||grad_means2D[i, 0:2]||              scene.py:460-461
+ *   denom[i]              += 1                                     scene.py:462
+ * radii int32 [n]; grad_means2D float32 rows of grad_stride floats (3 for the rasterizer's
+ * dL_dmeans2D); the three statistics float32 [n] (the reference keeps them as float tensors, [n] or
+ * [n,1]).  Any of the three statistics may be NULL (skipped).
+ * ------------------------------------------------------------------------------------------- */
+int hugs_b200_densification_stats(int n, const int* radii, const float* grad_means2D, int grad_stride,
+                                  float* xyz_gradient_accum, float* denom, float* max_radii2D,
+                                  hugs_b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Tri-plane feature sampling.  Replaces TriPlane.forward,
+ * hugs/models/modules/triplane.py:25-39: g = ((xyz - center)/scale + 0.5)*2 - 1, then three bilinear
+ * grid samples (zero padding, align_corners=True) of plane_xy at (g.x,g.y), plane_xz at (g.x,g.z),
+ * plane_yz at (g.y,g.z) -- the first coordinate indexes the LAST plane axis, as F.grid_sample does --
+ * concatenated to features [N, 3C].
+ * Planes are logically [1,C,resA,resB] (xy: resX,resY; xz: resX,resZ; yz: resY,resZ) and are passed
+ * CHANNELS-LAST, i.e. as dense [resA][resB][C] float32 (torch.channels_last of the same tensor).
+ * out_of_range (int32 on the device, may be NULL) is OR-ed with 1 when a normalised coordinate leaves
+ * [-eps, 1+eps] -- the condition the reference asserts on (triplane.py:28).
+ * backward: dL_dplane_* (same layout) are ACCUMULATED into (zero them first; NULL skips the planes);
+ * dL_dxyz [N,3] is written (NULL skips it).
+ * ------------------------------------------------------------------------------------------- */
+int hugs_b200_triplane_forward(int N, int C, int resX, int resY, int resZ, const float* plane_xy,
+                               const float* plane_xz, const float* plane_yz, const float* xyz, float center,
+                               float scale, float eps, float* features, int* out_of_range,
+                               hugs_b200_stream_t stream);
+int hugs_b200_triplane_backward(int N, int C, int resX, int resY, int resZ, const float* plane_xy,
+                                const float* plane_xz, const float* plane_yz, const float* xyz, float center,
+                                float scale, const float* dL_dfeatures, float* dL_dplane_xy, float* dL_dplane_xz,
+                                float* dL_dplane_yz, float* dL_dxyz, hugs_b200_stream_t stream);
 
 /* Number of kernel launches issued by this library (all host threads) since the last reset
  * (bench.py reports it as gpu_launches). */

@@ -777,4 +777,42 @@ int hugs_b200_knn_mean_dist2(int P, const float* points, float* mean_dist2, void
     return launch_knn_mean_dist2(P, points, mean_dist2, temp, temp_bytes, static_cast<cudaStream_t>(stream));
 }
 
+int hugs_b200_densification_stats(int n, const int* radii, const float* grad_means2D, int grad_stride,
+                                  float* xyz_gradient_accum, float* denom, float* max_radii2D,
+                                  hugs_b200_stream_t stream) {
+    if (n < 0 || (n > 0 && (!radii || (xyz_gradient_accum && (!grad_means2D || grad_stride < 2))))) {
+        set_error("densification_stats: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_densification_stats(n, radii, grad_means2D, grad_stride, xyz_gradient_accum, denom, max_radii2D,
+                                      static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_triplane_forward(int N, int C, int resX, int resY, int resZ, const float* plane_xy,
+                               const float* plane_xz, const float* plane_yz, const float* xyz, float center,
+                               float scale, float eps, float* features, int* out_of_range,
+                               hugs_b200_stream_t stream) {
+    if (N < 0 || C <= 0 || resX <= 0 || resY <= 0 || resZ <= 0 || scale == 0.f ||
+        (N > 0 && (!plane_xy || !plane_xz || !plane_yz || !xyz || !features))) {
+        set_error("triplane_forward: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_triplane_forward(N, C, resX, resY, resZ, plane_xy, plane_xz, plane_yz, xyz, center, scale, eps,
+                                   features, out_of_range, static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_triplane_backward(int N, int C, int resX, int resY, int resZ, const float* plane_xy,
+                                const float* plane_xz, const float* plane_yz, const float* xyz, float center,
+                                float scale, const float* dL_dfeatures, float* dL_dplane_xy, float* dL_dplane_xz,
+                                float* dL_dplane_yz, float* dL_dxyz, hugs_b200_stream_t stream) {
+    if (N < 0 || C <= 0 || resX <= 0 || resY <= 0 || resZ <= 0 || scale == 0.f ||
+        (N > 0 && (!plane_xy || !plane_xz || !plane_yz || !xyz || !dL_dfeatures))) {
+        set_error("triplane_backward: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_triplane_backward(N, C, resX, resY, resZ, plane_xy, plane_xz, plane_yz, xyz, center, scale,
+                                    dL_dfeatures, dL_dplane_xy, dL_dplane_xz, dL_dplane_yz, dL_dxyz,
+                                    static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

@@ -180,6 +180,18 @@ size_t knn_temp_bytes(int P);
 int launch_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* temp, size_t temp_bytes,
                           cudaStream_t stream);
 
+// ---- renderer post-ops (post_ops.cu) ------------------------------------------------------------
+int launch_densification_stats(int n, const int* radii, const float* grad, int grad_stride, float* grad_accum,
+                               float* denom, float* max_radii, cudaStream_t stream);
+
+// ---- tri-plane sampling (triplane.cu) ------------------------------------------------------------
+int launch_triplane_forward(int N, int C, int resX, int resY, int resZ, const float* plane_xy, const float* plane_xz,
+                            const float* plane_yz, const float* xyz, float center, float scale, float eps,
+                            float* out, int* flag, cudaStream_t stream);
+int launch_triplane_backward(int N, int C, int resX, int resY, int resZ, const float* plane_xy, const float* plane_xz,
+                             const float* plane_yz, const float* xyz, float center, float scale, const float* gout,
+                             float* g_xy, float* g_xz, float* g_yz, float* gxyz, cudaStream_t stream);
+
 // ---- device helpers ------------------------------------------------------------------------
 #ifdef __CUDACC__
 __device__ __forceinline__ float4 ldg_f4(const float4* p) { return __ldg(p); }

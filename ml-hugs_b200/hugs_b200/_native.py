@@ -108,6 +108,14 @@ l1_ssim_backward = _sig("hugs_b200_l1_ssim_backward", i32, [i32, i32, i32, fp, f
 knn_temp_bytes = _sig("hugs_b200_knn_temp_bytes", C.c_size_t, [i32])
 knn_mean_dist2 = _sig("hugs_b200_knn_mean_dist2", i32, [i32, fp, fp, fp, C.c_size_t, fp])
 
+densification_stats = _sig("hugs_b200_densification_stats", i32, [i32, fp, fp, i32, fp, fp, fp, fp])
+
+f32 = C.c_float
+triplane_forward = _sig("hugs_b200_triplane_forward", i32,
+                        [i32, i32, i32, i32, i32, fp, fp, fp, fp, f32, f32, f32, fp, fp, fp])
+triplane_backward = _sig("hugs_b200_triplane_backward", i32,
+                         [i32, i32, i32, i32, i32, fp, fp, fp, fp, f32, f32, fp, fp, fp, fp, fp, fp])
+
 mark_visible = _sig("hugs_b200_mark_visible", i32, [i32, fp, fp, fp, fp, fp])
 
 geom_layout_of = _sig("hugs_b200_geom_layout_of", i32, [i32, C.POINTER(GeomLayout)])
@@ -158,6 +166,8 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_lbs_forward", "hugs_b200_lbs_backward",
     "hugs_b200_l1_ssim_forward", "hugs_b200_l1_ssim_backward",
     "hugs_b200_knn_temp_bytes", "hugs_b200_knn_mean_dist2",
+    "hugs_b200_densification_stats",
+    "hugs_b200_triplane_forward", "hugs_b200_triplane_backward",
 ]
 
 

@@ -77,3 +77,20 @@ def test_lbs_extra_keeps_reference_signature():
 
     assert list(inspect.signature(hugs_b200.lbs_extra).parameters) == [
         "A", "v_shaped", "posedirs", "lbs_weights", "pose", "disable_posedirs", "pose2rot"]
+
+
+def test_renderer_glue_keeps_the_reference_signatures():
+    """hugs/renderer/gs_renderer.py:19-28 (render_human_scene) and :103 (render)."""
+    from hugs_b200 import renderer
+
+    assert list(inspect.signature(renderer.render_human_scene).parameters) == [
+        "data", "human_gs_out", "scene_gs_out", "bg_color", "human_bg_color", "scaling_modifier", "render_mode",
+        "render_human_separate"]
+    p = inspect.signature(renderer.render_human_scene).parameters
+    assert p["render_mode"].default == "human_scene" and p["render_human_separate"].default is False
+    assert list(inspect.signature(renderer.render).parameters) == [
+        "means3D", "feats", "opacity", "scales", "rotations", "data", "scaling_modifier", "bg_color",
+        "active_sh_degree"]
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        renderer.render(torch.zeros(2, 3), torch.zeros(2, 3), torch.zeros(2, 1), torch.zeros(2, 3),
+                        torch.zeros(2, 4), {})

@@ -1,0 +1,155 @@
+"""Renderer glue + post-ops against a torch restatement of the reference's own lines
+(hugs/renderer/gs_renderer.py:19-161, hugs/trainer/gs_trainer.py:406-411, hugs/models/scene.py:460-462).
+The densification statistics are floating point: tolerance 1e-6 relative on the accumulated norms;
+the max radii and the counters are exact."""
+import pytest
+import torch
+
+import refutil  # noqa: F401
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def _data_of(sc):
+    return dict(image_height=sc["image_height"], image_width=sc["image_width"], fovx=sc["fovx"], fovy=sc["fovy"],
+                world_view_transform=sc["viewmatrix"], full_proj_transform=sc["projmatrix"],
+                camera_center=sc["campos"])
+
+
+def _gs_out(sc, lo, hi, grad=True):
+    names = dict(xyz="means3D", shs="shs", opacity="opacity", scales="scales", rotq="rotations")
+    out = {k: sc[v][lo:hi].detach().clone().requires_grad_(grad) for k, v in names.items()}
+    out["active_sh_degree"] = sc["degree"]
+    return out
+
+
+def test_render_is_rasterizer_plus_clamp_and_filter():
+    import diff_gaussian_rasterization as dgr
+    from hugs_b200 import renderer
+    sc = scenes.make_scene(3000, 2000, 320, 200, 300.0, seed=11, device="cuda")
+    ref = scenes.run_module(sc, dgr, backward=False)
+    pkg = renderer.render(sc["means3D"], sc["shs"], sc["opacity"], sc["scales"], sc["rotations"], _data_of(sc),
+                          bg_color=sc["bg"], active_sh_degree=sc["degree"])
+    assert set(pkg) == {"render", "viewspace_points", "visibility_filter", "radii"}
+    assert torch.equal(pkg["render"], ref["color"].clamp(0.0, 1.0))
+    assert torch.equal(pkg["radii"], ref["radii"])
+    assert torch.equal(pkg["visibility_filter"], ref["radii"] > 0)
+    assert pkg["viewspace_points"].shape == sc["means3D"].shape
+
+
+def test_render_precomputed_colors_and_default_background():
+    from hugs_b200 import renderer
+    sc = scenes.make_scene(1500, 0, 160, 120, 150.0, seed=12, device="cuda")
+    rgb = torch.rand(1500, 3, device="cuda")
+    pkg = renderer.render(sc["means3D"], rgb, sc["opacity"], sc["scales"], sc["rotations"], _data_of(sc))
+    assert pkg["render"].shape == (3, 120, 160)
+    assert float(pkg["render"].min()) >= 0.0 and float(pkg["render"].max()) <= 1.0
+
+
+@pytest.mark.parametrize("separate", [False, True])
+def test_render_human_scene_modes(separate):
+    from hugs_b200 import renderer
+    n_h, n_s = 1800, 2600
+    sc = scenes.make_scene(n_s, n_h, 320, 200, 300.0, seed=13, device="cuda")
+    data = _data_of(sc)
+    human, scene = _gs_out(sc, 0, n_h), _gs_out(sc, n_h, n_h + n_s)
+    hbg = torch.tensor([1.0, 1.0, 1.0], device="cuda")
+    pkg = renderer.render_human_scene(data, human, scene, sc["bg"], human_bg_color=hbg,
+                                      render_mode="human_scene", render_human_separate=separate)
+    whole = renderer.render(sc["means3D"], sc["shs"], sc["opacity"], sc["scales"], sc["rotations"], data,
+                            bg_color=sc["bg"], active_sh_degree=sc["degree"])
+    assert torch.equal(pkg["render"], whole["render"])
+    assert torch.equal(pkg["scene_radii"], whole["radii"][n_h:])
+    assert torch.equal(pkg["scene_visibility_filter"], whole["radii"][n_h:] > 0)
+    if separate:
+        honly = renderer.render(human["xyz"], human["shs"], human["opacity"], human["scales"], human["rotq"], data,
+                                bg_color=hbg, active_sh_degree=sc["degree"])
+        assert torch.equal(pkg["human_img"], honly["render"])
+        assert torch.equal(pkg["human_radii"], honly["radii"])
+    else:
+        assert "human_img" not in pkg
+        assert torch.equal(pkg["human_radii"], whole["radii"][:n_h])
+    # gradients reach both models through the concatenation, and viewspace_points keeps its .grad
+    loss = (pkg["render"] * sc["dL_dcolor"]).sum()
+    if separate:
+        loss = loss + pkg["human_img"].sum()
+    loss.backward()
+    assert pkg["viewspace_points"].grad is not None and pkg["viewspace_points"].grad.shape == (n_h + n_s, 3)
+    for k in ("xyz", "shs", "opacity", "scales", "rotq"):
+        assert human[k].grad is not None and scene[k].grad is not None
+        assert float(human[k].grad.abs().sum()) > 0 and float(scene[k].grad.abs().sum()) > 0
+
+    only_h = renderer.render_human_scene(data, human, scene, sc["bg"], render_mode="human")
+    assert torch.equal(only_h["human_radii"], only_h["radii"]) and only_h["radii"].shape[0] == n_h
+    only_s = renderer.render_human_scene(data, human, scene, sc["bg"], render_mode="scene")
+    assert torch.equal(only_s["scene_visibility_filter"], only_s["radii"] > 0) and only_s["radii"].shape[0] == n_s
+    with pytest.raises(ValueError, match="Unknown render mode"):
+        renderer.render_human_scene(data, human, scene, sc["bg"], render_mode="both")
+
+
+def _reference_stats(radii, grad, acc, den, mx):
+    """The reference's lines, verbatim semantics (boolean-mask indexing)."""
+    vis = radii > 0
+    mx[vis] = torch.max(mx[vis], radii[vis])
+    acc[vis] += torch.norm(grad[:vis.shape[0]][vis, :2], dim=-1, keepdim=True)
+    den[vis] += 1
+
+
+@pytest.mark.parametrize("n,n_grad", [(0, 0), (1, 1), (1000, 1000), (70001, 90000), (1_000_003, 1_000_003)])
+def test_densification_stats_match_reference_lines(n, n_grad):
+    from hugs_b200 import renderer
+    g = torch.Generator(device="cuda").manual_seed(n + 1)
+    radii = torch.randint(-1, 40, (n,), generator=g, device="cuda", dtype=torch.int32).clamp_min(0)
+    grad = torch.randn(n_grad, 3, generator=g, device="cuda") * 1e-3
+    acc = torch.rand(n, 1, generator=g, device="cuda")
+    den = torch.randint(0, 9, (n, 1), generator=g, device="cuda").float()
+    mx = torch.randint(0, 40, (n,), generator=g, device="cuda").float()
+    r_acc, r_den, r_mx = acc.clone(), den.clone(), mx.clone()
+    _reference_stats(radii, grad, r_acc, r_den, r_mx)
+    renderer.add_densification_stats(radii, grad, xyz_gradient_accum=acc, denom=den, max_radii2D=mx)
+    assert torch.equal(mx, r_mx)
+    assert torch.equal(den, r_den)
+    assert torch.allclose(acc, r_acc, rtol=1e-6, atol=0.0)
+    invisible = radii <= 0
+    if n:
+        assert torch.equal(acc[invisible], r_acc[invisible])
+
+
+def test_densification_stats_after_a_render_on_slices():
+    """Scene statistics from the scene slice of radii and the FIRST n_scene gradient rows (the
+    reference's grad[:update_filter.shape[0]], scene.py:461), human ones from the human slice."""
+    from hugs_b200 import renderer
+    n_h, n_s = 1200, 2200
+    sc = scenes.make_scene(n_s, n_h, 320, 200, 300.0, seed=14, device="cuda")
+    human, scene = _gs_out(sc, 0, n_h), _gs_out(sc, n_h, n_h + n_s)
+    pkg = renderer.render_human_scene(_data_of(sc), human, scene, sc["bg"])
+    (pkg["render"] * sc["dL_dcolor"]).sum().backward()
+    grad = pkg["viewspace_points"].grad
+    for radii, n in ((pkg["scene_radii"], n_s), (pkg["human_radii"], n_h)):
+        acc, den, mx = (torch.zeros(n, 1, device="cuda"), torch.zeros(n, 1, device="cuda"),
+                        torch.zeros(n, device="cuda"))
+        r = [acc.clone(), den.clone(), mx.clone()]
+        _reference_stats(radii, grad, *r)
+        renderer.add_densification_stats(radii, grad, acc, den, mx)
+        assert torch.equal(mx, r[2]) and torch.equal(den, r[1])
+        assert torch.allclose(acc, r[0], rtol=1e-6, atol=0.0)
+        assert float(den.sum()) > 0
+
+
+def test_densification_stats_optional_outputs_and_errors():
+    from hugs_b200 import renderer
+    radii = torch.tensor([3, 0, 7], dtype=torch.int32, device="cuda")
+    mx = torch.tensor([5.0, 9.0, 1.0], device="cuda")
+    renderer.add_densification_stats(radii, None, max_radii2D=mx)
+    assert mx.tolist() == [5.0, 9.0, 7.0]
+    den = torch.zeros(3, device="cuda")
+    renderer.add_densification_stats(radii, None, denom=den)
+    assert den.tolist() == [1.0, 0.0, 1.0]
+    with pytest.raises(RuntimeError, match="viewspace_point_grad"):
+        renderer.add_densification_stats(radii, torch.zeros(2, 3, device="cuda"),
+                                         xyz_gradient_accum=torch.zeros(3, device="cuda"))
+    with pytest.raises(RuntimeError, match="int32"):
+        renderer.add_densification_stats(radii.float(), None, denom=den)
+    with pytest.raises(RuntimeError, match="float32"):
+        renderer.add_densification_stats(radii, None, denom=den.double())

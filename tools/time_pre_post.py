@@ -1,0 +1,114 @@
+"""GPU-box timing of the two widening rows either side of the path:
+  * tri-plane sampling, forward and forward+backward, 32 features, 256^3, 110 210 points, against the
+    reference's three F.grid_sample calls + cat on the same GPU.  Algorithmic HBM bytes: forward
+    N*(12 + 3C*4) + the planes once; backward N*(12 + 3C*4 + 12) + plane gradients zeroed and written
+    (2x) + the planes once.
+  * densification statistics on 1 M Gaussians against the reference's boolean-mask lines.
+Prints one JSON line per op."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "ml-hugs_b200"), os.path.join(ROOT, "tests")):
+    sys.path.insert(0, p)
+import torch
+import torch.nn.functional as F
+
+from hugs_b200 import renderer
+from hugs_b200.triplane import TriPlane
+
+
+def timeit(fn, iters=50, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def peak_gbs():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6551.4
+
+
+def triplane():
+    n, C, R = 110210, 32, 256
+    tp = TriPlane(check_range=False).cuda()
+    x = (torch.rand(n, 3, device="cuda") * 2 - 1).requires_grad_(True)
+    w = torch.randn(n, 3 * C, device="cuda")
+    planes = [p.detach().clone().contiguous().requires_grad_(True) for p in tp.parameters()]
+
+    def ours_f():
+        with torch.no_grad():
+            return tp(x)
+
+    def ours_fb():
+        x.grad = None
+        for p in tp.parameters():
+            p.grad = None
+        tp(x).backward(w)
+
+    def ref_fwd():
+        c = (((x - 0.0) / 2.0 + 0.5) * 2 - 1).reshape(1, -1, 1, 3)
+        return torch.cat([F.grid_sample(pl, c[..., idx], align_corners=True)[0, :, :, 0].transpose(0, 1)
+                          for pl, idx in zip(planes, ([0, 1], [0, 2], [1, 2]))], dim=1)
+
+    def ref_f():
+        with torch.no_grad():
+            return ref_fwd()
+
+    def ref_fb():
+        x.grad = None
+        for p in planes:
+            p.grad = None
+        ref_fwd().backward(w)
+
+    t = {k: timeit(f) for k, f in (("ours_f", ours_f), ("ours_fb", ours_fb), ("ref_f", ref_f), ("ref_fb", ref_fb))}
+    plane_bytes = 3 * C * R * R * 4
+    fwd_bytes = n * (12 + 3 * C * 4) + plane_bytes
+    bwd_bytes = n * (12 + 3 * C * 4 + 12) + 3 * plane_bytes
+    peak = peak_gbs()
+    t_b = max(t["ours_fb"] - t["ours_f"], 1e-6)
+    print(json.dumps({"op": "triplane 32x256^3, 110210 points", "ours_fwd_ms": round(t["ours_f"], 4),
+                      "ours_fwd_bwd_ms": round(t["ours_fb"], 4), "torch_reference_fwd_ms": round(t["ref_f"], 4),
+                      "torch_reference_fwd_bwd_ms": round(t["ref_fb"], 4),
+                      "speedup_fwd": round(t["ref_f"] / t["ours_f"], 2),
+                      "speedup_fwd_bwd": round(t["ref_fb"] / t["ours_fb"], 2),
+                      "fwd_algorithmic_bytes": fwd_bytes, "fwd_hbm_frac": round(fwd_bytes / t["ours_f"] / 1e6 / peak, 4),
+                      "bwd_algorithmic_bytes": bwd_bytes, "bwd_hbm_frac_incl_host": round(bwd_bytes / t_b / 1e6 / peak, 4)}))
+
+
+def stats():
+    n = 1_000_000
+    radii = torch.randint(-20, 40, (n,), device="cuda", dtype=torch.int32).clamp_min(0)
+    grad = torch.randn(n, 3, device="cuda") * 1e-3
+    acc, den, mx = torch.zeros(n, 1, device="cuda"), torch.zeros(n, 1, device="cuda"), torch.zeros(n, device="cuda")
+
+    def ours():
+        renderer.add_densification_stats(radii, grad, acc, den, mx)
+
+    def ref():
+        vis = radii > 0
+        mx[vis] = torch.max(mx[vis], radii[vis])
+        acc[vis] += torch.norm(grad[:vis.shape[0]][vis, :2], dim=-1, keepdim=True)
+        den[vis] += 1
+
+    t_o, t_r = timeit(ours), timeit(ref)
+    vis = int((radii > 0).sum())
+    nbytes = 4 * n + vis * (8 + 24)
+    print(json.dumps({"op": "densification stats, 1M Gaussians, %d visible" % vis, "ours_ms": round(t_o, 4),
+                      "torch_reference_ms": round(t_r, 4), "speedup": round(t_r / t_o, 2),
+                      "algorithmic_bytes": nbytes, "hbm_frac": round(nbytes / t_o / 1e6 / peak_gbs(), 4)}))
+
+
+if __name__ == "__main__":
+    triplane()
+    stats()
