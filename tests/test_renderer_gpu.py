@@ -153,3 +153,26 @@ def test_densification_stats_optional_outputs_and_errors():
         renderer.add_densification_stats(radii.float(), None, denom=den)
     with pytest.raises(RuntimeError, match="float32"):
         renderer.add_densification_stats(radii, None, denom=den.double())
+
+
+def test_checkpoint_and_ply_assets_render_like_the_tensors_they_hold(tmp_path):
+    """scene_*.pth / *_splat.ply -> scene_gs_out -> render_human_scene(mode='scene') gives the image of
+    the same Gaussians passed directly (N4 loaders feeding the path)."""
+    from hugs_b200 import checkpoint, ply, renderer
+    n = 4000
+    sc = scenes.make_scene(n, 0, 320, 200, 300.0, seed=15, device="cuda")
+    raw = dict(xyz=sc["means3D"], features_dc=sc["shs"][:, :1].contiguous(), features_rest=sc["shs"][:, 1:].contiguous(),
+               scaling=torch.log(sc["scales"]), rotation=sc["rotations"] * 1.7,
+               opacity=torch.log(sc["opacity"] / (1 - sc["opacity"])))
+    p_ckpt, p_ply = str(tmp_path / "scene_final.pth"), str(tmp_path / "scene_final_splat.ply")
+    checkpoint.save_scene_checkpoint(p_ckpt, checkpoint.make_scene_state(**{k: v.cpu() for k, v in raw.items()}))
+    ply.save_ply(p_ply, raw["xyz"], raw["features_dc"], raw["features_rest"], raw["opacity"], raw["scaling"],
+                 raw["rotation"])
+    direct = checkpoint.scene_gs_out_from_state(raw)
+    want = renderer.render_human_scene(_data_of(sc), None, direct, sc["bg"], render_mode="scene")["render"]
+    from_ckpt, _ = checkpoint.load_scene_checkpoint(p_ckpt)
+    from_ply = checkpoint.scene_gs_out_from_ply(p_ply)
+    for gs in (from_ckpt, from_ply):
+        got = renderer.render_human_scene(_data_of(sc), None, gs, sc["bg"], render_mode="scene")
+        assert torch.equal(got["render"], want)
+        assert int(got["scene_visibility_filter"].sum()) > 0
