@@ -136,3 +136,34 @@ def sum_over_ranks(values: Iterable[float], device=None) -> List[float]:
     t = torch.tensor(vals, dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return [float(x) for x in t.tolist()]
+
+
+class DensificationStatsSync:
+    """Keeps the reference's per-view densification statistics exact under view-batch data parallelism
+    (SURVEY.md 8(e) caveat).  hugs/models/scene.py:460-462 and hugs/trainer/gs_trainer.py:406-411 update
+    xyz_gradient_accum (+= norm), denom (+= 1) and max_radii2D (max) once per rendered view; with the
+    views of a step spread over ranks, each rank accumulates ITS views into per-step buffers, and
+    `finish_step` exchanges them: one allreduce(SUM) over [step_accum | step_denom] and one
+    allreduce(MAX) over max_radii2D, then folds the sums into the running totals.  Every rank ends the
+    step with the statistics a single process would have after all the step's views."""
+
+    def __init__(self, n: int, device=None):
+        self.n = int(n)
+        self.flat = torch.zeros(2 * self.n, dtype=torch.float32, device=device)
+        self.step_accum = self.flat[:self.n].view(self.n, 1)
+        self.step_denom = self.flat[self.n:].view(self.n, 1)
+
+    def begin_step(self):
+        self.flat.zero_()
+
+    def add_view(self, radii, viewspace_point_grad, max_radii2D):
+        """One rendered view of this rank (CUDA): the fused statistics kernel into the step buffers."""
+        from . import renderer
+        renderer.add_densification_stats(radii, viewspace_point_grad, self.step_accum, self.step_denom, max_radii2D)
+
+    def finish_step(self, xyz_gradient_accum, denom, max_radii2D, group=None):
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+            dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX, group=group)
+        xyz_gradient_accum += self.step_accum.view_as(xyz_gradient_accum)
+        denom += self.step_denom.view_as(denom)

@@ -62,7 +62,12 @@ class _TriPlaneSample(torch.autograd.Function):
         need_p = any(ctx.needs_input_grad[1:4])
         g = g_out.detach().float().contiguous()
         gx = torch.empty_like(pts) if need_x else None
-        gp = [torch.zeros_like(p) for p in (pxy, pxz, pyz)] if need_p else [None, None, None]
+        if need_p:      # one allocation and one memset for the three plane gradients
+            sizes = [p.numel() for p in (pxy, pxz, pyz)]
+            flat = torch.zeros(sum(sizes), dtype=torch.float32, device=device)
+            gp = [c.view(p.shape) for c, p in zip(flat.split(sizes), (pxy, pxz, pyz))]
+        else:
+            gp = [None, None, None]
         with torch.cuda.device(device):
             rc = N.triplane_backward(n, Cn, resX, resY, resZ, pxy.data_ptr(), pxz.data_ptr(), pyz.data_ptr(),
                                      N.ptr(pts), center, scale, N.ptr(g), N.ptr(gp[0]), N.ptr(gp[1]), N.ptr(gp[2]),

@@ -98,3 +98,53 @@ def test_flat_grad_buffer_views_and_alignment():
     assert float(buf.flat.abs().sum()) == 0.0
     with pytest.raises(ValueError):
         dp.FlatGradBuffer({"x": torch.zeros(3, dtype=torch.float64, requires_grad=True)})
+
+
+def _view_stats(view, n=40):
+    g = torch.Generator().manual_seed(100 + view)
+    radii = torch.randint(-3, 30, (n,), generator=g, dtype=torch.int32).clamp_min(0)
+    grad = torch.randn(n, 3, generator=g)
+    return radii, grad
+
+
+def _apply_reference_lines(radii, grad, acc, den, mx):
+    vis = radii > 0                                     # gs_renderer.py:156
+    mx[vis] = torch.max(mx[vis], radii[vis].float())    # gs_trainer.py:406-411
+    acc[vis] += torch.norm(grad[vis, :2], dim=-1, keepdim=True)   # scene.py:460-461
+    den[vis] += 1                                       # scene.py:462
+
+
+def _stats_worker(rank, world, port, n_views, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "ml-hugs_b200"))
+    from hugs_b200 import dp
+
+    dp.init_from_env("gloo")
+    n = 40
+    acc, den, mx = torch.full((n, 1), 0.5), torch.ones(n, 1), torch.full((n,), 2.0)
+    sync = dp.DensificationStatsSync(n)
+    for step in range(2):
+        sync.begin_step()
+        for v in dp.shard_views(n_views, rank, world):
+            radii, grad = _view_stats(10 * step + v)
+            _apply_reference_lines(radii, grad, sync.step_accum, sync.step_denom, mx)   # CPU stand-in of add_view
+        sync.finish_step(acc, den, mx)
+    torch.save({"acc": acc, "den": den, "mx": mx}, out + str(rank))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_views", [4, 5])
+def test_densification_stats_sync_equals_single_process(tmp_path, n_views):
+    out = str(tmp_path / "stats")
+    mp.spawn(_stats_worker, args=(2, _free_port(), n_views, out), nprocs=2, join=True)
+    n = 40
+    acc, den, mx = torch.full((n, 1), 0.5), torch.ones(n, 1), torch.full((n,), 2.0)
+    for step in range(2):
+        for v in range(n_views):
+            _apply_reference_lines(*_view_stats(10 * step + v), acc, den, mx)
+    for rank in range(2):
+        got = torch.load(out + str(rank))
+        assert torch.equal(got["den"], den) and torch.equal(got["mx"], mx)
+        assert torch.allclose(got["acc"], acc, rtol=1e-6, atol=1e-6)

@@ -176,3 +176,23 @@ def test_checkpoint_and_ply_assets_render_like_the_tensors_they_hold(tmp_path):
         got = renderer.render_human_scene(_data_of(sc), None, gs, sc["bg"], render_mode="scene")
         assert torch.equal(got["render"], want)
         assert int(got["scene_visibility_filter"].sum()) > 0
+
+
+def test_stats_sync_single_process_two_views():
+    """dp.DensificationStatsSync on the GPU (world size 1: no exchange): two views of a step give the
+    statistics of the reference's lines applied view after view."""
+    from hugs_b200 import dp
+    n = 5000
+    g = torch.Generator(device="cuda").manual_seed(21)
+    acc, den, mx = torch.zeros(n, 1, device="cuda"), torch.zeros(n, 1, device="cuda"), torch.zeros(n, device="cuda")
+    r = [acc.clone(), den.clone(), mx.clone()]
+    sync = dp.DensificationStatsSync(n, device="cuda")
+    sync.begin_step()
+    for _ in range(2):
+        radii = torch.randint(-5, 50, (n,), generator=g, device="cuda", dtype=torch.int32).clamp_min(0)
+        grad = torch.randn(n, 3, generator=g, device="cuda")
+        sync.add_view(radii, grad, mx)
+        _reference_stats(radii, grad, *r)
+    sync.finish_step(acc, den, mx)
+    assert torch.equal(mx, r[2]) and torch.equal(den, r[1])
+    assert torch.allclose(acc, r[0], rtol=1e-6, atol=0.0)
