@@ -90,115 +90,100 @@ __global__ void __launch_bounds__(kDupThreads)
                             const float2* __restrict__ means2D, const int* __restrict__ radii,
                             uint64_t* __restrict__ pairs, unsigned grid_x, unsigned grid_y, uint32_t cap,
                             const SortPassPlan plan, uint32_t* __restrict__ hist) {
-    __shared__ uint32_t s_off[kDupThreads + 1];
-    __shared__ uint32_t s_rect[kDupThreads];
-    __shared__ uint32_t s_inv[kDupThreads];  // ceil(2^32 / rect width): k / w == umulhi(k, inv) for k*w < 2^32
-    __shared__ uint32_t s_idx[kDupThreads];
+    // Each lane loads ONE depth-sorted Gaussian (slot range + tile rectangle); the slots are then
+    // written by groups of 8 lanes, every group walking the Gaussians its own 8 lanes hold, so four
+    // Gaussians are emitted per warp step and a typical 5..16-tile rectangle takes one or two steps.
+    // No slot-to-owner search, no CTA barrier in the emission loop: slot k of a Gaussian is tile
+    // (min_y + k / w, min_x + k % w), and a rectangle's slots are contiguous in the output.
+    // (History: per-slot binary search over the CTA's offsets, then a per-chunk max-scan of head
+    // markers -- 250 instructions per 32 slots, 72 % issue-bound; this form needs about a third.)
     __shared__ uint32_t s_hist[3][256];
-    __shared__ uint32_t s_head[kDupThreads];       // first-slot markers of the current output chunk
-    __shared__ uint32_t s_wmax[kDupThreads / 32];
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31u;
-    const int first = blockIdx.x * kDupThreads;
-    s_head[tid] = 0;
-    const int pos = first + tid;
+    const unsigned full = 0xffffffffu;
     for (int i = tid; i < plan.num_passes * 256; i += kDupThreads) s_hist[i >> 8][i & 255] = 0;
-    uint32_t end_off = 0;
-    if (pos < P) {
-        end_off = __ldg(offsets + pos);
-        const uint32_t idx = __ldg(perm + pos);
-        const int r = __ldg(radii + idx);
-        uint32_t rect = 0, inv = 0;
-        if (r > 0) {
-            // getRect (auxiliary.h:46-56), same float sequence as preprocess.
-            const float2 p = __ldg(means2D + idx);
-            const float rf = (float)r;
-            const unsigned min_x = min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.x, -rf), 0.0625f)));
-            const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
-            const unsigned max_x = min(
-                grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
-            const unsigned w = max_x - min_x;
-            rect = min_x | (min_y << 10) | (w << 20);
-            inv = (w > 1u) ? (uint32_t)((0x100000000ull + w - 1u) / w) : 0u;
-        }
-        s_rect[tid] = rect;
-        s_inv[tid] = inv;
-        s_idx[tid] = idx;
-    }
-    if (tid == 0) s_off[0] = (first == 0) ? 0u : __ldg(offsets + first - 1);
-    const int in_block = min(kDupThreads, P - first);
-    if (tid < in_block) s_off[tid + 1] = end_off;
     __syncthreads();
-    const uint32_t begin = s_off[0];
-    const uint32_t end = min(s_off[in_block], cap);
-    // digit layout of the first two sort passes relative to the tile id
+    const int pos = blockIdx.x * kDupThreads + tid;
+    uint32_t end_off = 0, idx = 0;
+    if (pos < P) end_off = __ldg(offsets + pos);
+    uint32_t start = __shfl_up_sync(full, end_off, 1);
+    if (lane == 0) start = (pos > 0 && pos < P) ? __ldg(offsets + pos - 1) : 0u;
+    uint32_t len = (pos < P) ? end_off - start : 0u;
+    // the workspace may be smaller than this frame needs (api.cu redoes the frame): never write past it
+    len = (start < cap) ? min(len, cap - start) : 0u;
+    uint32_t rect = 0;
+    if (len != 0u) {
+        idx = __ldg(perm + pos);
+        // getRect (auxiliary.h:46-56), same float sequence as preprocess.
+        const float2 p = __ldg(means2D + idx);
+        const float rf = (float)__ldg(radii + idx);
+        const unsigned min_x = min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.x, -rf), 0.0625f)));
+        const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
+        const unsigned max_x =
+            min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
+        rect = min_x | (min_y << 10) | ((max_x - min_x) << 20);
+    }
+    // digit layout of the sort passes relative to the tile id
     const int sh0 = plan.shift[0] - 32, sh1 = plan.shift[1] - 32, sh2 = plan.shift[2] - 32;
     const uint32_t mk0 = (1u << plan.bits[0]) - 1u, mk1 = (1u << plan.bits[1]) - 1u, mk2 = (1u << plan.bits[2]) - 1u;
-    const uint32_t my_start = (tid < in_block) ? s_off[tid] : 0u;
-    const uint32_t my_len = (tid < in_block) ? s_off[tid + 1] - my_start : 0u;
-    uint32_t carry = 0;  // owner of the slot before the current chunk (same value in every thread)
-    for (uint32_t ob = begin; ob < end; ob += kDupThreads) {
-        const uint32_t o = ob + tid;
-        const bool valid = o < end;
-        const unsigned active = __ballot_sync(0xffffffffu, valid);
-        // Owner of every slot of this 256-slot chunk without a search: each non-empty Gaussian whose
-        // first slot lies in the chunk drops its index there, an inclusive max-scan spreads it to the
-        // slots behind it, `carry` (the owner of the slot before the chunk) covers the chunk's head.
-        // (A binary search over s_off per slot was 47 % of this kernel's instructions.)
-        if (my_len != 0u && my_start - ob < (uint32_t)kDupThreads) s_head[my_start - ob] = (uint32_t)tid;
-        __syncthreads();
-        uint32_t own = s_head[tid];
-        s_head[tid] = 0;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, own, d);
-            if (lane >= (unsigned)d) own = max(own, t);
-        }
-        if (lane == 31) s_wmax[tid >> 5] = own;
-        __syncthreads();
-        {
-            uint32_t wv = (lane < (unsigned)(kDupThreads / 32)) ? s_wmax[lane] : 0u;
-#pragma unroll
-            for (int d = 1; d < kDupThreads / 32; d <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, wv, d);
-                if (lane >= (unsigned)d) wv = max(wv, t);
-            }
-            const uint32_t prev = __shfl_sync(0xffffffffu, wv, (int)((tid >> 5) + 31) & 31);  // warp 0 reads lane 31: 0
-            const uint32_t total = __shfl_sync(0xffffffffu, wv, kDupThreads / 32 - 1);
-            own = max(own, carry);
-            if ((tid >> 5) != 0) own = max(own, prev);
-            carry = max(carry, total);
-        }
-        if (valid) {
-            const int lo = (int)own;
-            const uint32_t rect = s_rect[lo];
-            const uint32_t k = o - s_off[lo];
-            const uint32_t w = rect >> 20;
-            const uint32_t q = (w > 1u) ? __umulhi(k, s_inv[lo]) : k;  // k / w
-            const uint32_t y = ((rect >> 10) & 1023u) + q;
-            const uint32_t x = (rect & 1023u) + (k - q * w);
-            const uint32_t tile = y * grid_x + x;
-            pairs[o] = ((uint64_t)tile << 32) | (uint64_t)s_idx[lo];
-            // Digit counts for the sort passes.  Neighbouring slots are neighbouring tiles: their low
-            // digits differ (plain shared-memory atomics, no conflicts), their higher digits mostly
-            // coincide (lanes that share the first active lane's digit are counted with one atomic).
-            atomicAdd(&s_hist[0][(tile >> sh0) & mk0], 1u);
-            const int first_lane = __ffs(active) - 1;
-            if (plan.num_passes > 1) {
-                const uint32_t d = (tile >> sh1) & mk1;
-                const uint32_t d0 = __shfl_sync(active, d, first_lane);
-                const unsigned same = __ballot_sync(active, d == d0);
-                if (d != d0) atomicAdd(&s_hist[1][d], 1u);
-                else if ((int)lane == first_lane) atomicAdd(&s_hist[1][d0], (uint32_t)__popc(same));
-            }
-            if (plan.num_passes > 2) {
-                const uint32_t d = (tile >> sh2) & mk2;
-                const uint32_t d0 = __shfl_sync(active, d, first_lane);
-                const unsigned same = __ballot_sync(active, d == d0);
-                if (d != d0) atomicAdd(&s_hist[2][d], 1u);
-                else if ((int)lane == first_lane) atomicAdd(&s_hist[2][d0], (uint32_t)__popc(same));
+    // emits slots first, first + step, ... (< g_len) of one rectangle; `iters` is warp-uniform
+    auto emit = [&](uint32_t first, uint32_t step, unsigned iters, uint32_t g_len, uint32_t g_start, uint32_t g_rect,
+                    uint32_t g_index) {
+        const uint32_t w = max(g_rect >> 20, 1u);
+        const uint32_t base_tile = ((g_rect >> 10) & 1023u) * grid_x + (g_rect & 1023u);
+        const float rcp = __frcp_rn((float)w);
+        uint64_t* out = pairs + g_start;
+        const uint64_t low = (uint64_t)g_index;
+#pragma unroll 1
+        for (unsigned i = 0; i < iters; ++i) {
+            const uint32_t k = first + step * i;
+            const bool valid = k < g_len;
+            const unsigned active = __ballot_sync(full, valid);
+            if (valid) {
+                // k / w through the float reciprocal: k < 2^20 and w <= 1023, so the estimate is q or q - 1
+                uint32_t q = (uint32_t)__fmul_rz((float)k, rcp);
+                uint32_t r = k - q * w;
+                if (r >= w) { q++; r -= w; }
+                const uint32_t tile = base_tile + q * grid_x + r;
+                out[k] = ((uint64_t)tile << 32) | low;
+                // Digit counts for the sort passes.  Neighbouring slots are neighbouring tiles: their low
+                // digits differ (plain shared-memory atomics), their higher digits mostly coincide
+                // (lanes with equal digits are counted with one atomic by the lowest of them).
+                atomicAdd(&s_hist[0][(tile >> sh0) & mk0], 1u);
+                if (plan.num_passes > 1) {
+                    const uint32_t d = (tile >> sh1) & mk1;
+                    const unsigned same = __match_any_sync(active, d);
+                    if ((int)lane == __ffs(same) - 1) atomicAdd(&s_hist[1][d], (uint32_t)__popc(same));
+                }
+                if (plan.num_passes > 2) {
+                    const uint32_t d = (tile >> sh2) & mk2;
+                    const unsigned same = __match_any_sync(active, d);
+                    if ((int)lane == __ffs(same) - 1) atomicAdd(&s_hist[2][d], (uint32_t)__popc(same));
+                }
             }
         }
+    };
+    // rectangles of more than kWide tiles: the whole warp, one rectangle at a time
+    constexpr uint32_t kWide = 32;
+    unsigned wide = __ballot_sync(full, len > kWide);
+    while (wide) {
+        const int src = __ffs(wide) - 1;
+        wide &= wide - 1u;
+        const uint32_t g_len = __shfl_sync(full, len, src);
+        emit(lane, 32u, (g_len + 31u) >> 5, g_len, __shfl_sync(full, start, src), __shfl_sync(full, rect, src),
+             __shfl_sync(full, idx, src));
+    }
+    // the rest: groups of 8 lanes, each walking the rectangles its own 8 lanes hold
+    const uint32_t small_len = (len > kWide) ? 0u : len;
+    const unsigned sub = lane & 7u, group_base = lane & 24u;
+#pragma unroll 1
+    for (unsigned j = 0; j < 8; ++j) {
+        const int src = (int)(group_base | j);
+        const uint32_t g_len = __shfl_sync(full, small_len, src);
+        const unsigned iters = __reduce_max_sync(full, (g_len + 7u) >> 3);      // warp-uniform trip count
+        if (iters == 0u) continue;
+        emit(sub, 8u, iters, g_len, __shfl_sync(full, start, src), __shfl_sync(full, rect, src),
+             __shfl_sync(full, idx, src));
     }
     __syncthreads();
     for (int i = tid; i < plan.num_passes * 256; i += kDupThreads) {
