@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 5
+#define HUGS_B200_ABI_VERSION 6
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -357,6 +357,38 @@ int hugs_b200_l1_ssim_backward(int C, int H, int W, const float* img1, const flo
 size_t hugs_b200_knn_temp_bytes(int P);
 int hugs_b200_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* temp, size_t temp_bytes,
                              hugs_b200_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Two input segments: the renderer's human_scene mode concatenates the human and
+ * the scene Gaussians with five torch.cat calls per render (hugs/renderer/gs_renderer.py:33-37), a
+ * copy of 236 B per Gaussian.  These entry points take the two sets of arrays as they are: Gaussians
+ * [0, P0) come from segment 0 (the human), [P0, P0+P1) from segment 1 (the scene).  SH path with
+ * scales / rotations only (what that renderer passes).  Outputs, workspaces and gradients are those
+ * of hugs_b200_rasterize_forward / _backward on the concatenation, bit for bit: radii and every
+ * dL_d* array have P0 + P1 rows, rows [0, P0) belonging to segment 0.
+ * ------------------------------------------------------------------------------------------- */
+int hugs_b200_rasterize_forward_seg2(
+    hugs_b200_resize_fn geometry_buffer, void* geometry_user,
+    hugs_b200_resize_fn binning_buffer,  void* binning_user,
+    hugs_b200_resize_fn image_buffer,    void* image_user,
+    int D, int M, const float* background, int width, int height,
+    int P0, const float* means3D0, const float* shs0, const float* opacities0, const float* scales0,
+    const float* rotations0,
+    int P1, const float* means3D1, const float* shs1, const float* opacities1, const float* scales1,
+    const float* rotations1,
+    float scale_modifier, const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+    float tan_fovx, float tan_fovy, int prefiltered, float* out_color, int* radii, int debug,
+    hugs_b200_stream_t stream, int* num_rendered);
+int hugs_b200_rasterize_backward_seg2(
+    int D, int M, int R, const float* background, int width, int height,
+    int P0, const float* means3D0, const float* shs0, const float* scales0, const float* rotations0,
+    int P1, const float* means3D1, const float* shs1, const float* scales1, const float* rotations1,
+    float scale_modifier, const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+    float tan_fovx, float tan_fovy, const int* radii, char* geom_buffer, char* binning_buffer,
+    size_t binning_bytes, char* image_buffer, const float* dL_dpix,
+    float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
+    float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, int debug,
+    hugs_b200_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Densification statistics after a backward pass, one launch, no host sync.

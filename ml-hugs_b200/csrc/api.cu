@@ -429,6 +429,31 @@ int hugs_b200_mark_visible(int P, const float* means3D, const float* viewmatrix,
     return launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, static_cast<cudaStream_t>(stream));
 }
 
+// Second input segment of the *_seg2 entry points: rows [P0, P) of the per-Gaussian inputs come from a
+// second set of arrays.  Every per-Gaussian OUTPUT of the preprocess kernels is a plain array indexed by
+// the Gaussian, so a segment is just one more launch of the same kernel with the output pointers moved to
+// the segment's first row; everything downstream (scan, binning, sort, blend) sees one Gaussian range.
+struct SecondSegment {
+    int P0;
+    const float* means3D;
+    const float* shs;
+    const float* opacities;
+    const float* scales;
+    const float* rotations;
+};
+static thread_local const SecondSegment* tl_seg2 = nullptr;   // set only for the duration of a *_seg2 call
+
+static GeomView geom_rows_from(const GeomView& g, int row0) {
+    GeomView o = g;
+    o.depths += row0;
+    o.means2D += row0;
+    o.conic_opacity += row0;
+    o.rgb += row0;
+    o.clamped += row0;
+    o.tiles_touched += row0;
+    return o;
+}
+
 int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geometry_user,
                                 hugs_b200_resize_fn binning_buffer, void* binning_user,
                                 hugs_b200_resize_fn image_buffer, void* image_user, int P, int D, int M,
@@ -503,6 +528,17 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         }
         geom = carve_geom(geom_base, P);
 
+        if (const SecondSegment* s2 = tl_seg2) {
+            if (s2->P0 > 0)
+                HB_STAGE(launch_preprocess(s2->P0, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
+                                           nullptr, nullptr, cam, radii, geom, prefiltered != 0, stream),
+                         ST_PREPROCESS);
+            if (P - s2->P0 > 0)
+                HB_STAGE(launch_preprocess(P - s2->P0, D, M, s2->means3D, s2->scales, scale_modifier, s2->rotations,
+                                           s2->opacities, s2->shs, nullptr, nullptr, cam, radii + s2->P0,
+                                           geom_rows_from(geom, s2->P0), prefiltered != 0, stream),
+                         ST_PREPROCESS);
+        } else
         HB_STAGE(launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
                                    (scales && rotations) ? nullptr : cov3D_precomp, colors_precomp, cam, radii, geom,
                                    prefiltered != 0, stream),
@@ -695,6 +731,23 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
                                       dL_dcolor, stream);
     };
     HB_STAGE(blend_backward(), ST_RENDER_BWD);
+    if (const SecondSegment* s2 = tl_seg2) {
+        const size_t r0 = (size_t)s2->P0;
+        if (s2->P0 > 0)
+            HB_STAGE(launch_preprocess_backward(s2->P0, D, M, means3D, radii, shs, geom.clamped, scales, rotations,
+                                                scale_modifier, nullptr, cam, dL_dmean2D, dL_dconic, dL_dmean3D,
+                                                dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
+                                                dL_dsh_accumulate != 0, stream),
+                     ST_PREPROCESS_BWD);
+        if (P - s2->P0 > 0)
+            HB_STAGE(launch_preprocess_backward(P - s2->P0, D, M, s2->means3D, radii + r0, s2->shs, geom.clamped + r0,
+                                                s2->scales, s2->rotations, scale_modifier, nullptr, cam,
+                                                dL_dmean2D + 3 * r0, dL_dconic + 4 * r0, dL_dmean3D + 3 * r0,
+                                                dL_dcolor + 3 * r0, dL_dcov3D + 6 * r0, dL_dsh + (size_t)M * 3 * r0,
+                                                dL_dscale + 3 * r0, dL_drot + 4 * r0, dL_dsh_accumulate != 0, stream),
+                     ST_PREPROCESS_BWD);
+        return 0;
+    }
     HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,
                                         rotations, scale_modifier, cov3D_precomp, cam, dL_dmean2D, dL_dconic,
                                         dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
@@ -775,6 +828,72 @@ int hugs_b200_knn_mean_dist2(int P, const float* points, float* mean_dist2, void
         return HUGS_B200_EINVAL;
     }
     return launch_knn_mean_dist2(P, points, mean_dist2, temp, temp_bytes, static_cast<cudaStream_t>(stream));
+}
+
+static int check_seg2(const char* what, int P0, int P1, const float* const* a, const float* const* b) {
+    if (P0 < 0 || P1 < 0 || (long long)P0 + P1 > 0x7fffffffll) {
+        set_error("%s: bad segment sizes %d + %d", what, P0, P1);
+        return HUGS_B200_EINVAL;
+    }
+    for (int i = 0; i < 5; i++)
+        if ((P0 > 0 && !a[i]) || (P1 > 0 && !b[i])) {
+            set_error("%s: a segment lacks means3D / shs / opacities / scales / rotations", what);
+            return HUGS_B200_EINVAL;
+        }
+    return 0;
+}
+
+int hugs_b200_rasterize_forward_seg2(hugs_b200_resize_fn geometry_buffer, void* geometry_user,
+                                     hugs_b200_resize_fn binning_buffer, void* binning_user,
+                                     hugs_b200_resize_fn image_buffer, void* image_user, int D, int M,
+                                     const float* background, int width, int height, int P0, const float* means3D0,
+                                     const float* shs0, const float* opacities0, const float* scales0,
+                                     const float* rotations0, int P1, const float* means3D1, const float* shs1,
+                                     const float* opacities1, const float* scales1, const float* rotations1,
+                                     float scale_modifier, const float* viewmatrix, const float* projmatrix,
+                                     const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered,
+                                     float* out_color, int* radii, int debug, hugs_b200_stream_t stream,
+                                     int* num_rendered) {
+    const float* a[5] = {means3D0, shs0, opacities0, scales0, rotations0};
+    const float* b[5] = {means3D1, shs1, opacities1, scales1, rotations1};
+    if (const int rc = check_seg2("rasterize_forward_seg2", P0, P1, a, b)) return rc;
+    const bool first_empty = P0 == 0;   // the argument checks below look at the first segment's pointers
+    const SecondSegment s2{P0, means3D1, shs1, opacities1, scales1, rotations1};
+    tl_seg2 = &s2;
+    const int rc = hugs_b200_rasterize_forward(
+        geometry_buffer, geometry_user, binning_buffer, binning_user, image_buffer, image_user, P0 + P1, D, M,
+        background, width, height, first_empty ? means3D1 : means3D0, first_empty ? shs1 : shs0, nullptr,
+        first_empty ? opacities1 : opacities0, first_empty ? scales1 : scales0, scale_modifier,
+        first_empty ? rotations1 : rotations0, nullptr, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy,
+        prefiltered, out_color, radii, debug, stream, num_rendered);
+    tl_seg2 = nullptr;
+    return rc;
+}
+
+int hugs_b200_rasterize_backward_seg2(int D, int M, int R, const float* background, int width, int height, int P0,
+                                      const float* means3D0, const float* shs0, const float* scales0,
+                                      const float* rotations0, int P1, const float* means3D1, const float* shs1,
+                                      const float* scales1, const float* rotations1, float scale_modifier,
+                                      const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                                      float tan_fovx, float tan_fovy, const int* radii, char* geom_buffer,
+                                      char* binning_buffer, size_t binning_bytes, char* image_buffer,
+                                      const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                                      float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                                      float* dL_dscale, float* dL_drot, int debug, hugs_b200_stream_t stream) {
+    const float* a[5] = {means3D0, shs0, means3D0, scales0, rotations0};
+    const float* b[5] = {means3D1, shs1, means3D1, scales1, rotations1};
+    if (const int rc = check_seg2("rasterize_backward_seg2", P0, P1, a, b)) return rc;
+    const bool first_empty = P0 == 0;
+    const SecondSegment s2{P0, means3D1, shs1, nullptr, scales1, rotations1};
+    tl_seg2 = &s2;
+    const int rc = hugs_b200_rasterize_backward_acc(
+        P0 + P1, D, M, R, background, width, height, first_empty ? means3D1 : means3D0, first_empty ? shs1 : shs0,
+        nullptr, first_empty ? scales1 : scales0, scale_modifier, first_empty ? rotations1 : rotations0, nullptr,
+        viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer, binning_bytes,
+        image_buffer, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
+        dL_drot, debug, stream, 0);
+    tl_seg2 = nullptr;
+    return rc;
 }
 
 int hugs_b200_densification_stats(int n, const int* radii, const float* grad_means2D, int grad_stride,

@@ -102,6 +102,29 @@ rasterize_backward_acc = _sig("hugs_b200_rasterize_backward_acc", i32, [
     i32,                      # dL_dsh_accumulate
 ])
 
+rasterize_forward_seg2 = _sig("hugs_b200_rasterize_forward_seg2", i32, [
+    RESIZE_FN, C.c_void_p, RESIZE_FN, C.c_void_p, RESIZE_FN, C.c_void_p,
+    i32, i32, fp, i32, i32,   # D, M, background, width, height
+    i32, fp, fp, fp, fp, fp,  # P0, means3D0, shs0, opacities0, scales0, rotations0
+    i32, fp, fp, fp, fp, fp,  # P1, means3D1, shs1, opacities1, scales1, rotations1
+    C.c_float, fp, fp, fp,    # scale_modifier, viewmatrix, projmatrix, cam_pos
+    C.c_float, C.c_float, i32,  # tan_fovx, tan_fovy, prefiltered
+    fp, fp, i32, fp,          # out_color, radii, debug, stream
+    C.POINTER(i32),
+])
+
+rasterize_backward_seg2 = _sig("hugs_b200_rasterize_backward_seg2", i32, [
+    i32, i32, i32, fp, i32, i32,   # D, M, R, background, width, height
+    i32, fp, fp, fp, fp,      # P0, means3D0, shs0, scales0, rotations0
+    i32, fp, fp, fp, fp,      # P1, means3D1, shs1, scales1, rotations1
+    C.c_float, fp, fp, fp,    # scale_modifier, viewmatrix, projmatrix, cam_pos
+    C.c_float, C.c_float,     # tan_fovx, tan_fovy
+    fp, fp, fp, C.c_size_t, fp,  # radii, geom, binning, binning_bytes, image
+    fp,                       # dL_dpix
+    fp, fp, fp, fp, fp, fp, fp, fp, fp,  # 9 gradient outputs
+    i32, fp,                  # debug, stream
+])
+
 l1_ssim_forward = _sig("hugs_b200_l1_ssim_forward", i32, [i32, i32, i32, fp, fp, fp, fp, fp])
 l1_ssim_backward = _sig("hugs_b200_l1_ssim_backward", i32, [i32, i32, i32, fp, fp, fp, fp, fp, fp])
 
@@ -168,6 +191,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_knn_temp_bytes", "hugs_b200_knn_mean_dist2",
     "hugs_b200_densification_stats",
     "hugs_b200_triplane_forward", "hugs_b200_triplane_backward",
+    "hugs_b200_rasterize_forward_seg2", "hugs_b200_rasterize_backward_seg2",
 ]
 
 

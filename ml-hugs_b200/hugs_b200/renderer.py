@@ -3,7 +3,8 @@
 Mirrors hugs/renderer/gs_renderer.py with the same names, arguments and result keys:
   render              :103-161   settings from the camera dict, rasterize, clamp(0,1), radii > 0
   render_human_scene  :19-100    human / scene / human_scene modes, optional separate human render
-and the trainer's densification bookkeeping as ONE kernel without boolean-mask indexing:
+In human_scene mode with SH colours the two models' tensors go to the rasterizer as two segments
+(segments.py) instead of through five torch.cat calls.  The trainer's densification bookkeeping is ONE kernel without boolean-mask indexing:
   add_densification_stats   hugs/models/scene.py:460-462 + hugs/trainer/gs_trainer.py:406-411,:429-435
 """
 import ctypes as C
@@ -63,6 +64,34 @@ def render(means3D, feats, opacity, scales, rotations, data, scaling_modifier=1.
     }
 
 
+def _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_color, active_sh_degree):
+    """`render` (gs_renderer.py:103-161) of human || scene without building the concatenation."""
+    from .segments import rasterize_two_segments
+    device = human_gs_out['xyz'].device
+    if bg_color is None:
+        bg_color = torch.zeros(3, dtype=torch.float32, device=device)
+    n = human_gs_out['xyz'].shape[0] + scene_gs_out['xyz'].shape[0]
+    screenspace_points = torch.zeros(n, 3, dtype=human_gs_out['xyz'].dtype, device=device, requires_grad=True) + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    settings = GaussianRasterizationSettings(
+        image_height=int(data['image_height']), image_width=int(data['image_width']),
+        tanfovx=math.tan(data['fovx'] * 0.5), tanfovy=math.tan(data['fovy'] * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=data['world_view_transform'],
+        projmatrix=data['full_proj_transform'], sh_degree=active_sh_degree, campos=data['camera_center'],
+        prefiltered=False, debug=False)
+    seg = lambda o: (o['xyz'], o['shs'], o['opacity'], o['scales'], o['rotq'])  # noqa: E731
+    rendered_image, radii = rasterize_two_segments(seg(human_gs_out), seg(scene_gs_out), screenspace_points, settings)
+    return {
+        "render": torch.clamp(rendered_image, 0.0, 1.0),
+        "viewspace_points": screenspace_points,
+        "visibility_filter": radii > 0,
+        "radii": radii,
+    }
+
+
 _KEYS = (("shs", "feats"), ("xyz", "means3D"), ("opacity", "opacity"), ("scales", "scales"), ("rotq", "rotations"))
 
 
@@ -74,8 +103,11 @@ def render_human_scene(data, human_gs_out, scene_gs_out, bg_color, human_bg_colo
                        render_mode='human_scene', render_human_separate=False):
     """hugs/renderer/gs_renderer.py:19-100."""
     if render_mode == 'human_scene':
-        args = {arg: torch.cat([human_gs_out[key], scene_gs_out[key]], dim=0) for key, arg in _KEYS}
         active_sh_degree = human_gs_out['active_sh_degree']
+        if human_gs_out['shs'].dim() == 3 and scene_gs_out['shs'].dim() == 3:
+            args = None     # SH colours: the two segments go to the rasterizer as they are, no torch.cat
+        else:
+            args = {arg: torch.cat([human_gs_out[key], scene_gs_out[key]], dim=0) for key, arg in _KEYS}
     elif render_mode == 'human':
         args, active_sh_degree = _pick(human_gs_out), human_gs_out['active_sh_degree']
     elif render_mode == 'scene':
@@ -83,8 +115,12 @@ def render_human_scene(data, human_gs_out, scene_gs_out, bg_color, human_bg_colo
     else:
         raise ValueError(f'Unknown render mode: {render_mode}')
 
-    render_pkg = render(data=data, scaling_modifier=scaling_modifier, bg_color=bg_color,
-                        active_sh_degree=active_sh_degree, **args)
+    if args is None:
+        render_pkg = _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_color,
+                                          active_sh_degree)
+    else:
+        render_pkg = render(data=data, scaling_modifier=scaling_modifier, bg_color=bg_color,
+                            active_sh_degree=active_sh_degree, **args)
 
     if render_human_separate and render_mode == 'human_scene':
         human_pkg = render(data=data, scaling_modifier=scaling_modifier,

@@ -196,3 +196,60 @@ def test_stats_sync_single_process_two_views():
     sync.finish_step(acc, den, mx)
     assert torch.equal(mx, r[2]) and torch.equal(den, r[1])
     assert torch.allclose(acc, r[0], rtol=1e-6, atol=0.0)
+
+
+@pytest.mark.parametrize("n_h,n_s", [(1800, 2600), (0, 3000), (2500, 0), (33, 1), (110210, 200000)])
+def test_two_segments_equal_the_concatenation(n_h, n_s):
+    """hugs_b200_rasterize_*_seg2: image, radii and num_rendered bit-identical to the rasterizer on
+    torch.cat(human, scene); every gradient within 1e-4 of its largest element (the blend backward's
+    atomics are unordered in both; two runs of the SAME call differ by as much)."""
+    import diff_gaussian_rasterization as dgr
+    from hugs_b200.segments import rasterize_two_segments
+    big = n_h + n_s > 100000
+    W, H, focal = (1920, 1080, 1400.0) if big else (320, 200, 300.0)
+    sc = scenes.make_scene(n_s, n_h, W, H, focal, seed=16, device="cuda")
+    settings = scenes.settings_of(sc, dgr)
+    names = ("means3D", "shs", "opacity", "scales", "rotations")
+    whole = [sc[k].detach().clone().requires_grad_(True) for k in names]
+    m2d_w = torch.zeros(n_h + n_s, 3, device="cuda", requires_grad=True)
+    color_w, radii_w = dgr.GaussianRasterizer(settings)(
+        means3D=whole[0], means2D=m2d_w, shs=whole[1], opacities=whole[2], scales=whole[3], rotations=whole[4])
+    (color_w * sc["dL_dcolor"]).sum().backward()
+
+    seg0 = [sc[k][:n_h].detach().clone().requires_grad_(True) for k in names]
+    seg1 = [sc[k][n_h:].detach().clone().requires_grad_(True) for k in names]
+    m2d = torch.zeros(n_h + n_s, 3, device="cuda", requires_grad=True)
+    color, radii = rasterize_two_segments(seg0, seg1, m2d, settings)
+    assert torch.equal(color, color_w) and torch.equal(radii, radii_w)
+    assert color.grad_fn.num_rendered == color_w.grad_fn.num_rendered
+    (color * sc["dL_dcolor"]).sum().backward()
+
+    def close(a, b, what):
+        scale, err = float(b.abs().max()), float((a - b).abs().max())
+        assert err <= 1e-4 * max(scale, 1e-30), "%s: max|diff| %.3e against max|grad| %.3e" % (what, err, scale)
+    close(m2d.grad, m2d_w.grad, "means2D")
+    for k, w, a, b in zip(names, whole, seg0, seg1):
+        if n_h:
+            close(a.grad, w.grad[:n_h], k + " (segment 0)")
+        if n_s:
+            close(b.grad, w.grad[n_h:], k + " (segment 1)")
+
+
+def test_two_segments_argument_errors():
+    import diff_gaussian_rasterization as dgr
+    from hugs_b200.segments import rasterize_two_segments
+    sc = scenes.make_scene(40, 0, 64, 64, 60.0, seed=17, device="cuda")
+    settings = scenes.settings_of(sc, dgr)
+    names = ("means3D", "shs", "opacity", "scales", "rotations")
+    seg = [sc[k] for k in names]
+    m2d = torch.zeros(80, 3, device="cuda")
+    bad = list(seg)
+    bad[3] = seg[3][:10]
+    with pytest.raises(RuntimeError, match="row count"):
+        rasterize_two_segments(seg, bad, m2d, settings)
+    bad = list(seg)
+    bad[1] = seg[1][:, :9].contiguous()
+    with pytest.raises(RuntimeError, match="same M"):
+        rasterize_two_segments(seg, bad, m2d, settings)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        rasterize_two_segments([x.cpu() for x in seg], seg, m2d, settings)
