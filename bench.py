@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """bench.py -- fwd+bwd frames/s of the HUGS splat hot path on N B200s (BASELINE.json metric).
 
-A "step" on each rank is --views-per-rank (default 4) frames of the human+scene workload (BASELINE.json configs[2]: 110 210
+A "step" on each rank is --views-per-rank (default 8) frames of the human+scene workload (BASELINE.json configs[2]: 110 210
 LBS-deformed human Gaussians + 1 000 000 scene Gaussians, SH degree 3, 1920x1080):
     LBS forward -> rasterizer forward -> loss=(color*G).sum() -> rasterizer backward -> LBS backward
 per frame, gradients accumulated over the rank's frames, followed, for N > 1, by one NCCL
@@ -59,7 +59,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="human_scene_1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--views-per-rank", type=int, default=4,
+    ap.add_argument("--views-per-rank", type=int, default=8,
                     help="views each rank renders per step before the gradient allreduce (view batch = this x N)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-baseline-seconds", type=float, default=20.0)
