@@ -165,9 +165,9 @@ __global__ void __launch_bounds__(kLbsThreads)
 }
 
 // Backward.  One thread per Gaussian, frames looped inside (F = 1 in training).  dA is reduced
-// per warp through shared memory (each lane owns ceil(12J/32) entries of the J x 12 matrix and
-// sums them over the warp's 32 Gaussians), accumulated in registers over the CTA's grid-stride
-// chunks, and flushed with one atomicAdd per entry per warp at the end.
+// per warp through shared memory (lane j owns row j of the J x 12 matrix and sums w_j * dT over the
+// warp's 32 Gaussians: one weight load + three broadcast 16-byte loads per 12 FMAs), accumulated in
+// registers over the CTA's grid-stride chunks, and flushed with one atomicAdd per entry per warp.
 __global__ void __launch_bounds__(kLbsThreads)
     lbs_backward_kernel(int F, int N, int J, const float* __restrict__ A, const float* __restrict__ xyz,
                         const float* __restrict__ weights, const float* __restrict__ rotmat,
@@ -178,9 +178,9 @@ __global__ void __launch_bounds__(kLbsThreads)
                         float* __restrict__ d_transl, float* __restrict__ d_smpl_scale, int w_vec4) {
     __shared__ float sA[kMaxJoints * 16];
     __shared__ float s_w[kLbsThreads / 32][32][kMaxJoints + 1];
-    __shared__ float s_dT[kLbsThreads / 32][32][13];
+    __shared__ __align__(16) float s_dT[kLbsThreads / 32][32][12];
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const int nA = J * 12;
+    (void)0;
     const int chunks = (N + kLbsThreads - 1) / kLbsThreads;
     (void)transl;
 
@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(kLbsThreads)
         __syncthreads();
         for (int k = threadIdx.x; k < J * 16; k += kLbsThreads) sA[k] = __ldg(A + (size_t)f * J * 16 + k);
         __syncthreads();
-        float accA[12];  // entries lane, lane+32, ... of the J x 12 gradient
+        float accA[12];  // lane j owns row j of the J x 12 gradient (J <= 32)
 #pragma unroll
         for (int k = 0; k < 12; k++) accA[k] = 0.f;
         float acc_tr[3] = {0.f, 0.f, 0.f};
@@ -324,26 +324,29 @@ __global__ void __launch_bounds__(kLbsThreads)
             for (int j = 0; j < kMaxJoints; j++)
                 if (j < J) s_w[warp][lane][j] = w[j];
             __syncwarp();
-#pragma unroll
-            for (int e = 0; e < 12; e++) {
-                const int idx = (int)lane + 32 * e;
-                if (idx < nA) {
-                    const int j = idx / 12, k = idx % 12;
-                    float s = 0.f;
-                    for (int t = 0; t < 32; t++) s = fmaf(s_w[warp][t][j], s_dT[warp][t][k], s);
-                    accA[e] += s;
+            // lane j: accA[k] += sum_t w[t][j] * dT[t][k]; the dT row is a broadcast of three 16-byte loads,
+            // the weight column a conflict-free stride-1 load (rows of 33 floats)
+            if ((int)lane < J) {
+#pragma unroll 4
+                for (int t = 0; t < 32; t++) {
+                    const float wj = s_w[warp][t][lane];
+                    const float4* row = reinterpret_cast<const float4*>(&s_dT[warp][t][0]);
+                    const float4 d0 = row[0], d1 = row[1], d2 = row[2];
+                    accA[0] = fmaf(wj, d0.x, accA[0]); accA[1] = fmaf(wj, d0.y, accA[1]);
+                    accA[2] = fmaf(wj, d0.z, accA[2]); accA[3] = fmaf(wj, d0.w, accA[3]);
+                    accA[4] = fmaf(wj, d1.x, accA[4]); accA[5] = fmaf(wj, d1.y, accA[5]);
+                    accA[6] = fmaf(wj, d1.z, accA[6]); accA[7] = fmaf(wj, d1.w, accA[7]);
+                    accA[8] = fmaf(wj, d2.x, accA[8]); accA[9] = fmaf(wj, d2.y, accA[9]);
+                    accA[10] = fmaf(wj, d2.z, accA[10]); accA[11] = fmaf(wj, d2.w, accA[11]);
                 }
             }
             __syncwarp();
         }
         // flush dA for this frame (rows 0..2 of each joint's 4x4; the bottom row gets no gradient)
+        if ((int)lane < J) {
 #pragma unroll
-        for (int e = 0; e < 12; e++) {
-            const int idx = (int)lane + 32 * e;
-            if (idx < nA && accA[e] != 0.f) {
-                const int j = idx / 12, k = idx % 12;
-                atomicAdd(dA + ((size_t)f * J + j) * 16 + k, accA[e]);
-            }
+            for (int k = 0; k < 12; k++)
+                if (accA[k] != 0.f) atomicAdd(dA + ((size_t)f * J + lane) * 16 + k, accA[k]);
         }
         // translation / scale gradients: warp reduce, one atomic per warp
 #pragma unroll
