@@ -98,12 +98,18 @@ __global__ void __launch_bounds__(kDupThreads)
     // (History: per-slot binary search over the CTA's offsets, then a per-chunk max-scan of head
     // markers -- 250 instructions per 32 slots, 72 % issue-bound; this form needs about a third.)
     __shared__ uint32_t s_hist[3][256];
+    __shared__ uint4 s_huge[kDupThreads];   // (start, len, rect, index) of rectangles the whole CTA emits
+    __shared__ int s_nhuge;
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31u;
     const unsigned full = 0xffffffffu;
     for (int i = tid; i < plan.num_passes * 256; i += kDupThreads) s_hist[i >> 8][i & 255] = 0;
+    if (tid == 0) s_nhuge = 0;
     __syncthreads();
-    const int pos = blockIdx.x * kDupThreads + tid;
+    // Warp w of CTA b takes the 32 depth-sorted positions of chunk w * gridDim.x + b: neighbouring chunks
+    // (the nearest Gaussians come first and have by far the largest rectangles) land on different CTAs
+    // and SMs instead of piling up in the first few CTAs.
+    const int pos = (int)(((unsigned)(tid >> 5) * gridDim.x + blockIdx.x) * 32u + lane);
     uint32_t end_off = 0, idx = 0;
     if (pos < P) end_off = __ldg(offsets + pos);
     uint32_t start = __shfl_up_sync(full, end_off, 1);
@@ -163,9 +169,12 @@ __global__ void __launch_bounds__(kDupThreads)
             }
         }
     };
+    // rectangles of more than kHuge tiles (close-ups: up to the whole tile grid) are queued for the whole
+    // CTA; a warp left alone with 32 of them (a quarter of a million slots) was a 0.2 ms tail
+    constexpr uint32_t kWide = 32, kHuge = 512;
+    if (len > kHuge) s_huge[atomicAdd(&s_nhuge, 1)] = make_uint4(start, len, rect, idx);
     // rectangles of more than kWide tiles: the whole warp, one rectangle at a time
-    constexpr uint32_t kWide = 32;
-    unsigned wide = __ballot_sync(full, len > kWide);
+    unsigned wide = __ballot_sync(full, len > kWide && len <= kHuge);
     while (wide) {
         const int src = __ffs(wide) - 1;
         wide &= wide - 1u;
@@ -184,6 +193,11 @@ __global__ void __launch_bounds__(kDupThreads)
         if (iters == 0u) continue;
         emit(sub, 8u, iters, g_len, __shfl_sync(full, start, src), __shfl_sync(full, rect, src),
              __shfl_sync(full, idx, src));
+    }
+    __syncthreads();
+    for (int e = 0, n = s_nhuge; e < n; ++e) {
+        const uint4 h = s_huge[e];
+        emit((uint32_t)tid, (uint32_t)kDupThreads, (h.y + kDupThreads - 1) / kDupThreads, h.y, h.x, h.z, h.w);
     }
     __syncthreads();
     for (int i = tid; i < plan.num_passes * 256; i += kDupThreads) {
