@@ -40,29 +40,39 @@ enum Stage {
     ST_PREPROCESS_BWD,
     ST_LBS_FWD,
     ST_LBS_BWD,
+    ST_TILE_SPLIT,
     ST_COUNT
 };
 static_assert(ST_COUNT == HUGS_B200_NUM_STAGES, "stage table out of sync with the header");
 static const char* const kStageNames[ST_COUNT] = {
     "preprocess", "inclusive_scan", "duplicate_with_keys", "sort_pairs", "identify_tile_ranges",
-    "render_forward", "render_backward", "preprocess_backward", "lbs_forward", "lbs_backward"};
+    "render_forward", "render_backward", "preprocess_backward", "lbs_forward", "lbs_backward",
+    "tile_split"};
 
 struct StageTimer {
     std::mutex mu;
     std::atomic<int> enabled{0};
     struct Pair {
-        int stage;
+        int stage, dev;
         cudaEvent_t a, b;
     };
     std::vector<Pair> pending;
-    std::vector<cudaEvent_t> free_events;
+    // CUDA events belong to the device that was current when they were created: one pool per device
+    static constexpr int kMaxDevices = 64;
+    std::vector<cudaEvent_t> free_events[kMaxDevices];
     double ms[ST_COUNT] = {0};
     long long calls[ST_COUNT] = {0};
 
-    cudaEvent_t get() {
-        if (!free_events.empty()) {
-            cudaEvent_t e = free_events.back();
-            free_events.pop_back();
+    static int device_slot() {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return -1;
+        return dev;
+    }
+    cudaEvent_t get(int dev) {
+        if (dev < 0) return nullptr;
+        if (!free_events[dev].empty()) {
+            cudaEvent_t e = free_events[dev].back();
+            free_events[dev].pop_back();
             return e;
         }
         cudaEvent_t e = nullptr;
@@ -76,22 +86,24 @@ struct StageScope {
     int stage;
     cudaStream_t stream;
     cudaEvent_t a = nullptr;
+    int dev = -1;
     StageScope(int st, cudaStream_t s) : stage(st), stream(s) {
         if (g_timer.enabled.load(std::memory_order_relaxed)) {
             std::lock_guard<std::mutex> lk(g_timer.mu);
-            a = g_timer.get();
+            dev = StageTimer::device_slot();
+            a = g_timer.get(dev);
             if (a) cudaEventRecord(a, stream);
         }
     }
     ~StageScope() {
         if (a) {
             std::lock_guard<std::mutex> lk(g_timer.mu);
-            cudaEvent_t b = g_timer.get();
+            cudaEvent_t b = g_timer.get(dev);
             if (b) {
                 cudaEventRecord(b, stream);
-                g_timer.pending.push_back({stage, a, b});
+                g_timer.pending.push_back({stage, dev, a, b});
             } else {
-                g_timer.free_events.push_back(a);
+                g_timer.free_events[dev].push_back(a);
             }
         }
     }
@@ -126,6 +138,11 @@ GeomView carve_geom(char* base, int P) {
     g.dsort_vals_tmp = take<uint32_t>(p, n);
     g.dsort_temp_bytes = sort_temp_bytes(P);
     g.dsort_temp = take<char>(p, g.dsort_temp_bytes);
+    // appended after every exported offset
+    g.grad_pack = take<float>(p, 8 * n);
+    g.rects = take<uint2>(p, n);
+    g.st_touched = take<uint32_t>(p, n);
+    g.pair_counts = take<uint32_t>(p, 2);
     g.total = (size_t)(p - base);
     return g;
 }
@@ -142,16 +159,19 @@ ImageView carve_image(char* base, int W, int H) {
     return v;
 }
 
-BinningView carve_binning(char* base, int R, int num_tiles) {
+BinningView carve_binning(char* base, int R, int grid_x, int grid_y) {
     BinningView b;
     char* p = base;
     const size_t n = (size_t)(R > 0 ? R : 0);
+    const int num_tiles = grid_x * grid_y;
     b.list = take<uint32_t>(p, n);  // first: the backward pass finds it without knowing the capacity
     b.keys = take<uint64_t>(p, n);
     b.keys_unsorted = take<uint64_t>(p, n);
     b.list_unsorted = take<uint32_t>(p, n);
     b.sort_temp_bytes = sort_temp_bytes(R);
     b.sort_temp = take<char>(p, b.sort_temp_bytes);
+    b.l2_temp_bytes = carve_l2_temp(nullptr, R > 0 ? R : 0, super_grid_x(grid_x) * super_grid_y(grid_y), num_tiles).total;
+    b.l2_temp = take<char>(p, b.l2_temp_bytes);
     // last, so that no other offset depends on the tile count
     b.hit_words = take<uint32_t>(p, ((n + 31) / 32 + (size_t)(num_tiles > 0 ? num_tiles : 0) + 1) * 8);
     b.total = (size_t)(p - base);
@@ -181,37 +201,45 @@ static int* pinned_counter() {
     return p;
 }
 
-// Event that marks "the pair count has landed in the pinned counter" (one per host thread).
+// Event that marks "the pair count has landed in the pinned counter": one per host thread and device
+// (an event can only be recorded on a stream of the device it was created on).
 static cudaEvent_t count_event() {
-    static thread_local cudaEvent_t e = nullptr;
-    if (e == nullptr) {
-        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) e = nullptr;
+    static thread_local cudaEvent_t ev[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (ev[dev] == nullptr) {
+        if (cudaEventCreateWithFlags(&ev[dev], cudaEventDisableTiming) != cudaSuccess) ev[dev] = nullptr;
     }
-    return e;
+    return ev[dev];
 }
 
 static std::atomic<int> g_binning_mode{HUGS_B200_BINNING_ASYNC};
 
 // Pair-count history per (P, W, H): capacity = recent maximum + 25 % slack, decaying slowly.
 struct CapacityHint {
-    int P, W, H, cap;
+    int P, W, H, cap, cap1;   // cap: (Gaussian, tile) pairs; cap1: level-1 (Gaussian, super-tile) entries
     unsigned long long stamp;
 };
 static thread_local CapacityHint g_hints[8];
 static thread_local unsigned long long g_hint_clock = 0;
 
-static int capacity_hint(int P, int W, int H) {
+static int capacity_hint(int P, int W, int H, int* cap1) {
     for (CapacityHint& h : g_hints)
         if (h.cap > 0 && h.P == P && h.W == W && h.H == H) {
             h.stamp = ++g_hint_clock;
+            *cap1 = h.cap1;
             return h.cap;
         }
     return 0;
 }
 
-static void update_capacity_hint(int P, int W, int H, int R) {
+static int with_slack(int R) {
     const long long want_ll = (long long)R + R / 4 + 4096;
-    const int want = want_ll > 0x7fff0000LL ? 0x7fff0000 : (int)want_ll;
+    return want_ll > 0x7fff0000LL ? 0x7fff0000 : (int)want_ll;
+}
+
+static void update_capacity_hint(int P, int W, int H, int R, int R1) {
+    const int want = with_slack(R), want1 = with_slack(R1);
     CapacityHint* slot = nullptr;
     for (CapacityHint& h : g_hints)
         if (h.cap > 0 && h.P == P && h.W == W && h.H == H) slot = &h;
@@ -220,12 +248,14 @@ static void update_capacity_hint(int P, int W, int H, int R) {
         for (CapacityHint& h : g_hints)
             if (h.stamp < slot->stamp) slot = &h;
         slot->cap = 0;
+        slot->cap1 = 0;
     }
-    const int decayed = (int)(slot->cap * 0.98);
+    const int decayed = (int)(slot->cap * 0.98), decayed1 = (int)(slot->cap1 * 0.98);
     slot->P = P;
     slot->W = W;
     slot->H = H;
     slot->cap = want > decayed ? want : decayed;
+    slot->cap1 = want1 > decayed1 ? want1 : decayed1;
     slot->stamp = ++g_hint_clock;
 }
 
@@ -279,19 +309,22 @@ long long hugs_b200_launch_count(int reset) {
 }
 
 int hugs_b200_set_binning_mode(int mode) {
-    if (mode < HUGS_B200_BINNING_ASYNC || mode > HUGS_B200_BINNING_REFERENCE) return HUGS_B200_EINVAL;
+    if (mode < HUGS_B200_BINNING_ASYNC || mode > HUGS_B200_BINNING_TILESORT) return HUGS_B200_EINVAL;
     return g_binning_mode.exchange(mode);
 }
 
 static int tiles_of(int width, int height) { return cdiv(width, HB_TILE_X) * cdiv(height, HB_TILE_Y); }
+static BinningView carve_binning_wh(char* base, int R, int width, int height) {
+    return carve_binning(base, R, cdiv(width, HB_TILE_X), cdiv(height, HB_TILE_Y));
+}
 
 size_t hugs_b200_binning_capacity_of(size_t nbytes, int width, int height) {
     // largest capacity whose layout fits in nbytes (the layout size is monotone in the capacity)
-    const int tiles = (width > 0 && height > 0) ? tiles_of(width, height) : 0;
+    if (width <= 0 || height <= 0) return 0;
     size_t lo = 0, hi = nbytes / 24 + 1;
     while (lo < hi) {
         const size_t mid = lo + (hi - lo + 1) / 2;
-        if (mid <= 0x7fffffffULL && carve_binning(nullptr, (int)mid, tiles).total <= nbytes) lo = mid;
+        if (mid <= 0x7fffffffULL && carve_binning_wh(nullptr, (int)mid, width, height).total <= nbytes) lo = mid;
         else hi = mid - 1;
     }
     return lo;
@@ -311,8 +344,8 @@ int hugs_b200_stage_timing_read(double* ms_sum, long long* calls, int reset) {
             g_timer.ms[p.stage] += ms;
             g_timer.calls[p.stage] += 1;
         }
-        g_timer.free_events.push_back(p.a);
-        g_timer.free_events.push_back(p.b);
+        g_timer.free_events[p.dev].push_back(p.a);
+        g_timer.free_events[p.dev].push_back(p.b);
     }
     g_timer.pending.clear();
     for (int i = 0; i < ST_COUNT; i++) {
@@ -355,7 +388,7 @@ int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out
 
 int hugs_b200_binning_layout_of(int R, int width, int height, hugs_b200_binning_layout* out) {
     if (!out || R < 0 || width <= 0 || height <= 0) return HUGS_B200_EINVAL;
-    const BinningView b = carve_binning(nullptr, R, tiles_of(width, height));
+    const BinningView b = carve_binning_wh(nullptr, R, width, height);
     out->point_list_keys = (size_t)reinterpret_cast<char*>(b.keys);
     out->point_list = (size_t)reinterpret_cast<char*>(b.list);
     out->point_list_keys_unsorted = (size_t)reinterpret_cast<char*>(b.keys_unsorted);
@@ -451,6 +484,8 @@ static GeomView geom_rows_from(const GeomView& g, int row0) {
     o.rgb += row0;
     o.clamped += row0;
     o.tiles_touched += row0;
+    o.rects += row0;
+    o.st_touched += row0;
     return o;
 }
 
@@ -712,45 +747,44 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
         set_error("rasterize_backward: binning buffer of %zu bytes cannot hold %d pairs", binning_bytes, R);
         return HUGS_B200_EINVAL;
     }
-    const BinningView bin = carve_binning(binning_buffer, (int)cap, cam.grid_x * cam.grid_y);
+    const BinningView bin = carve_binning(binning_buffer, (int)cap, cam.grid_x, cam.grid_y);
     const ImageView img = carve_image(image_buffer, width, height);
 
     const float* color_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
     const int stride = colors_precomp != nullptr ? 3 : 4;
-    // The blend backward accumulates into these with atomics, so they are cleared first (part of
-    // the stage's cost).
+    // The blend backward accumulates with reductions into the packed per-Gaussian records (geometry
+    // workspace) and into dL_dopacity, so both are cleared first (part of the stage's cost); the
+    // per-Gaussian kernel below unpacks the records into dL_dmean2D / dL_dconic / dL_dcolor.
     auto blend_backward = [&]() -> int {
-        HB_CUDA_OK(cudaMemsetAsync(dL_dmean2D, 0, sizeof(float) * 3 * (size_t)P, stream));
-        HB_CUDA_OK(cudaMemsetAsync(dL_dconic, 0, sizeof(float) * 4 * (size_t)P, stream));
+        HB_CUDA_OK(cudaMemsetAsync(geom.grad_pack, 0, sizeof(float) * 8 * (size_t)P, stream));
         HB_CUDA_OK(cudaMemsetAsync(dL_dopacity, 0, sizeof(float) * (size_t)P, stream));
-        HB_CUDA_OK(cudaMemsetAsync(dL_dcolor, 0, sizeof(float) * 3 * (size_t)P, stream));
         if (R <= 0) return 0;
         return launch_render_backward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y, background,
                                       geom.means2D, geom.conic_opacity, color_ptr, stride, img.accum_alpha,
-                                      img.n_contrib, bin.hit_words, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity,
-                                      dL_dcolor, stream);
+                                      img.n_contrib, bin.hit_words, dL_dpix, geom.grad_pack, dL_dopacity, stream);
     };
     HB_STAGE(blend_backward(), ST_RENDER_BWD);
     if (const SecondSegment* s2 = tl_seg2) {
         const size_t r0 = (size_t)s2->P0;
         if (s2->P0 > 0)
             HB_STAGE(launch_preprocess_backward(s2->P0, D, M, means3D, radii, shs, geom.clamped, scales, rotations,
-                                                scale_modifier, nullptr, cam, dL_dmean2D, dL_dconic, dL_dmean3D,
-                                                dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
+                                                scale_modifier, nullptr, cam, geom.grad_pack, dL_dmean2D, dL_dconic,
+                                                dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
                                                 dL_dsh_accumulate != 0, stream),
                      ST_PREPROCESS_BWD);
         if (P - s2->P0 > 0)
             HB_STAGE(launch_preprocess_backward(P - s2->P0, D, M, s2->means3D, radii + r0, s2->shs, geom.clamped + r0,
                                                 s2->scales, s2->rotations, scale_modifier, nullptr, cam,
-                                                dL_dmean2D + 3 * r0, dL_dconic + 4 * r0, dL_dmean3D + 3 * r0,
+                                                geom.grad_pack + 8 * r0, dL_dmean2D + 3 * r0, dL_dconic + 4 * r0,
+                                                dL_dmean3D + 3 * r0,
                                                 dL_dcolor + 3 * r0, dL_dcov3D + 6 * r0, dL_dsh + (size_t)M * 3 * r0,
                                                 dL_dscale + 3 * r0, dL_drot + 4 * r0, dL_dsh_accumulate != 0, stream),
                      ST_PREPROCESS_BWD);
         return 0;
     }
     HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,
-                                        rotations, scale_modifier, cov3D_precomp, cam, dL_dmean2D, dL_dconic,
-                                        dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
+                                        rotations, scale_modifier, cov3D_precomp, cam, geom.grad_pack, dL_dmean2D,
+                                        dL_dconic, dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
                                         dL_dsh_accumulate != 0, stream),
              ST_PREPROCESS_BWD);
     return 0;

@@ -85,9 +85,13 @@ __global__ void __launch_bounds__(kDupThreads)
 // histogram pass of its own.  Emission is clamped to `cap` slots: the workspace is sized from the
 // previous frames' pair count before the real count has reached the host (api.cu); an overflow is
 // detected there and redone.
+// kSuper: the units are super-tiles (8x4 tiles, binning2.cu) instead of tiles; the rectangle comes from the
+// packed tile rectangle the preprocess kernel left (`rects`), grid_x is the super-tile grid width.
+template <bool kSuper>
 __global__ void __launch_bounds__(kDupThreads)
     duplicate_sorted_kernel(int P, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ offsets,
                             const float2* __restrict__ means2D, const int* __restrict__ radii,
+                            const uint2* __restrict__ rects,
                             uint64_t* __restrict__ pairs, unsigned grid_x, unsigned grid_y, uint32_t cap,
                             const SortPassPlan plan, uint32_t* __restrict__ hist) {
     // Each lane loads ONE depth-sorted Gaussian (slot range + tile rectangle); the slots are then
@@ -120,14 +124,20 @@ __global__ void __launch_bounds__(kDupThreads)
     uint32_t rect = 0;
     if (len != 0u) {
         idx = __ldg(perm + pos);
-        // getRect (auxiliary.h:46-56), same float sequence as preprocess.
-        const float2 p = __ldg(means2D + idx);
-        const float rf = (float)__ldg(radii + idx);
-        const unsigned min_x = min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.x, -rf), 0.0625f)));
-        const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
-        const unsigned max_x =
-            min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
-        rect = min_x | (min_y << 10) | ((max_x - min_x) << 20);
+        if (kSuper) {
+            const uint2 r = __ldg(rects + idx);
+            const unsigned sx0 = (r.x & 0xffffu) >> 3, sx1 = ((r.x >> 16) + 7u) >> 3, sy0 = (r.y & 0xffffu) >> 2;
+            rect = sx0 | (sy0 << 10) | ((sx1 - sx0) << 20);
+        } else {
+            // getRect (auxiliary.h:46-56), same float sequence as preprocess.
+            const float2 p = __ldg(means2D + idx);
+            const float rf = (float)__ldg(radii + idx);
+            const unsigned min_x = min(grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.x, -rf), 0.0625f)));
+            const unsigned min_y = min(grid_y, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(p.y, -rf), 0.0625f)));
+            const unsigned max_x = min(
+                grid_x, (unsigned)max(0, (int)__fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(p.x, rf), 16.f), -1.f), 0.0625f)));
+            rect = min_x | (min_y << 10) | ((max_x - min_x) << 20);
+        }
     }
     // digit layout of the sort passes relative to the tile id
     const int sh0 = plan.shift[0] - 32, sh1 = plan.shift[1] - 32, sh2 = plan.shift[2] - 32;
@@ -372,9 +382,27 @@ int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* offsets
         set_error("duplicate_sorted: tile grid %dx%d too large", grid_x, grid_y);
         return HUGS_B200_EUNSUP_INTERNAL;
     }
-    duplicate_sorted_kernel<<<cdiv(P, kDupThreads), kDupThreads, 0, stream>>>(
-        P, perm, offsets, means2D, radii, pairs, (unsigned)grid_x, (unsigned)grid_y, (uint32_t)cap, plan, hist);
+    duplicate_sorted_kernel<false><<<cdiv(P, kDupThreads), kDupThreads, 0, stream>>>(
+        P, perm, offsets, means2D, radii, nullptr, pairs, (unsigned)grid_x, (unsigned)grid_y, (uint32_t)cap, plan,
+        hist);
     HB_LAUNCH_OK("duplicate_with_keys", stream, false);
+    return 0;
+}
+
+// Level 1 of the two-level binning (binning2.cu): (super-tile << 32 | Gaussian index) entries in depth order.
+// `offsets` is the inclusive scan of the per-Gaussian super-tile counts in depth order, gx_s x gy_s the
+// super-tile grid.
+int launch_duplicate_super(int P, const uint32_t* perm, const uint32_t* offsets, const uint2* rects, uint64_t* pairs,
+                           int gx_s, int gy_s, int cap1, const SortPassPlan& plan, uint32_t* hist,
+                           cudaStream_t stream) {
+    if (P <= 0) return 0;
+    if (gx_s > 1023 || gy_s > 1023 || plan.num_passes > 3) {
+        set_error("duplicate_super: super-tile grid %dx%d too large", gx_s, gy_s);
+        return HUGS_B200_EUNSUP_INTERNAL;
+    }
+    duplicate_sorted_kernel<true><<<cdiv(P, kDupThreads), kDupThreads, 0, stream>>>(
+        P, perm, offsets, nullptr, nullptr, rects, pairs, (unsigned)gx_s, (unsigned)gy_s, (uint32_t)cap1, plan, hist);
+    HB_LAUNCH_OK("duplicate_super", stream, false);
     return 0;
 }
 

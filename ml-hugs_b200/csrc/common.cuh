@@ -52,7 +52,7 @@ struct GeomView {
     float4* rgb;
     uint8_t* clamped;
     uint32_t* tiles_touched;
-    uint32_t* point_offsets;  // inclusive scan of tiles_touched in depth-sorted order
+    uint32_t* point_offsets;  // inclusive scan, in depth-sorted order, of st_touched (tiles_touched in TILESORT mode)
     char* scan_temp;
     size_t scan_temp_bytes;
     uint32_t* sorted_depths;  // depth bits, ascending (culled Gaussians: 0xFFFFFFFF, last)
@@ -61,6 +61,10 @@ struct GeomView {
     uint32_t* dsort_vals_tmp;
     char* dsort_temp;
     size_t dsort_temp_bytes;
+    float* grad_pack;         // [P][8] backward scratch: dL/d(colour 3, mean2D 2, conic 3), see render_backward.cu
+    uint2* rects;             // tile rectangle of every Gaussian (x0 | x1 << 16, y0 | y1 << 16)
+    uint32_t* st_touched;     // super-tiles its rectangle overlaps
+    uint32_t* pair_counts;    // [0] R = sum of tiles_touched, [1] R1 = sum of st_touched
     size_t total;
 };
 struct ImageView {
@@ -76,12 +80,33 @@ struct BinningView {
     uint32_t* list_unsorted;
     char* sort_temp;
     size_t sort_temp_bytes;
+    char* l2_temp;        // level-2 binning scratch (binning2.cu: carve_l2_temp)
+    size_t l2_temp_bytes;
     uint32_t* hit_words;  // [(R+31)/32 + tiles + 1][8 warps]: what each warp of the forward blend actually blended
     size_t total;
 };
+// Super-tiles: 8 x 4 tiles.
+static inline int super_grid_x(int grid_x) { return (grid_x + 7) / 8; }
+static inline int super_grid_y(int grid_y) { return (grid_y + 3) / 4; }
+struct L2Temp {
+    uint32_t chunk_cap;
+    uint32_t* counts;          // [chunk_cap][32]
+    uint2* chunks;             // [chunk_cap] (super-tile | entries << 16, first list position)
+    uint2* st_ranges;          // [n_st] list range of every super-tile
+    uint32_t* st_chunk_start;  // [n_st + 1]
+    uint32_t* tile_total;      // [tiles]
+    uint32_t* tile_start;      // [tiles]
+    uint32_t* n_chunks;        // [1]
+    size_t total;
+};
+L2Temp carve_l2_temp(char* base, int cap, int n_st, int num_tiles);
+int launch_l2_split(const L2Temp& t, const uint32_t* st_list, const uint2* rects, int n_st, int gx_s, int grid_x,
+                    int grid_y, int cap1, int cap, uint32_t* list, uint2* ranges, cudaStream_t stream);
+int launch_keys_from_ranges(int num_tiles, const uint2* ranges, const uint32_t* list, const uint32_t* depth_bits,
+                            uint64_t* keys, cudaStream_t stream);
 GeomView carve_geom(char* base, int P);
 ImageView carve_image(char* base, int W, int H);
-BinningView carve_binning(char* base, int R, int num_tiles);
+BinningView carve_binning(char* base, int R, int grid_x, int grid_y);
 
 constexpr int kSortMaxPasses = 8;
 struct SortPassPlan {  // pass p sorts on `bits[p]` key bits starting at bit `shift[p]`
@@ -117,6 +142,9 @@ int launch_duplicate(int P, const float2* means2D, const float* depths, const ui
 int launch_duplicate_sorted(int P, const uint32_t* perm, const uint32_t* offsets, const float2* means2D,
                             const int* radii, uint64_t* pairs, int grid_x, int grid_y, int cap,
                             const SortPassPlan& plan, uint32_t* hist, cudaStream_t stream);
+int launch_duplicate_super(int P, const uint32_t* perm, const uint32_t* offsets, const uint2* rects, uint64_t* pairs,
+                           int gx_s, int gy_s, int cap1, const SortPassPlan& plan, uint32_t* hist,
+                           cudaStream_t stream);
 int launch_tile_ranges(int R, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t stream,
                        const uint32_t* n_dev = nullptr);
 // the same from the per-position tile ids the two-level sort leaves behind (u16 or u32)
@@ -150,13 +178,12 @@ int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int 
                            const float* bg, const float2* means2D, const float4* conic_opacity,
                            const float* colors, int color_stride, const float* final_T,
                            const uint32_t* n_contrib, const uint32_t* hit_words, const float* dL_dpix,
-                           float* dL_dmean2D /*[P,3]*/,
-                           float* dL_dconic /*[P,4]*/, float* dL_dopacity, float* dL_dcolor /*[P,3]*/,
+                           float* grad_pack /*[P,8], zeroed*/, float* dL_dopacity /*[P], zeroed*/,
                            cudaStream_t stream);
 int launch_preprocess_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
                                const uint8_t* clamped, const float* scales, const float* rotations,
                                float scale_modifier, const float* cov3D_precomp, const Camera& cam,
-                               const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
+                               const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                                float* dL_drot, bool sh_accumulate, cudaStream_t stream);
 

@@ -52,6 +52,9 @@ struct PreprocessArgs {
     float4* rgb;
     uint8_t* clamped;
     uint32_t* tiles_touched;
+    uint2* rects;            // tile rectangle (x0 | x1 << 16, y0 | y1 << 16), zero for culled Gaussians
+    uint32_t* st_touched;    // super-tiles (8x4 tiles) the rectangle overlaps
+    uint32_t* pair_counts;   // [0] += sum of tiles_touched, [1] += sum of st_touched (zeroed by the caller)
     int prefiltered;
     int sh_vec4;  // shs is [P,16,3] and 16-byte aligned: use 128-bit loads
     int rot_vec4;
@@ -160,6 +163,7 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const Prepro
     float conic_x = 0.f, conic_y = 0.f, conic_z = 0.f, opacity = 0.f;
     int radius = 0;
     unsigned tiles = 0;
+    unsigned rx0 = 0, rx1 = 0, ry0 = 0, ry1 = 0;
 
     if (valid) do {
         // ---- every per-Gaussian input except the SH row, requested up front -----------------
@@ -272,6 +276,10 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const Prepro
             min(gy, (unsigned)max(0, (int)RN_MUL(RN_ADD(RN_ADD(RN_ADD(pix_y, rf), 16.f), -1.f), 0.0625f)));
         tiles = (max_x - min_x) * (max_y - min_y);
         if (tiles == 0) break;
+        rx0 = min_x;
+        rx1 = max_x;
+        ry0 = min_y;
+        ry1 = max_y;
         vis = true;
     } while (0);
 
@@ -354,6 +362,22 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const Prepro
         a.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opacity);
         a.tiles_touched[idx] = tiles;
     }
+    // Binning inputs (binning2.cu): the rectangle itself, the number of 8x4-tile super-tiles it overlaps,
+    // and the two totals -- the pair count R the host needs, and the level-1 entry count.
+    if (a.rects != nullptr) {
+        unsigned st = 0;
+        if (vis) st = (((rx1 + 7u) >> 3) - (rx0 >> 3)) * (((ry1 + 3u) >> 2) - (ry0 >> 2));
+        if (valid) {
+            a.rects[idx] = vis ? make_uint2(rx0 | (rx1 << 16), ry0 | (ry1 << 16)) : make_uint2(0u, 0u);
+            a.st_touched[idx] = st;
+        }
+        const unsigned sum_t = __reduce_add_sync(0xffffffffu, vis ? tiles : 0u);
+        const unsigned sum_s = __reduce_add_sync(0xffffffffu, st);
+        if ((threadIdx.x & 31u) == 0u && sum_t != 0u) {
+            atomicAdd(a.pair_counts + 0, sum_t);
+            atomicAdd(a.pair_counts + 1, sum_s);
+        }
+    }
 }
 
 int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
@@ -390,6 +414,9 @@ int launch_preprocess(int P, int D, int M, const float* means3D, const float* sc
     a.rgb = g.rgb;
     a.clamped = g.clamped;
     a.tiles_touched = g.tiles_touched;
+    a.rects = g.rects;
+    a.st_touched = g.st_touched;
+    a.pair_counts = g.pair_counts;
     a.prefiltered = prefiltered ? 1 : 0;
     a.sh_vec4 = (shs != nullptr && M == 16 && (reinterpret_cast<uintptr_t>(shs) & 15u) == 0) ? 1 : 0;
     a.rot_vec4 = (rotations != nullptr && (reinterpret_cast<uintptr_t>(rotations) & 15u) == 0) ? 1 : 0;

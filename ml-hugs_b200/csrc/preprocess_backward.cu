@@ -29,10 +29,11 @@ struct PreBwdArgs {
     const float* proj;
     const float* campos;
     float tan_fovx, tan_fovy, focal_x, focal_y;
-    const float* dL_dmean2D;  // [P,3]
-    const float* dL_dconic;   // [P,4]
+    const float* grad_pack;   // [P,8]  (input: accumulated by the blend backward) colour 3, mean2D 2, conic 3
+    float* dL_dmean2D;        // [P,3]  (output: unpacked record, z = 0)
+    float* dL_dconic;         // [P,4]  (output: unpacked record, (x, y, 0, w))
     float* dL_dmean3D;        // [P,3]
-    float* dL_dcolor;         // [P,3]  (input: accumulated by the blend backward)
+    float* dL_dcolor;         // [P,3]  (output: unpacked record)
     float* dL_dcov3D;         // [P,6]
     float* dL_dsh;            // [P,M,3]
     float* dL_dscale;         // [P,3]
@@ -208,6 +209,13 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
 
     if (valid && !vis) {
         out_mean[0] = out_mean[1] = out_mean[2] = 0.f;
+        a.dL_dmean2D[3 * (size_t)idx + 0] = 0.f;
+        a.dL_dmean2D[3 * (size_t)idx + 1] = 0.f;
+        a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+        reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        a.dL_dcolor[3 * (size_t)idx + 0] = 0.f;
+        a.dL_dcolor[3 * (size_t)idx + 1] = 0.f;
+        a.dL_dcolor[3 * (size_t)idx + 2] = 0.f;
 #pragma unroll
         for (int i = 0; i < 6; i++) out_cov[i] = 0.f;
         if (a.dL_dscale != nullptr) {
@@ -231,18 +239,26 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
         mx = __ldg(a.means3D + 3 * (size_t)idx + 0);
         my = __ldg(a.means3D + 3 * (size_t)idx + 1);
         mz = __ldg(a.means3D + 3 * (size_t)idx + 2);
-        const float4 dconic4 = __ldg(reinterpret_cast<const float4*>(a.dL_dconic) + idx);
-        const float g2x = __ldg(a.dL_dmean2D + 3 * (size_t)idx + 0);
-        const float g2y = __ldg(a.dL_dmean2D + 3 * (size_t)idx + 1);
+        // the blend backward's packed record: one 32-byte sector
+        const float4 pk0 = __ldg(reinterpret_cast<const float4*>(a.grad_pack) + 2 * (size_t)idx);
+        const float4 pk1 = __ldg(reinterpret_cast<const float4*>(a.grad_pack) + 2 * (size_t)idx + 1);
+        const float4 dconic4 = make_float4(pk1.y, pk1.z, 0.f, pk1.w);
+        const float g2x = pk0.w, g2y = pk1.x;
         if (a.shs != nullptr) {
             const uint8_t cl = __ldg(a.clamped + idx);
-            const float c0 = __ldg(a.dL_dcolor + 3 * (size_t)idx + 0);
-            const float c1 = __ldg(a.dL_dcolor + 3 * (size_t)idx + 1);
-            const float c2 = __ldg(a.dL_dcolor + 3 * (size_t)idx + 2);
-            dRGB[0] = (cl & 1) ? 0.f : c0;
-            dRGB[1] = (cl & 2) ? 0.f : c1;
-            dRGB[2] = (cl & 4) ? 0.f : c2;
+            dRGB[0] = (cl & 1) ? 0.f : pk0.x;
+            dRGB[1] = (cl & 2) ? 0.f : pk0.y;
+            dRGB[2] = (cl & 4) ? 0.f : pk0.z;
         }
+        // the reference's arrays (rasterize_points.cu:151-159 allocates them; dL_dmeans2D and dL_dcolors go
+        // back to Python)
+        a.dL_dmean2D[3 * (size_t)idx + 0] = g2x;
+        a.dL_dmean2D[3 * (size_t)idx + 1] = g2y;
+        a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+        reinterpret_cast<float4*>(a.dL_dconic)[idx] = dconic4;
+        a.dL_dcolor[3 * (size_t)idx + 0] = pk0.x;
+        a.dL_dcolor[3 * (size_t)idx + 1] = pk0.y;
+        a.dL_dcolor[3 * (size_t)idx + 2] = pk0.z;
         float cov3[6];
         if (has_scale) {
             sx = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 0);
@@ -427,8 +443,8 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
             if (have_gsh) {
                 float* dst = a.dL_dsh + (size_t)idx * a.M * 3;
 #pragma unroll
-                for (int i = 0; i < 48; i++)
-                    if (i < a.M * 3) dst[i] += gsh[i];
+                for (int i = 0; i < 48; i++)   // other views may be adding to the same row on other streams
+                    if (i < a.M * 3) atomicAdd(dst + i, gsh[i]);
             }
         } else if (sh_out) {
             if (!have_gsh) {
@@ -504,7 +520,8 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
 int launch_preprocess_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
                                const uint8_t* clamped, const float* scales, const float* rotations,
                                float scale_modifier, const float* cov3D_precomp, const Camera& cam,
-                               const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D, float* dL_dcolor,
+                               const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
+                               float* dL_dcolor,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
                                bool sh_accumulate, cudaStream_t stream) {
     PreBwdArgs a;
@@ -526,6 +543,7 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
     a.tan_fovy = cam.tan_fovy;
     a.focal_x = cam.focal_x;
     a.focal_y = cam.focal_y;
+    a.grad_pack = grad_pack;
     a.dL_dmean2D = dL_dmean2D;
     a.dL_dconic = dL_dconic;
     a.dL_dmean3D = dL_dmean3D;

@@ -25,7 +25,6 @@
 // of the R pairs on the tile bits only (2 passes at 1080p instead of 6).  See DESIGN.md.
 #include "common.cuh"
 
-#include <cstdlib>
 #include <cstring>
 
 namespace hb {
@@ -204,7 +203,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                           KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n_host,
                           const uint32_t* __restrict__ n_dev, int shift, uint32_t digit_mask, int pass,
                           const uint32_t* __restrict__ pass_offsets, unsigned long long* lookback,
-                          unsigned* tickets, int tile16, int dbg_no_lookback) {
+                          unsigned* tickets, int tile16) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int kSortThreads = THREADS, kSortItems = ITEMS, kSortWarps = THREADS / 32, kSortTile = THREADS * ITEMS;
     static_assert(THREADS >= kRadix && THREADS % kRadix == 0, "digit phases use the first kRadix threads");
@@ -307,8 +306,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
         const int d = tid / T, sub = tid & (T - 1);
         if (d < bins) {
             const unsigned gmask = (T == 32) ? 0xffffffffu : (((1u << T) - 1u) << (lane & ~(unsigned)(T - 1)));
-            const uint32_t prefix =
-                dbg_no_lookback ? 0u : lookback_prefix(lookback, tile, d, sub, T, gmask, flag_agg, flag_inc);
+            const uint32_t prefix = lookback_prefix(lookback, tile, d, sub, T, gmask, flag_agg, flag_inc);
             if (sub == 0) {
                 const uint32_t cnt = s.count[d];
                 if (tile != 0)
@@ -395,18 +393,20 @@ int launch_pass_bits(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t*
     constexpr int THREADS = kSortThreads, ITEMS = kSortItems;
     using Smem = SortSmem<KeyT, THREADS, ITEMS, MODE>;
     auto kernel = radix_onesweep_kernel<KeyT, THREADS, ITEMS, 2, MODE, BITS>;
-    static bool configured = false;  // per instantiation; the attribute is per device function, idempotent
-    if (!configured) {
-        HB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-        HB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                        cudaSharedmemCarveoutMaxShared));
-        configured = true;
+    {  // opt in to > 48 KB of dynamic shared memory: per instantiation and per device
+        static bool configured[64] = {false};
+        int dev = 0;
+        HB_CUDA_OK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !configured[dev]) {
+            HB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+            HB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            cudaSharedmemCarveoutMaxShared));
+            if (dev >= 0 && dev < 64) configured[dev] = true;
+        }
     }
-    static const int no_lookback = getenv("HB_SORT_NOLOOK") ? 1 : 0;  // timing experiments only: wrong output
     const int tiles = cdiv(n_cap, THREADS * ITEMS);
     kernel<<<tiles, THREADS, sizeof(Smem), stream>>>(kin, vin, kout, vout, n_cap, n_dev, shift, mask, pass,
-                                                     t.hist + pass * kRadix, t.lookback, t.tickets, tile16,
-                                                     no_lookback);
+                                                     t.hist + pass * kRadix, t.lookback, t.tickets, tile16);
     HB_LAUNCH_OK("radix_onesweep", stream, false);
     return 0;
 }

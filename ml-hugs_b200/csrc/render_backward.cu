@@ -2,25 +2,30 @@
 // Replaces renderCUDA<3> backward (cuda_rasterizer/backward.cu:399-557).
 //
 // The reference issues 9 global float atomicAdds per (pixel, Gaussian) hit, all 256 pixels of a
-// tile hammering the same 9 addresses in lock step.  This kernel is issue-bound (not HBM-bound),
-// so everything below is about executing fewer warp instructions per blended Gaussian:
-//   * a warp owns an 8x4 sub-tile and walks ONLY the Gaussians it blended in the forward pass: the
-//     forward blend leaves one 32-bit mask per (32 list positions, warp) (render_forward.cu), so
-//     there is no cull test and no evaluation that ends in "no pixel of this warp was hit";
-//     positions behind the warp's own largest contributor count are never visited
-//     (backward.cu:486-488 skips them pixel by pixel);
-//   * the 9 partial gradients of a Gaussian are reduced over the warp's 32 pixels with a halving
-//     butterfly (12 SHFL instead of 45) and STORED -- not added -- to the warp's private slot of
-//     the staged batch: each warp meets each Gaussian once per batch, so the 8 warps of a tile
-//     need neither shared-memory atomics nor a zero fill; the flush sums the slots whose mask bit
-//     is set and issues one set of 9 global reductions per (tile, Gaussian) -- 256x fewer global
-//     atomics than the reference;
-//   * dL/dmean2D and dL/dconic are accumulated in a factored form (sums of X, Y, X dx, X dy, Y dy
-//     with X = dL/dG G dx, Y = dL/dG G dy) and multiplied by the conic once per (tile, Gaussian);
-//   * gradients need 1e-3, not bit-exactness: exp and the reciprocal of (1 - alpha) use the
-//     special-function unit (ex2.approx / rcp.approx) instead of the IEEE sequences the forward
-//     pass keeps for its contributor counts.
-// Batches are aligned to multiples of 128 list positions so that the forward masks line up.
+// tile hammering the same 9 addresses in lock step.  This stage is bound by instruction issue, not
+// by HBM, so the design is about warp instructions per blended (warp, Gaussian):
+//
+//   * a warp owns an 8x4 sub-tile and works on its own, with no CTA barrier anywhere: it walks ONLY
+//     the Gaussians it blended in the forward pass (render_forward.cu leaves one 32-bit mask per
+//     32 list positions and warp), back to front, starting at its own largest contributor count;
+//   * the hits are taken 16 at a time and every batch runs in two phases with two thread layouts:
+//       phase 1, lane = pixel.  The sequential part of backward.cu:486-535 (transmittance,
+//         colour-behind recurrence, dL/dalpha).  Per (pixel, Gaussian) it leaves just two numbers
+//         in shared memory: w = alpha T (the weight of the pixel's dL/dpixel in dL/dcolour) and
+//         Z = G dL/dalpha (every geometric gradient is o Z times a polynomial in the pixel offset);
+//       phase 2, lane = Gaussian (half-warp h takes the pixels 16h..16h+15).  Each lane runs down
+//         its Gaussian's row of w and Z and accumulates the 9 sums in registers -- no cross-lane
+//         reduction per hit (round 1's kernel spent 43 of its 111 instructions per (warp, Gaussian)
+//         in a 9-value shuffle butterfly); one shuffle per sum and batch joins the two halves;
+//   * a (warp, Gaussian) ends in two 16-byte vector reductions into a packed 32-byte gradient record
+//     (colour 3, mean2D 2, conic 3) plus one scalar reduction for the opacity; the per-Gaussian
+//     backward kernel reads the record (one sector) and writes the reference's arrays;
+//   * gradients need 1e-3, not bit-exactness: exp and the reciprocal of (1 - alpha) are the bare
+//     special-function instructions, and the conic is pre-scaled by -log2(e)/2 at staging so that
+//     the exponent costs three multiplies and two FMAs.  Deviation from the reference: a pixel whose
+//     alpha lies within rounding of 1/255 can be classified differently from the forward pass (which
+//     uses the IEEE sequence); the pixel's earlier Gaussians then see T off by 1/255.  Measured:
+//     below the 1e-3 bar at every size tested (tests/test_parity_gpu.py, element-wise metric).
 // Per-hit arithmetic follows backward.cu:490-554.
 #include "render_common.cuh"
 
@@ -28,50 +33,16 @@ namespace hb {
 
 namespace {
 
-constexpr int kBwdBatch = 128;                 // Gaussians staged per round
-constexpr int kBwdChunks = kBwdBatch / 32;     // forward-mask words per warp and round
+constexpr int kBwdG = 16;                       // Gaussians per batch
 constexpr int kBwdWarps = kBlendThreads / 32;  // 8
 
-// Sum 9 per-lane values over the warp and store the totals to the 9 floats at shared address `dst`.
-__device__ __forceinline__ void warp_reduce9_store(const float (&v)[9], uint32_t dst, unsigned lane) {
-    const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u, b1 = lane & 2u;
-    float w[4], p8 = v[8];
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const float send = b4 ? v[i] : v[i + 4];
-        const float keep = b4 ? v[i + 4] : v[i];
-        w[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
-    p8 += __shfl_xor_sync(0xffffffffu, p8, 16);
-    float x[2];
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-        const float send = b3 ? w[i] : w[i + 2];
-        const float keep = b3 ? w[i + 2] : w[i];
-        x[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
-    p8 += __shfl_xor_sync(0xffffffffu, p8, 8);
-    float y;
-    {
-        const float send = b2 ? x[0] : x[1];
-        const float keep = b2 ? x[1] : x[0];
-        y = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-    p8 += __shfl_xor_sync(0xffffffffu, p8, 4);
-    // y: value (lane >> 2) summed over the 8 lanes that share (lane & 3); p8: value 8, likewise.
-    // Lanes with bit 1 clear finish y, lanes with bit 1 set finish p8.
-    float r;
-    {
-        const float send = b1 ? y : p8;
-        const float keep = b1 ? p8 : y;
-        r = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    r += __shfl_xor_sync(0xffffffffu, r, 1);
-    // lanes 0,4,..,28 hold values 0..7, lane 2 holds value 8: one predicated store
-    const unsigned slot = (lane == 2u) ? 8u : (lane >> 2);
-    if ((lane & 3u) == 0u || lane == 2u)
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(dst + 4u * slot), "f"(r) : "memory");
-}
+struct __align__(16) BwdWarpSmem {
+    float4 rec[kBwdG][3];   // (x, y, A', B') (C', opacity, r, g) (b, list position, Gaussian index, -)
+    float sw[kBwdG][32];    // w of (Gaussian k, pixel p) at column (p + 4k) & 31
+    float sz[kBwdG][32];    // Z, same layout
+    float4 pixc[32];        // dL/dpixel of the warp's 32 pixels
+    uint32_t slot[kBwdG];   // list positions of the batch being assembled, descending
+};
 
 __device__ __forceinline__ float ex2_ftz(float x) {
     float y;
@@ -83,195 +54,227 @@ __device__ __forceinline__ float rcp_ftz(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+__device__ __forceinline__ float2 lds_f2(uint32_t addr) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_f1(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red_add_f1(float* p, float a) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
+}
 
-__global__ void __launch_bounds__(kBlendThreads, 5)
+constexpr float kLog2e = 1.4426950408889634f;
+
+__global__ void __launch_bounds__(kBlendThreads, 4)
     render_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                            int grid_x, const float* __restrict__ bg, const float2* __restrict__ means2D,
                            const float4* __restrict__ conic_opacity, const float* __restrict__ colors,
                            int color_stride, const float* __restrict__ final_T,
                            const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ hit_words,
-                           const float* __restrict__ dL_dpix, float* __restrict__ dL_dmean2D,
-                           float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
-                           float* __restrict__ dL_dcolor) {
-    __shared__ uint32_t s_id[kBwdBatch];
-    __shared__ __align__(16) unsigned char s_stage[kBwdBatch * kStageBytes];
-    __shared__ float s_part[kBwdWarps][kBwdBatch][9];
-    __shared__ uint32_t s_hit[kBwdChunks][kBwdWarps];    // forward masks of this round
-    __shared__ uint32_t s_touch[kBwdWarps][kBwdChunks];  // what each warp actually wrote to s_part
-    __shared__ uint32_t s_max[kBwdWarps];
-    const uint32_t s_base = (uint32_t)__cvta_generic_to_shared(s_stage);
+                           const float* __restrict__ dL_dpix, float* __restrict__ grad_pack,
+                           float* __restrict__ dL_dopacity) {
+    __shared__ BwdWarpSmem s_all[kBwdWarps];
 
     const unsigned tile_x = blockIdx.x, tile_y = blockIdx.y;
     const unsigned tile_id = tile_y * grid_x + tile_x;
     const PixelMap pm = pixel_map(tile_x, tile_y);
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t part_base = (uint32_t)__cvta_generic_to_shared(&s_part[warp][0][0]);
     const bool inside = pm.px < (unsigned)W && pm.py < (unsigned)H;
     const float pixfx = (float)pm.px, pixfy = (float)pm.py;
     const size_t pix_id = (size_t)W * pm.py + pm.px;
     const size_t plane = (size_t)W * H;
 
-    const uint2 range = __ldg(ranges + tile_id);
+    // In the forward, we stored the final value for T, the product of all (1 - alpha) factors, and the
+    // (1-based) list position of the pixel's last contributor.
+    const uint32_t last_contributor = inside ? __ldg(n_contrib + pix_id) : 0u;
+    // Nothing behind the warp's largest contributor count was blended by any of its pixels.
+    const uint32_t warp_max = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (warp_max == 0u) return;  // the whole warp leaves; no CTA barrier follows
 
-    // In the forward, we stored the final value for T, the product of all (1 - alpha) factors,
-    // and the (1-based) list position of the last contributing Gaussian of each pixel.
+    BwdWarpSmem& s = s_all[warp];
+    const uint32_t s_rec = (uint32_t)__cvta_generic_to_shared(&s.rec[0][0]);
+    const uint32_t s_sw = (uint32_t)__cvta_generic_to_shared(&s.sw[0][0]);
+    const uint32_t s_sz = (uint32_t)__cvta_generic_to_shared(&s.sz[0][0]);
+    const uint32_t s_pixc = (uint32_t)__cvta_generic_to_shared(&s.pixc[0]);
+
+    const uint2 range = __ldg(ranges + tile_id);
     const float T_final = inside ? __ldg(final_T + pix_id) : 0.f;
     float T = T_final;
-    const uint32_t last_contributor = inside ? __ldg(n_contrib + pix_id) : 0u;
-
-    // Largest contributor count of this warp / of the tile: nothing behind it was blended.
-    const uint32_t warp_max = __reduce_max_sync(0xffffffffu, last_contributor);
-    if (lane == 0) s_max[warp] = warp_max;
-    __syncthreads();
-    uint32_t max_contrib = 0;
-#pragma unroll
-    for (int w = 0; w < kBwdWarps; w++) max_contrib = max(max_contrib, s_max[w]);
-    const int todo = (int)min(max_contrib, range.y - range.x);
-    if (todo == 0) return;
-
     float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f;
     if (inside) {
         dLp0 = __ldg(dL_dpix + pix_id);
         dLp1 = __ldg(dL_dpix + plane + pix_id);
         dLp2 = __ldg(dL_dpix + 2 * plane + pix_id);
     }
-    // alpha also influences how much of the background colour is added (backward.cu:531-534)
+    sts_f4(s_pixc + lane * 16u, dLp0, dLp1, dLp2, 0.f);
+    // alpha also decides how much of the background colour is added (backward.cu:531-534)
     const float bg_term = -T_final * (__ldg(bg + 0) * dLp0 + __ldg(bg + 1) * dLp1 + __ldg(bg + 2) * dLp2);
-
-    float accum0 = 0.f, accum1 = 0.f, accum2 = 0.f;
-    float last_alpha = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f;
+    // colour accumulated behind the Gaussian at hand, updated eagerly: after Gaussian j it is
+    // alpha_j c_j + (1 - alpha_j) acc, which is what backward.cu:505-507 computes one step later
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;
 
     // Gradient of pixel coordinate w.r.t. normalized screen-space viewport coordinates (-1 to 1).
     const float ddelx_dx = 0.5f * W;
     const float ddely_dy = 0.5f * H;
-    const uint32_t* const hit_base = hit_words + ((size_t)(range.x >> 5) + tile_id) * kBwdWarps;
 
-    // The list entries of the next round are fetched while this one is processed (first of the two
-    // dependent round trips of the gather).
-    const int pb0 = ((todo - 1) / kBwdBatch) * kBwdBatch;
-    uint32_t next_id = 0;
-    if ((int)threadIdx.x < todo - pb0) next_id = __ldg(point_list + range.x + (uint32_t)(pb0 + (int)threadIdx.x));
+    // phase-2 identity of this lane: Gaussian e of the batch, pixels 16 half .. 16 half + 15
+    const unsigned e = lane & 15u, half = lane >> 4;
+    const float org_x = pm.x0, org_y = pm.y0 + 2.f * (float)half;
 
-    for (int pb = pb0; pb >= 0; pb -= kBwdBatch) {
-        __syncthreads();  // the previous round's flush has read s_part / s_touch / s_id / s_stage
-        const int nb = min(kBwdBatch, todo - pb);
-        // Stage list positions [pb, pb + nb): slot j holds position pb + j.
-        if ((int)threadIdx.x < nb) {
-            s_id[threadIdx.x] = next_id;
-            store_gaussian(s_base + threadIdx.x * kStageBytes,
-                           load_gaussian(next_id, means2D, conic_opacity, colors, color_stride));
-        } else if (threadIdx.x >= kBwdBatch && threadIdx.x < kBwdBatch + kBwdChunks * kBwdWarps) {
-            const int q = ((int)threadIdx.x - kBwdBatch) / kBwdWarps, w = ((int)threadIdx.x - kBwdBatch) % kBwdWarps;
-            uint32_t m = 0;
-            if (pb + 32 * q < todo) m = __ldg(hit_base + (size_t)((pb >> 5) + q) * kBwdWarps + w);
-            s_hit[q][w] = m;
-        }
-        if (pb >= kBwdBatch && threadIdx.x < kBwdBatch)  // the round after this one is always a full batch
-            next_id = __ldg(point_list + range.x + (uint32_t)(pb - kBwdBatch + (int)threadIdx.x));
-        __syncthreads();
+    // ---- the warp's hit masks, most distant list positions first ----------------------------------
+    const uint32_t* const hit_base = hit_words + ((size_t)(range.x >> 5) + tile_id) * kBwdWarps + warp;
+    const int nwords = (int)((warp_max + 31u) >> 5);
+    int qb = nwords - 1;      // word index held by lane 0 of the current group of 32 words
+    uint32_t mw = 0;          // lane i holds word qb - i
+    unsigned nz = 0;          // lanes of the group whose word still has bits
+    uint32_t m = 0;           // bits left in the current word
+    int q = 0;                // index of the current word
+    bool group_loaded = false;
+    int fill = 0;
 
-        // This warp's masks, clipped to positions below its own largest contributor count (words
-        // beyond it were never written by the forward pass).
-        uint32_t mq = 0;
-        if (lane < (unsigned)kBwdChunks) {
-            const int p0 = pb + 32 * (int)lane;
-            if (p0 < (int)warp_max) {
-                mq = s_hit[lane][warp];
-                const int rem = (int)warp_max - p0;
-                if (rem < 32) mq &= (1u << rem) - 1u;
-            }
-            s_touch[warp][lane] = mq;
-        }
-#pragma unroll 1
-        for (int q = kBwdChunks - 1; q >= 0; q--) {
-            unsigned m = __shfl_sync(0xffffffffu, mq, q);
-            while (m) {
-                const int bit = 31 - __clz(m);
-                m ^= 1u << bit;
-                const int e = 32 * q + bit;
-                const uint32_t addr = s_base + (uint32_t)e * kStageBytes;
-                const float4 g0 = lds_f4(addr);       // x, y, A, B
-                const float4 g1 = lds_f4(addr + 16);  // C, opacity, r, g
-                const float cb = lds_f1(addr + 32);   // b
-                // Straight-line: nearly every lane is hit by a Gaussian its warp blended (measured: 28
-                // of 32), so the state updates are predicated instead of branched around.
-                const float dx = g0.x - pixfx;
-                const float dy = g0.y - pixfy;
-                const float power = -0.5f * (g0.z * dx * dx + g1.x * dy * dy) - g0.w * dx * dy;
-                // clamp: a lane outside the footprint must not make inf.  ex2 / rcp are the bare
-                // special-function instructions (flush-to-zero forms: no denormal fix-up code; 1 - alpha
-                // >= 0.01 and a G that underflows belongs to a lane that is not hit).
-                const float G = ex2_ftz(fminf(power, 0.f) * 1.4426950408889634f);
-                const float alpha = fminf(0.99f, g1.y * G);
-                // Skip if this one is behind the last contributor of this pixel, or was skipped by it
-                // in the forward pass (backward.cu:486-501).
-                const bool hit = ((uint32_t)(pb + e) < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                const float rcp = rcp_ftz(1.f - alpha);
-                if (hit) {
-                    T *= rcp;
-                    accum0 = fmaf(last_alpha, last_c0 - accum0, accum0);
-                    accum1 = fmaf(last_alpha, last_c1 - accum1, accum1);
-                    accum2 = fmaf(last_alpha, last_c2 - accum2, accum2);
-                    last_c0 = g1.z;
-                    last_c1 = g1.w;
-                    last_c2 = cb;
-                    last_alpha = alpha;
+    for (;;) {
+        // ---- assemble a batch: the next (up to) 16 set bits, descending list position -------------
+        while (fill < kBwdG) {
+            if (m == 0u) {
+                if (nz == 0u) {
+                    if (group_loaded) qb -= 32;
+                    if (qb < 0) break;
+                    const int myq = qb - (int)lane;
+                    mw = (myq >= 0) ? __ldg(hit_base + (size_t)myq * kBwdWarps) : 0u;
+                    if (myq == nwords - 1) {  // words are only valid below the warp's contributor count
+                        const uint32_t rem = warp_max - 32u * (uint32_t)myq;
+                        if (rem < 32u) mw &= (1u << rem) - 1u;
+                    }
+                    nz = __ballot_sync(0xffffffffu, mw != 0u);
+                    group_loaded = true;
+                    continue;
                 }
-                // Propagate gradients to per-Gaussian colours and keep gradients w.r.t. alpha
-                // (blending factor for a Gaussian/pixel pair); both vanish for a lane that is not hit.
-                const float dchannel_dcolor = hit ? alpha * T : 0.f;
-                float dL_dalpha = (g1.z - accum0) * dLp0 + (g1.w - accum1) * dLp1 + (cb - accum2) * dLp2;
-                dL_dalpha = hit ? fmaf(dL_dalpha, T, bg_term * rcp) : 0.f;
-                const float dL_dG = g1.y * dL_dalpha;
-                const float X = dL_dG * (G * dx);
-                const float Y = dL_dG * (G * dy);
-                float g[9];
-                g[0] = dchannel_dcolor * dLp0;
-                g[1] = dchannel_dcolor * dLp1;
-                g[2] = dchannel_dcolor * dLp2;
-                g[3] = X;
-                g[4] = Y;
-                g[5] = X * dx;
-                g[6] = X * dy;
-                g[7] = Y * dy;
-                g[8] = G * dL_dalpha;
-                warp_reduce9_store(g, part_base + (uint32_t)e * 36u, lane);
+                const int i = __ffs(nz) - 1;
+                nz &= nz - 1u;
+                m = __shfl_sync(0xffffffffu, mw, i);
+                q = qb - i;
             }
+            const bool mine = (m >> lane) & 1u;
+            const int above = __popc((m >> lane) >> 1);  // set bits at higher list positions
+            const bool take = mine && above < kBwdG - fill;
+            if (take) s.slot[fill + above] = 32u * (uint32_t)q + lane;
+            const unsigned taken = __ballot_sync(0xffffffffu, take);
+            m &= ~taken;
+            fill += __popc(taken);
         }
-        __syncthreads();
+        if (fill == 0) break;
+        const int n = fill;
+        fill = 0;
+        __syncwarp();
 
-        // One set of global reductions per (tile, Gaussian) pair that some warp blended.
-        if ((int)threadIdx.x < nb) {
-            const int e = (int)threadIdx.x;
-            float S[9];
+        // ---- stage the batch: lane k < n fetches Gaussian k ----------------------------------------
+        if ((int)lane < n) {
+            const uint32_t pos = s.slot[lane];
+            const uint32_t id = __ldg(point_list + range.x + pos);
+            const StagedGaussian g = load_gaussian(id, means2D, conic_opacity, colors, color_stride);
+            const uint32_t a = s_rec + lane * 48u;
+            sts_f4(a, g.xy.x, g.xy.y, g.co.x * (-0.5f * kLog2e), g.co.y * (-kLog2e));
+            sts_f4(a + 16, g.co.z * (-0.5f * kLog2e), g.co.w, g.r, g.g);
+            sts_f4(a + 32, g.b, __uint_as_float(pos), __uint_as_float(id), 0.f);
+        }
+        __syncwarp();
+
+        // ---- phase 1: lane = pixel --------------------------------------------------------------
+#pragma unroll 2
+        for (int k = 0; k < n; k++) {
+            const uint32_t a = s_rec + (uint32_t)k * 48u;
+            const float4 g0 = lds_f4(a);       // x, y, A', B'
+            const float4 g1 = lds_f4(a + 16);  // C', opacity, r, g
+            const float2 g2 = lds_f2(a + 32);  // b, list position
+            const float dx = g0.x - pixfx;
+            const float dy = g0.y - pixfy;
+            // log2(e) * power, power = -0.5 (A dx^2 + C dy^2) - B dx dy
+            const float p2 = fmaf(g0.w * dx, dy, fmaf(g1.x * dy, dy, (g0.z * dx) * dx));
+            // clamp: a lane outside the footprint must not make inf (1 - alpha >= 0.01; a G that
+            // underflows belongs to a lane that is not hit)
+            const float G = ex2_ftz(fminf(p2, 0.f));
+            const float alpha = fminf(0.99f, g1.y * G);
+            // Skip if this one is behind the last contributor of this pixel, or was skipped by it in
+            // the forward pass (backward.cu:486-501).
+            const bool hit = (__float_as_uint(g2.y) < last_contributor) && !(p2 > 0.0f) && !(alpha < 1.0f / 255.0f);
+            const float rcp = rcp_ftz(1.f - alpha);
+            if (hit) T *= rcp;
+            const float d0 = g1.z - acc0, d1 = g1.w - acc1, d2 = g2.x - acc2;
+            float dL_dalpha = fmaf(d2, dLp2, fmaf(d1, dLp1, d0 * dLp0));
+            dL_dalpha = fmaf(dL_dalpha, T, bg_term * rcp);
+            const float w = hit ? alpha * T : 0.f;
+            const float Z = hit ? G * dL_dalpha : 0.f;
+            if (hit) {
+                acc0 = fmaf(alpha, d0, acc0);
+                acc1 = fmaf(alpha, d1, acc1);
+                acc2 = fmaf(alpha, d2, acc2);
+            }
+            const uint32_t col = ((lane + 4u * (uint32_t)k) & 31u) * 4u + (uint32_t)k * 128u;
+            sts_f1(s_sw + col, w);
+            sts_f1(s_sz + col, Z);
+        }
+        __syncwarp();
+
+        // ---- phase 2: lane = (Gaussian e, half of the pixels) ----------------------------------
+        {
+            const float4 r0 = lds_f4(s_rec + e * 48u);       // x, y, A', B'
+            const float4 r1 = lds_f4(s_rec + e * 48u + 16);  // C', opacity, -, -
+            const float gxl = r0.x - org_x, gyl = r0.y - org_y;
+            float c0 = 0.f, c1 = 0.f, c2 = 0.f, M0 = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f;
 #pragma unroll
-            for (int v = 0; v < 9; v++) S[v] = 0.f;
-            bool any = false;
+            for (int j = 0; j < 4; j++) {
+                const uint32_t col = ((16u * half + 4u * (uint32_t)j + 4u * e) & 31u) * 4u + e * 128u;
+                const float4 w4 = lds_f4(s_sw + col);
+                const float4 z4 = lds_f4(s_sz + col);
+                const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+                const float zv[4] = {z4.x, z4.y, z4.z, z4.w};
 #pragma unroll
-            for (int w = 0; w < kBwdWarps; w++) {
-                if ((s_touch[w][e >> 5] >> (e & 31)) & 1u) {
-                    any = true;
-#pragma unroll
-                    for (int v = 0; v < 9; v++) S[v] += s_part[w][e][v];
+                for (int i = 0; i < 4; i++) {
+                    const int sidx = 4 * j + i;  // pixel 16 half + sidx sits at (sidx & 7, 2 half + (sidx >> 3))
+                    const float4 pc = lds_f4(s_pixc + (16u * half + (uint32_t)sidx) * 16u);
+                    c0 = fmaf(wv[i], pc.x, c0);
+                    c1 = fmaf(wv[i], pc.y, c1);
+                    c2 = fmaf(wv[i], pc.z, c2);
+                    const float dx = gxl - (float)(sidx & 7);
+                    const float dy = gyl - (float)(sidx >> 3);
+                    const float zx = zv[i] * dx, zy = zv[i] * dy;
+                    M0 += zv[i];
+                    Sx += zx;
+                    Sy += zy;
+                    Sxx = fmaf(zx, dx, Sxx);
+                    Sxy = fmaf(zx, dy, Sxy);
+                    Syy = fmaf(zy, dy, Syy);
                 }
             }
-            if (any) {
-                const size_t id = s_id[e];
-                const float4 r0 = lds_f4(s_base + (uint32_t)e * kStageBytes);       // x, y, A, B
-                const float cC = lds_f1(s_base + (uint32_t)e * kStageBytes + 16);   // C
-                const float4 co = make_float4(r0.z, r0.w, cC, 0.f);
-                atomicAdd(dL_dcolor + id * 3 + 0, S[0]);
-                atomicAdd(dL_dcolor + id * 3 + 1, S[1]);
-                atomicAdd(dL_dcolor + id * 3 + 2, S[2]);
-                // dG/ddelx = -G dx A - G dy B, dG/ddely = -G dy C - G dx B (backward.cu:520-521)
-                atomicAdd(dL_dmean2D + id * 3 + 0, -(co.x * S[3] + co.y * S[4]) * ddelx_dx);
-                atomicAdd(dL_dmean2D + id * 3 + 1, -(co.z * S[4] + co.y * S[3]) * ddely_dy);
-                atomicAdd(dL_dconic + id * 4 + 0, -0.5f * S[5]);
-                atomicAdd(dL_dconic + id * 4 + 1, -0.5f * S[6]);
-                atomicAdd(dL_dconic + id * 4 + 3, -0.5f * S[7]);
-                atomicAdd(dL_dopacity + id, S[8]);
+            c0 += __shfl_xor_sync(0xffffffffu, c0, 16);
+            c1 += __shfl_xor_sync(0xffffffffu, c1, 16);
+            c2 += __shfl_xor_sync(0xffffffffu, c2, 16);
+            M0 += __shfl_xor_sync(0xffffffffu, M0, 16);
+            Sx += __shfl_xor_sync(0xffffffffu, Sx, 16);
+            Sy += __shfl_xor_sync(0xffffffffu, Sy, 16);
+            Sxx += __shfl_xor_sync(0xffffffffu, Sxx, 16);
+            Sxy += __shfl_xor_sync(0xffffffffu, Sxy, 16);
+            Syy += __shfl_xor_sync(0xffffffffu, Syy, 16);
+            if ((int)lane < n) {
+                const float cA = r0.z * (-2.f / kLog2e), cB = r0.w * (-1.f / kLog2e), cC = r1.x * (-2.f / kLog2e);
+                const float o = r1.y;
+                // X = dL/dG G dx = o Z dx, Y likewise; dG/ddelx = -G dx A - G dy B,
+                // dG/ddely = -G dy C - G dx B (backward.cu:520-521)
+                const float X = o * Sx, Y = o * Sy;
+                const size_t id = __float_as_uint(lds_f1(s_rec + e * 48u + 40));
+                float* rec = grad_pack + id * 8;
+                red_add_v4(rec, c0, c1, c2, -(cA * X + cB * Y) * ddelx_dx);
+                red_add_v4(rec + 4, -(cC * Y + cB * X) * ddely_dy, -0.5f * o * Sxx, -0.5f * o * Sxy, -0.5f * o * Syy);
+                red_add_f1(dL_dopacity + id, M0);
             }
         }
+        // the next batch's staging is separated from these reads by the barrier after its assembly
     }
 }
 }  // namespace
@@ -279,12 +282,12 @@ __global__ void __launch_bounds__(kBlendThreads, 5)
 int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
                            const float* bg, const float2* means2D, const float4* conic_opacity, const float* colors,
                            int color_stride, const float* final_T, const uint32_t* n_contrib,
-                           const uint32_t* hit_words, const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                           const uint32_t* hit_words, const float* dL_dpix, float* grad_pack, float* dL_dopacity,
                            cudaStream_t stream) {
     const dim3 grid((unsigned)grid_x, (unsigned)grid_y, 1);
     render_backward_kernel<<<grid, kBlendThreads, 0, stream>>>(ranges, point_list, W, H, grid_x, bg, means2D,
                                                                conic_opacity, colors, color_stride, final_T, n_contrib,
-                                                               hit_words, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+                                                               hit_words, dL_dpix, grad_pack, dL_dopacity);
     HB_LAUNCH_OK("render_backward", stream, false);
     return 0;
 }

@@ -41,7 +41,7 @@ def _vs_oracle(sc, backward=True):
         pairs = dict(means3D="dL_dmean3D", means2D="dL_dmean2D", opacity="dL_dopacity", shs="dL_dsh",
                      scales="dL_dscale", rotations="dL_drot")
         for k, v in pairs.items():
-            assert refutil.rel_err(n(o["grads"][k]), orc["grads"][v].reshape(n(o["grads"][k]).shape)) <= 1e-3, k
+            refutil.assert_grad_close(n(o["grads"][k]), orc["grads"][v].reshape(n(o["grads"][k]).shape), k)
     return o
 
 
