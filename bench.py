@@ -424,6 +424,9 @@ def stage_bytes(P, visible, R, W, H, n_human, sort_bits, views=1, sh_sink=False)
         "duplicate_with_keys": 24 * P + 12 * R,
         "sort_pairs": (8 + 24 * passes) * R,
         "identify_tile_ranges": 8 * R + 8 * tiles,
+        # level 2 of the two-level binning (csrc/binning2.cu): the compulsory output -- the sorted list and
+        # the ranges; it replaces the per-pair sort passes and identifyTileRanges of the reference structure
+        "tile_split": 4 * R + 8 * tiles,
         "render_forward": 40 * R + 20 * W * H + 8 * tiles,
         "render_backward": 76 * R + 20 * W * H,
         # per view.  With the SH gradient sink, views 2..V of a step ADD their 192-B SH gradient row to the

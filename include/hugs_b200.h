@@ -241,21 +241,27 @@ int hugs_b200_image_layout_of(int width, int height, hugs_b200_image_layout* out
 int hugs_b200_binning_layout_of(int R, int width, int height, hugs_b200_binning_layout* out);
 
 /* ---------------------------------------------------------------------------------------------
- * How the forward pass bins (Gaussian, tile) pairs.  All three produce bit-identical keys, lists,
+ * How the forward pass bins (Gaussian, tile) pairs.  All four produce bit-identical keys, lists,
  * ranges and images; they differ in structure and in when the host learns R.
- *   ASYNC      (default) depth argsort of the P Gaussians, pairs emitted in depth order, stable sort
- *              of the pairs on the tile bits only; the workspace is sized from the pair counts of
- *              earlier calls with the same (P, W, H), the whole stage is enqueued before R reaches
- *              the host, R is checked before returning and an overflow is redone with the exact size.
+ *   ASYNC      (default) depth argsort of the P Gaussians; the depth-ordered Gaussians are split
+ *              stably by super-tile (8x4 tiles; one radix pass over ~1.5 P entries), then every
+ *              super-tile list is split into its 32 tile lists by transposing 32-bit coverage masks
+ *              (csrc/binning2.cu): 4 bytes written per pair, no per-pair sort.  The workspace is sized
+ *              from the pair counts of earlier calls with the same (P, W, H), the whole stage is enqueued
+ *              before R reaches the host, R is checked before returning and an overflow is redone with
+ *              the exact size.
  *   SYNC       same kernels, but the host waits for R before sizing the workspace (what
  *              cuda_rasterizer/rasterizer_impl.cu:281 does).
  *   REFERENCE  the reference's structure: pairs emitted in Gaussian-index order, one sort over all
  *              32+bit key bits (rasterizer_impl.cu:289-308), host waits for R.
+ *   TILESORT   round-1 structure, kept for cross-checks: depth argsort, pairs emitted in depth order,
+ *              stable radix sort of the R pairs on the tile bits only; sized like ASYNC.
  * Returns the previous mode, or HUGS_B200_EINVAL.  Process-wide.
  * ------------------------------------------------------------------------------------------- */
 #define HUGS_B200_BINNING_ASYNC     0
 #define HUGS_B200_BINNING_SYNC      1
 #define HUGS_B200_BINNING_REFERENCE 2
+#define HUGS_B200_BINNING_TILESORT  3
 int hugs_b200_set_binning_mode(int mode);
 
 /* ---------------------------------------------------------------------------------------------
@@ -436,9 +442,9 @@ long long hugs_b200_launch_count(int reset);
  * caller's stream.  hugs_b200_stage_timing_read waits for the recorded events, adds them to the
  * per-stage totals and copies the totals out (ms_sum / calls: HUGS_B200_NUM_STAGES entries each).
  * Stage order: preprocess, inclusive_scan, duplicate_with_keys, sort_pairs, identify_tile_ranges,
- * render_forward, render_backward, preprocess_backward, lbs_forward, lbs_backward.
+ * render_forward, render_backward, preprocess_backward, lbs_forward, lbs_backward, tile_split.
  * ------------------------------------------------------------------------------------------- */
-#define HUGS_B200_NUM_STAGES 10
+#define HUGS_B200_NUM_STAGES 11
 int         hugs_b200_stage_timing_enable(int on); /* returns the previous setting */
 int         hugs_b200_stage_timing_read(double* ms_sum, long long* calls, int reset);
 const char* hugs_b200_stage_name(int stage);

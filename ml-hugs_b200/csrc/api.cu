@@ -544,11 +544,18 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     memset(&bin, 0, sizeof(bin));
     const int tile_bits = (int)higher_msb((uint32_t)num_tiles);
     const int mode = g_binning_mode.load(std::memory_order_relaxed);
-    // Two-level binning (depth argsort of the Gaussians + tile-bit sort of the pairs) needs the packed
-    // rectangle format of the duplicate kernel; otherwise fall back to the reference's structure.
-    const bool two_level = (mode != HUGS_B200_BINNING_REFERENCE) && cam.grid_x <= 1023 && cam.grid_y <= 1023;
+    // Both two-level structures start from a depth argsort of the Gaussians and need tile grids of at most
+    // 1023 x 1023 (packed rectangles); otherwise fall back to the reference's structure.
+    //   multisplit (ASYNC / SYNC, the default): super-tile split + mask transposition (binning2.cu)
+    //   tilesort   (TILESORT, round 1): radix sort of the R pairs on their tile bits
+    const bool fits = cam.grid_x <= 1023 && cam.grid_y <= 1023;
+    const bool multisplit = fits && (mode == HUGS_B200_BINNING_ASYNC || mode == HUGS_B200_BINNING_SYNC);
+    const bool tilesort = fits && mode == HUGS_B200_BINNING_TILESORT;
+    const bool two_level = tilesort;
+    const bool async = (mode == HUGS_B200_BINNING_ASYNC || mode == HUGS_B200_BINNING_TILESORT) && !debug;
     const bool tile16 = num_tiles <= 65536;
-    uint32_t* R_dev = nullptr;
+    const int gx_s = super_grid_x(cam.grid_x), gy_s = super_grid_y(cam.grid_y), n_st = gx_s * gy_s;
+    uint32_t* R_dev = nullptr;   // tilesort: pair count; multisplit: level-1 entry count
     int* pinned = pinned_counter();
     cudaEvent_t ev = count_event();
     if (P > 0) {
@@ -562,6 +569,7 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
             return HUGS_B200_ENOMEM;
         }
         geom = carve_geom(geom_base, P);
+        HB_CUDA_OK(cudaMemsetAsync(geom.pair_counts, 0, 2 * sizeof(uint32_t), stream));
 
         if (const SecondSegment* s2 = tl_seg2) {
             if (s2->P0 > 0)
@@ -578,25 +586,29 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                    (scales && rotations) ? nullptr : cov3D_precomp, colors_precomp, cam, radii, geom,
                                    prefiltered != 0, stream),
                  ST_PREPROCESS);
-        if (two_level) {
+        // The number of (Gaussian, tile) pairs must reach the host (rasterizer_impl.cu:281).  The preprocess
+        // kernel has summed it (and the level-1 entry count): async copy into pinned memory on the caller's
+        // stream + an event, instead of a blocking cudaMemcpy after the scan.
+        HB_CUDA_OK(cudaMemcpyAsync(pinned, geom.pair_counts, 2 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+        HB_CUDA_OK(cudaEventRecord(ev, stream));
+        if (multisplit || tilesort) {
             HB_STAGE(launch_depth_argsort(reinterpret_cast<const uint32_t*>(geom.depths), geom.dsort_keys_tmp,
                                           geom.dsort_vals_tmp, geom.sorted_depths, geom.perm, P, geom.dsort_temp,
                                           geom.dsort_temp_bytes, stream),
                      ST_SORT);
         }
-        HB_STAGE(launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_temp,
-                                       geom.scan_temp_bytes, stream, two_level ? geom.perm : nullptr),
+        HB_STAGE(launch_inclusive_scan(multisplit ? geom.st_touched : geom.tiles_touched, geom.point_offsets, P,
+                                       geom.scan_temp, geom.scan_temp_bytes, stream,
+                                       (multisplit || tilesort) ? geom.perm : nullptr),
                  ST_SCAN);
-        // The number of (Gaussian, tile) pairs must reach the host (rasterizer_impl.cu:281): async copy
-        // into pinned memory on the caller's stream + an event, instead of a blocking cudaMemcpy.
         R_dev = geom.point_offsets + (P - 1);
-        HB_CUDA_OK(cudaMemcpyAsync(pinned, R_dev, sizeof(int), cudaMemcpyDeviceToHost, stream));
-        HB_CUDA_OK(cudaEventRecord(ev, stream));
     }
+    int R1 = 0;
     bool R_known = (P == 0);
     auto wait_R = [&]() -> int {
         HB_CUDA_OK(cudaEventSynchronize(ev));
-        R = *pinned;
+        R = pinned[0];
+        R1 = pinned[1];
         R_known = true;
         if (R < 0) {
             set_error("rasterize_forward: more than 2^31 (Gaussian, tile) pairs");
@@ -607,25 +619,55 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     // Workspace capacity: in the default mode it comes from the pair counts of earlier calls with the
     // same (P, W, H), so everything below is enqueued before the count has arrived; the count is
     // checked before returning and an overflow is redone with the exact size.
-    int cap = 0;
-    if (P > 0 && two_level && mode == HUGS_B200_BINNING_ASYNC && !debug) cap = capacity_hint(P, width, height);
+    int cap = 0, cap1 = 0;
+    if (P > 0 && (multisplit || tilesort) && async) cap = capacity_hint(P, width, height, &cap1);
     if (cap <= 0 && !R_known) {
         const int rc = wait_R();
         if (rc) return rc;
         cap = R;
+        cap1 = R1;
     }
     const float* feature_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
     const int stride = colors_precomp != nullptr ? 3 : 4;
     if (P == 0) feature_ptr = nullptr;
     for (;;) {
-        char* bin_base = binning_buffer(binning_user, carve_binning(nullptr, cap, num_tiles).total);
+        char* bin_base = binning_buffer(binning_user, carve_binning(nullptr, cap, cam.grid_x, cam.grid_y).total);
         if (!bin_base) {
             set_error("rasterize_forward: binning buffer callback returned NULL");
             return HUGS_B200_ENOMEM;
         }
-        bin = carve_binning(bin_base, cap, num_tiles);
+        bin = carve_binning(bin_base, cap, cam.grid_x, cam.grid_y);
+        if (cap1 > cap) cap1 = cap;   // a level-1 entry holds at least one pair; the buffers are sized by cap
         const uint32_t* n_dev = nullptr;
-        if (cap > 0 && two_level) {
+        if (cap > 0 && multisplit) {
+            // Level 1: (super-tile << 32 | Gaussian) entries in depth order, stably sorted on the super-tile
+            // bits (one 8-bit pass at 1080p).  The entries ping-pong between the two 64-bit regions; the last
+            // pass leaves the Gaussian list in `list_unsorted` and the super-tile of every position (u16) in
+            // the then dead `keys_unsorted` region.
+            const SortPassPlan plan = tile_pass_plan((int)higher_msb((uint32_t)n_st));
+            uint64_t* const buf_a = bin.keys_unsorted;
+            uint64_t* const buf_b = bin.keys;
+            uint64_t* first_buf = (plan.num_passes % 2 == 0) ? buf_a : buf_b;
+            const L2Temp l2 = carve_l2_temp(bin.l2_temp, cap, n_st, num_tiles);
+            auto emit = [&]() -> int {
+                const int rc = sort_temp_clear(bin.sort_temp, bin.sort_temp_bytes, cap1, stream);
+                if (rc) return rc;
+                return launch_duplicate_super(P, geom.perm, geom.point_offsets, geom.rects, first_buf, gx_s, gy_s,
+                                              cap1, plan, sort_temp_histogram(bin.sort_temp), stream);
+            };
+            HB_STAGE(emit(), ST_DUPLICATE);
+            HB_STAGE(launch_tile_sort(buf_a, buf_b, bin.keys_unsorted, bin.list_unsorted, true, cap1, R_dev, plan,
+                                      bin.sort_temp, bin.sort_temp_bytes, stream),
+                     ST_SORT);
+            // Level 2: super-tile lists -> tile lists and ranges.
+            auto split = [&]() -> int {
+                const int rc = launch_tile_ranges_ids(cap1, bin.keys_unsorted, true, l2.st_ranges, n_st, stream, R_dev);
+                if (rc) return rc;
+                return launch_l2_split(l2, bin.list_unsorted, geom.rects, n_st, gx_s, cam.grid_x, cam.grid_y, cap1, cap,
+                                       bin.list, img.ranges, stream);
+            };
+            HB_STAGE(split(), ST_TILE_SPLIT);
+        } else if (cap > 0 && two_level) {
             n_dev = R_dev;
             const SortPassPlan plan = tile_pass_plan(tile_bits);
             // Packed (tile << 32 | index) pairs ping-pong between the two 64-bit regions; the last pass
@@ -669,7 +711,9 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                            cudaMemcpyDeviceToDevice, stream));
             }
         }
-        if (cap > 0 && two_level)
+        if (multisplit) {
+            if (cap <= 0) HB_CUDA_OK(cudaMemsetAsync(img.ranges, 0, sizeof(uint2) * (size_t)num_tiles, stream));
+        } else if (cap > 0 && two_level)
             HB_STAGE(launch_tile_ranges_ids(cap, bin.keys_unsorted, tile16, img.ranges, num_tiles, stream, n_dev),
                      ST_RANGES);
         else
@@ -683,10 +727,11 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
             const int rc = wait_R();
             if (rc) return rc;
         }
-        if (R <= cap) break;
+        if (R <= cap && (!multisplit || R1 <= cap1)) break;
         cap = R;  // the hint was too small: redo the binning with the exact size
+        cap1 = R1;
     }
-    if (P > 0) update_capacity_hint(P, width, height, R);
+    if (P > 0) update_capacity_hint(P, width, height, R, R1);
     *num_rendered = R;
     return 0;
 }
@@ -699,8 +744,10 @@ int hugs_b200_materialize_sorted_keys(int P, int R, int width, int height, char*
         return HUGS_B200_EINVAL;
     }
     const int grid_x = cdiv(width, HB_TILE_X), grid_y = cdiv(height, HB_TILE_Y);
-    const bool two_level =
-        g_binning_mode.load(std::memory_order_relaxed) != HUGS_B200_BINNING_REFERENCE && grid_x <= 1023 && grid_y <= 1023;
+    const int mode = g_binning_mode.load(std::memory_order_relaxed);
+    const bool fits = grid_x <= 1023 && grid_y <= 1023;
+    const bool two_level = fits && mode != HUGS_B200_BINNING_REFERENCE;
+    const bool multisplit = fits && (mode == HUGS_B200_BINNING_ASYNC || mode == HUGS_B200_BINNING_SYNC);
     if (!two_level || R == 0) return 0;  // the reference-structure sort leaves the keys in place
     const size_t cap = hugs_b200_binning_capacity_of(binning_bytes, width, height);
     if ((size_t)R > cap) {
@@ -708,7 +755,12 @@ int hugs_b200_materialize_sorted_keys(int P, int R, int width, int height, char*
         return HUGS_B200_EINVAL;
     }
     const GeomView geom = carve_geom(geom_buffer, P);
-    const BinningView bin = carve_binning(binning_buffer, (int)cap, grid_x * grid_y);
+    const BinningView bin = carve_binning(binning_buffer, (int)cap, grid_x, grid_y);
+    if (multisplit) {
+        const L2Temp l2 = carve_l2_temp(bin.l2_temp, (int)cap, super_grid_x(grid_x) * super_grid_y(grid_y), grid_x * grid_y);
+        return launch_keys_from_ranges(grid_x * grid_y, l2.tile_start, l2.tile_total, bin.list,
+                                       reinterpret_cast<const uint32_t*>(geom.depths), bin.keys, stream);
+    }
     return launch_materialize_keys(R, bin.keys_unsorted, grid_x * grid_y <= 65536, bin.list,
                                    reinterpret_cast<const uint32_t*>(geom.depths), bin.keys, stream);
 }

@@ -304,10 +304,11 @@ __global__ void __launch_bounds__(kL2Chunk)
 
 // keys[i] = tile << 32 | depth bits of list[i], for every list position of every tile (parity tests only)
 __global__ void __launch_bounds__(256)
-    keys_from_ranges_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list,
-                            const uint32_t* __restrict__ depth_bits, uint64_t* __restrict__ keys) {
-    const uint2 r = __ldg(ranges + blockIdx.x);
-    for (uint32_t i = r.x + threadIdx.x; i < r.y; i += 256u)
+    keys_from_ranges_kernel(const uint32_t* __restrict__ tile_start, const uint32_t* __restrict__ tile_total,
+                            const uint32_t* __restrict__ list, const uint32_t* __restrict__ depth_bits,
+                            uint64_t* __restrict__ keys) {
+    const uint32_t begin = __ldg(tile_start + blockIdx.x), end = begin + __ldg(tile_total + blockIdx.x);
+    for (uint32_t i = begin + threadIdx.x; i < end; i += 256u)
         keys[i] = ((uint64_t)blockIdx.x << 32) | (uint64_t)__ldg(depth_bits + __ldg(list + i));
 }
 }  // namespace
@@ -359,10 +360,10 @@ int launch_l2_split(const L2Temp& t, const uint32_t* st_list, const uint2* rects
     return 0;
 }
 
-int launch_keys_from_ranges(int num_tiles, const uint2* ranges, const uint32_t* list, const uint32_t* depth_bits,
-                            uint64_t* keys, cudaStream_t stream) {
+int launch_keys_from_ranges(int num_tiles, const uint32_t* tile_start, const uint32_t* tile_total,
+                            const uint32_t* list, const uint32_t* depth_bits, uint64_t* keys, cudaStream_t stream) {
     if (num_tiles <= 0) return 0;
-    keys_from_ranges_kernel<<<num_tiles, 256, 0, stream>>>(ranges, list, depth_bits, keys);
+    keys_from_ranges_kernel<<<num_tiles, 256, 0, stream>>>(tile_start, tile_total, list, depth_bits, keys);
     HB_LAUNCH_OK("keys_from_ranges", stream, false);
     return 0;
 }

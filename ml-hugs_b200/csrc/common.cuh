@@ -102,8 +102,8 @@ struct L2Temp {
 L2Temp carve_l2_temp(char* base, int cap, int n_st, int num_tiles);
 int launch_l2_split(const L2Temp& t, const uint32_t* st_list, const uint2* rects, int n_st, int gx_s, int grid_x,
                     int grid_y, int cap1, int cap, uint32_t* list, uint2* ranges, cudaStream_t stream);
-int launch_keys_from_ranges(int num_tiles, const uint2* ranges, const uint32_t* list, const uint32_t* depth_bits,
-                            uint64_t* keys, cudaStream_t stream);
+int launch_keys_from_ranges(int num_tiles, const uint32_t* tile_start, const uint32_t* tile_total,
+                            const uint32_t* list, const uint32_t* depth_bits, uint64_t* keys, cudaStream_t stream);
 GeomView carve_geom(char* base, int P);
 ImageView carve_image(char* base, int W, int H);
 BinningView carve_binning(char* base, int R, int grid_x, int grid_y);

@@ -148,7 +148,7 @@ binning_layout_of = _sig("hugs_b200_binning_layout_of", i32, [i32, i32, i32, C.P
 materialize_sorted_keys = _sig("hugs_b200_materialize_sorted_keys", i32,
                                [i32, i32, i32, i32, fp, fp, C.c_size_t, fp])
 binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_size_t, i32, i32])
-BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE = 0, 1, 2
+BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE, BINNING_TILESORT = 0, 1, 2, 3
 set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
 
 sort_bits = _sig("hugs_b200_sort_bits", i32, [i32, i32])
@@ -163,7 +163,7 @@ lbs_forward = _sig("hugs_b200_lbs_forward", i32, [
 lbs_backward = _sig("hugs_b200_lbs_backward", i32, [
     i32, i32, i32, fp, fp, fp, fp, fp, fp, C.c_float, fp, fp, fp, fp, fp, fp, fp, fp, fp, fp, fp])
 
-NUM_STAGES = 10
+NUM_STAGES = 11
 stage_timing_enable = _sig("hugs_b200_stage_timing_enable", i32, [i32])
 stage_timing_read = _sig("hugs_b200_stage_timing_read", i32, [C.POINTER(C.c_double), C.POINTER(C.c_longlong), i32])
 stage_name = _sig("hugs_b200_stage_name", C.c_char_p, [i32])

@@ -212,17 +212,20 @@ def _forward_state(sc):
                 grads={k: v.clone() for k, v in o["grads"].items()})
 
 
-@pytest.mark.parametrize("W,H,focal", [(640, 360, 466.0), (256, 256, 187.0), (48, 32, 40.0)])
+@pytest.mark.parametrize("W,H,focal", [(640, 360, 466.0), (256, 256, 187.0), (48, 32, 40.0), (2560, 1440, 1866.0),
+                                       (1000, 70, 700.0)])
 def test_binning_modes_agree_bit_for_bit(W, H, focal):
-    """Two-level async (default), two-level sync and the reference-structured full-key sort produce
-    identical keys / lists / ranges / contributor counts / images (13-, 9- and 3-bit tile ids:
-    2-pass, 2-pass and 1-pass tile sorts)."""
+    """Super-tile multisplit async (default) and sync, the round-1 tile-bit sort and the reference-structured
+    full-key sort produce identical keys / lists / ranges / contributor counts / images (13-, 9- and 3-bit
+    tile ids; 255, 32 and 1 super-tiles; 2560x1440 has 460 super-tiles = two level-1 radix passes; 1000x70 has
+    ragged super-tiles on both axes)."""
     from hugs_b200 import _native as N
 
     sc = scenes.make_scene(60000, 8000, W, H, focal, 91, device="cuda")
     res = {}
     try:
-        for mode in (N.BINNING_REFERENCE, N.BINNING_SYNC, N.BINNING_ASYNC, N.BINNING_ASYNC):
+        for mode in (N.BINNING_REFERENCE, N.BINNING_SYNC, N.BINNING_ASYNC, N.BINNING_ASYNC, N.BINNING_TILESORT,
+                     N.BINNING_TILESORT):
             N.set_binning_mode(mode)
             res.setdefault(mode, []).append(_forward_state(sc))
     finally:
