@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 6
+#define HUGS_B200_ABI_VERSION 7
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -395,6 +395,54 @@ int hugs_b200_rasterize_backward_seg2(
     float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
     float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, int debug,
     hugs_b200_stream_t stream);
+
+
+/* ---- a second image of the first n_layer Gaussians, from the same sorted lists -----------------------
+ * Replaces the second, human-only render() of hugs/renderer/gs_renderer.py:68-82 (consumed by
+ * hugs/trainer/gs_trainer.py:255-271 and the human-separate loss): instead of a second complete
+ * rasterizer pass over the human Gaussians, the joint pass's tile lists are filtered (stable) to the
+ * Gaussians with index < n_layer and blended against `background`; contributor counts, transmittance and
+ * image are those of CudaRasterizer::Rasterizer::forward (cuda_rasterizer/rasterizer_impl.cu:198-336) on
+ * the first n_layer Gaussians alone.  Call after hugs_b200_rasterize_forward[_seg2] on the same stream with
+ * that call's three workspaces; `layer_buffer` (caller-owned, hugs_b200_layer_bytes) keeps what the
+ * backward needs.  colors_precomp as in the forward call (NULL with SHs). */
+size_t hugs_b200_layer_bytes(int n_layer, size_t binning_bytes, int width, int height);
+/* byte offsets inside the layer buffer, for tests: filtered list u32[capacity], hit masks, final T f32[W*H],
+ * contributor counts u32[W*H], tile ranges u32x2[tiles], packed gradient records f32[n_layer][8] */
+int hugs_b200_layer_layout_of(int n_layer, size_t binning_bytes, int width, int height, size_t* offsets6);
+int hugs_b200_layer_forward(int P, int n_layer, const float* background, int width, int height,
+                            const float* colors_precomp, char* geom_buffer, char* binning_buffer,
+                            size_t binning_bytes, char* image_buffer, char* layer_buffer, size_t layer_bytes,
+                            float* out_color, int debug, hugs_b200_stream_t stream);
+/* hugs_b200_rasterize_backward_acc with the layer's image gradient consumed in the same pass
+ * (CudaRasterizer::Rasterizer::backward, rasterizer_impl.cu:340-434, run once instead of twice): every
+ * gradient is the sum over both images, except dL_dmean2D, which stays the main image's (the reference's
+ * second pass has its own, unread, screen-space tensor).  dL_dpix_layer == NULL: plain backward. */
+int hugs_b200_rasterize_backward_layer(int P, int D, int M, int R, const float* background, int width, int height,
+                                       const float* means3D, const float* shs, const float* colors_precomp,
+                                       const float* scales, float scale_modifier, const float* rotations,
+                                       const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                       const float* cam_pos, float tan_fovx, float tan_fovy, const int* radii,
+                                       char* geom_buffer, char* binning_buffer, size_t binning_bytes,
+                                       char* image_buffer, const float* dL_dpix, float* dL_dmean2D, float* dL_dconic,
+                                       float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
+                                       float* dL_dsh, float* dL_dscale, float* dL_drot, int debug,
+                                       hugs_b200_stream_t stream, int dL_dsh_accumulate, int n_layer,
+                                       const float* background_layer, char* layer_buffer, size_t layer_bytes,
+                                       const float* dL_dpix_layer);
+int hugs_b200_rasterize_backward_seg2_layer(int D, int M, int R, const float* background, int width, int height,
+                                            int P0, const float* means3D0, const float* shs0, const float* scales0,
+                                            const float* rotations0, int P1, const float* means3D1,
+                                            const float* shs1, const float* scales1, const float* rotations1,
+                                            float scale_modifier, const float* viewmatrix, const float* projmatrix,
+                                            const float* cam_pos, float tan_fovx, float tan_fovy, const int* radii,
+                                            char* geom_buffer, char* binning_buffer, size_t binning_bytes,
+                                            char* image_buffer, const float* dL_dpix, float* dL_dmean2D,
+                                            float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
+                                            float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                            int debug, hugs_b200_stream_t stream, int n_layer,
+                                            const float* background_layer, char* layer_buffer, size_t layer_bytes,
+                                            const float* dL_dpix_layer);
 
 /* ---------------------------------------------------------------------------------------------
  * Densification statistics after a backward pass, one launch, no host sync.

@@ -178,6 +178,22 @@ BinningView carve_binning(char* base, int R, int grid_x, int grid_y) {
     return b;
 }
 
+LayerView carve_layer(char* base, int R, int n_layer, int W, int H) {
+    LayerView v;
+    char* p = base;
+    const size_t n = (size_t)(R > 0 ? R : 0);
+    const size_t pix = (size_t)W * (size_t)H;
+    const size_t tiles = (size_t)cdiv(W, HB_TILE_X) * (size_t)cdiv(H, HB_TILE_Y);
+    v.list = take<uint32_t>(p, n);
+    v.hit_words = take<uint32_t>(p, ((n + 31) / 32 + tiles + 1) * 8);
+    v.accum_alpha = take<float>(p, pix);
+    v.n_contrib = take<uint32_t>(p, pix);
+    v.ranges = take<uint2>(p, tiles);
+    v.grad_pack = take<float>(p, 8 * (size_t)(n_layer > 0 ? n_layer : 0));
+    v.total = (size_t)(p - base);
+    return v;
+}
+
 // Helper function to find the next-highest bit of the MSB (rasterizer_impl.cu:35-50): the
 // reference sorts on 32 + this many key bits.
 static uint32_t higher_msb(uint32_t n) {
@@ -475,6 +491,17 @@ struct SecondSegment {
     const float* rotations;
 };
 static thread_local const SecondSegment* tl_seg2 = nullptr;   // set only for the duration of a *_seg2 call
+
+// Second image of the first `n` Gaussians (hugs_b200_layer_forward): its blend backward runs between the
+// main blend backward and the per-Gaussian backward of the *_layer entry points.
+struct LayerBackward {
+    int n;
+    const float* background;
+    char* buffer;
+    size_t bytes;
+    const float* dL_dpix;
+};
+static thread_local const LayerBackward* tl_layer = nullptr;   // set only for the duration of a *_layer call
 
 static GeomView geom_rows_from(const GeomView& g, int row0) {
     GeomView o = g;
@@ -816,13 +843,39 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
                                       img.n_contrib, bin.hit_words, dL_dpix, geom.grad_pack, dL_dopacity, stream);
     };
     HB_STAGE(blend_backward(), ST_RENDER_BWD);
+    // The layer's blend backward: same kernel on the filtered lists, gradients into the layer's own packed
+    // records (summed with the main ones by the per-Gaussian kernel) and into the shared dL_dopacity.
+    const float* pack2 = nullptr;
+    int n2 = 0;
+    if (const LayerBackward* L = tl_layer) {
+        if (L->n < 0 || L->n > P || !L->buffer || !L->dL_dpix || !L->background) {
+            set_error("rasterize_backward_layer: bad layer arguments");
+            return HUGS_B200_EINVAL;
+        }
+        if (L->bytes < carve_layer(nullptr, (int)cap, L->n, width, height).total) {
+            set_error("rasterize_backward_layer: layer buffer of %zu bytes is too small", L->bytes);
+            return HUGS_B200_EINVAL;
+        }
+        const LayerView lay = carve_layer(L->buffer, (int)cap, L->n, width, height);
+        auto layer_backward = [&]() -> int {
+            HB_CUDA_OK(cudaMemsetAsync(lay.grad_pack, 0, sizeof(float) * 8 * (size_t)L->n, stream));
+            if (R <= 0 || L->n == 0) return 0;
+            return launch_render_backward(lay.ranges, lay.list, width, height, cam.grid_x, cam.grid_y, L->background,
+                                          geom.means2D, geom.conic_opacity, color_ptr, stride, lay.accum_alpha,
+                                          lay.n_contrib, lay.hit_words, L->dL_dpix, lay.grad_pack, dL_dopacity,
+                                          stream);
+        };
+        HB_STAGE(layer_backward(), ST_RENDER_BWD);
+        pack2 = lay.grad_pack;
+        n2 = L->n;
+    }
     if (const SecondSegment* s2 = tl_seg2) {
         const size_t r0 = (size_t)s2->P0;
         if (s2->P0 > 0)
             HB_STAGE(launch_preprocess_backward(s2->P0, D, M, means3D, radii, shs, geom.clamped, scales, rotations,
                                                 scale_modifier, nullptr, cam, geom.grad_pack, dL_dmean2D, dL_dconic,
                                                 dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
-                                                dL_dsh_accumulate != 0, stream),
+                                                dL_dsh_accumulate != 0, stream, pack2, n2 < s2->P0 ? n2 : s2->P0),
                      ST_PREPROCESS_BWD);
         if (P - s2->P0 > 0)
             HB_STAGE(launch_preprocess_backward(P - s2->P0, D, M, s2->means3D, radii + r0, s2->shs, geom.clamped + r0,
@@ -830,16 +883,90 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
                                                 geom.grad_pack + 8 * r0, dL_dmean2D + 3 * r0, dL_dconic + 4 * r0,
                                                 dL_dmean3D + 3 * r0,
                                                 dL_dcolor + 3 * r0, dL_dcov3D + 6 * r0, dL_dsh + (size_t)M * 3 * r0,
-                                                dL_dscale + 3 * r0, dL_drot + 4 * r0, dL_dsh_accumulate != 0, stream),
+                                                dL_dscale + 3 * r0, dL_drot + 4 * r0, dL_dsh_accumulate != 0, stream,
+                                                pack2 ? pack2 + 8 * r0 : nullptr, n2 > s2->P0 ? n2 - s2->P0 : 0),
                      ST_PREPROCESS_BWD);
         return 0;
     }
     HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,
                                         rotations, scale_modifier, cov3D_precomp, cam, geom.grad_pack, dL_dmean2D,
                                         dL_dconic, dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
-                                        dL_dsh_accumulate != 0, stream),
+                                        dL_dsh_accumulate != 0, stream, pack2, n2),
              ST_PREPROCESS_BWD);
     return 0;
+}
+
+size_t hugs_b200_layer_bytes(int n_layer, size_t binning_bytes, int width, int height) {
+    if (n_layer < 0 || width <= 0 || height <= 0) return 0;
+    const size_t cap = hugs_b200_binning_capacity_of(binning_bytes, width, height);
+    return carve_layer(nullptr, (int)cap, n_layer, width, height).total;
+}
+
+int hugs_b200_layer_layout_of(int n_layer, size_t binning_bytes, int width, int height, size_t* offsets6) {
+    if (!offsets6 || n_layer < 0 || width <= 0 || height <= 0) return HUGS_B200_EINVAL;
+    const size_t cap = hugs_b200_binning_capacity_of(binning_bytes, width, height);
+    const LayerView v = carve_layer(nullptr, (int)cap, n_layer, width, height);
+    offsets6[0] = (size_t)reinterpret_cast<char*>(v.list);
+    offsets6[1] = (size_t)reinterpret_cast<char*>(v.hit_words);
+    offsets6[2] = (size_t)reinterpret_cast<char*>(v.accum_alpha);
+    offsets6[3] = (size_t)reinterpret_cast<char*>(v.n_contrib);
+    offsets6[4] = (size_t)reinterpret_cast<char*>(v.ranges);
+    offsets6[5] = (size_t)reinterpret_cast<char*>(v.grad_pack);
+    return 6;
+}
+
+int hugs_b200_layer_forward(int P, int n_layer, const float* background, int width, int height,
+                            const float* colors_precomp, char* geom_buffer, char* binning_buffer,
+                            size_t binning_bytes, char* image_buffer, char* layer_buffer, size_t layer_bytes,
+                            float* out_color, int debug, hugs_b200_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (P <= 0 || n_layer < 0 || n_layer > P || width <= 0 || height <= 0 || !background || !out_color || !geom_buffer ||
+        !binning_buffer || !image_buffer || !layer_buffer) {
+        set_error("layer_forward: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    const int grid_x = cdiv(width, HB_TILE_X), grid_y = cdiv(height, HB_TILE_Y);
+    const size_t cap = hugs_b200_binning_capacity_of(binning_bytes, width, height);
+    if (layer_bytes < carve_layer(nullptr, (int)cap, n_layer, width, height).total) {
+        set_error("layer_forward: layer buffer of %zu bytes is too small (hugs_b200_layer_bytes)", layer_bytes);
+        return HUGS_B200_EINVAL;
+    }
+    const GeomView geom = carve_geom(geom_buffer, P);
+    const BinningView bin = carve_binning(binning_buffer, (int)cap, grid_x, grid_y);
+    const ImageView img = carve_image(image_buffer, width, height);
+    const LayerView lay = carve_layer(layer_buffer, (int)cap, n_layer, width, height);
+    const float* feature_ptr = colors_precomp != nullptr ? colors_precomp : reinterpret_cast<const float*>(geom.rgb);
+    const int stride = colors_precomp != nullptr ? 3 : 4;
+    HB_STAGE(launch_layer_filter(grid_x * grid_y, img.ranges, bin.list, n_layer, lay.list, lay.ranges, stream),
+             ST_RANGES);
+    HB_STAGE(launch_render_forward(lay.ranges, lay.list, width, height, grid_x, grid_y, geom.means2D, feature_ptr, stride,
+                                   geom.conic_opacity, lay.accum_alpha, lay.n_contrib, background, out_color,
+                                   lay.hit_words, stream),
+             ST_RENDER_FWD);
+    return 0;
+}
+
+int hugs_b200_rasterize_backward_layer(int P, int D, int M, int R, const float* background, int width, int height,
+                                       const float* means3D, const float* shs, const float* colors_precomp,
+                                       const float* scales, float scale_modifier, const float* rotations,
+                                       const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                       const float* cam_pos, float tan_fovx, float tan_fovy, const int* radii,
+                                       char* geom_buffer, char* binning_buffer, size_t binning_bytes,
+                                       char* image_buffer, const float* dL_dpix, float* dL_dmean2D, float* dL_dconic,
+                                       float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
+                                       float* dL_dsh, float* dL_dscale, float* dL_drot, int debug,
+                                       hugs_b200_stream_t stream, int dL_dsh_accumulate, int n_layer,
+                                       const float* background_layer, char* layer_buffer, size_t layer_bytes,
+                                       const float* dL_dpix_layer) {
+    const LayerBackward L{n_layer, background_layer, layer_buffer, layer_bytes, dL_dpix_layer};
+    tl_layer = dL_dpix_layer ? &L : nullptr;   // no gradient for the layer image: plain backward
+    const int rc = hugs_b200_rasterize_backward_acc(
+        P, D, M, R, background, width, height, means3D, shs, colors_precomp, scales, scale_modifier, rotations,
+        cov3D_precomp, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, radii, geom_buffer, binning_buffer,
+        binning_bytes, image_buffer, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D,
+        dL_dsh, dL_dscale, dL_drot, debug, stream, dL_dsh_accumulate);
+    tl_layer = nullptr;
+    return rc;
 }
 
 int hugs_b200_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height,
@@ -979,6 +1106,30 @@ int hugs_b200_rasterize_backward_seg2(int D, int M, int R, const float* backgrou
         image_buffer, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale,
         dL_drot, debug, stream, 0);
     tl_seg2 = nullptr;
+    return rc;
+}
+
+int hugs_b200_rasterize_backward_seg2_layer(int D, int M, int R, const float* background, int width, int height,
+                                            int P0, const float* means3D0, const float* shs0, const float* scales0,
+                                            const float* rotations0, int P1, const float* means3D1,
+                                            const float* shs1, const float* scales1, const float* rotations1,
+                                            float scale_modifier, const float* viewmatrix, const float* projmatrix,
+                                            const float* cam_pos, float tan_fovx, float tan_fovy, const int* radii,
+                                            char* geom_buffer, char* binning_buffer, size_t binning_bytes,
+                                            char* image_buffer, const float* dL_dpix, float* dL_dmean2D,
+                                            float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
+                                            float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                            int debug, hugs_b200_stream_t stream, int n_layer,
+                                            const float* background_layer, char* layer_buffer, size_t layer_bytes,
+                                            const float* dL_dpix_layer) {
+    const LayerBackward L{n_layer, background_layer, layer_buffer, layer_bytes, dL_dpix_layer};
+    tl_layer = dL_dpix_layer ? &L : nullptr;
+    const int rc = hugs_b200_rasterize_backward_seg2(
+        D, M, R, background, width, height, P0, means3D0, shs0, scales0, rotations0, P1, means3D1, shs1, scales1,
+        rotations1, scale_modifier, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, radii, geom_buffer,
+        binning_buffer, binning_bytes, image_buffer, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D,
+        dL_dcov3D, dL_dsh, dL_dscale, dL_drot, debug, stream);
+    tl_layer = nullptr;
     return rc;
 }
 

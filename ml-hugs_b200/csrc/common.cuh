@@ -73,6 +73,15 @@ struct ImageView {
     uint2* ranges;
     size_t total;
 };
+struct LayerView {   // second image of the first n Gaussians (layer.cu)
+    uint32_t* list;       // [capacity] filtered tile lists, each at its joint offset
+    uint32_t* hit_words;  // same shape as BinningView::hit_words
+    float* accum_alpha;   // [W*H]
+    uint32_t* n_contrib;  // [W*H]
+    uint2* ranges;        // [tiles]
+    float* grad_pack;     // [n][8] the layer's share of the packed blend gradients
+    size_t total;
+};
 struct BinningView {
     uint64_t* keys;
     uint32_t* list;
@@ -107,6 +116,7 @@ int launch_keys_from_ranges(int num_tiles, const uint32_t* tile_start, const uin
 GeomView carve_geom(char* base, int P);
 ImageView carve_image(char* base, int W, int H);
 BinningView carve_binning(char* base, int R, int grid_x, int grid_y);
+LayerView carve_layer(char* base, int R, int n_layer, int W, int H);
 
 constexpr int kSortMaxPasses = 8;
 struct SortPassPlan {  // pass p sorts on `bits[p]` key bits starting at bit `shift[p]`
@@ -185,7 +195,10 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                float scale_modifier, const float* cov3D_precomp, const Camera& cam,
                                const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
-                               float* dL_drot, bool sh_accumulate, cudaStream_t stream);
+                               float* dL_drot, bool sh_accumulate, cudaStream_t stream,
+                               const float* grad_pack2 = nullptr, int n2 = 0);
+int launch_layer_filter(int num_tiles, const uint2* ranges, const uint32_t* list, int n_layer, uint32_t* list_out,
+                        uint2* ranges_out, cudaStream_t stream);
 
 int launch_lbs_forward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
                        const float* rotmat, const float* scales, const float* transl, float smpl_scale,

@@ -30,6 +30,8 @@ struct PreBwdArgs {
     const float* campos;
     float tan_fovx, tan_fovy, focal_x, focal_y;
     const float* grad_pack;   // [P,8]  (input: accumulated by the blend backward) colour 3, mean2D 2, conic 3
+    const float* grad_pack2;  // [n2,8] or null: a second image's share for the rows below n2 (layer.cu)
+    int n2;
     float* dL_dmean2D;        // [P,3]  (output: unpacked record, z = 0)
     float* dL_dconic;         // [P,4]  (output: unpacked record, (x, y, 0, w))
     float* dL_dmean3D;        // [P,3]
@@ -240,8 +242,17 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
         my = __ldg(a.means3D + 3 * (size_t)idx + 1);
         mz = __ldg(a.means3D + 3 * (size_t)idx + 2);
         // the blend backward's packed record: one 32-byte sector
-        const float4 pk0 = __ldg(reinterpret_cast<const float4*>(a.grad_pack) + 2 * (size_t)idx);
-        const float4 pk1 = __ldg(reinterpret_cast<const float4*>(a.grad_pack) + 2 * (size_t)idx + 1);
+        float4 pk0 = __ldg(reinterpret_cast<const float4*>(a.grad_pack) + 2 * (size_t)idx);
+        float4 pk1 = __ldg(reinterpret_cast<const float4*>(a.grad_pack) + 2 * (size_t)idx + 1);
+        // dL/dmean2D as REPORTED is the main image's alone: the reference's second render() has a
+        // screen-space tensor of its own that nothing reads (gs_renderer.py:68-82)
+        const float out2x = pk0.w, out2y = pk1.x;
+        if (a.grad_pack2 != nullptr && idx < a.n2) {
+            const float4 q0 = __ldg(reinterpret_cast<const float4*>(a.grad_pack2) + 2 * (size_t)idx);
+            const float4 q1 = __ldg(reinterpret_cast<const float4*>(a.grad_pack2) + 2 * (size_t)idx + 1);
+            pk0.x += q0.x; pk0.y += q0.y; pk0.z += q0.z; pk0.w += q0.w;
+            pk1.x += q1.x; pk1.y += q1.y; pk1.z += q1.z; pk1.w += q1.w;
+        }
         const float4 dconic4 = make_float4(pk1.y, pk1.z, 0.f, pk1.w);
         const float g2x = pk0.w, g2y = pk1.x;
         if (a.shs != nullptr) {
@@ -252,8 +263,8 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
         }
         // the reference's arrays (rasterize_points.cu:151-159 allocates them; dL_dmeans2D and dL_dcolors go
         // back to Python)
-        a.dL_dmean2D[3 * (size_t)idx + 0] = g2x;
-        a.dL_dmean2D[3 * (size_t)idx + 1] = g2y;
+        a.dL_dmean2D[3 * (size_t)idx + 0] = out2x;
+        a.dL_dmean2D[3 * (size_t)idx + 1] = out2y;
         a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
         reinterpret_cast<float4*>(a.dL_dconic)[idx] = dconic4;
         a.dL_dcolor[3 * (size_t)idx + 0] = pk0.x;
@@ -523,7 +534,7 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                               bool sh_accumulate, cudaStream_t stream) {
+                               bool sh_accumulate, cudaStream_t stream, const float* grad_pack2, int n2) {
     PreBwdArgs a;
     a.P = P;
     a.D = D;
@@ -544,6 +555,8 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
     a.focal_x = cam.focal_x;
     a.focal_y = cam.focal_y;
     a.grad_pack = grad_pack;
+    a.grad_pack2 = n2 > 0 ? grad_pack2 : nullptr;
+    a.n2 = n2;
     a.dL_dmean2D = dL_dmean2D;
     a.dL_dconic = dL_dconic;
     a.dL_dmean3D = dL_dmean3D;

@@ -125,6 +125,19 @@ rasterize_backward_seg2 = _sig("hugs_b200_rasterize_backward_seg2", i32, [
     i32, fp,                  # debug, stream
 ])
 
+layer_bytes = _sig("hugs_b200_layer_bytes", C.c_size_t, [i32, C.c_size_t, i32, i32])
+layer_layout_of = _sig("hugs_b200_layer_layout_of", i32, [i32, C.c_size_t, i32, i32, C.POINTER(C.c_size_t)])
+layer_forward = _sig("hugs_b200_layer_forward", i32, [
+    i32, i32, fp, i32, i32,   # P, n_layer, background, width, height
+    fp, fp, fp, C.c_size_t, fp,  # colors_precomp, geom, binning, binning_bytes, image
+    fp, C.c_size_t, fp, i32, fp,  # layer buffer, layer bytes, out_color, debug, stream
+])
+_LAYER_TAIL = [i32, fp, fp, C.c_size_t, fp]   # n_layer, background_layer, layer buffer, layer bytes, dL_dpix_layer
+rasterize_backward_layer = _sig("hugs_b200_rasterize_backward_layer", i32,
+                                list(rasterize_backward_acc.argtypes) + _LAYER_TAIL)
+rasterize_backward_seg2_layer = _sig("hugs_b200_rasterize_backward_seg2_layer", i32,
+                                     list(rasterize_backward_seg2.argtypes) + _LAYER_TAIL)
+
 l1_ssim_forward = _sig("hugs_b200_l1_ssim_forward", i32, [i32, i32, i32, fp, fp, fp, fp, fp])
 l1_ssim_backward = _sig("hugs_b200_l1_ssim_backward", i32, [i32, i32, i32, fp, fp, fp, fp, fp, fp])
 
@@ -192,6 +205,8 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_densification_stats",
     "hugs_b200_triplane_forward", "hugs_b200_triplane_backward",
     "hugs_b200_rasterize_forward_seg2", "hugs_b200_rasterize_backward_seg2",
+    "hugs_b200_layer_bytes", "hugs_b200_layer_layout_of", "hugs_b200_layer_forward", "hugs_b200_rasterize_backward_layer",
+    "hugs_b200_rasterize_backward_seg2_layer",
 ]
 
 

@@ -64,9 +64,13 @@ def render(means3D, feats, opacity, scales, rotations, data, scaling_modifier=1.
     }
 
 
-def _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_color, active_sh_degree):
-    """`render` (gs_renderer.py:103-161) of human || scene without building the concatenation."""
+def _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_color, active_sh_degree,
+                         human_bg_color=None, human_separate=False):
+    """`render` (gs_renderer.py:103-161) of human || scene without building the concatenation; with
+    `human_separate` also the human-only image of gs_renderer.py:68-82, from the same sorted lists
+    (layer.py) instead of a second rasterizer pass."""
     from .segments import rasterize_two_segments
+    from .layer import rasterize_two_segments_with_layer
     device = human_gs_out['xyz'].device
     if bg_color is None:
         bg_color = torch.zeros(3, dtype=torch.float32, device=device)
@@ -83,13 +87,64 @@ def _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_
         projmatrix=data['full_proj_transform'], sh_degree=active_sh_degree, campos=data['camera_center'],
         prefiltered=False, debug=False)
     seg = lambda o: (o['xyz'], o['shs'], o['opacity'], o['scales'], o['rotq'])  # noqa: E731
-    rendered_image, radii = rasterize_two_segments(seg(human_gs_out), seg(scene_gs_out), screenspace_points, settings)
-    return {
+    human_image = None
+    if human_separate:
+        rendered_image, human_image, radii = rasterize_two_segments_with_layer(
+            seg(human_gs_out), seg(scene_gs_out), screenspace_points, settings,
+            human_bg_color if human_bg_color is not None else bg_color)
+    else:
+        rendered_image, radii = rasterize_two_segments(seg(human_gs_out), seg(scene_gs_out), screenspace_points,
+                                                       settings)
+    pkg = {
         "render": torch.clamp(rendered_image, 0.0, 1.0),
         "viewspace_points": screenspace_points,
         "visibility_filter": radii > 0,
         "radii": radii,
     }
+    if human_image is not None:
+        _add_human_layer(pkg, human_image, radii, human_gs_out['xyz'].shape[0])
+    return pkg
+
+
+def _add_human_layer(pkg, human_image, radii, n_human):
+    # the keys gs_renderer.py:80-82 copies from its second render(); radii are per Gaussian and do not
+    # depend on which other Gaussians are rendered with it
+    pkg['human_img'] = torch.clamp(human_image, 0.0, 1.0)
+    pkg['human_radii'] = radii[:n_human]
+    pkg['human_visibility_filter'] = pkg['human_radii'] > 0
+
+
+def _render_with_human_layer(args, n_human, data, scaling_modifier, bg_color, human_bg_color, active_sh_degree):
+    """`render` of the concatenated tensors plus the human-only image (precomputed-colour / mixed inputs)."""
+    from .layer import rasterize_with_layer
+    means3D = args['means3D']
+    device = means3D.device
+    if bg_color is None:
+        bg_color = torch.zeros(3, dtype=torch.float32, device=device)
+    screenspace_points = torch.zeros_like(means3D, dtype=means3D.dtype, requires_grad=True, device=device) + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    feats = args['feats']
+    shs, rgb = (None, feats) if feats.dim() == 2 else (feats, None)
+    settings = GaussianRasterizationSettings(
+        image_height=int(data['image_height']), image_width=int(data['image_width']),
+        tanfovx=math.tan(data['fovx'] * 0.5), tanfovy=math.tan(data['fovy'] * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=data['world_view_transform'],
+        projmatrix=data['full_proj_transform'], sh_degree=active_sh_degree, campos=data['camera_center'],
+        prefiltered=False, debug=False)
+    rendered_image, human_image, radii = rasterize_with_layer(
+        means3D, screenspace_points, args['opacity'], args['scales'], args['rotations'], settings, n_human,
+        human_bg_color if human_bg_color is not None else bg_color, shs=shs, colors_precomp=rgb)
+    pkg = {
+        "render": torch.clamp(rendered_image, 0.0, 1.0),
+        "viewspace_points": screenspace_points,
+        "visibility_filter": radii > 0,
+        "radii": radii,
+    }
+    _add_human_layer(pkg, human_image, radii, n_human)
+    return pkg
 
 
 _KEYS = (("shs", "feats"), ("xyz", "means3D"), ("opacity", "opacity"), ("scales", "scales"), ("rotq", "rotations"))
@@ -115,20 +170,18 @@ def render_human_scene(data, human_gs_out, scene_gs_out, bg_color, human_bg_colo
     else:
         raise ValueError(f'Unknown render mode: {render_mode}')
 
+    # gs_renderer.py:68-82 renders the human a second time for `human_img`; here it is a second blend over
+    # the joint pass's lists (ONE rasterizer forward and backward per step)
+    separate = bool(render_human_separate) and render_mode == 'human_scene'
     if args is None:
         render_pkg = _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_color,
-                                          active_sh_degree)
+                                          active_sh_degree, human_bg_color, separate)
+    elif separate:
+        render_pkg = _render_with_human_layer(args, human_gs_out['xyz'].shape[0], data, scaling_modifier, bg_color,
+                                              human_bg_color, active_sh_degree)
     else:
         render_pkg = render(data=data, scaling_modifier=scaling_modifier, bg_color=bg_color,
                             active_sh_degree=active_sh_degree, **args)
-
-    if render_human_separate and render_mode == 'human_scene':
-        human_pkg = render(data=data, scaling_modifier=scaling_modifier,
-                           bg_color=human_bg_color if human_bg_color is not None else bg_color,
-                           active_sh_degree=human_gs_out['active_sh_degree'], **_pick(human_gs_out))
-        render_pkg['human_img'] = human_pkg['render']
-        render_pkg['human_visibility_filter'] = human_pkg['visibility_filter']
-        render_pkg['human_radii'] = human_pkg['radii']
 
     if render_mode == 'human':
         render_pkg['human_visibility_filter'] = render_pkg['visibility_filter']
