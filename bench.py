@@ -43,13 +43,40 @@ import torch  # noqa: E402
 
 METRIC = "fwd+bwd frames/s, 1.1M Gaussians @1080p"
 UNIT = "frames/s"
+# mode: "train" = LBS + rasterizer forward + loss + backward per view, gradients accumulated, allreduce per step
+#       "train_separate" = the same with the trainer's separate human image (gs_renderer.py:68-82, two losses)
+#       "forward" = rendering only (no_grad), the image is the result
+#       "animation" = `frames` pose frames per step, split over the ranks: batched LBS + render, no collective
+def _w(n_human, n_scene, W=1920, H=1080, focal=1400.0, mode="train", **kw):
+    return dict(n_human=n_human, n_scene=n_scene, W=W, H=H, focal=focal, mode=mode, **kw)
+
+
 WORKLOADS = {
-    # name: (n_human, n_scene, W, H, focal)
-    "human_scene_1080p": (110210, 1_000_000, 1920, 1080, 1400.0),   # BASELINE.json configs[2] (the metric's config)
-    "human_only_1080p": (110210, 0, 1920, 1080, 1400.0),            # configs[1]
-    "smoke_256": (4096, 20000, 256, 256, 187.0),
+    "human_scene_1080p": _w(110210, 1_000_000),                              # BASELINE.json configs[2] (the metric's)
+    "human_only_1080p": _w(110210, 0),                                       # configs[1]
+    "human_scene_separate_1080p": _w(110210, 1_000_000, mode="train_separate"),   # configs[2] as the trainer runs it
+    "scene_only_3M_forward": _w(0, 3_000_000, mode="forward"),               # configs[3]
+    "pose_animation_300": _w(110210, 0, mode="animation", frames=300),       # configs[4]
+    "human_only_256": _w(110210, 0, 256, 256, 187.0, cpu="torch"),           # configs[0]: the CPU-runnable case
+    "smoke_256": _w(4096, 20000, 256, 256, 187.0),
+    "smoke_separate_256": _w(4096, 20000, 256, 256, 187.0, mode="train_separate"),
+    "smoke_forward_256": _w(0, 30000, 256, 256, 187.0, mode="forward"),
+    "smoke_animation_256": _w(4096, 0, 256, 256, 187.0, mode="animation", frames=12),
 }
 SEED = 1002
+
+
+def load_synth():
+    """hugs_b200/synth.py loaded by path: pure torch, and the reference arm must not import the product
+    package (importing hugs_b200 loads libhugs_b200.so)."""
+    import importlib.util
+    if "hb_synth" not in sys.modules:
+        spec = importlib.util.spec_from_file_location(
+            "hb_synth", os.path.join(ROOT, "ml-hugs_b200", "hugs_b200", "synth.py"))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules["hb_synth"] = mod
+        spec.loader.exec_module(mod)
+    return sys.modules["hb_synth"]
 
 
 def parse_args():
@@ -61,6 +88,9 @@ def parse_args():
     ap.add_argument("--workload", default="human_scene_1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--views-per-rank", type=int, default=8,
                     help="views each rank renders per step before the gradient allreduce (view batch = this x N)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --views-per-rank views on every rank; strong: --global-batch views split over the ranks")
+    ap.add_argument("--global-batch", type=int, default=0, help="view batch of a step under --scaling strong")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-baseline-seconds", type=float, default=20.0)
     return ap.parse_args()
@@ -136,20 +166,35 @@ class ClockSampler:
 def make_workload(name, rank, world, device, views=1):
     """Seeded synthetic tensors of the workload.  Parameters are identical on every
     rank (replicas); the step's view batch of world x views views on the orbit is split across the
-    ranks, and every view has its own camera, SMPL joint transforms and image-space loss gradient."""
-    from hugs_b200 import synth
+    ranks, and every view has its own camera, SMPL joint transforms and image-space loss gradient.
+    animation: the step's `frames` pose frames are split round-robin instead."""
+    synth = load_synth()
 
-    n_human, n_scene, W, H, focal = WORKLOADS[name]
-    n_views = max(world, 1) * views
-    # round-robin split of the step's view batch (hugs_b200.dp.shard_views): every rank gets the same
-    # mix of orbit positions, so the ranks' pair counts -- and step times -- stay balanced
-    mine = [v * max(world, 1) + rank for v in range(views)]
+    w = WORKLOADS[name]
+    n_human, n_scene, W, H, focal, mode = w["n_human"], w["n_scene"], w["W"], w["H"], w["focal"], w["mode"]
+    if mode == "animation":
+        n_views = w["frames"]
+        mine = list(range(rank, n_views, max(world, 1)))
+    else:
+        n_views = max(world, 1) * views
+        # round-robin split of the step's view batch (hugs_b200.dp.shard_views): every rank gets the same
+        # mix of orbit positions, so the ranks' pair counts -- and step times -- stay balanced
+        mine = [v * max(world, 1) + rank for v in range(views)]
     cams = [synth.make_camera(W, H, focal, view=i, n_views=n_views, seed=SEED) for i in mine]
-    h = synth.make_human_gaussians(n_human, seed=SEED + 1)
-    As = [synth.make_joint_transforms(1, SEED + 100 + i)[0] for i in mine]
-    Gs = [synth.make_dL_dcolor(W, H, SEED + i) for i in mine]
-    parts = dict(human=h, A=As[0], cam=cams[0], G=Gs[0], As=As, cams=cams, Gs=Gs, W=W, H=H, n_human=n_human,
-                 n_scene=n_scene)
+    parts = dict(cam=cams[0], cams=cams, W=W, H=H, n_human=n_human, n_scene=n_scene, mode=mode, view_ids=mine)
+    if n_human > 0:
+        parts["human"] = synth.make_human_gaussians(n_human, seed=SEED + 1)
+        if mode == "animation":   # one smooth pose sequence, every rank takes its frames of it
+            seq = synth.make_joint_transforms(n_views, SEED + 100)
+            parts["As"] = [seq[i] for i in mine]
+        else:
+            parts["As"] = [synth.make_joint_transforms(1, SEED + 100 + i)[0] for i in mine]
+        parts["A"] = parts["As"][0]
+    if mode in ("train", "train_separate"):
+        parts["Gs"] = [synth.make_dL_dcolor(W, H, SEED + i) for i in mine]
+        parts["G"] = parts["Gs"][0]
+    if mode == "train_separate":
+        parts["Ghs"] = [synth.make_dL_dcolor(W, H, SEED + 5000 + i) for i in mine]
     if n_scene > 0:
         # scene frustum is laid out for the central camera so every rank holds the same replica
         cam0 = synth.make_camera(W, H, focal, seed=SEED)
@@ -160,24 +205,35 @@ def make_workload(name, rank, world, device, views=1):
 class Replica:
     """Device-resident parameter replica + the per-frame inputs, and the frame step itself."""
 
-    def __init__(self, wl, device, module, lbs_impl, sh_sink=False):
+    def __init__(self, wl, device, impl, sh_sink=False):
         self.device = device
-        self.module = module      # a diff_gaussian_rasterization-shaped module (ours or the reference)
-        self.lbs_impl = lbs_impl  # callable(A, xyz, w, rotmat, scales, transl) -> (xyz', rotq, scales')
-        h = wl["human"]
+        self.module = impl["module"]      # a diff_gaussian_rasterization-shaped module (ours or the reference)
+        self.lbs_impl = impl["lbs"]       # callable(A, xyz, w, rotmat, scales, transl) -> (xyz', rotq, scales')
+        self.lbs_frames = impl.get("lbs_frames")      # batched over pose frames (animation), or None
+        self.render_separate = impl.get("separate")   # (settings, tensors, n_human, human_bg) -> (color, human_color, radii)
+        self.mode = wl["mode"]
+        self.training = self.mode in ("train", "train_separate")
         d = lambda t: t.to(device).contiguous()  # noqa: E731
-        leaf = lambda t: d(t).requires_grad_(True)  # noqa: E731
+        leaf = (lambda t: d(t).requires_grad_(True)) if self.training else d  # noqa: E731
         self.W, self.H = wl["W"], wl["H"]
         self.n_human, self.n_scene = wl["n_human"], wl["n_scene"]
-        self.h_xyz, self.h_rotmat = leaf(h["xyz"]), leaf(h["rotmat"])
-        self.h_scales, self.h_weights = leaf(h["scales"]), leaf(h["lbs_weights"])
-        opac, shs = [h["opacity"]], [h["shs"]]
+        opac, shs, n_small = [], [], 0
+        self.h_xyz = self.h_rotmat = self.h_scales = self.h_weights = self.transl = None
+        if self.n_human > 0:
+            h = wl["human"]
+            self.h_xyz, self.h_rotmat = leaf(h["xyz"]), leaf(h["rotmat"])
+            self.h_scales, self.h_weights = leaf(h["scales"]), leaf(h["lbs_weights"])
+            self.transl = d(h["transl"][0])
+            opac.append(h["opacity"])
+            shs.append(h["shs"])
+            n_small += sum(t.numel() for t in (h["xyz"], h["rotmat"], h["scales"], h["lbs_weights"]))
         self.s_means = self.s_scales = self.s_rots = None
         if self.n_scene > 0:
-            s = wl["scene"]
-            self.s_means, self.s_scales, self.s_rots = leaf(s["means3D"]), leaf(s["scales"]), leaf(s["rotations"])
-            opac.append(s["opacity"])
-            shs.append(s["shs"])
+            sc = wl["scene"]
+            self.s_means, self.s_scales, self.s_rots = leaf(sc["means3D"]), leaf(sc["scales"]), leaf(sc["rotations"])
+            opac.append(sc["opacity"])
+            shs.append(sc["shs"])
+            n_small += sum(sc[k].numel() for k in ("means3D", "scales", "rotations"))
         # attributes that do not pass through LBS are kept concatenated (human first,
         # hugs/renderer/gs_renderer.py:33-37)
         self.opacity = leaf(torch.cat(opac))
@@ -186,45 +242,53 @@ class Replica:
         # our arm: every view's SH gradient (81 % of the gradient bytes) is accumulated by the backward
         # kernel itself, in the buffer the allreduce then works on (hugs_b200.ShGradSink)
         self.sh_sink = None
-        if sh_sink:
+        if sh_sink and self.training:
             import hugs_b200
             # one flat gradient buffer: [SH gradient (the sink) | every other gradient], so the exchange is
             # ONE collective over 275 MB
             n_sh = self.shs.numel()
-            n_small = sum(t.numel() for t in (h["xyz"], h["rotmat"], h["scales"], h["lbs_weights"])) + self.opacity.numel()
-            if self.n_scene > 0:
-                n_small += sum(wl["scene"][k].numel() for k in ("means3D", "scales", "rotations"))
-            self.flat_all = torch.zeros(n_sh + n_small, device=device)
+            self.flat_all = torch.zeros(n_sh + n_small + self.opacity.numel(), device=device)
             self.sh_sink = hugs_b200.attach_sh_grad_sink(self.shs, self.flat_all[:n_sh].view_as(self.shs))
         self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
         # views of a step alternate between `n_streams` CUDA streams: the issue-bound blend kernels of one
         # view overlap the latency- and HBM-bound binning / per-Gaussian kernels of the next
         self.n_streams = max(1, int(os.environ.get("HB_STREAMS", "2"))) if sh_sink else 1
         self.streams = [torch.cuda.Stream(device) for _ in range(self.n_streams)] if self.n_streams > 1 else []
-        self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=True)
-        self.transl = d(h["transl"][0])
+        self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=self.training)
         # per-frame inputs: pinned host copies (for e2e) and resident device copies (for value)
         self.tanfovx, self.tanfovy = wl["cam"]["tanfovx"], wl["cam"]["tanfovy"]
         self.hosts, self.devs = [], []
-        for cam, A, G in zip(wl["cams"], wl["As"], wl["Gs"]):
+        for i, cam in enumerate(wl["cams"]):
             host = {k: cam[k].clone().pin_memory() for k in ("viewmatrix", "projmatrix", "campos", "bg")}
-            host["A"] = A.clone().pin_memory()
-            host["G"] = G.clone().pin_memory()
+            if self.n_human > 0:
+                host["A"] = wl["As"][i].clone().pin_memory()
+            if self.training:
+                host["G"] = wl["Gs"][i].clone().pin_memory()
+            if self.mode == "train_separate":
+                host["Gh"] = wl["Ghs"][i].clone().pin_memory()
             self.hosts.append(host)
             self.devs.append({k: v.to(device) for k, v in host.items()})
+        self.human_bg = torch.tensor([1.0, 1.0, 1.0], device=device)
         self.views = len(self.hosts)
         self.h2d_bytes = sum(v.numel() * v.element_size() for host in self.hosts for v in host.values())
+        self.d2h_bytes = (4 + 4) * self.views if self.training else 3 * self.W * self.H * 4 * self.views
         self.last_nodes, self.last_radii_v = [None] * self.views, [None] * self.views
-        # e2e plumbing: the image-space loss gradient (the stand-in for the training target, 25 MB) is
-        # uploaded on a copy stream into one of two device buffers while the forward pass runs; the
+        self.last_node = self.last_radii = None
+        # e2e plumbing (training): the image-space loss gradient (the stand-in for the training target, 25 MB)
+        # is uploaded on a copy stream into one of two device buffers while the forward pass runs; the
         # loss of every step is copied to pinned memory and read one step later, so the host never
         # stalls the device (what a training loop's prefetcher / async logger does).
         self.copy_stream = torch.cuda.Stream(device)
-        self.G_dev = [torch.empty_like(self.devs[0]["G"]) for _ in range(2)]
+        big = [k for k in ("G", "Gh") if k in self.hosts[0]]
+        self.G_dev = [{k: torch.empty_like(self.devs[0][k]) for k in big} for _ in range(2)]
         self.G_ready = [torch.cuda.Event() for _ in range(2)]
         self.step_done = [None, None]
         self.loss_host = [torch.zeros(1).pin_memory() for _ in range(4)]
         self.loss_ready = [None] * 4
+        # e2e plumbing (rendering): every frame's image goes to one of four pinned host buffers
+        self.img_host = [] if self.training else [torch.empty(3, self.H, self.W).pin_memory() for _ in range(4)]
+        self.img_ready = [None] * 4
+        self.images_read = 0
         self.e2e_step = 0
         self.losses = []
         self.flat_small = None
@@ -234,6 +298,8 @@ class Replica:
         return {n: getattr(self, n) for n in names if getattr(self, n) is not None}
 
     def zero_grad(self):
+        if not self.training:
+            return
         for n, p in self.leaves().items():
             if n == "shs" and self.sh_sink is not None:
                 if self.n_streams > 1:
@@ -244,81 +310,139 @@ class Replica:
                 p.grad = None
         self.means2D.grad = None
 
+    def _gaussians(self, inp):
+        """LBS of the human + the scene: the rasterizer's (means3D, scales, rotations)."""
+        if self.n_human > 0:
+            if "deformed" in inp:
+                xyz, rotq, hsc = inp["deformed"]
+            else:
+                A = inp["A"].requires_grad_(True) if self.training else inp["A"]
+                xyz, rotq, hsc = self.lbs_impl(A, self.h_xyz, self.h_weights, self.h_rotmat, self.h_scales, self.transl)
+            if self.n_scene > 0:
+                return torch.cat([xyz, self.s_means]), torch.cat([hsc, self.s_scales]), torch.cat([rotq, self.s_rots])
+            return xyz, hsc, rotq
+        return self.s_means, self.s_scales, self.s_rots
+
     def frame(self, inp):
-        """One forward + backward of one view.  Returns the loss tensor (device)."""
-        A = inp["A"].requires_grad_(True)
-        xyz, rotq, hsc = self.lbs_impl(A, self.h_xyz, self.h_weights, self.h_rotmat, self.h_scales, self.transl)
-        if self.n_scene > 0:
-            means3D = torch.cat([xyz, self.s_means])
-            scales = torch.cat([hsc, self.s_scales])
-            rots = torch.cat([rotq, self.s_rots])
-        else:
-            means3D, scales, rots = xyz, hsc, rotq
+        """One forward (+ backward when training) of one view.  Returns the loss tensor / the image (device)."""
+        if not self.training:
+            with torch.no_grad():
+                return self._frame(inp)
+        return self._frame(inp)
+
+    def _frame(self, inp):
+        means3D, scales, rots = self._gaussians(inp)
         settings = self.module.GaussianRasterizationSettings(
             image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=inp["bg"],
             scale_modifier=1.0, viewmatrix=inp["viewmatrix"], projmatrix=inp["projmatrix"], sh_degree=3,
             campos=inp["campos"], prefiltered=False, debug=False)
-        color, radii = self.module.GaussianRasterizer(settings)(
-            means3D=means3D, means2D=self.means2D, opacities=self.opacity, shs=self.shs, scales=scales,
-            rotations=rots)
+        color_h = None
+        if self.mode == "train_separate":
+            color, color_h, radii = self.render_separate(
+                settings, dict(means3D=means3D, means2D=self.means2D, opacities=self.opacity, shs=self.shs,
+                               scales=scales, rotations=rots), self.n_human, self.human_bg)
+        else:
+            color, radii = self.module.GaussianRasterizer(settings)(
+                means3D=means3D, means2D=self.means2D, opacities=self.opacity, shs=self.shs, scales=scales,
+                rotations=rots)
+        self.last_radii = radii
+        self.last_node = color.grad_fn
+        if not self.training:
+            if "img_out" in inp:   # e2e: the image is the result, it goes back to the host
+                inp["img_out"].copy_(color, non_blocking=True)
+                inp["img_event"].record()
+            return color
         if "G_ready" in inp:  # the upload of G runs on the copy stream; it is first needed here
             torch.cuda.current_stream(self.device).wait_event(inp["G_ready"])
         loss = (color * inp["G"]).sum()
+        if color_h is not None:
+            loss = loss + (color_h * inp["Gh"]).sum()
         if "loss_out" in inp:
             inp["loss_out"].copy_(loss.detach().reshape(1), non_blocking=True)
             inp["loss_event"].record()
         loss.backward()
-        self.last_radii = radii
-        self.last_node = color.grad_fn
         return loss.detach()
+
+    def _deform_all(self, As):
+        """animation: the rank's pose frames of the step through ONE batched LBS call when the
+        implementation has one (ours), else frame by frame inside frame()."""
+        if self.mode != "animation" or self.lbs_frames is None:
+            return None
+        with torch.no_grad():
+            xyz, rotq, hsc = self.lbs_frames(As, self.h_xyz, self.h_weights, self.h_rotmat, self.h_scales,
+                                             self.transl[None])
+        return xyz, rotq, hsc
 
     def step_resident(self):
         """One step: every view of this rank's share of the view batch, gradients accumulated."""
         self.zero_grad()
+        if self.mode == "animation" and self.lbs_frames is not None:
+            if not hasattr(self, "A_all"):
+                self.A_all = torch.stack([dv["A"] for dv in self.devs])
+            dall = self._deform_all(self.A_all)
+        else:
+            dall = None
+
+        def inputs(v):
+            inp = dict(self.devs[v])
+            if dall is not None:
+                inp["deformed"] = (dall[0][v], dall[1][v], dall[2][v])
+            return inp
+
         if self.n_streams > 1:
             main = torch.cuda.current_stream(self.device)
             for s in self.streams:
                 s.wait_stream(main)
             for v in range(self.views):
                 with torch.cuda.stream(self.streams[v % self.n_streams]):
-                    self.frame(dict(self.devs[v]))
+                    self.frame(inputs(v))
                 self.last_nodes[v] = self.last_node
                 self.last_radii_v[v] = self.last_radii
             for s in self.streams:
                 main.wait_stream(s)
             return
         for v in range(self.views):
-            self.frame(dict(self.devs[v]))
+            self.frame(inputs(v))
             self.last_nodes[v] = self.last_node
             self.last_radii_v[v] = self.last_radii
 
     def step_e2e(self):
         self.zero_grad()
+        dall = None
+        if self.mode == "animation" and self.lbs_frames is not None:
+            # the step's joint transforms travel as one pinned block
+            if not hasattr(self, "A_host"):
+                self.A_host = torch.stack([h["A"] for h in self.hosts]).pin_memory()
+            dall = self._deform_all(self.A_host.to(self.device, non_blocking=True))
         if self.n_streams > 1:
             main = torch.cuda.current_stream(self.device)
             for s in self.streams:
                 s.wait_stream(main)
             for v in range(self.views):
                 with torch.cuda.stream(self.streams[v % self.n_streams]):
-                    self.frame_e2e(self.hosts[v])
+                    self.frame_e2e(self.hosts[v], None if dall is None else (dall[0][v], dall[1][v], dall[2][v]))
             for s in self.streams:
                 main.wait_stream(s)
             return
         for v in range(self.views):
-            self.frame_e2e(self.hosts[v])
+            self.frame_e2e(self.hosts[v], None if dall is None else (dall[0][v], dall[1][v], dall[2][v]))
 
-    def frame_e2e(self, host):
+    def frame_e2e(self, host, deformed=None):
         """One frame with every per-frame input copied from pinned host memory (camera, joint
-        transforms on the compute stream; G on the copy stream) and the loss read back on the host."""
+        transforms on the compute stream; G on the copy stream) and the result read back on the host:
+        the loss when training, the IMAGE when rendering."""
         i = self.e2e_step % 2
         main = torch.cuda.current_stream(self.device)
-        with torch.cuda.stream(self.copy_stream):
-            if self.step_done[i] is not None:  # buffer i was last read by the step before the previous one
-                self.copy_stream.wait_event(self.step_done[i])
-            self.G_dev[i].copy_(host["G"], non_blocking=True)
-            self.G_ready[i].record(self.copy_stream)
+        big = ("G", "Gh", "_packed")
+        if self.training:
+            with torch.cuda.stream(self.copy_stream):
+                if self.step_done[i] is not None:  # buffer i was last read by the step before the previous one
+                    self.copy_stream.wait_event(self.step_done[i])
+                for k, buf in self.G_dev[i].items():
+                    buf.copy_(host[k], non_blocking=True)
+                self.G_ready[i].record(self.copy_stream)
         # camera + joint transforms travel as ONE pinned record (one async copy instead of five)
-        small = [(k, v) for k, v in host.items() if k != "G" and k != "_packed"]
+        small = [(k, v) for k, v in host.items() if k not in big and not (deformed is not None and k == "A")]
         if "_packed" not in host:
             host["_packed"] = torch.cat([v.reshape(-1) for _, v in small]).pin_memory()
         rec = host["_packed"].to(self.device, non_blocking=True)
@@ -326,33 +450,49 @@ class Replica:
         for k, v in small:
             inp[k] = rec[off:off + v.numel()].view(v.shape)
             off += v.numel()
-        # Loss read-back: every frame's loss is copied to a pinned slot of a small ring and read by the
-        # host when the slot comes round again (4 frames later: the copy has long landed, the host never
-        # stalls the device); drain_e2e reads what is still pending before the closing event.
-        s = self.e2e_step % len(self.loss_host)
-        if self.loss_ready[s] is not None:
-            self.loss_ready[s].synchronize()
-            self.losses.append(float(self.loss_host[s][0]))
+        if deformed is not None:
+            inp["deformed"] = deformed
+        # Read-back: every frame's result is copied to a pinned slot of a small ring and read by the host
+        # when the slot comes round again (4 frames later; the host does not stall the device for the
+        # 4-byte loss, and waits on PCIe for the 25 MB image when the copy is the bottleneck);
+        # drain_e2e reads what is still pending before the closing event.
+        s = self.e2e_step % 4
         ev = torch.cuda.Event()
-        inp.update(G=self.G_dev[i], G_ready=self.G_ready[i], loss_out=self.loss_host[s], loss_event=ev)
-        self.frame(inp)
-        self.loss_ready[s] = ev
+        if self.training:
+            if self.loss_ready[s] is not None:
+                self.loss_ready[s].synchronize()
+                self.losses.append(float(self.loss_host[s][0]))
+            inp.update(self.G_dev[i])
+            inp.update(G_ready=self.G_ready[i], loss_out=self.loss_host[s], loss_event=ev)
+            self.frame(inp)
+            self.loss_ready[s] = ev
+        else:
+            if self.img_ready[s] is not None:
+                self.img_ready[s].synchronize()
+                self.images_read += 1
+            inp.update(img_out=self.img_host[s], img_event=ev)
+            self.frame(inp)
+            self.img_ready[s] = ev
         done = torch.cuda.Event()
         done.record(main)
         self.step_done[i] = done
         self.e2e_step += 1
 
     def drain_e2e(self):
-        """Read the losses still pending (called inside the timed region, after the last step)."""
-        for s in range(len(self.loss_host)):
+        """Read the results still pending (called inside the timed region, after the last step)."""
+        for s in range(4):
             if self.loss_ready[s] is not None:
                 self.loss_ready[s].synchronize()
                 self.loss_ready[s] = None
                 self.losses.append(float(self.loss_host[s][0]))
+            if self.img_ready[s] is not None:
+                self.img_ready[s].synchronize()
+                self.img_ready[s] = None
+                self.images_read += 1
 
     def allreduce_grads(self):
         import torch.distributed as dist
-        if not dist.is_initialized() or dist.get_world_size() == 1:
+        if not self.training or not dist.is_initialized() or dist.get_world_size() == 1:
             return
         # Two collectives: the SH gradient (81 % of the bytes) in place, everything else through one
         # flat buffer (a collective per small tensor costs more in launch latency than in transfer).
@@ -385,11 +525,20 @@ class Replica:
 def our_impl():
     import diff_gaussian_rasterization as dgr
     import hugs_b200
+    from hugs_b200 import layer
 
     def lbs_impl(A, xyz, w, rotmat, scales, transl):
         return hugs_b200.deform_gaussians(A, xyz, w, rotmat, scales, smpl_scale=1.0, transl=transl)
 
-    return dgr, lbs_impl
+    def lbs_frames(As, xyz, w, rotmat, scales, transl):
+        return hugs_b200.lbs_deform_frames(As, xyz, w, rotmat, scales, transl.expand(As.shape[0], 3).contiguous(), 1.0)
+
+    def separate(settings, t, n_human, human_bg):
+        # ONE rasterizer pass: the human image comes from the joint pass's sorted lists (hugs_b200/layer.py)
+        return layer.rasterize_with_layer(t["means3D"], t["means2D"], t["opacities"], t["scales"], t["rotations"],
+                                          settings, n_human, human_bg, shs=t["shs"])
+
+    return dict(module=dgr, lbs=lbs_impl, lbs_frames=lbs_frames, separate=separate)
 
 
 def reference_impl():
@@ -407,7 +556,15 @@ def reference_impl():
         T = T.squeeze(0)
         return dxyz, rot.matrix_to_quaternion(T[:, :3, :3] @ rotmat), scales * 1.0
 
-    return ref, lbs_impl
+    def separate(settings, t, n_human, human_bg):
+        # hugs/renderer/gs_renderer.py:56-82: render(everything), then render(the human alone)
+        color, radii = ref.GaussianRasterizer(settings)(**t)
+        h = {k: v[:n_human] for k, v in t.items() if k != "means2D"}
+        h["means2D"] = torch.zeros(n_human, 3, device=color.device, requires_grad=True)
+        color_h, _ = ref.GaussianRasterizer(settings._replace(bg=human_bg))(**h)
+        return color, color_h, radii
+
+    return dict(module=ref, lbs=lbs_impl, lbs_frames=None, separate=separate)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -468,28 +625,29 @@ def cpu_oracle_frames(wl, seconds, min_frames=2):
     from oracle import oracle as O
     import numpy as np
 
-    h, cam = wl["human"], wl["cam"]
+    cam = wl["cam"]
     n = lambda t: t.detach().cpu().numpy()  # noqa: E731
     W, H = wl["W"], wl["H"]
     threads = os.cpu_count() or 1
+    training = wl["mode"] in ("train", "train_separate")
 
     def one():
-        xyz, q, hs, _ = O.lbs_forward(n(wl["A"]), n(h["xyz"]), n(h["lbs_weights"]), n(h["rotmat"]), n(h["scales"]),
-                                      n(h["transl"][0]), 1.0)
+        parts = []
+        if wl["n_human"] > 0:
+            h = wl["human"]
+            xyz, q, hs, _ = O.lbs_forward(n(wl["A"]), n(h["xyz"]), n(h["lbs_weights"]), n(h["rotmat"]), n(h["scales"]),
+                                          n(h["transl"][0]), 1.0)
+            parts.append((xyz, hs, q, n(h["opacity"]), n(h["shs"])))
         if wl["n_scene"] > 0:
             s = wl["scene"]
-            means = np.concatenate([xyz, n(s["means3D"])])
-            scales = np.concatenate([hs, n(s["scales"])])
-            rots = np.concatenate([q, n(s["rotations"])])
-            opac = np.concatenate([n(h["opacity"]), n(s["opacity"])])
-            shs = np.concatenate([n(h["shs"]), n(s["shs"])])
-        else:
-            means, scales, rots, opac, shs = xyz, hs, q, n(h["opacity"]), n(h["shs"])
+            parts.append((n(s["means3D"]), n(s["scales"]), n(s["rotations"]), n(s["opacity"]), n(s["shs"])))
+        means, scales, rots, opac, shs = (np.concatenate([p[i] for p in parts]) for i in range(5))
         kw = dict(shs=shs, degree=3, scales=scales, rotations=rots)
         fw = O.forward(means, opac, n(cam["viewmatrix"]), n(cam["projmatrix"]), n(cam["campos"]), n(cam["bg"]), W, H,
                        cam["tanfovx"], cam["tanfovy"], **kw)
-        O.backward(fw, n(wl["G"]), means, n(cam["viewmatrix"]), n(cam["projmatrix"]), n(cam["campos"]), n(cam["bg"]),
-                   W, H, cam["tanfovx"], cam["tanfovy"], **kw)
+        if training:
+            O.backward(fw, n(wl["G"]), means, n(cam["viewmatrix"]), n(cam["projmatrix"]), n(cam["campos"]),
+                       n(cam["bg"]), W, H, cam["tanfovx"], cam["tanfovy"], **kw)
 
     one()  # warm-up (page-in, OpenMP pool)
     t0 = time.perf_counter()
@@ -500,12 +658,60 @@ def cpu_oracle_frames(wl, seconds, min_frames=2):
         if frames >= 200:
             break
     dt = time.perf_counter() - t0
-    return frames / dt, threads, frames
+    what = "LBS fwd + raster fwd + bwd" if training else "LBS fwd + raster fwd"
+    return frames / dt, threads, "%d full frames of %s (%s) on the C/OpenMP oracle" % (frames, wl["name"], what)
+
+
+def cpu_torch_frames(wl, seconds, min_frames=1):
+    """BASELINE.json configs[0]: the pure-PyTorch CPU evaluation of the reference math (oracle/torch_cpu.py:
+    the reference's own lbs_extra / matrix_to_quaternion / eval_sh + torch restatements of the CUDA-only
+    preprocess and tile composite), forward + autograd backward, on the host cores."""
+    from oracle import torch_cpu as TC
+    h, cam = wl["human"], wl["cam"]
+    names = ("xyz", "rotmat", "scales", "lbs_weights", "opacity", "shs")
+    threads = torch.get_num_threads()
+
+    def one():
+        t = {k: h[k].detach().clone().requires_grad_(True) for k in names}
+        A = wl["A"].clone().requires_grad_(True)
+        xyz, q, sc = TC.deform(A, t["xyz"], t["lbs_weights"], t["rotmat"], t["scales"], h["transl"][0])
+        img = TC.render(xyz, sc, q, t["opacity"], t["shs"], 3, cam["viewmatrix"], cam["projmatrix"], cam["campos"],
+                        cam["bg"], wl["W"], wl["H"], cam["tanfovx"], cam["tanfovy"])
+        (img * wl["G"]).sum().backward()
+
+    one()
+    t0 = time.perf_counter()
+    frames = 0
+    while frames < min_frames or (time.perf_counter() - t0) < seconds:
+        one()
+        frames += 1
+    dt = time.perf_counter() - t0
+    return frames / dt, threads, ("%d full frames of %s (reference lbs_extra + eval_sh, torch preprocess + tile "
+                                  "composite, autograd backward) in pure PyTorch on the CPU" % (frames, wl["name"]))
+
+
+def cpu_baseline_of(name, seconds, min_frames=2):
+    wl = make_workload(name, 0, 1, "cpu")
+    wl["name"] = name
+    if WORKLOADS[name].get("cpu") == "torch":
+        fps, threads, sample = cpu_torch_frames(wl, seconds)
+    else:
+        fps, threads, sample = cpu_oracle_frames(wl, seconds, min_frames)
+    return {"value": round(fps, 4), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
 
 
 # ------------------------------------------------------------------------------------------------
 # main
 # ------------------------------------------------------------------------------------------------
+def metric_of(name):
+    w = WORKLOADS[name]
+    what = {"train": "fwd+bwd", "train_separate": "fwd+bwd (joint + separate human image)", "forward": "forward-only",
+            "animation": "LBS + forward-only"}[w["mode"]]
+    if name == "human_scene_1080p":
+        return METRIC
+    return "%s frames/s, %s" % (what, name)
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -514,14 +720,29 @@ def main():
     if world != max(args.gpus, 1) and world > 1:
         print("warning: --gpus %d but WORLD_SIZE=%d" % (args.gpus, world), file=sys.stderr)
     n_gpus = world
-    n_human, n_scene, W, H, _ = WORKLOADS[args.workload]
+    w = WORKLOADS[args.workload]
+    n_human, n_scene, W, H, mode = w["n_human"], w["n_scene"], w["W"], w["H"], w["mode"]
+    training = mode in ("train", "train_separate")
+    scaling = args.scaling
+    if mode == "animation":
+        scaling = "strong"       # the step is the workload's `frames` pose frames, whatever N is
+    elif scaling == "strong":
+        gb = args.global_batch or args.views_per_rank
+        if gb % n_gpus:
+            raise SystemExit("--global-batch %d is not a multiple of %d ranks" % (gb, n_gpus))
+        args.views_per_rank = gb // n_gpus
+    frames_per_step = w["frames"] if mode == "animation" else args.views_per_rank * n_gpus
     config = {"workload": args.workload, "n_human": n_human, "n_scene": n_scene, "image": "%dx%d" % (W, H),
-              "sh_degree": 3, "views_per_rank_per_step": args.views_per_rank,
-              "global_view_batch": args.views_per_rank * n_gpus,
-              "cuda_streams_per_rank": max(1, int(os.environ.get("HB_STREAMS", "2"))) if args.impl == "ours" else 1,
-              "parallelism": "dp%d (view batch split round-robin across ranks, gradients accumulated over a rank's "
-                             "views, one allreduce of the parameter gradients per step)" % n_gpus,
+              "sh_degree": 3, "mode": mode,
+              "views_per_rank_per_step": (frames_per_step / n_gpus if mode == "animation" else args.views_per_rank),
+              "global_view_batch": frames_per_step,
+              "parallelism": ("dp%d (view batch split round-robin across ranks, gradients accumulated over a rank's "
+                              "views, one allreduce of the parameter gradients per step)" % n_gpus) if training else
+                             ("frames split round-robin over %d rank(s), no collective" % n_gpus),
               "l2": "inputs larger than L2 (per-frame working set > 1 GB vs 126 MB L2), no flush"}
+    if H * W < 1920 * 1080:
+        config["l2"] = ("per-frame working set ~%d MB, below the 126 MB L2: successive views use different cameras, "
+                        "joint transforms and loss gradients, no flush" % ((n_human + n_scene) * 300 // 1_000_000))
 
     # ---- reference arm -------------------------------------------------------------------------
     if args.impl == "reference":
@@ -542,10 +763,10 @@ def main():
             dist.barrier()
 
     from hugs_b200 import _native
-    module, lbs_impl = our_impl()
     V = args.views_per_rank
     wl = make_workload(args.workload, rank, world, device, views=V)
-    rep = Replica(wl, device, module, lbs_impl, sh_sink=True)
+    rep = Replica(wl, device, our_impl(), sh_sink=True)
+    V = rep.views        # animation: this rank's share of the step's frames
 
     def step_resident():
         rep.step_resident()
@@ -559,8 +780,18 @@ def main():
         step_resident()
     torch.cuda.synchronize(device)
     # pair / visible counts: mean over this rank's views (they size the per-stage algorithmic bytes)
-    R = int(round(sum(int(nd.num_rendered) for nd in rep.last_nodes) / V))
     visible = int(round(sum(int((r > 0).sum()) for r in rep.last_radii_v) / V))
+    if training:
+        R = int(round(sum(int(nd.num_rendered) for nd in rep.last_nodes) / V))
+    else:   # rendering runs under no_grad (no autograd node): count the pairs of this rank's first view once
+        from hugs_b200 import rasterizer as _rz
+        inp = dict(rep.devs[0])
+        with torch.no_grad():
+            m3, sc_, rq = rep._gaussians(inp)
+        R = _rz.rasterize_gaussians_forward(
+            inp["bg"], m3, torch.Tensor([]), rep.opacity, sc_, rq, 1.0, torch.Tensor([]), inp["viewmatrix"],
+            inp["projmatrix"], rep.tanfovx, rep.tanfovy, H, W, rep.shs, 3, inp["campos"], False, False)[0]
+        del m3, sc_, rq
 
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
@@ -572,9 +803,13 @@ def main():
         step_e2e()
     rep.drain_e2e()
     rep.losses.clear()
+    rep.images_read = 0
     ms_e2e = timed_loop(step_e2e, args.steps, device, barrier, finish=rep.drain_e2e)
-    assert len(rep.losses) == args.steps * V and all(math.isfinite(x) for x in rep.losses), \
-        "e2e: a loss was not read back"
+    if training:
+        assert len(rep.losses) == args.steps * V and all(math.isfinite(x) for x in rep.losses), \
+            "e2e: a loss was not read back"
+    else:
+        assert rep.images_read == args.steps * V, "e2e: an image was not read back"
     clocks = sampler.stop() if sampler else None
 
     # per-stage device times: same K steps again with the library's stage events switched on
@@ -592,7 +827,7 @@ def main():
     comm_ms = sum(a.elapsed_time(b) for a, b in rep.comm_events) / max(len(rep.comm_events), 1)
     rep.comm_events = None
     dp_info = None
-    if world > 1:
+    if world > 1 and training:
         t = torch.tensor([comm_ms, ms_staged / args.steps], dtype=torch.float64, device=device)
         allt = [torch.zeros_like(t) for _ in range(world)]
         dist.all_gather(allt, t)
@@ -624,42 +859,52 @@ def main():
                         "frac": round(gbs / peak, 4)}
     dominant = max(stages, key=lambda k: stages[k]["ms"]) if stages else None
     roofline = None
-    # DRAM bytes per launch from the committed ncu --set full capture of this workload (null for others)
-    traffic, traffic_src, issue_pct = None, None, {}
+    # DRAM bytes per launch + issue-slot utilisation from the committed ncu --set full capture of the
+    # headline workload (null for the others)
+    traffic, traffic_src, issue_pct, issue_src = None, None, {}, None
     try:
-        if args.workload == "human_scene_1080p":
+        if args.workload in ("human_scene_1080p", "human_scene_separate_1080p"):
             with open(os.path.join(ROOT, "profiles", "ncu_dram_traffic.json")) as f:
                 tj = json.load(f)
             traffic, traffic_src = tj["bytes_per_frame"], tj["source"]
-            issue_pct = tj.get("issue_active_pct", {})
+            issue_pct, issue_src = tj.get("issue_active_pct", {}), tj.get("issue_source")
             for name in stages:
-                if name in traffic:
+                if name in traffic and args.workload == "human_scene_1080p":
                     stages[name]["dram_traffic"] = int(traffic[name])
+                if name in issue_pct:
+                    stages[name]["issue_active_pct_ncu"] = issue_pct[name]
     except Exception:
         traffic = None
     if dominant:
         s = stages[dominant]
         issue_bound = dominant in ("render_forward", "render_backward")
-        roofline = {"kernel": dominant, "bound": "hbm", "achieved": s["gbs"], "peak": peak, "unit": "GB/s",
-                    "frac": s["frac"], "traffic": int(traffic[dominant]) if traffic and dominant in traffic else None,
+        roofline = {"kernel": dominant, "bound": "issue" if issue_bound else "hbm",
+                    "achieved": s["gbs"], "peak": peak, "unit": "GB/s", "frac": s["frac"],
+                    "traffic": int(traffic[dominant]) if traffic and dominant in traffic else None,
                     "traffic_source": traffic_src,
-                    "issue_active_pct_ncu": issue_pct.get(dominant),
-                    "limiter": ("instruction issue (ncu: 86-92 % issue-slot active, DRAM traffic far below the "
-                                "algorithmic gather bytes because a tile's Gaussians are served by L2): see "
-                                "DESIGN.md section 5; the HBM-bound stages are in `stages`") if issue_bound else "hbm",
+                    "issue_frac": round(issue_pct[dominant] / 100.0, 4) if dominant in issue_pct else None,
+                    "issue_source": issue_src,
+                    "limiter": ("instruction issue: the blend kernels keep the warp schedulers' issue slots busy "
+                                "(`issue_frac`, ncu) while their DRAM traffic (`traffic`) is a small fraction of the "
+                                "algorithmic gather bytes -- a tile's Gaussians are served by L2; `achieved`/`frac` "
+                                "are the HBM figures on the algorithmic bytes of SURVEY.md 8(d), kept for comparison "
+                                "(DESIGN.md section 5); the HBM-bound stages are in `stages`") if issue_bound else "hbm",
                     "peak_source": peak_kind,
                     "ms_per_launch": s["ms"], "algorithmic_bytes": s["bytes"],
                     "timed": "per-stage CUDA events on the launching stream, %d frames on ONE stream (%.3f ms/frame "
                              "with events on; the timed region above alternates views over %d streams)"
                              % (args.steps * V, ms_staged / (args.steps * V), rep.n_streams)}
-    frame_bytes = sum(nbytes.values())
+    frame_bytes = sum(nbytes[k] for k in stages)
+    total_frames = frames_per_step * args.steps
     line = {
-        "metric": METRIC, "value": round(n_gpus * V * args.steps / (ms * 1e-3), 3), "unit": UNIT, "n_gpus": n_gpus,
-        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "metric": metric_of(args.workload), "value": round(total_frames / (ms * 1e-3), 3), "unit": UNIT,
+        "n_gpus": n_gpus, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
+        "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": dict(config, P=rep.P, R=R, visible=visible, sort_bits=sort_bits),
-        "e2e": {"value": round(n_gpus * V * args.steps / (ms_e2e * 1e-3), 3), "unit": UNIT,
-                "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": (4 + 4) * V,
+        "impl": {"name": "ours", "cuda_streams_per_rank": rep.n_streams},
+        "e2e": {"value": round(total_frames / (ms_e2e * 1e-3), 3), "unit": UNIT,
+                "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": int(rep.d2h_bytes),
+                "result_read_back": "loss (4 B) per view" if training else "the rendered image (3xHxW f32) per frame",
                 "ms_per_step": round(ms_e2e / args.steps, 4)},
         "gpu_launches": launches,
         "dp": dp_info,
@@ -667,14 +912,11 @@ def main():
         "roofline": roofline,
         "stages": stages,
         "frame": {"algorithmic_bytes": int(frame_bytes),
-                  "ms": round(ms / (args.steps * V), 4),
-                  "hbm_frac": round(frame_bytes / (ms / (args.steps * V) * 1e-3) / 1e9 / peak, 4)},
+                  "ms": round(ms * n_gpus / total_frames, 4),
+                  "hbm_frac": round(frame_bytes / (ms * n_gpus / total_frames * 1e-3) / 1e9 / peak, 4)},
     }
     if n_gpus == 1 and not args.no_cpu_baseline:
-        fps, threads, frames = cpu_oracle_frames(make_workload(args.workload, 0, 1, "cpu"), args.cpu_baseline_seconds)
-        line["cpu_baseline"] = {"value": round(fps, 4), "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": "%d full frames of %s (LBS fwd + raster fwd + bwd) on the C/OpenMP oracle"
-                                          % (frames, args.workload)}
+        line["cpu_baseline"] = cpu_baseline_of(args.workload, args.cpu_baseline_seconds)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -685,17 +927,19 @@ def run_reference(args, config):
     """Reference arm: the unmodified reference through its own public API (rank 0 only)."""
     import refutil
 
-    n_human, n_scene, W, H, _ = WORKLOADS[args.workload]
-    base = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": config}
+    w = WORKLOADS[args.workload]
+    training = w["mode"] in ("train", "train_separate")
+    base = {"impl": "reference", "metric": metric_of(args.workload), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "higher_is_better": True, "scaling": config.get("scaling", "weak"),
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config}
+    base["scaling"] = "strong" if w["mode"] == "animation" or args.scaling == "strong" else "weak"
     if torch.cuda.is_available() and refutil.ref_available():
         device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
         torch.cuda.set_device(device)
-        module, lbs_impl = reference_impl()
         V = args.views_per_rank
         wl = make_workload(args.workload, 0, 1, device, views=V)
-        rep = Replica(wl, device, module, lbs_impl)
+        rep = Replica(wl, device, reference_impl())
+        V = rep.views
         for _ in range(max(args.warmup, 3)):
             rep.step_resident()
         sampler = ClockSampler(device.index or 0)
@@ -705,33 +949,34 @@ def run_reference(args, config):
             rep.step_e2e()
         rep.drain_e2e()
         rep.losses.clear()
+        rep.images_read = 0
         ms_e2e = timed_loop(rep.step_e2e, args.steps, device, lambda: None, finish=rep.drain_e2e)
-        assert len(rep.losses) == args.steps * V, "e2e: a loss was not read back"
+        assert (len(rep.losses) if training else rep.images_read) == args.steps * V, "e2e: a result was not read back"
         clocks = sampler.stop()
         v = V * args.steps / (ms * 1e-3)
         ve = V * args.steps / (ms_e2e * 1e-3)
         base.update({
             "value": round(v, 3), "ms_per_step": round(ms / args.steps, 4), "clocks": clocks,
             "e2e": {"value": round(ve, 3), "unit": UNIT, "h2d_bytes_per_step": int(rep.h2d_bytes),
-                    "d2h_bytes_per_step": 8 * V, "ms_per_step": round(ms_e2e / args.steps, 4)},
+                    "d2h_bytes_per_step": int(rep.d2h_bytes), "ms_per_step": round(ms_e2e / args.steps, 4)},
             "cpu_baseline": {"value": round(ve, 3), "unit": UNIT, "cores": 0, "kind": "reference",
                              "sample": "the reference has no CPU rasterizer: this is its own CUDA build "
                                        "(oracle/_ref, unmodified sources, sm_100) + its PyTorch LBS chain on the "
                                        "same B200, full frames of " + args.workload},
             "reference_device": "cuda",
         })
-        base["config"] = dict(config, P=rep.P,
-                              R=int(round(sum(int(nd.num_rendered) for nd in rep.last_nodes) / V)))
+        base["config"] = dict(config, P=rep.P)
+        if training:
+            base["config"]["R"] = int(round(sum(int(nd.num_rendered) for nd in rep.last_nodes) / V))
         print(json.dumps(base), flush=True)
         return 0
     # no GPU or no reference build: the CPU oracle port on the host cores
-    fps, threads, frames = cpu_oracle_frames(make_workload(args.workload, 0, 1, "cpu"),
-                                             max(10.0, args.cpu_baseline_seconds), min_frames=max(args.steps, 2))
+    cb = cpu_baseline_of(args.workload, max(10.0, args.cpu_baseline_seconds), min_frames=max(args.steps, 2))
+    fps = cb["value"]
     base.update({
-        "value": round(fps, 4), "ms_per_step": round(1e3 / fps, 3),
-        "e2e": {"value": round(fps, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "cpu_baseline": {"value": round(fps, 4), "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": "%d full frames on the C/OpenMP oracle port" % frames},
+        "value": fps, "ms_per_step": round(1e3 / fps, 3),
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "cpu_baseline": cb,
         "reference_device": "cpu",
     })
     print(json.dumps(base), flush=True)
