@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 7
+#define HUGS_B200_ABI_VERSION 8
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -443,6 +443,37 @@ int hugs_b200_rasterize_backward_seg2_layer(int D, int M, int R, const float* ba
                                             int debug, hugs_b200_stream_t stream, int n_layer,
                                             const float* background_layer, char* layer_buffer, size_t layer_bytes,
                                             const float* dL_dpix_layer);
+
+
+/* ---- gradient sinks (view-batched training) ------------------------------------------------------------
+ * The reference renders one view per optimiser step (hugs/trainer/gs_trainer.py:226-290); torch's
+ * AccumulateGrad adds every further view's gradients to .grad with one elementwise kernel per parameter.
+ * Here the per-Gaussian backward can deliver a segment's rows of a gradient straight into the parameter's
+ * accumulation buffer: entry [s] != NULL means "rows of segment s (0: [0,P0), 1: [P0,P0+P1)) of this
+ * gradient are ADDED, for visible Gaussians only, to this [P_s, ...] buffer (16-byte aligned) and the
+ * segment's rows of the joint output array are left unwritten".  The caller zeroes the buffers at the
+ * start of a step; several views may add concurrently from different streams. */
+typedef struct hugs_b200_grad_sinks {
+    float* means3D[2];    /* [P_s,3]   */
+    float* sh[2];         /* [P_s,M,3] */
+    float* opacity[2];    /* [P_s,1]   */
+    float* scales[2];     /* [P_s,3]   */
+    float* rotations[2];  /* [P_s,4]   */
+} hugs_b200_grad_sinks;
+/* hugs_b200_rasterize_backward_seg2_layer + optional sinks (NULL: none); dL_dpix_layer == NULL: no layer. */
+int hugs_b200_rasterize_backward_seg2_ex(int D, int M, int R, const float* background, int width, int height,
+                                         int P0, const float* means3D0, const float* shs0, const float* scales0,
+                                         const float* rotations0, int P1, const float* means3D1, const float* shs1,
+                                         const float* scales1, const float* rotations1, float scale_modifier,
+                                         const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                                         float tan_fovx, float tan_fovy, const int* radii, char* geom_buffer,
+                                         char* binning_buffer, size_t binning_bytes, char* image_buffer,
+                                         const float* dL_dpix, float* dL_dmean2D, float* dL_dconic,
+                                         float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
+                                         float* dL_dsh, float* dL_dscale, float* dL_drot, int debug,
+                                         hugs_b200_stream_t stream, int n_layer, const float* background_layer,
+                                         char* layer_buffer, size_t layer_bytes, const float* dL_dpix_layer,
+                                         const hugs_b200_grad_sinks* sinks);
 
 /* ---------------------------------------------------------------------------------------------
  * Densification statistics after a backward pass, one launch, no host sync.

@@ -140,6 +140,7 @@ GeomView carve_geom(char* base, int P) {
     g.dsort_temp = take<char>(p, g.dsort_temp_bytes);
     // appended after every exported offset
     g.grad_pack = take<float>(p, 8 * n);
+    g.grad_opac = take<float>(p, n);   // right behind grad_pack: one fill clears both
     g.rects = take<uint2>(p, n);
     g.st_touched = take<uint32_t>(p, n);
     g.pair_counts = take<uint32_t>(p, 2);
@@ -502,6 +503,7 @@ struct LayerBackward {
     const float* dL_dpix;
 };
 static thread_local const LayerBackward* tl_layer = nullptr;   // set only for the duration of a *_layer call
+static thread_local const hugs_b200_grad_sinks* tl_sinks = nullptr;   // likewise, for *_seg2_ex
 
 static GeomView geom_rows_from(const GeomView& g, int row0) {
     GeomView o = g;
@@ -834,13 +836,24 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
     // The blend backward accumulates with reductions into the packed per-Gaussian records (geometry
     // workspace) and into dL_dopacity, so both are cleared first (part of the stage's cost); the
     // per-Gaussian kernel below unpacks the records into dL_dmean2D / dL_dconic / dL_dcolor.
+    // Gradient sinks (two-segment calls only): a segment's rows of a gradient are ADDED to the caller's
+    // accumulation buffer by the per-Gaussian kernel.  dL/dopacity is produced by the blend backward, so with
+    // an opacity sink it goes through a scratch array of the geometry workspace first.
+    const hugs_b200_grad_sinks* sinks = tl_seg2 ? tl_sinks : nullptr;
+    const bool opac_scratch = sinks && (sinks->opacity[0] || sinks->opacity[1]);
+    float* const opac_target = opac_scratch ? geom.grad_opac : dL_dopacity;
     auto blend_backward = [&]() -> int {
-        HB_CUDA_OK(cudaMemsetAsync(geom.grad_pack, 0, sizeof(float) * 8 * (size_t)P, stream));
-        HB_CUDA_OK(cudaMemsetAsync(dL_dopacity, 0, sizeof(float) * (size_t)P, stream));
+        if (opac_scratch) {   // grad_pack and grad_opac are neighbours: one fill
+            const size_t span = (size_t)(reinterpret_cast<char*>(geom.grad_opac + P) - reinterpret_cast<char*>(geom.grad_pack));
+            HB_CUDA_OK(cudaMemsetAsync(geom.grad_pack, 0, span, stream));
+        } else {
+            HB_CUDA_OK(cudaMemsetAsync(geom.grad_pack, 0, sizeof(float) * 8 * (size_t)P, stream));
+            HB_CUDA_OK(cudaMemsetAsync(dL_dopacity, 0, sizeof(float) * (size_t)P, stream));
+        }
         if (R <= 0) return 0;
         return launch_render_backward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y, background,
                                       geom.means2D, geom.conic_opacity, color_ptr, stride, img.accum_alpha,
-                                      img.n_contrib, bin.hit_words, dL_dpix, geom.grad_pack, dL_dopacity, stream);
+                                      img.n_contrib, bin.hit_words, dL_dpix, geom.grad_pack, opac_target, stream);
     };
     HB_STAGE(blend_backward(), ST_RENDER_BWD);
     // The layer's blend backward: same kernel on the filtered lists, gradients into the layer's own packed
@@ -862,7 +875,7 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
             if (R <= 0 || L->n == 0) return 0;
             return launch_render_backward(lay.ranges, lay.list, width, height, cam.grid_x, cam.grid_y, L->background,
                                           geom.means2D, geom.conic_opacity, color_ptr, stride, lay.accum_alpha,
-                                          lay.n_contrib, lay.hit_words, L->dL_dpix, lay.grad_pack, dL_dopacity,
+                                          lay.n_contrib, lay.hit_words, L->dL_dpix, lay.grad_pack, opac_target,
                                           stream);
         };
         HB_STAGE(layer_backward(), ST_RENDER_BWD);
@@ -871,27 +884,46 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
     }
     if (const SecondSegment* s2 = tl_seg2) {
         const size_t r0 = (size_t)s2->P0;
-        if (s2->P0 > 0)
-            HB_STAGE(launch_preprocess_backward(s2->P0, D, M, means3D, radii, shs, geom.clamped, scales, rotations,
-                                                scale_modifier, nullptr, cam, geom.grad_pack, dL_dmean2D, dL_dconic,
-                                                dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
-                                                dL_dsh_accumulate != 0, stream, pack2, n2 < s2->P0 ? n2 : s2->P0),
+        for (int seg = 0; seg < 2; seg++) {
+            const int n = seg == 0 ? s2->P0 : P - s2->P0;
+            if (n <= 0) continue;
+            const size_t o = seg == 0 ? 0 : r0;   // first row of the segment in the joint arrays
+            PreBwdExtra ex;
+            ex.grad_pack2 = pack2 ? pack2 + 8 * o : nullptr;
+            ex.n2 = seg == 0 ? (n2 < s2->P0 ? n2 : s2->P0) : (n2 > s2->P0 ? n2 - s2->P0 : 0);
+            float* o_mean = dL_dmean3D + 3 * o;
+            float* o_scale = dL_dscale + 3 * o;
+            float* o_rot = dL_drot + 4 * o;
+            float* o_sh = dL_dsh + (size_t)M * 3 * o;
+            bool sh_acc = dL_dsh_accumulate != 0;
+            if (opac_scratch) {
+                ex.opac_scratch = geom.grad_opac + o;
+                ex.dL_dopacity = dL_dopacity + o;
+            }
+            if (sinks) {
+                if (sinks->means3D[seg]) { o_mean = sinks->means3D[seg]; ex.acc_mask |= kAccMean3D; }
+                if (sinks->scales[seg]) { o_scale = sinks->scales[seg]; ex.acc_mask |= kAccScale; }
+                if (sinks->rotations[seg]) { o_rot = sinks->rotations[seg]; ex.acc_mask |= kAccRot; }
+                if (sinks->opacity[seg]) { ex.dL_dopacity = sinks->opacity[seg]; ex.acc_mask |= kAccOpacity; }
+                if (sinks->sh[seg]) { o_sh = sinks->sh[seg]; sh_acc = true; }
+            }
+            HB_STAGE(launch_preprocess_backward(n, D, M, seg == 0 ? means3D : s2->means3D, radii + o,
+                                                seg == 0 ? shs : s2->shs, geom.clamped + o,
+                                                seg == 0 ? scales : s2->scales, seg == 0 ? rotations : s2->rotations,
+                                                scale_modifier, nullptr, cam, geom.grad_pack + 8 * o,
+                                                dL_dmean2D + 3 * o, dL_dconic + 4 * o, o_mean, dL_dcolor + 3 * o,
+                                                dL_dcov3D + 6 * o, o_sh, o_scale, o_rot, sh_acc, stream, &ex),
                      ST_PREPROCESS_BWD);
-        if (P - s2->P0 > 0)
-            HB_STAGE(launch_preprocess_backward(P - s2->P0, D, M, s2->means3D, radii + r0, s2->shs, geom.clamped + r0,
-                                                s2->scales, s2->rotations, scale_modifier, nullptr, cam,
-                                                geom.grad_pack + 8 * r0, dL_dmean2D + 3 * r0, dL_dconic + 4 * r0,
-                                                dL_dmean3D + 3 * r0,
-                                                dL_dcolor + 3 * r0, dL_dcov3D + 6 * r0, dL_dsh + (size_t)M * 3 * r0,
-                                                dL_dscale + 3 * r0, dL_drot + 4 * r0, dL_dsh_accumulate != 0, stream,
-                                                pack2 ? pack2 + 8 * r0 : nullptr, n2 > s2->P0 ? n2 - s2->P0 : 0),
-                     ST_PREPROCESS_BWD);
+        }
         return 0;
     }
+    PreBwdExtra ex1;
+    ex1.grad_pack2 = pack2;
+    ex1.n2 = n2;
     HB_STAGE(launch_preprocess_backward(P, D, M, means3D, radii, colors_precomp ? nullptr : shs, geom.clamped, scales,
                                         rotations, scale_modifier, cov3D_precomp, cam, geom.grad_pack, dL_dmean2D,
                                         dL_dconic, dL_dmean3D, dL_dcolor, dL_dcov3D, dL_dsh, dL_dscale, dL_drot,
-                                        dL_dsh_accumulate != 0, stream, pack2, n2),
+                                        dL_dsh_accumulate != 0, stream, &ex1),
              ST_PREPROCESS_BWD);
     return 0;
 }
@@ -1130,6 +1162,30 @@ int hugs_b200_rasterize_backward_seg2_layer(int D, int M, int R, const float* ba
         binning_buffer, binning_bytes, image_buffer, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D,
         dL_dcov3D, dL_dsh, dL_dscale, dL_drot, debug, stream);
     tl_layer = nullptr;
+    return rc;
+}
+
+int hugs_b200_rasterize_backward_seg2_ex(int D, int M, int R, const float* background, int width, int height,
+                                         int P0, const float* means3D0, const float* shs0, const float* scales0,
+                                         const float* rotations0, int P1, const float* means3D1, const float* shs1,
+                                         const float* scales1, const float* rotations1, float scale_modifier,
+                                         const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                                         float tan_fovx, float tan_fovy, const int* radii, char* geom_buffer,
+                                         char* binning_buffer, size_t binning_bytes, char* image_buffer,
+                                         const float* dL_dpix, float* dL_dmean2D, float* dL_dconic,
+                                         float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D, float* dL_dcov3D,
+                                         float* dL_dsh, float* dL_dscale, float* dL_drot, int debug,
+                                         hugs_b200_stream_t stream, int n_layer, const float* background_layer,
+                                         char* layer_buffer, size_t layer_bytes, const float* dL_dpix_layer,
+                                         const hugs_b200_grad_sinks* sinks) {
+    tl_sinks = sinks;
+    const int rc = hugs_b200_rasterize_backward_seg2_layer(
+        D, M, R, background, width, height, P0, means3D0, shs0, scales0, rotations0, P1, means3D1, shs1, scales1,
+        rotations1, scale_modifier, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy, radii, geom_buffer,
+        binning_buffer, binning_bytes, image_buffer, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_dmean3D,
+        dL_dcov3D, dL_dsh, dL_dscale, dL_drot, debug, stream, n_layer, background_layer, layer_buffer, layer_bytes,
+        dL_dpix_layer);
+    tl_sinks = nullptr;
     return rc;
 }
 

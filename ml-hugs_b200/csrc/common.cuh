@@ -61,6 +61,7 @@ struct GeomView {
     uint32_t* dsort_vals_tmp;
     char* dsort_temp;
     size_t dsort_temp_bytes;
+    float* grad_opac;         // [P] backward scratch: dL/dopacity when it is bound for a gradient sink
     float* grad_pack;         // [P][8] backward scratch: dL/d(colour 3, mean2D 2, conic 3), see render_backward.cu
     uint2* rects;             // tile rectangle of every Gaussian (x0 | x1 << 16, y0 | y1 << 16)
     uint32_t* st_touched;     // super-tiles its rectangle overlaps
@@ -190,13 +191,22 @@ int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int 
                            const uint32_t* n_contrib, const uint32_t* hit_words, const float* dL_dpix,
                            float* grad_pack /*[P,8], zeroed*/, float* dL_dopacity /*[P], zeroed*/,
                            cudaStream_t stream);
+// Optional inputs of the per-Gaussian backward: a second image's packed records (layer.cu) and gradient sinks.
+constexpr int kAccMean3D = 1, kAccScale = 2, kAccRot = 4, kAccOpacity = 8;
+struct PreBwdExtra {
+    const float* grad_pack2 = nullptr;  // [n2][8], rows [0, n2)
+    int n2 = 0;
+    int acc_mask = 0;                   // kAcc* bits: that output is ADDED for visible rows, culled rows untouched
+    const float* opac_scratch = nullptr;   // [P]: when set, dL/dopacity is taken from here and written / added to dL_dopacity
+    float* dL_dopacity = nullptr;
+};
 int launch_preprocess_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
                                const uint8_t* clamped, const float* scales, const float* rotations,
                                float scale_modifier, const float* cov3D_precomp, const Camera& cam,
                                const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                                float* dL_drot, bool sh_accumulate, cudaStream_t stream,
-                               const float* grad_pack2 = nullptr, int n2 = 0);
+                               const struct PreBwdExtra* extra = nullptr);
 int launch_layer_filter(int num_tiles, const uint2* ranges, const uint32_t* list, int n_layer, uint32_t* list_out,
                         uint2* ranges_out, cudaStream_t stream);
 

@@ -342,13 +342,18 @@ __global__ void __launch_bounds__(kLbsThreads)
             }
             __syncwarp();
         }
-        // flush dA for this frame (rows 0..2 of each joint's 4x4; the bottom row gets no gradient)
+        // flush dA for this frame (rows 0..2 of each joint's 4x4; the bottom row gets no gradient): the
+        // CTA's warps are summed in shared memory first, then ONE atomic per entry and CTA.  (One atomic
+        // per entry and WARP -- 1.4 M reductions onto 288 addresses when every Gaussian has a gradient --
+        // made this kernel 4x slower on views where the human is unoccluded: same-address atomics
+        // serialise at the L2.)
+        __syncthreads();   // every warp is done with s_dT
+        float* const s_red = &s_dT[0][0][0];   // [warps][kMaxJoints][12], exactly s_dT's size
         if ((int)lane < J) {
 #pragma unroll
-            for (int k = 0; k < 12; k++)
-                if (accA[k] != 0.f) atomicAdd(dA + ((size_t)f * J + lane) * 16 + k, accA[k]);
+            for (int k = 0; k < 12; k++) s_red[(warp * kMaxJoints + lane) * 12 + k] = accA[k];
         }
-        // translation / scale gradients: warp reduce, one atomic per warp
+        // translation / scale gradients: warp reduce
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
             acc_tr[0] += __shfl_xor_sync(0xffffffffu, acc_tr[0], d);
@@ -356,13 +361,30 @@ __global__ void __launch_bounds__(kLbsThreads)
             acc_tr[2] += __shfl_xor_sync(0xffffffffu, acc_tr[2], d);
             acc_scale += __shfl_xor_sync(0xffffffffu, acc_scale, d);
         }
+        constexpr int kWarps = kLbsThreads / 32;
+        float* const s_tail = &s_w[0][0][0];   // [warps][4]
         if (lane == 0) {
-            if (d_transl != nullptr) {
-                atomicAdd(d_transl + 3 * f + 0, acc_tr[0]);
-                atomicAdd(d_transl + 3 * f + 1, acc_tr[1]);
-                atomicAdd(d_transl + 3 * f + 2, acc_tr[2]);
+            s_tail[warp * 4 + 0] = acc_tr[0];
+            s_tail[warp * 4 + 1] = acc_tr[1];
+            s_tail[warp * 4 + 2] = acc_tr[2];
+            s_tail[warp * 4 + 3] = acc_scale;
+        }
+        __syncthreads();
+        for (int e = threadIdx.x; e < J * 12; e += kLbsThreads) {
+            float v = 0.f;
+#pragma unroll
+            for (int wp = 0; wp < kWarps; wp++) v += s_red[(wp * kMaxJoints + e / 12) * 12 + e % 12];
+            if (v != 0.f) atomicAdd(dA + ((size_t)f * J + e / 12) * 16 + e % 12, v);
+        }
+        if (threadIdx.x < 4) {
+            float v = 0.f;
+#pragma unroll
+            for (int wp = 0; wp < kWarps; wp++) v += s_tail[wp * 4 + threadIdx.x];
+            if (threadIdx.x < 3) {
+                if (d_transl != nullptr) atomicAdd(d_transl + 3 * f + threadIdx.x, v);
+            } else if (d_smpl_scale != nullptr) {
+                atomicAdd(d_smpl_scale, v);
             }
-            if (d_smpl_scale != nullptr) atomicAdd(d_smpl_scale, acc_scale);
         }
     }
 }

@@ -32,6 +32,9 @@ struct PreBwdArgs {
     const float* grad_pack;   // [P,8]  (input: accumulated by the blend backward) colour 3, mean2D 2, conic 3
     const float* grad_pack2;  // [n2,8] or null: a second image's share for the rows below n2 (layer.cu)
     int n2;
+    int acc_mask;             // kAcc* bits: ADD the visible rows of that output into its buffer, leave culled rows alone
+    const float* opac_scratch;  // [P] or null: the blend backward's dL/dopacity, moved / added to dL_dopacity here
+    float* dL_dopacity;
     float* dL_dmean2D;        // [P,3]  (output: unpacked record, z = 0)
     float* dL_dconic;         // [P,4]  (output: unpacked record, (x, y, 0, w))
     float* dL_dmean3D;        // [P,3]
@@ -43,6 +46,24 @@ struct PreBwdArgs {
     int sh_vec4;
     int sh_accumulate;  // add visible rows of dL_dsh into the existing contents, leave culled rows alone
 };
+
+// Gradient sinks (view-batched training): an output with its kAcc bit set is a leaf parameter's accumulation
+// buffer shared by all views of the step; fire-and-forget reductions at the L2 instead of a store, and no
+// zero rows for culled Gaussians.
+__device__ __forceinline__ void red_f1(float* p, float v) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void put3(float* p, float x, float y, float z, bool acc) {
+    if (acc) {
+        red_f1(p, x);
+        red_f1(p + 1, y);
+        red_f1(p + 2, z);
+    } else {
+        p[0] = x;
+        p[1] = y;
+        p[2] = z;
+    }
+}
 
 __device__ __forceinline__ void store_sh_grad(const PreBwdArgs& a, int idx, const float* g /*48*/) {
     if (a.sh_vec4) {
@@ -209,8 +230,19 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
     float* out_cov = a.dL_dcov3D + 6 * (size_t)idx;
     const bool has_scale = (a.cov3D_precomp == nullptr);
 
+    const bool acc_mean = (a.acc_mask & kAccMean3D) != 0, acc_scale = (a.acc_mask & kAccScale) != 0,
+               acc_rot = (a.acc_mask & kAccRot) != 0, acc_opac = (a.acc_mask & kAccOpacity) != 0;
+    if (valid && a.opac_scratch != nullptr) {
+        if (vis) {
+            const float v = __ldg(a.opac_scratch + idx);
+            if (acc_opac) red_f1(a.dL_dopacity + idx, v);
+            else a.dL_dopacity[idx] = v;
+        } else if (!acc_opac) {
+            a.dL_dopacity[idx] = 0.f;
+        }
+    }
     if (valid && !vis) {
-        out_mean[0] = out_mean[1] = out_mean[2] = 0.f;
+        if (!acc_mean) out_mean[0] = out_mean[1] = out_mean[2] = 0.f;
         a.dL_dmean2D[3 * (size_t)idx + 0] = 0.f;
         a.dL_dmean2D[3 * (size_t)idx + 1] = 0.f;
         a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
@@ -220,12 +252,12 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
         a.dL_dcolor[3 * (size_t)idx + 2] = 0.f;
 #pragma unroll
         for (int i = 0; i < 6; i++) out_cov[i] = 0.f;
-        if (a.dL_dscale != nullptr) {
+        if (a.dL_dscale != nullptr && !acc_scale) {
             a.dL_dscale[3 * (size_t)idx + 0] = 0.f;
             a.dL_dscale[3 * (size_t)idx + 1] = 0.f;
             a.dL_dscale[3 * (size_t)idx + 2] = 0.f;
         }
-        if (a.dL_drot != nullptr) reinterpret_cast<float4*>(a.dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.dL_drot != nullptr && !acc_rot) reinterpret_cast<float4*>(a.dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 
     // state that crosses the cooperative SH phase
@@ -467,9 +499,7 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
     }
 
     if (!vis) return;
-    out_mean[0] = dmean_x;
-    out_mean[1] = dmean_y;
-    out_mean[2] = dmean_z;
+    put3(out_mean, dmean_x, dmean_y, dmean_z, acc_mean);
 
     // ---- cov3D backward (backward.cu:278-341) --------------------------------------------------
     if (has_scale && a.dL_dscale != nullptr) {
@@ -499,9 +529,7 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
         float dsc[3];
 #pragma unroll
         for (int k = 0; k < 3; k++) dsc[k] = R[0][k] * dM[0][k] + R[1][k] * dM[1][k] + R[2][k] * dM[2][k];
-        a.dL_dscale[3 * (size_t)idx + 0] = dsc[0];
-        a.dL_dscale[3 * (size_t)idx + 1] = dsc[1];
-        a.dL_dscale[3 * (size_t)idx + 2] = dsc[2];
+        put3(a.dL_dscale + 3 * (size_t)idx, dsc[0], dsc[1], dsc[2], acc_scale);
         // dL_dMt[k] *= s[k]   ->  Mt[c][r] = dM[r][c] * s[c]
         float Mt[3][3];
 #pragma unroll
@@ -516,14 +544,20 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
                4.f * qy * (Mt[2][2] + Mt[0][0]);
         dq.w = 2.f * qr * (Mt[0][1] - Mt[1][0]) + 2.f * qx * (Mt[2][0] + Mt[0][2]) + 2.f * qy * (Mt[1][2] + Mt[2][1]) -
                4.f * qz * (Mt[1][1] + Mt[0][0]);
-        reinterpret_cast<float4*>(a.dL_drot)[idx] = dq;
+        if (acc_rot) {
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(reinterpret_cast<float4*>(a.dL_drot) + idx),
+                         "f"(dq.x), "f"(dq.y), "f"(dq.z), "f"(dq.w)
+                         : "memory");
+        } else {
+            reinterpret_cast<float4*>(a.dL_drot)[idx] = dq;
+        }
     } else {
-        if (a.dL_dscale != nullptr) {
+        if (a.dL_dscale != nullptr && !acc_scale) {
             a.dL_dscale[3 * (size_t)idx + 0] = 0.f;
             a.dL_dscale[3 * (size_t)idx + 1] = 0.f;
             a.dL_dscale[3 * (size_t)idx + 2] = 0.f;
         }
-        if (a.dL_drot != nullptr) reinterpret_cast<float4*>(a.dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.dL_drot != nullptr && !acc_rot) reinterpret_cast<float4*>(a.dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
 }  // namespace
@@ -534,7 +568,9 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                               bool sh_accumulate, cudaStream_t stream, const float* grad_pack2, int n2) {
+                               bool sh_accumulate, cudaStream_t stream, const PreBwdExtra* extra) {
+    const float* grad_pack2 = extra ? extra->grad_pack2 : nullptr;
+    const int n2 = extra ? extra->n2 : 0;
     PreBwdArgs a;
     a.P = P;
     a.D = D;
@@ -557,6 +593,9 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
     a.grad_pack = grad_pack;
     a.grad_pack2 = n2 > 0 ? grad_pack2 : nullptr;
     a.n2 = n2;
+    a.acc_mask = extra ? extra->acc_mask : 0;
+    a.opac_scratch = extra ? extra->opac_scratch : nullptr;
+    a.dL_dopacity = extra ? extra->dL_dopacity : nullptr;
     a.dL_dmean2D = dL_dmean2D;
     a.dL_dconic = dL_dconic;
     a.dL_dmean3D = dL_dmean3D;

@@ -13,12 +13,16 @@ from .rasterizer import (
     ShGradSink,
     attach_sh_grad_sink,
     detach_sh_grad_sink,
+    GradSink,
+    attach_grad_sink,
+    detach_grad_sink,
 )
 from .lbs import lbs_extra, deform_gaussians, lbs_deform_frames, matrix_to_quaternion
 
 __all__ = [
     "GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
     "rasterize_gaussians_forward", "rasterize_gaussians_backward", "mark_visible",
-    "ShGradSink", "attach_sh_grad_sink", "detach_sh_grad_sink",
+    "ShGradSink", "attach_sh_grad_sink", "detach_sh_grad_sink", "GradSink", "attach_grad_sink",
+    "detach_grad_sink",
     "lbs_extra", "deform_gaussians", "lbs_deform_frames", "matrix_to_quaternion",
 ]

@@ -138,6 +138,16 @@ rasterize_backward_layer = _sig("hugs_b200_rasterize_backward_layer", i32,
 rasterize_backward_seg2_layer = _sig("hugs_b200_rasterize_backward_seg2_layer", i32,
                                      list(rasterize_backward_seg2.argtypes) + _LAYER_TAIL)
 
+
+
+class GradSinks(C.Structure):
+    """hugs_b200_grad_sinks: per segment, the accumulation buffer a gradient is ADDED to (NULL: none)."""
+    _fields_ = [(n, C.c_void_p * 2) for n in ("means3D", "sh", "opacity", "scales", "rotations")]
+
+
+rasterize_backward_seg2_ex = _sig("hugs_b200_rasterize_backward_seg2_ex", i32,
+                                  list(rasterize_backward_seg2.argtypes) + _LAYER_TAIL + [C.POINTER(GradSinks)])
+
 l1_ssim_forward = _sig("hugs_b200_l1_ssim_forward", i32, [i32, i32, i32, fp, fp, fp, fp, fp])
 l1_ssim_backward = _sig("hugs_b200_l1_ssim_backward", i32, [i32, i32, i32, fp, fp, fp, fp, fp, fp])
 
@@ -206,7 +216,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_triplane_forward", "hugs_b200_triplane_backward",
     "hugs_b200_rasterize_forward_seg2", "hugs_b200_rasterize_backward_seg2",
     "hugs_b200_layer_bytes", "hugs_b200_layer_layout_of", "hugs_b200_layer_forward", "hugs_b200_rasterize_backward_layer",
-    "hugs_b200_rasterize_backward_seg2_layer",
+    "hugs_b200_rasterize_backward_seg2_layer", "hugs_b200_rasterize_backward_seg2_ex",
 ]
 
 

@@ -52,6 +52,14 @@ class FlatGradBuffer:
     def nbytes(self) -> int:
         return self.flat.numel() * 4
 
+    def attach_sinks(self, names: Iterable[str]):
+        """Let the rasterizer's backward ADD the gradients of these parameters (inputs of a two-segment
+        render) straight into their slices of the flat buffer (hugs_b200.attach_grad_sink): no per-view
+        AccumulateGrad kernels, and what the allreduce works on is complete when the last backward returns."""
+        from .rasterizer import attach_grad_sink
+        for n in names:
+            attach_grad_sink(self.params[n], self.params[n].grad)
+
     def zero_(self):
         self.flat.zero_()
 

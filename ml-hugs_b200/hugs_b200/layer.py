@@ -140,6 +140,8 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
         if not all(x.is_cuda for x in t):
             raise RuntimeError("hugs_b200 has no CPU path: segment tensors must be CUDA tensors")
         ctx.set_materialize_grads(False)
+        from .segments import sinks_of
+        ctx.sinks, ctx.sunk = sinks_of(a, b)
         device = a[0].device
         a = [_f32c(x, device) for x in a]
         b = [_f32c(x, device) for x in b]
@@ -177,17 +179,18 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
         dL = _f32c(grad_color, device) if grad_color is not None else torch.zeros(3, H, W, device=device)
         dLl = _f32c(grad_layer, device) if grad_layer is not None else None
         with torch.cuda.device(device):
-            rc = N.rasterize_backward_seg2_layer(
+            rc = N.rasterize_backward_seg2_ex(
                 int(s.sh_degree), M, int(ctx.num_rendered), N.ptr(bg), W, H,
                 P0, N.ptr(a[0]), N.ptr(a[1]), N.ptr(a[3]), N.ptr(a[4]),
                 P1, N.ptr(b[0]), N.ptr(b[1]), N.ptr(b[3]), N.ptr(b[4]),
                 float(s.scale_modifier), N.ptr(view), N.ptr(proj), N.ptr(campos), float(s.tanfovx), float(s.tanfovy),
                 radii.data_ptr(), N.ptr(geom), N.ptr(binning), int(binning.numel()), N.ptr(img), dL.data_ptr(),
                 *_grad_ptrs(g), int(bool(s.debug)), _stream_ptr(device),
-                n_layer, N.ptr(bg_layer), layer.data_ptr(), int(layer.numel()), N.ptr(dLl))
+                n_layer, N.ptr(bg_layer), layer.data_ptr(), int(layer.numel()), N.ptr(dLl),
+                C.byref(ctx.sinks) if ctx.sinks is not None else None)
         N.check(rc, "rasterize_two_segments_with_layer backward")
-        order = ("means3D", "sh", "opacity", "scales", "rotations")
-        return (g["means2D"], None, None, None, *[g[k][:P0] for k in order], *[g[k][P0:] for k in order])
+        from .segments import segment_grads
+        return (g["means2D"], None, None, None, *segment_grads(g, P0, ctx.sunk))
 
 
 def rasterize_two_segments_with_layer(segment0, segment1, means2D, raster_settings, bg_layer, n_layer=None):

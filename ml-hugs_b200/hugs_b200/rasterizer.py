@@ -282,6 +282,44 @@ def _sink_of(sh):
     return sink if (sink is not None and sink.param is sh) else None
 
 
+class GradSink:
+    """Where the gradient of ONE leaf parameter of a two-segment render goes during view-batched training
+    (means3D / shs / opacities / scales / rotations of either segment): the per-Gaussian backward ADDS the
+    rows of the visible Gaussians straight into ``buffer`` (hugs_b200_grad_sinks) and autograd sees no
+    gradient for that input -- no zero rows written, no AccumulateGrad kernel per view and parameter.
+    The owner zeroes ``buffer`` at the start of a step (``hugs_b200.dp.FlatGradBuffer.zero_``)."""
+
+    def __init__(self, param, buffer=None):
+        if not (param.is_leaf and param.dtype == torch.float32 and param.is_contiguous() and param.is_cuda):
+            raise ValueError("a gradient sink needs a contiguous float32 CUDA leaf tensor")
+        self.param = param
+        self.buffer = torch.zeros_like(param) if buffer is None else buffer
+        b = self.buffer
+        if (tuple(b.shape) != tuple(param.shape) or b.dtype != torch.float32 or b.device != param.device
+                or not b.is_contiguous() or b.data_ptr() % 16):
+            raise ValueError("sink buffer must match the parameter (contiguous float32, same shape and device, "
+                             "16-byte aligned)")
+        param.grad = self.buffer
+
+
+_grad_sinks = {}
+
+
+def attach_grad_sink(param, buffer=None):
+    sink = GradSink(param, buffer)
+    _grad_sinks[id(param)] = sink
+    return sink
+
+
+def detach_grad_sink(param):
+    _grad_sinks.pop(id(param), None)
+
+
+def grad_sink_of(t):
+    sink = _grad_sinks.get(id(t))
+    return sink if (sink is not None and sink.param is t) else None
+
+
 def rasterize_gaussians(
     means3D,
     means2D,

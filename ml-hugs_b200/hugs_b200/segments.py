@@ -13,9 +13,24 @@ import ctypes as C
 import torch
 
 from . import _native as N
-from .rasterizer import _Workspace, _f32c, _stream_ptr
+from .rasterizer import _Workspace, _f32c, _stream_ptr, grad_sink_of
 
 _NAMES = ("means3D", "shs", "opacities", "scales", "rotations")
+_SINK_FIELDS = ("means3D", "sh", "opacity", "scales", "rotations")   # hugs_b200_grad_sinks, in _NAMES order
+
+
+def sinks_of(raw_a, raw_b):
+    """(GradSinks struct or None, [10 bools]) for the raw input tensors of the two segments: an input that
+    has a gradient sink attached (hugs_b200.attach_grad_sink) gets its gradient delivered there."""
+    st, flags, any_sink = N.GradSinks(), [], False
+    for seg, raw in enumerate((raw_a, raw_b)):
+        for field, t in zip(_SINK_FIELDS, raw):
+            sink = grad_sink_of(t)
+            flags.append(sink is not None)
+            if sink is not None:
+                getattr(st, field)[seg] = sink.buffer.data_ptr()
+                any_sink = True
+    return (st if any_sink else None), flags
 
 
 class _RasterizeTwoSegments(torch.autograd.Function):
@@ -24,6 +39,7 @@ class _RasterizeTwoSegments(torch.autograd.Function):
         a, b = t[:5], t[5:]
         if not all(x.is_cuda for x in t):
             raise RuntimeError("hugs_b200 has no CPU path: segment tensors must be CUDA tensors")
+        ctx.sinks, ctx.sunk = sinks_of(a, b)
         device = a[0].device
         a = [_f32c(x, device) for x in a]
         b = [_f32c(x, device) for x in b]
@@ -81,7 +97,7 @@ class _RasterizeTwoSegments(torch.autograd.Function):
         if P > 0:
             dL = _f32c(grad_color, device)
             with torch.cuda.device(device):
-                rc = N.rasterize_backward_seg2(
+                rc = N.rasterize_backward_seg2_ex(
                     int(s.sh_degree), M, int(ctx.num_rendered), N.ptr(bg), W, H,
                     P0, N.ptr(a[0]), N.ptr(a[1]), N.ptr(a[3]), N.ptr(a[4]),
                     P1, N.ptr(b[0]), N.ptr(b[1]), N.ptr(b[3]), N.ptr(b[4]),
@@ -91,12 +107,17 @@ class _RasterizeTwoSegments(torch.autograd.Function):
                     dL.data_ptr(),
                     g["means2D"].data_ptr(), g["conic"].data_ptr(), g["opacity"].data_ptr(), g["colors"].data_ptr(),
                     g["means3D"].data_ptr(), g["cov3D"].data_ptr(), g["sh"].data_ptr(), g["scales"].data_ptr(),
-                    g["rotations"].data_ptr(), int(bool(s.debug)), _stream_ptr(device))
+                    g["rotations"].data_ptr(), int(bool(s.debug)), _stream_ptr(device),
+                    0, None, None, 0, None, C.byref(ctx.sinks) if ctx.sinks is not None else None)
             N.check(rc, "rasterize_two_segments backward")
-        order = ("means3D", "sh", "opacity", "scales", "rotations")
-        seg0 = [g[k][:P0] for k in order]
-        seg1 = [g[k][P0:] for k in order]
-        return (g["means2D"], None, *seg0, *seg1)
+        return (g["means2D"], None, *segment_grads(g, P0, ctx.sunk))
+
+
+def segment_grads(g, P0, sunk):
+    """The ten per-segment input gradients as views of the joint arrays; None where a sink took delivery."""
+    order = ("means3D", "sh", "opacity", "scales", "rotations")
+    out = [g[k][:P0] for k in order] + [g[k][P0:] for k in order]
+    return [None if s else v for v, s in zip(out, sunk)]
 
 
 def rasterize_two_segments(segment0, segment1, means2D, raster_settings):
