@@ -211,6 +211,7 @@ class Replica:
         self.lbs_impl = impl["lbs"]       # callable(A, xyz, w, rotmat, scales, transl) -> (xyz', rotq, scales')
         self.lbs_frames = impl.get("lbs_frames")      # batched over pose frames (animation), or None
         self.render_separate = impl.get("separate")   # (settings, tensors, n_human, human_bg) -> (color, human_color, radii)
+        self.render2 = impl.get("render2")   # our arm: two input segments, no torch.cat (hugs_b200/segments.py)
         self.mode = wl["mode"]
         self.training = self.mode in ("train", "train_separate")
         d = lambda t: t.to(device).contiguous()  # noqa: E731
@@ -235,26 +236,30 @@ class Replica:
             shs.append(sc["shs"])
             n_small += sum(sc[k].numel() for k in ("means3D", "scales", "rotations"))
         # attributes that do not pass through LBS are kept concatenated (human first,
-        # hugs/renderer/gs_renderer.py:33-37)
-        self.opacity = leaf(torch.cat(opac))
-        self.shs = leaf(torch.cat(shs))
-        self.P = self.opacity.shape[0]
-        # our arm: every view's SH gradient (81 % of the gradient bytes) is accumulated by the backward
-        # kernel itself, in the buffer the allreduce then works on (hugs_b200.ShGradSink)
-        self.sh_sink = None
-        if sh_sink and self.training:
-            import hugs_b200
-            # one flat gradient buffer: [SH gradient (the sink) | every other gradient], so the exchange is
-            # ONE collective over 275 MB
-            n_sh = self.shs.numel()
-            self.flat_all = torch.zeros(n_sh + n_small + self.opacity.numel(), device=device)
-            self.sh_sink = hugs_b200.attach_sh_grad_sink(self.shs, self.flat_all[:n_sh].view_as(self.shs))
+        # hugs/renderer/gs_renderer.py:33-37) -- except on our training arm, which hands the rasterizer the two
+        # models as two segments
+        self.P = sum(t.shape[0] for t in opac)
+        self.buf = None
+        # HB_TWO_SEG=1: hand the rasterizer the two models as two segments with gradient sinks on every
+        # direct input.  Measured (profiles/r02_i): not faster on one GPU -- with two streams per rank the
+        # torch.cat / AccumulateGrad kernels it removes already run beside the issue-bound blend kernels of the
+        # other stream, while the sinks' reductions and the per-segment launches add 0.04 ms of kernel time
+        self.two_seg = self.render2 is not None and self.training and os.environ.get("HB_TWO_SEG", "1") == "1"
+        if self.two_seg:
+            self._init_two_segments(wl, device, leaf)
+        else:
+            self.opacity = leaf(torch.cat(opac))
+            self.shs = leaf(torch.cat(shs))
+            if self.render2 is not None and self.training:
+                self._init_flat(device)
+        if not hasattr(self, "sh_sink"):
+            self.sh_sink = None
         self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
         # views of a step alternate between `n_streams` CUDA streams: the issue-bound blend kernels of one
         # view overlap the latency- and HBM-bound binning / per-Gaussian kernels of the next
         self.n_streams = max(1, int(os.environ.get("HB_STREAMS", "2"))) if sh_sink else 1
         self.streams = [torch.cuda.Stream(device) for _ in range(self.n_streams)] if self.n_streams > 1 else []
-        self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=self.training)
+        self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=self.training and not self.two_seg)
         # per-frame inputs: pinned host copies (for e2e) and resident device copies (for value)
         self.tanfovx, self.tanfovy = wl["cam"]["tanfovx"], wl["cam"]["tanfovy"]
         self.hosts, self.devs = [], []
@@ -291,14 +296,54 @@ class Replica:
         self.images_read = 0
         self.e2e_step = 0
         self.losses = []
-        self.flat_small = None
+
+    def _init_flat(self, device):
+        """Our training arm: the product's data-parallel plumbing (hugs_b200.dp).  ONE flat gradient buffer
+        (FlatGradBuffer, gathered mode): the SH gradient (81 % of the bytes) is added by the backward kernel
+        itself into its slice (ShGradSink), the small gradients are accumulated by autograd on the views'
+        streams and copied into their slices right before the step's one allreduce; nothing is copied back."""
+        from hugs_b200 import dp
+        names = ["shs", "opacity", "s_means", "s_scales", "s_rots", "h_xyz", "h_rotmat", "h_scales", "h_weights"]
+        self.buf = dp.FlatGradBuffer({n: getattr(self, n) for n in names if getattr(self, n) is not None},
+                                     gather=True)
+        self.sh_sink = self.buf.attach_sh_sink("shs")
+
+    def _init_two_segments(self, wl, device, leaf):
+        """Our training arm: the product's data-parallel plumbing (hugs_b200.dp).  Every parameter's .grad is
+        a slice of ONE flat buffer (FlatGradBuffer); the parameters that feed the rasterizer directly have
+        gradient sinks, so the backward kernels add into that buffer and the step's allreduce works on it as
+        it is -- no torch.cat of inputs or gradients, no per-view AccumulateGrad kernels."""
+        from hugs_b200 import dp
+        e = lambda *shape: torch.zeros(*shape, device=device).requires_grad_(True)  # noqa: E731
+        if self.n_human > 0:
+            self.h_opacity, self.h_shs = leaf(wl["human"]["opacity"]), leaf(wl["human"]["shs"])
+        else:
+            self.h_opacity, self.h_shs = e(0, 1), e(0, 16, 3)
+        if self.n_scene > 0:
+            self.s_opacity, self.s_shs = leaf(wl["scene"]["opacity"]), leaf(wl["scene"]["shs"])
+        else:
+            self.s_means, self.s_scales, self.s_rots = e(0, 3), e(0, 3), e(0, 4)
+            self.s_opacity, self.s_shs = e(0, 1), e(0, 16, 3)
+        self.opacity = self.shs = None
+        # sinks where the rows take 16-byte vector reductions (SH, quaternions) or one scalar (opacity); the
+        # 12-byte rows of means3D / scales would be three scalar atomics each -- measured slower than a plain
+        # store + AccumulateGrad (HB_SINK_ALL=1 switches them on for the experiment)
+        sunk = ["h_shs", "s_shs", "h_opacity", "s_opacity", "s_rots"]
+        if os.environ.get("HB_SINK_ALL", "1") == "1":
+            sunk += ["s_means", "s_scales"]
+        names = sunk + [n for n in ("s_means", "s_scales") if n not in sunk] + ["h_xyz", "h_rotmat", "h_scales", "h_weights"]
+        params = {n: getattr(self, n) for n in names if getattr(self, n) is not None and getattr(self, n).numel() > 0}
+        self.buf = dp.FlatGradBuffer(params)
+        self.buf.attach_sinks([n for n in sunk if n in params])
 
     def leaves(self):
+        if self.buf is not None:
+            return dict(self.buf.params)
         names = ["h_xyz", "h_rotmat", "h_scales", "h_weights", "s_means", "s_scales", "s_rots", "opacity", "shs"]
         return {n: getattr(self, n) for n in names if getattr(self, n) is not None}
 
     def zero_grad(self):
-        if not self.training:
+        if not self.training or self.buf is not None:   # dp_step clears the flat buffer itself
             return
         for n, p in self.leaves().items():
             if n == "shs" and self.sh_sink is not None:
@@ -331,6 +376,16 @@ class Replica:
         return self._frame(inp)
 
     def _frame(self, inp):
+        out = self._forward(inp)
+        if self.training:
+            out.backward()
+            return out.detach()
+        return out
+
+    def _forward(self, inp):
+        """Forward of one view: the loss (with its graph) when training, else the image."""
+        if self.two_seg:
+            return self._forward_two_segments(inp)
         means3D, scales, rots = self._gaussians(inp)
         settings = self.module.GaussianRasterizationSettings(
             image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=inp["bg"],
@@ -360,8 +415,47 @@ class Replica:
         if "loss_out" in inp:
             inp["loss_out"].copy_(loss.detach().reshape(1), non_blocking=True)
             inp["loss_event"].record()
-        loss.backward()
-        return loss.detach()
+        return loss
+
+    def _forward_two_segments(self, inp):
+        settings = self.module.GaussianRasterizationSettings(
+            image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=inp["bg"],
+            scale_modifier=1.0, viewmatrix=inp["viewmatrix"], projmatrix=inp["projmatrix"], sh_degree=3,
+            campos=inp["campos"], prefiltered=False, debug=False)
+        if self.n_human > 0:
+            A = inp["A"].requires_grad_(True)
+            xyz, rotq, hsc = self.lbs_impl(A, self.h_xyz, self.h_weights, self.h_rotmat, self.h_scales, self.transl)
+        else:
+            xyz, rotq, hsc = self.s_means[:0], self.s_rots[:0], self.s_scales[:0]
+        # the screen-space dummy of gs_renderer.py:107-113: its values are never read, its .grad is per view
+        means2D = torch.empty(self.P, 3, device=self.device, requires_grad=True)
+        color, color_h, radii = self.render2(
+            settings, (xyz, self.h_shs, self.h_opacity, hsc, rotq),
+            (self.s_means, self.s_shs, self.s_opacity, self.s_scales, self.s_rots), means2D,
+            self.human_bg if self.mode == "train_separate" else None)
+        self.last_radii, self.last_node = radii, color.grad_fn
+        if "G_ready" in inp:
+            torch.cuda.current_stream(self.device).wait_event(inp["G_ready"])
+        loss = (color * inp["G"]).sum()
+        if color_h is not None:
+            loss = loss + (color_h * inp["Gh"]).sum()
+        if "loss_out" in inp:
+            inp["loss_out"].copy_(loss.detach().reshape(1), non_blocking=True)
+            inp["loss_event"].record()
+        return loss
+
+    def _dp_step(self, forward_of_view, after_view=None):
+        """The product's data-parallel step (hugs_b200.dp.dp_step): clear the flat gradient buffer, this rank's
+        views over the streams, backward of each, ONE allreduce of the flat buffer."""
+        from hugs_b200 import dp
+        self.means2D.grad = None
+
+        def render_view(v):
+            loss = forward_of_view(v)
+            self.last_nodes[v], self.last_radii_v[v] = int(self.last_node.num_rendered), self.last_radii
+            return loss
+        dp.dp_step(render_view, list(range(self.views)), self.buf, 0, 1,
+                   streams=self.streams if self.n_streams > 1 else (), read_loss=False, after_view=after_view)
 
     def _deform_all(self, As):
         """animation: the rank's pose frames of the step through ONE batched LBS call when the
@@ -375,6 +469,8 @@ class Replica:
 
     def step_resident(self):
         """One step: every view of this rank's share of the view batch, gradients accumulated."""
+        if self.buf is not None:
+            return self._dp_step(lambda v: self._forward(dict(self.devs[v])))
         self.zero_grad()
         if self.mode == "animation" and self.lbs_frames is not None:
             if not hasattr(self, "A_all"):
@@ -407,6 +503,13 @@ class Replica:
             self.last_radii_v[v] = self.last_radii
 
     def step_e2e(self):
+        if self.buf is not None:
+            def release(v):   # the view's backward has been enqueued: its G buffer may be refilled after it
+                done = torch.cuda.Event()
+                done.record()
+                self.step_done[self._g_slot[v]] = done
+            self._g_slot = {}
+            return self._dp_step(lambda v: self.frame_e2e(self.hosts[v], forward_only=True, view=v), release)
         self.zero_grad()
         dall = None
         if self.mode == "animation" and self.lbs_frames is not None:
@@ -427,7 +530,7 @@ class Replica:
         for v in range(self.views):
             self.frame_e2e(self.hosts[v], None if dall is None else (dall[0][v], dall[1][v], dall[2][v]))
 
-    def frame_e2e(self, host, deformed=None):
+    def frame_e2e(self, host, deformed=None, forward_only=False, view=None):
         """One frame with every per-frame input copied from pinned host memory (camera, joint
         transforms on the compute stream; G on the copy stream) and the result read back on the host:
         the loss when training, the IMAGE when rendering."""
@@ -464,7 +567,7 @@ class Replica:
                 self.losses.append(float(self.loss_host[s][0]))
             inp.update(self.G_dev[i])
             inp.update(G_ready=self.G_ready[i], loss_out=self.loss_host[s], loss_event=ev)
-            self.frame(inp)
+            out = self._forward(inp) if forward_only else self.frame(inp)
             self.loss_ready[s] = ev
         else:
             if self.img_ready[s] is not None:
@@ -473,10 +576,14 @@ class Replica:
             inp.update(img_out=self.img_host[s], img_event=ev)
             self.frame(inp)
             self.img_ready[s] = ev
+        self.e2e_step += 1
+        if self.training and forward_only:
+            self._g_slot[view] = i   # released by _dp_step's after_view, once the backward is enqueued too
+            return out
         done = torch.cuda.Event()
         done.record(main)
         self.step_done[i] = done
-        self.e2e_step += 1
+        return None
 
     def drain_e2e(self):
         """Read the results still pending (called inside the timed region, after the last step)."""
@@ -491,41 +598,15 @@ class Replica:
                 self.images_read += 1
 
     def allreduce_grads(self):
-        import torch.distributed as dist
-        if not self.training or not dist.is_initialized() or dist.get_world_size() == 1:
-            return
-        # Two collectives: the SH gradient (81 % of the bytes) in place, everything else through one
-        # flat buffer (a collective per small tensor costs more in launch latency than in transfer).
-        leaves = self.leaves()
-        if self.comm_events is not None:
-            ev0 = torch.cuda.Event(enable_timing=True)
-            ev0.record()
-        small = [p.grad for n, p in leaves.items() if n != "shs"]
-        if self.sh_sink is not None:
-            n_sh = self.shs.numel()
-            self.flat_small = self.flat_all[n_sh:]
-            torch.cat([g.reshape(-1) for g in small], out=self.flat_small)
-            dist.all_reduce(self.flat_all, op=dist.ReduceOp.SUM)
-        else:
-            dist.all_reduce(leaves["shs"].grad, op=dist.ReduceOp.SUM)
-            if self.flat_small is None:
-                self.flat_small = torch.empty(sum(g.numel() for g in small), device=self.device)
-            torch.cat([g.reshape(-1) for g in small], out=self.flat_small)
-            dist.all_reduce(self.flat_small, op=dist.ReduceOp.SUM)
-        off = 0
-        for g in small:
-            g.copy_(self.flat_small[off:off + g.numel()].view_as(g))
-            off += g.numel()
-        if self.comm_events is not None:
-            ev1 = torch.cuda.Event(enable_timing=True)
-            ev1.record()
-            self.comm_events.append((ev0, ev1))
+        """The gradient exchange is part of the product's step (hugs_b200.dp.dp_step -> FlatGradBuffer.allreduce,
+        inside _dp_step); the reference arm is single-GPU (the reference has no multi-GPU path)."""
+        return
 
 
 def our_impl():
     import diff_gaussian_rasterization as dgr
     import hugs_b200
-    from hugs_b200 import layer
+    from hugs_b200 import layer, segments
 
     def lbs_impl(A, xyz, w, rotmat, scales, transl):
         return hugs_b200.deform_gaussians(A, xyz, w, rotmat, scales, smpl_scale=1.0, transl=transl)
@@ -538,7 +619,14 @@ def our_impl():
         return layer.rasterize_with_layer(t["means3D"], t["means2D"], t["opacities"], t["scales"], t["rotations"],
                                           settings, n_human, human_bg, shs=t["shs"])
 
-    return dict(module=dgr, lbs=lbs_impl, lbs_frames=lbs_frames, separate=separate)
+    def render2(settings, seg0, seg1, means2D, human_bg):
+        # two input segments (no torch.cat); with `human_bg` also the separate human image, same pass
+        if human_bg is not None:
+            return layer.rasterize_two_segments_with_layer(seg0, seg1, means2D, settings, human_bg)
+        color, radii = segments.rasterize_two_segments(seg0, seg1, means2D, settings)
+        return color, None, radii
+
+    return dict(module=dgr, lbs=lbs_impl, lbs_frames=lbs_frames, separate=separate, render2=render2)
 
 
 def reference_impl():
@@ -782,7 +870,7 @@ def main():
     # pair / visible counts: mean over this rank's views (they size the per-stage algorithmic bytes)
     visible = int(round(sum(int((r > 0).sum()) for r in rep.last_radii_v) / V))
     if training:
-        R = int(round(sum(int(nd.num_rendered) for nd in rep.last_nodes) / V))
+        R = int(round(sum(int(nd if isinstance(nd, int) else nd.num_rendered) for nd in rep.last_nodes) / V))
     else:   # rendering runs under no_grad (no autograd node): count the pairs of this rank's first view once
         from hugs_b200 import rasterizer as _rz
         inp = dict(rep.devs[0])
@@ -817,6 +905,8 @@ def main():
     # (one stream in this pass: a stage's events must not span the other stream's kernels)
     _native.stage_timing_enable(1)
     rep.comm_events = []
+    if rep.buf is not None:
+        rep.buf.exchange_events = rep.comm_events
     n_streams, rep.n_streams = rep.n_streams, 1
     ms_staged = timed_loop(step_resident, args.steps, device, barrier)
     rep.n_streams = n_streams
@@ -826,6 +916,8 @@ def main():
     # the slowest rank included -- on every rank
     comm_ms = sum(a.elapsed_time(b) for a, b in rep.comm_events) / max(len(rep.comm_events), 1)
     rep.comm_events = None
+    if rep.buf is not None:
+        rep.buf.exchange_events = None
     dp_info = None
     if world > 1 and training:
         t = torch.tensor([comm_ms, ms_staged / args.steps], dtype=torch.float64, device=device)
@@ -835,6 +927,7 @@ def main():
                    "exchange_ms_min": round(min(float(x[0]) for x in allt), 3),
                    "gradient_bytes": int(sum(p.numel() * 4 for p in rep.leaves().values())),
                    "collectives_per_step": 1,
+                   "through": "hugs_b200.dp.dp_step / FlatGradBuffer.allreduce (the product's API)",
                    "note": "min over ranks ~ pure transfer (the last rank to arrive does not wait); the rest is "
                            "waiting for the slowest rank's views"}
 
@@ -848,7 +941,7 @@ def main():
 
     peak, peak_kind = peaks()
     sort_bits = int(_native.sort_bits(W, H))
-    nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits, views=V, sh_sink=rep.sh_sink is not None)
+    nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits, views=V, sh_sink=(rep.sh_sink is not None or rep.buf is not None))
     stages = {}
     for name, (tot, calls) in stage_ms.items():
         if calls == 0:

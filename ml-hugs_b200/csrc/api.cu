@@ -601,15 +601,20 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         HB_CUDA_OK(cudaMemsetAsync(geom.pair_counts, 0, 2 * sizeof(uint32_t), stream));
 
         if (const SecondSegment* s2 = tl_seg2) {
-            if (s2->P0 > 0)
-                HB_STAGE(launch_preprocess(s2->P0, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
-                                           nullptr, nullptr, cam, radii, geom, prefiltered != 0, stream),
-                         ST_PREPROCESS);
-            if (P - s2->P0 > 0)
-                HB_STAGE(launch_preprocess(P - s2->P0, D, M, s2->means3D, s2->scales, scale_modifier, s2->rotations,
+            // both segments in ONE launch (SegBatch): the human segment alone would be a 431-block grid
+            auto both = [&]() -> int {
+                SegBatch batch;
+                int rc = 0;
+                if (s2->P0 > 0)
+                    rc = launch_preprocess(s2->P0, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
+                                           nullptr, nullptr, cam, radii, geom, prefiltered != 0, stream, &batch);
+                if (rc == 0 && P - s2->P0 > 0)
+                    rc = launch_preprocess(P - s2->P0, D, M, s2->means3D, s2->scales, scale_modifier, s2->rotations,
                                            s2->opacities, s2->shs, nullptr, nullptr, cam, radii + s2->P0,
-                                           geom_rows_from(geom, s2->P0), prefiltered != 0, stream),
-                         ST_PREPROCESS);
+                                           geom_rows_from(geom, s2->P0), prefiltered != 0, stream, &batch);
+                return rc ? rc : flush_preprocess(batch, stream);
+            };
+            HB_STAGE(both(), ST_PREPROCESS);
         } else
         HB_STAGE(launch_preprocess(P, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
                                    (scales && rotations) ? nullptr : cov3D_precomp, colors_precomp, cam, radii, geom,
@@ -884,6 +889,8 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
     }
     if (const SecondSegment* s2 = tl_seg2) {
         const size_t r0 = (size_t)s2->P0;
+        SegBatch batch;   // both segments in one launch
+        auto both = [&]() -> int {
         for (int seg = 0; seg < 2; seg++) {
             const int n = seg == 0 ? s2->P0 : P - s2->P0;
             if (n <= 0) continue;
@@ -907,14 +914,16 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
                 if (sinks->opacity[seg]) { ex.dL_dopacity = sinks->opacity[seg]; ex.acc_mask |= kAccOpacity; }
                 if (sinks->sh[seg]) { o_sh = sinks->sh[seg]; sh_acc = true; }
             }
-            HB_STAGE(launch_preprocess_backward(n, D, M, seg == 0 ? means3D : s2->means3D, radii + o,
-                                                seg == 0 ? shs : s2->shs, geom.clamped + o,
-                                                seg == 0 ? scales : s2->scales, seg == 0 ? rotations : s2->rotations,
-                                                scale_modifier, nullptr, cam, geom.grad_pack + 8 * o,
-                                                dL_dmean2D + 3 * o, dL_dconic + 4 * o, o_mean, dL_dcolor + 3 * o,
-                                                dL_dcov3D + 6 * o, o_sh, o_scale, o_rot, sh_acc, stream, &ex),
-                     ST_PREPROCESS_BWD);
+            const int rc = launch_preprocess_backward(
+                n, D, M, seg == 0 ? means3D : s2->means3D, radii + o, seg == 0 ? shs : s2->shs, geom.clamped + o,
+                seg == 0 ? scales : s2->scales, seg == 0 ? rotations : s2->rotations, scale_modifier, nullptr, cam,
+                geom.grad_pack + 8 * o, dL_dmean2D + 3 * o, dL_dconic + 4 * o, o_mean, dL_dcolor + 3 * o,
+                dL_dcov3D + 6 * o, o_sh, o_scale, o_rot, sh_acc, stream, &ex, &batch);
+            if (rc) return rc;
         }
+        return flush_preprocess_backward(batch, stream);
+        };
+        HB_STAGE(both(), ST_PREPROCESS_BWD);
         return 0;
     }
     PreBwdExtra ex1;

@@ -139,7 +139,8 @@ struct Camera {
 int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
                       const float* rotations, const float* opacities, const float* shs,
                       const float* cov3D_precomp, const float* colors_precomp, const Camera& cam,
-                      int* radii, const GeomView& g, bool prefiltered, cudaStream_t stream);
+                      int* radii, const GeomView& g, bool prefiltered, cudaStream_t stream,
+                      struct SegBatch* batch = nullptr);
 int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj, uint8_t* present,
                         cudaStream_t stream);
 
@@ -191,6 +192,17 @@ int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int 
                            const uint32_t* n_contrib, const uint32_t* hit_words, const float* dL_dpix,
                            float* grad_pack /*[P,8], zeroed*/, float* dL_dopacity /*[P], zeroed*/,
                            cudaStream_t stream);
+// Two-segment calls: the per-segment launches of a per-Gaussian kernel are collected here and issued as ONE
+// launch (flush_*): the human segment alone (110 k rows) is too small a grid to fill the machine.
+struct SegBatch {
+    int n = 0;
+    alignas(16) unsigned char args[2][768];   // the kernel's argument record (private to its .cu file)
+    int blocks[2] = {0, 0};
+    size_t smem[2] = {0, 0};
+};
+int flush_preprocess(SegBatch& b, cudaStream_t stream);
+int flush_preprocess_backward(SegBatch& b, cudaStream_t stream);
+
 // Optional inputs of the per-Gaussian backward: a second image's packed records (layer.cu) and gradient sinks.
 constexpr int kAccMean3D = 1, kAccScale = 2, kAccRot = 4, kAccOpacity = 8;
 struct PreBwdExtra {
@@ -206,7 +218,7 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                                float* dL_drot, bool sh_accumulate, cudaStream_t stream,
-                               const struct PreBwdExtra* extra = nullptr);
+                               const struct PreBwdExtra* extra = nullptr, SegBatch* batch = nullptr);
 int launch_layer_filter(int num_tiles, const uint2* ranges, const uint32_t* list, int n_layer, uint32_t* list_out,
                         uint2* ranges_out, cudaStream_t stream);
 

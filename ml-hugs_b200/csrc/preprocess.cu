@@ -15,6 +15,8 @@
 // Division, reciprocal and square root are the IEEE round-to-nearest versions (the reference
 // is built without -use_fast_math).
 #include "common.cuh"
+
+#include <cstring>
 #include <cstdio>
 
 namespace hb {
@@ -146,7 +148,15 @@ __device__ __forceinline__ void cp_async_wait_all() {
 //     moves 16-byte word 32 j + l of it with cp.async (global -> shared, no registers, all twelve
 //     copies of a lane in flight at once), so every request is 512 contiguous bytes minus the rows of
 //     culled Gaussians, and each thread then reads its own row out of shared memory.
-__global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const PreprocessArgs a) {
+//
+// Two input segments in ONE launch (hugs_b200_rasterize_forward_seg2): blocks [0, nb0) work on a0, the rest
+// on a1 -- the second segment's outputs are the same arrays moved to its first row, so a segment is just a
+// second argument record; with one segment a1 == a0 and nb0 == gridDim.x.
+__global__ void __launch_bounds__(kPreThreads, 6)
+    preprocess_kernel(const PreprocessArgs a0, const PreprocessArgs a1, const int nb0) {
+    const bool second = (int)blockIdx.x >= nb0;
+    const PreprocessArgs& a = second ? a1 : a0;
+    const unsigned blk = second ? blockIdx.x - (unsigned)nb0 : blockIdx.x;
     extern __shared__ __align__(16) unsigned char s_rows[];  // [256][208 B] SH rows (vec4 path)
     __shared__ float s_cam[36];  // view[16], proj[16], campos[3]
     if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(a.view + threadIdx.x);
@@ -156,7 +166,7 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const Prepro
     const float* V = s_cam;
     const float* Pm = s_cam + 16;
 
-    const int idx = blockIdx.x * kPreThreads + threadIdx.x;
+    const int idx = blk * kPreThreads + threadIdx.x;
     const bool valid = idx < a.P;
     bool vis = false;
     float px = 0.f, py = 0.f, pz = 0.f, depth = 0.f, pix_x = 0.f, pix_y = 0.f;
@@ -300,7 +310,7 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const Prepro
                 const int nv = (nf + 3) >> 2;
                 const uint32_t s_warp = (uint32_t)__cvta_generic_to_shared(s_rows) + warp * 32u * kShRowBytes;
                 const float4* g_warp =
-                    reinterpret_cast<const float4*>(a.shs) + 12 * ((size_t)blockIdx.x * kPreThreads + warp * 32u);
+                    reinterpret_cast<const float4*>(a.shs) + 12 * ((size_t)blk * kPreThreads + warp * 32u);
                 unsigned row = lane / 12u, col = lane % 12u;  // 16-byte word 32 j + lane = (row, col)
 #pragma unroll
                 for (int j = 0; j < 12; j++) {
@@ -383,7 +393,8 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_kernel(const Prepro
 int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
                       const float* rotations, const float* opacities, const float* shs,
                       const float* cov3D_precomp, const float* colors_precomp, const Camera& cam, int* radii,
-                      const GeomView& g, bool prefiltered, cudaStream_t stream) {
+                      const GeomView& g, bool prefiltered, cudaStream_t stream, SegBatch* batch) {
+    static_assert(sizeof(PreprocessArgs) <= sizeof(SegBatch::args[0]), "SegBatch record too small");
     PreprocessArgs a;
     a.P = P;
     a.D = D;
@@ -430,7 +441,29 @@ int launch_preprocess(int P, int D, int M, const float* means3D, const float* sc
             if (dev >= 0 && dev < 64) configured[dev] = true;
         }
     }
-    preprocess_kernel<<<cdiv(P, kPreThreads), kPreThreads, a.sh_vec4 ? kPreSmemBytes : 0, stream>>>(a);
+    if (batch != nullptr) {   // a segment of a two-segment call: launched by flush_preprocess
+        if (batch->n >= 2) return -1;
+        memcpy(batch->args[batch->n], &a, sizeof(a));
+        batch->blocks[batch->n] = cdiv(P, kPreThreads);
+        batch->smem[batch->n] = a.sh_vec4 ? kPreSmemBytes : 0;
+        batch->n++;
+        return 0;
+    }
+    preprocess_kernel<<<cdiv(P, kPreThreads), kPreThreads, a.sh_vec4 ? kPreSmemBytes : 0, stream>>>(
+        a, a, cdiv(P, kPreThreads));
+    HB_LAUNCH_OK("preprocess", stream, false);
+    return 0;
+}
+
+int flush_preprocess(SegBatch& b, cudaStream_t stream) {
+    if (b.n == 0) return 0;
+    PreprocessArgs a0, a1;
+    memcpy(&a0, b.args[0], sizeof(a0));
+    memcpy(&a1, b.args[b.n - 1], sizeof(a1));
+    const int nb0 = b.blocks[0], nb = nb0 + (b.n == 2 ? b.blocks[1] : 0);
+    const size_t smem = b.smem[0] > b.smem[b.n - 1] ? b.smem[0] : b.smem[b.n - 1];
+    b.n = 0;
+    preprocess_kernel<<<nb, kPreThreads, smem, stream>>>(a0, a1, nb0);
     HB_LAUNCH_OK("preprocess", stream, false);
     return 0;
 }

@@ -11,6 +11,8 @@
 // Algorithmic traffic at SH degree 3: ~303 B read + 256 B written per visible Gaussian.
 #include "common.cuh"
 
+#include <cstring>
+
 namespace hb {
 
 namespace {
@@ -187,14 +189,19 @@ __device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c,
 //   * dL/dsh is assembled row by row in the same shared-memory slots and written by the whole warp
 //     as twelve 512-byte contiguous stores (zero rows for culled Gaussians included), instead of
 //     twelve 16-byte stores per thread at a 192-byte stride.
-__global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(const PreBwdArgs a) {
+// Two segments in one launch: blocks [0, nb0) work on a0, the rest on a1 (see preprocess.cu).
+__global__ void __launch_bounds__(kPbThreads, 4)
+    preprocess_backward_kernel(const PreBwdArgs a0, const PreBwdArgs a1, const int nb0) {
+    const bool second = (int)blockIdx.x >= nb0;
+    const PreBwdArgs& a = second ? a1 : a0;
+    const unsigned blk = second ? blockIdx.x - (unsigned)nb0 : blockIdx.x;
     extern __shared__ __align__(16) unsigned char s_rows[];  // [256][208 B] SH rows / dL_dsh rows (vec4 path)
     __shared__ float s_cam[36];
     if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(a.view + threadIdx.x);
     else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(a.proj + threadIdx.x - 16);
     else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(a.campos + threadIdx.x - 32);
 
-    const int idx = blockIdx.x * kPbThreads + threadIdx.x;
+    const int idx = blk * kPbThreads + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const bool valid = idx < a.P;
     const bool vis = valid && (__ldg(a.radii + idx) > 0);
@@ -203,7 +210,7 @@ __global__ void __launch_bounds__(kPbThreads, 4) preprocess_backward_kernel(cons
     const int nf = 3 * (deg + 1) * (deg + 1);
     const int nv = (nf + 3) >> 2;
     const uint32_t s_warp = (uint32_t)__cvta_generic_to_shared(s_rows) + warp * 32u * kPbRowBytes;
-    const size_t warp_row0 = (size_t)blockIdx.x * kPbThreads + warp * 32u;
+    const size_t warp_row0 = (size_t)blk * kPbThreads + warp * 32u;
     const unsigned alive = __ballot_sync(0xffffffffu, vis);
 
     // ---- SH rows of the visible Gaussians of this warp: in flight from here on ------------------
@@ -568,7 +575,8 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                const float* grad_pack, float* dL_dmean2D, float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
-                               bool sh_accumulate, cudaStream_t stream, const PreBwdExtra* extra) {
+                               bool sh_accumulate, cudaStream_t stream, const PreBwdExtra* extra, SegBatch* batch) {
+    static_assert(sizeof(PreBwdArgs) <= sizeof(SegBatch::args[0]), "SegBatch record too small");
     const float* grad_pack2 = extra ? extra->grad_pack2 : nullptr;
     const int n2 = extra ? extra->n2 : 0;
     PreBwdArgs a;
@@ -623,7 +631,29 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
             if (dev >= 0 && dev < 64) configured[dev] = true;
         }
     }
-    preprocess_backward_kernel<<<cdiv(P, kPbThreads), kPbThreads, a.sh_vec4 ? kPbSmemBytes : 0, stream>>>(a);
+    if (batch != nullptr) {   // a segment of a two-segment call: launched by flush_preprocess_backward
+        if (batch->n >= 2) return -1;
+        memcpy(batch->args[batch->n], &a, sizeof(a));
+        batch->blocks[batch->n] = cdiv(P, kPbThreads);
+        batch->smem[batch->n] = a.sh_vec4 ? kPbSmemBytes : 0;
+        batch->n++;
+        return 0;
+    }
+    preprocess_backward_kernel<<<cdiv(P, kPbThreads), kPbThreads, a.sh_vec4 ? kPbSmemBytes : 0, stream>>>(
+        a, a, cdiv(P, kPbThreads));
+    HB_LAUNCH_OK("preprocess_backward", stream, false);
+    return 0;
+}
+
+int flush_preprocess_backward(SegBatch& b, cudaStream_t stream) {
+    if (b.n == 0) return 0;
+    PreBwdArgs a0, a1;
+    memcpy(&a0, b.args[0], sizeof(a0));
+    memcpy(&a1, b.args[b.n - 1], sizeof(a1));
+    const int nb0 = b.blocks[0], nb = nb0 + (b.n == 2 ? b.blocks[1] : 0);
+    const size_t smem = b.smem[0] > b.smem[b.n - 1] ? b.smem[0] : b.smem[b.n - 1];
+    b.n = 0;
+    preprocess_backward_kernel<<<nb, kPbThreads, smem, stream>>>(a0, a1, nb0);
     HB_LAUNCH_OK("preprocess_backward", stream, false);
     return 0;
 }

@@ -22,16 +22,25 @@ def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
 
 
 class FlatGradBuffer:
-    """All parameter gradients of a replica in one contiguous fp32 buffer.
+    """All parameter gradients of a replica in one contiguous fp32 buffer (what the step's ONE allreduce
+    works on).  ``params`` maps names to leaf tensors; order is the insertion order (identical on every rank).
 
-    ``params`` maps names to leaf tensors.  Each leaf's ``.grad`` is made a view into the flat
-    buffer, so autograd accumulates the per-view gradients in place and the allreduce needs no
-    gather/scatter copies.  Order is the insertion order of ``params`` (identical on every rank).
+    Two ways a parameter's gradient reaches its slice:
+      * in place (``gather=False``, the default): ``.grad`` IS the slice for the whole run; autograd
+        accumulates the per-view gradients into it and the allreduce needs no gather/scatter copies;
+      * gathered (``gather=True``): ``.grad`` is left to autograd during the step (reset to None by
+        ``zero_``, so the first view's gradient is adopted without a kernel and AccumulateGrad runs on the
+        views' own streams), copied into the slice right before the allreduce, and re-pointed at the slice
+        afterwards (no copy back).  With a single rank nothing is copied at all.
+    Parameters with a gradient sink (``attach_sinks`` / ``attach_sh_sink``) are always in place: the
+    rasterizer's backward kernels add into the slice directly.
     """
 
-    def __init__(self, params: Dict[str, torch.Tensor]):
+    def __init__(self, params: Dict[str, torch.Tensor], gather: bool = False):
         self.names = list(params.keys())
         self.params = params
+        self.gather = bool(gather)
+        self.sunk = set()
         leaves = [params[n] for n in self.names]
         if not leaves:
             raise ValueError("no parameters")
@@ -45,8 +54,11 @@ class FlatGradBuffer:
             self.offsets.append(off)
             off += (p.numel() + 31) // 32 * 32
         self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
-        for p, o in zip(leaves, self.offsets):
-            p.grad = self.flat[o:o + p.numel()].view_as(p)
+        self.slices = {n: self.flat[o:o + params[n].numel()].view_as(params[n]) for n, o in zip(self.names, self.offsets)}
+        if not self.gather:
+            for n in self.names:
+                params[n].grad = self.slices[n]
+        self.exchange_events = None   # set to a list to collect (start, end) CUDA events of every allreduce
 
     @property
     def nbytes(self) -> int:
@@ -58,10 +70,29 @@ class FlatGradBuffer:
         AccumulateGrad kernels, and what the allreduce works on is complete when the last backward returns."""
         from .rasterizer import attach_grad_sink
         for n in names:
-            attach_grad_sink(self.params[n], self.params[n].grad)
+            attach_grad_sink(self.params[n], self.slices[n])
+            self.sunk.add(n)
+
+    def attach_sh_sink(self, name: str):
+        """The SH gradient of ``GaussianRasterizer(shs=params[name])`` renders (81 % of the gradient bytes) is
+        added by the per-Gaussian backward kernel into the slice (hugs_b200.ShGradSink)."""
+        from .rasterizer import attach_sh_grad_sink
+        sink = attach_sh_grad_sink(self.params[name], self.slices[name])
+        sink.fresh = False   # zero_() clears the slice; every view adds
+        self.sunk.add(name)
+        return sink
 
     def zero_(self):
-        self.flat.zero_()
+        if not self.gather:
+            self.flat.zero_()
+            return
+        for n in self.names:
+            if n in self.sunk:
+                self.slices[n].zero_()
+                if self.params[n].grad is not self.slices[n]:
+                    self.params[n].grad = self.slices[n]
+            else:
+                self.params[n].grad = None
 
     def grads(self) -> Dict[str, torch.Tensor]:
         return {n: self.params[n].grad for n in self.names}
@@ -71,11 +102,28 @@ class FlatGradBuffer:
         with a single rank."""
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return None
-        return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+        timed = self.exchange_events is not None and self.flat.is_cuda
+        if timed:
+            ev0 = torch.cuda.Event(enable_timing=True)
+            ev0.record()
+        if self.gather:
+            for n in self.names:
+                g = self.params[n].grad
+                if g is None:
+                    self.slices[n].zero_()
+                elif g is not self.slices[n] and g.data_ptr() != self.slices[n].data_ptr():
+                    self.slices[n].copy_(g)
+                self.params[n].grad = self.slices[n]
+        work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+        if timed:
+            ev1 = torch.cuda.Event(enable_timing=True)
+            ev1.record()
+            self.exchange_events.append((ev0, ev1))
+        return work
 
 
 def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, world_size: int,
-            group=None, streams: Sequence = ()) -> float:
+            group=None, streams: Sequence = (), read_loss: bool = True, after_view=None):
     """One data-parallel step: ``render_view(v)`` must return the scalar loss tensor of view ``v``
     (forward through LBS + rasterizer); this rank handles ``shard_views`` of ``views``, calls
     backward on each loss (gradients accumulate in ``buf``), then allreduces.  Returns the local
@@ -84,29 +132,43 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     ``streams`` (CUDA only): the rank's views alternate between these streams, so the issue-bound
     blend kernels of one view overlap the latency- and HBM-bound binning / per-Gaussian kernels of
     the next (measured +5 % frames/s with two streams on B200); autograd orders the gradient
-    accumulation.  The losses are summed on the device and read once, after the last view."""
+    accumulation.  The losses are summed on the device and read once, after the last view
+    (``read_loss=False``: not read at all -- the host does not wait for the step -- and the device-side
+    list of losses is returned instead).  ``after_view(v)`` is called on the view's stream once its backward
+    pass has been enqueued (e.g. to record the event that releases the view's input buffers)."""
     buf.zero_()
     mine = shard_views(len(views), rank, world_size)
+
+    def one(view):
+        # in a function of its own: the view's graph must be gone before the next view's forward pass runs
+        # (a loss tensor kept in a loop variable keeps the leaves' AccumulateGrad nodes -- and the stream they
+        # were created on -- alive, and autograd then synchronises the views' streams with each other)
+        loss = render_view(view)
+        loss.backward()
+        out = loss.detach()
+        del loss
+        if after_view is not None:
+            after_view(view)
+        return out
+
     if not streams:
-        total = 0.0
-        for i in mine:
-            loss = render_view(views[i])
-            loss.backward()
-            total += float(loss.detach())
+        losses = [one(views[i]) for i in mine]
         buf.allreduce(group)
-        return total
+        if not read_loss:
+            return losses
+        return float(sum(float(x) for x in losses))
     main = torch.cuda.current_stream()
     for s in streams:
         s.wait_stream(main)
     losses = []
     for k, i in enumerate(mine):
         with torch.cuda.stream(streams[k % len(streams)]):
-            loss = render_view(views[i])
-            loss.backward()
-            losses.append(loss.detach())
+            losses.append(one(views[i]))
     for s in streams:
         main.wait_stream(s)
     buf.allreduce(group)
+    if not read_loss:
+        return losses
     return float(torch.stack(losses).sum()) if losses else 0.0
 
 

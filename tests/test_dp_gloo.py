@@ -33,7 +33,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, n_views, out):
+def _worker(rank, world, port, n_views, out, gather=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
                       LOCAL_RANK=str(rank))
     import sys
@@ -43,7 +43,7 @@ def _worker(rank, world, port, n_views, out):
     r, _, w = dp.init_from_env("gloo")
     assert (r, w) == (rank, world)
     params = _params()
-    buf = dp.FlatGradBuffer(params)
+    buf = dp.FlatGradBuffer(params, gather=gather)
     views = list(range(n_views))
     for _ in range(2):  # two steps: the buffer must be cleared between steps
         local = dp.dp_step(lambda v: _loss(params, v), views, buf, rank, world)
@@ -54,10 +54,11 @@ def _worker(rank, world, port, n_views, out):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("gather", [False, True])
 @pytest.mark.parametrize("n_views", [4, 5])
-def test_dp_allreduce_equals_single_process_gradient(tmp_path, n_views):
+def test_dp_allreduce_equals_single_process_gradient(tmp_path, n_views, gather):
     out = str(tmp_path / "r0.pt")
-    mp.spawn(_worker, args=(2, _free_port(), n_views, out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), n_views, out, gather), nprocs=2, join=True)
     got = torch.load(out)
     params = _params()
     loss = sum(_loss(params, v) for v in range(n_views))
