@@ -1,7 +1,9 @@
 // Single-pass inclusive prefix sum of u32 with decoupled look-back (chained scan), sm_100a.
 // Replaces cub::DeviceScan::InclusiveSum at cuda_rasterizer/rasterizer_impl.cu:277.
 //
-// One CTA per 2048-item tile, tiles handed out by an atomic ticket so that every predecessor
+// One CTA per 8192-item tile (the look-back walks its predecessors 32 at a time, one L2 round trip per
+// window: with 2048-item tiles the last of 543 tiles needed up to 17 dependent round trips -- the stage took
+// 22 us for 9 MB; 136 tiles need at most 5), tiles handed out by an atomic ticket so that every predecessor
 // of a running tile has already started (forward progress for the look-back spin).  Per-tile
 // state is one 64-bit word (flag << 32 | value) so flag and value are read atomically.
 // Algorithmic traffic: 4 B read + 4 B written per item.
@@ -10,8 +12,8 @@
 namespace hb {
 
 namespace {
-constexpr int kScanThreads = 256;
-constexpr int kScanItems = 8;
+constexpr int kScanThreads = 512;
+constexpr int kScanItems = 16;
 constexpr int kScanTile = kScanThreads * kScanItems;
 constexpr unsigned long long kFlagAggregate = 1ull << 32;
 constexpr unsigned long long kFlagInclusive = 2ull << 32;
@@ -43,24 +45,27 @@ __global__ void __launch_bounds__(kScanThreads) inclusive_scan_kernel(const uint
     const int base = tile * kScanTile + tid * kScanItems;
 
     uint32_t v[kScanItems];
+    const bool full = base + kScanItems <= n;
     if (gather != nullptr) {
         uint32_t g[kScanItems];
-        if (base + kScanItems <= n) {
-            const uint4 a = __ldg(reinterpret_cast<const uint4*>(gather + base));
-            const uint4 b = __ldg(reinterpret_cast<const uint4*>(gather + base) + 1);
-            g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w;
-            g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+        if (full) {
+#pragma unroll
+            for (int q = 0; q < kScanItems / 4; q++) {
+                const uint4 a = __ldg(reinterpret_cast<const uint4*>(gather + base) + q);
+                g[4 * q + 0] = a.x; g[4 * q + 1] = a.y; g[4 * q + 2] = a.z; g[4 * q + 3] = a.w;
+            }
 #pragma unroll
             for (int i = 0; i < kScanItems; i++) v[i] = __ldg(in + g[i]);
         } else {
 #pragma unroll
             for (int i = 0; i < kScanItems; i++) v[i] = (base + i < n) ? __ldg(in + __ldg(gather + base + i)) : 0u;
         }
-    } else if (base + kScanItems <= n) {
-        const uint4 a = __ldg(reinterpret_cast<const uint4*>(in + base));
-        const uint4 b = __ldg(reinterpret_cast<const uint4*>(in + base) + 1);
-        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-        v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else if (full) {
+#pragma unroll
+        for (int q = 0; q < kScanItems / 4; q++) {
+            const uint4 a = __ldg(reinterpret_cast<const uint4*>(in + base) + q);
+            v[4 * q + 0] = a.x; v[4 * q + 1] = a.y; v[4 * q + 2] = a.z; v[4 * q + 3] = a.w;
+        }
     } else {
 #pragma unroll
         for (int i = 0; i < kScanItems; i++) v[i] = (base + i < n) ? __ldg(in + base + i) : 0u;
@@ -114,12 +119,13 @@ __global__ void __launch_bounds__(kScanThreads) inclusive_scan_kernel(const uint
     }
     __syncthreads();
     const uint32_t add = s_prefix + thread_excl;
-    if (base + kScanItems <= n) {
-        uint4 a, b;
-        a.x = v[0] + add; a.y = v[1] + add; a.z = v[2] + add; a.w = v[3] + add;
-        b.x = v[4] + add; b.y = v[5] + add; b.z = v[6] + add; b.w = v[7] + add;
-        reinterpret_cast<uint4*>(out + base)[0] = a;
-        reinterpret_cast<uint4*>(out + base)[1] = b;
+    if (full) {
+#pragma unroll
+        for (int q = 0; q < kScanItems / 4; q++) {
+            uint4 a;
+            a.x = v[4 * q + 0] + add; a.y = v[4 * q + 1] + add; a.z = v[4 * q + 2] + add; a.w = v[4 * q + 3] + add;
+            reinterpret_cast<uint4*>(out + base)[q] = a;
+        }
     } else {
 #pragma unroll
         for (int i = 0; i < kScanItems; i++)

@@ -87,7 +87,7 @@ def test_argument_errors_are_reported_without_a_gpu():
                                 None, None, 0, None) == -1
     assert N.mark_visible(-3, None, None, None, None, None) == -1
     assert N.stage_name(0) == b"preprocess" and N.stage_name(99) is None
-    assert N.sort_temp_bytes(0) > 0 and N.scan_temp_bytes(10**6) > 8 * (10**6 // 2048)
+    assert N.sort_temp_bytes(0) > 0 and N.scan_temp_bytes(10**6) > 8 * (10**6 // 8192)
 
 
 def test_product_never_touches_the_oracle():

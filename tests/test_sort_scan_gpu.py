@@ -62,7 +62,7 @@ def test_sort_all_equal_and_presorted_and_reversed():
         assert (ko == keys[order]).all() and (vo == vals[order]).all()
 
 
-@pytest.mark.parametrize("n", [1, 7, 2047, 2048, 2049, 65536, 1_110_210, 5_000_003])
+@pytest.mark.parametrize("n", [1, 7, 2047, 2048, 2049, 8191, 8192, 8193, 65536, 1_110_210, 5_000_003])
 def test_inclusive_scan(n):
     from hugs_b200 import _native as N
 

@@ -40,6 +40,15 @@ WANT = [
     ("launch__grid_size", "grid"),
     ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm%"),
     ("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smem_wavefronts"),
+    ("smsp__inst_executed.sum", "warp_inst"),
+    ("sm__inst_executed_pipe_fma.sum", "pipe_fma"),
+    ("sm__inst_executed_pipe_alu.sum", "pipe_alu"),
+    ("sm__inst_executed_pipe_xu.sum", "pipe_xu"),
+    ("sm__inst_executed_pipe_lsu.sum", "pipe_lsu"),
+    ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "fma%"),
+    ("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "alu%"),
+    ("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "xu%"),
+    ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "lsu%"),
 ]
 
 

@@ -17,8 +17,8 @@ def main():
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
     _native.set_binning_mode(mode)
-    module, lbs_impl = bench.our_impl()
-    rep = bench.Replica(bench.make_workload(workload, 0, 1, dev), dev, module, lbs_impl)
+    rep = bench.Replica(bench.make_workload(workload, 0, 1, dev), dev, bench.our_impl(), sh_sink=True)
+    rep.n_streams = 1
     for _ in range(3):
         rep.step_resident()
     torch.cuda.synchronize()
@@ -26,7 +26,9 @@ def main():
     rep.step_resident()
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStop()
-    print("profiled one frame: P=%d R=%d mode=%d" % (rep.P, rep.last_node.num_rendered, mode))  # views=1
+    nd = rep.last_nodes[0]
+    print("profiled one frame: P=%d R=%s mode=%d" % (rep.P, nd if isinstance(nd, int) or nd is None else nd.num_rendered,
+                                                     mode))  # views=1
 
 
 if __name__ == "__main__":
