@@ -31,7 +31,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 8
+#define HUGS_B200_ABI_VERSION 9
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
@@ -474,6 +474,39 @@ int hugs_b200_rasterize_backward_seg2_ex(int D, int M, int R, const float* backg
                                          hugs_b200_stream_t stream, int n_layer, const float* background_layer,
                                          char* layer_buffer, size_t layer_bytes, const float* dL_dpix_layer,
                                          const hugs_b200_grad_sinks* sinks);
+
+
+/* ---- fused decoder MLPs on the tensor cores (tcgen05 / TMEM, 3xTF32) -----------------------------------
+ * Replaces the torch.nn.Linear / GELU chains of hugs/models/modules/decoders.py:24-110 (AppearanceDecoder
+ * :24-44, DeformationDecoder :47-84, GeometryDecoder :87-110) as hugs/models/hugs_trimlp.py:205-238 runs them
+ * on the [N, 96] tri-plane features.  A chain is a sequence of Linear layers: every layer but the last is
+ * followed by `act` and feeds the next; the last layer's columns are written to up to three outputs, each
+ * with its own activation (the decoders' heads concatenated into one layer).  Up to three chains read the
+ * same input in one launch.  Weights are handed over in the packed form hugs_b200_mlp_pack produces from a
+ * Linear's [n_true, K] weight and [n_true] bias (n_pad: n_true rounded up to 16, hidden layers to 32).
+ * z_out (optional): the layer's pre-activations [rows, N], kept for the backward pass. */
+#define HUGS_B200_MLP_ACT_NONE    0
+#define HUGS_B200_MLP_ACT_GELU    1   /* exact, erf: torch.nn.GELU() */
+#define HUGS_B200_MLP_ACT_SIGMOID 2
+typedef struct hugs_b200_mlp_out {
+    float* ptr;             /* out[row * ld + (col - col0)] for col in [col0, col0 + ncols) */
+    int ld, col0, ncols, act;
+} hugs_b200_mlp_out;
+typedef struct hugs_b200_mlp_layer {
+    int K, N, act;          /* N: padded width */
+    const float* packed;
+    float* z_out;
+} hugs_b200_mlp_layer;
+typedef struct hugs_b200_mlp_chain {
+    int n_layers, n_outs;
+    hugs_b200_mlp_layer layer[4];
+    hugs_b200_mlp_out out[3];
+} hugs_b200_mlp_chain;
+size_t hugs_b200_mlp_packed_floats(int K, int n_pad);
+int hugs_b200_mlp_pack(const float* W, const float* bias, int n_true, int n_pad, int K, float* packed,
+                       hugs_b200_stream_t stream);
+int hugs_b200_mlp_chains_forward(int rows, const float* x, int ldx, int Kx, int n_chains,
+                                 const hugs_b200_mlp_chain* chains, hugs_b200_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Densification statistics after a backward pass, one launch, no host sync.

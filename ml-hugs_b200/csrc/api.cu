@@ -1198,6 +1198,55 @@ int hugs_b200_rasterize_backward_seg2_ex(int D, int M, int R, const float* backg
     return rc;
 }
 
+size_t hugs_b200_mlp_packed_floats(int K, int n_pad) {
+    return (K > 0 && n_pad > 0) ? mlp_packed_floats(K, n_pad) : 0;
+}
+
+int hugs_b200_mlp_pack(const float* W, const float* bias, int n_true, int n_pad, int K, float* packed,
+                       hugs_b200_stream_t stream) {
+    if (!W || !packed || n_true <= 0) {
+        set_error("mlp_pack: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_mlp_pack(W, bias, n_true, n_pad, K, packed, static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_mlp_chains_forward(int rows, const float* x, int ldx, int Kx, int n_chains,
+                                 const hugs_b200_mlp_chain* chains, hugs_b200_stream_t stream) {
+    if (rows < 0 || n_chains < 1 || n_chains > HB_MLP_MAX_CHAINS || !chains || (rows > 0 && !x)) {
+        set_error("mlp_chains_forward: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    MlpArgs a;
+    memset(&a, 0, sizeof(a));
+    a.rows = rows;
+    a.x = x;
+    a.ldx = ldx;
+    a.Kx = Kx;
+    a.n_chains = n_chains;
+    for (int c = 0; c < n_chains; c++) {
+        const hugs_b200_mlp_chain& src = chains[c];
+        if (src.n_layers < 1 || src.n_layers > HB_MLP_MAX_LAYERS || src.n_outs < 0 || src.n_outs > HB_MLP_MAX_OUTS) {
+            set_error("mlp_chains_forward: chain %d: bad layer / output count", c);
+            return HUGS_B200_EINVAL;
+        }
+        MlpChainArgs& dst = a.chain[c];
+        dst.n_layers = src.n_layers;
+        dst.n_outs = src.n_outs;
+        for (int l = 0; l < src.n_layers; l++)
+            dst.layer[l] = MlpLayerArgs{src.layer[l].K, src.layer[l].N, src.layer[l].act, src.layer[l].packed,
+                                        src.layer[l].z_out};
+        for (int o = 0; o < src.n_outs; o++) {
+            if (!src.out[o].ptr || src.out[o].ncols <= 0 || src.out[o].col0 < 0) {
+                set_error("mlp_chains_forward: chain %d output %d is malformed", c, o);
+                return HUGS_B200_EINVAL;
+            }
+            dst.out[o] = MlpOut{src.out[o].ptr, src.out[o].ld, src.out[o].col0, src.out[o].ncols, src.out[o].act};
+        }
+    }
+    return launch_mlp_chains(a, static_cast<cudaStream_t>(stream));
+}
+
 int hugs_b200_densification_stats(int n, const int* radii, const float* grad_means2D, int grad_stride,
                                   float* xyz_gradient_accum, float* denom, float* max_radii2D,
                                   hugs_b200_stream_t stream) {

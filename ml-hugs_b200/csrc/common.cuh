@@ -222,6 +222,37 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
 int launch_layer_filter(int num_tiles, const uint2* ranges, const uint32_t* list, int n_layer, uint32_t* list_out,
                         uint2* ranges_out, cudaStream_t stream);
 
+// ---- fused decoder MLPs on tcgen05 (mlp_tc.cu) -----------------------------------------------------------
+#define HB_MLP_ACT_NONE 0
+#define HB_MLP_ACT_GELU 1
+#define HB_MLP_ACT_SIGMOID 2
+#define HB_MLP_MAX_CHAINS 3
+#define HB_MLP_MAX_LAYERS 4
+#define HB_MLP_MAX_OUTS 3
+struct MlpOut {          // columns [col0, col0 + ncols) of a chain's last layer -> out[row * ld + (col - col0)]
+    float* ptr;
+    int ld, col0, ncols, act;
+};
+struct MlpLayerArgs {
+    int K, N;            // N padded to a multiple of 16 (hidden layers: of 32)
+    int act;             // activation between this layer and the next (hidden layers)
+    const float* packed; // mlp_pack_kernel's output for this layer
+    float* z_out;        // optional [rows x N] pre-activations (bias included)
+};
+struct MlpChainArgs {
+    int n_layers, n_outs;
+    MlpLayerArgs layer[HB_MLP_MAX_LAYERS];
+    MlpOut out[HB_MLP_MAX_OUTS];
+};
+struct MlpArgs {
+    int rows, Kx, ldx, n_chains;
+    const float* x;      // [rows x ldx], the first Kx columns are the input features
+    MlpChainArgs chain[HB_MLP_MAX_CHAINS];
+};
+size_t mlp_packed_floats(int K, int n_pad);
+int launch_mlp_pack(const float* W, const float* bias, int n_true, int n_pad, int K, float* packed, cudaStream_t stream);
+int launch_mlp_chains(const MlpArgs& a, cudaStream_t stream);
+
 int launch_lbs_forward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
                        const float* rotmat, const float* scales, const float* transl, float smpl_scale,
                        float* out_xyz, float* out_rotq, float* out_scales, float* out_T, cudaStream_t stream);

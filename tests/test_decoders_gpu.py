@@ -1,0 +1,94 @@
+"""The decoder MLPs on tcgen05 (csrc/mlp_tc.cu, hugs_b200/decoders.py) against golden vectors generated from
+the reference's own modules (tests/golden/make_golden_decoders.py imports
+hugs/models/modules/decoders.py:24-110 on the CPU, float32).  Tolerances: forward outputs 2e-5 of the
+output's largest magnitude (3xTF32 products, fp32 accumulation in a different order than the CPU GEMM),
+gradients 1e-4 of the gradient's largest magnitude."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "decoders_golden.npz")
+
+
+def _golden():
+    return dict(np.load(GOLD))
+
+
+def _build(tag, g, device):
+    from hugs_b200 import decoders as D
+    m = {"appearance": lambda: D.AppearanceDecoder(n_features=96),
+         "geometry": lambda: D.GeometryDecoder(n_features=96),
+         "deformation": lambda: D.DeformationDecoder(n_features=96, disable_posedirs=True)}[tag]()
+    sd = {k[len(tag) + 7:]: torch.from_numpy(v) for k, v in g.items() if k.startswith(tag + "/param/")}
+    m.load_state_dict(sd)   # same keys as the reference's state_dict
+    return m.to(device)
+
+
+def test_state_dict_keys_are_the_reference_ones():
+    g = _golden()
+    for tag in ("appearance", "geometry", "deformation"):
+        m = _build(tag, g, "cpu")
+        want = sorted(k[len(tag) + 7:] for k in g if k.startswith(tag + "/param/"))
+        assert sorted(m.state_dict().keys()) == want
+
+
+def _close(a, b, tol):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.abs(a - b).max()) <= tol * max(float(np.abs(b).max()), 1e-30)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["appearance", "geometry", "deformation"])
+def test_decoder_forward_and_backward_match_reference_golden(tag):
+    g = _golden()
+    m = _build(tag, g, "cuda")
+    x = torch.from_numpy(g["x"]).cuda().requires_grad_(True)
+    res = m(x)
+    keys = [k[len(tag) + 5:] for k in g if k.startswith(tag + "/out/")]
+    assert sorted(k for k, v in res.items() if v is not None) == sorted(keys)
+    loss = 0.0
+    for k in keys:
+        assert res[k].shape == g["%s/out/%s" % (tag, k)].shape
+        assert _close(res[k].detach().cpu().numpy(), g["%s/out/%s" % (tag, k)], 2e-5), k
+        loss = loss + (res[k] * torch.from_numpy(g["%s/w/%s" % (tag, k)]).cuda()).sum()
+    loss.backward()
+    assert _close(x.grad.cpu().numpy(), g[tag + "/dx"], 1e-4)
+    for name, p in m.named_parameters():
+        assert p.grad is not None, name
+        assert _close(p.grad.cpu().numpy(), g["%s/grad/%s" % (tag, name)], 1e-4), name
+
+
+@pytest.mark.gpu
+def test_decode_all_is_one_launch_and_equals_the_separate_calls():
+    from hugs_b200 import _native, decoders as D
+    g = _golden()
+    app, geo, dfm = (_build(t, g, "cuda") for t in ("appearance", "geometry", "deformation"))
+    x = torch.from_numpy(g["x"]).cuda()
+    sep = (app(x), geo(x), dfm(x))
+    torch.cuda.synchronize()
+    _native.launch_count(1)
+    a, b, c = D.decode_all(x, app, geo, dfm)
+    torch.cuda.synchronize()
+    launches = _native.launch_count(0)
+    assert launches == 10 + 1     # one weight-packing launch per (concatenated) Linear, ONE fused launch for the rest
+    for got, want in zip((a, b, c), sep):
+        for k, v in want.items():
+            assert (got[k] is None and v is None) or torch.equal(got[k], v), k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rows", [0, 1, 127, 128, 129, 110_210])
+def test_decoder_row_counts(rows):
+    """ragged tiles, and the model's own size against torch's fp32 evaluation of the same module"""
+    g = _golden()
+    geo = _build("geometry", g, "cuda")
+    x = torch.randn(rows, 96, device="cuda", generator=torch.Generator(device="cuda").manual_seed(rows + 1))
+    got = geo(x)
+    h = geo.net(x)
+    want = {"xyz": geo.xyz[1](h), "rotations": geo.rotations[1](h), "scales": torch.nn.functional.gelu(geo.scales[1](h))}
+    for k, v in want.items():
+        assert got[k].shape == v.shape
+        if rows:
+            assert _close(got[k].detach().cpu().numpy(), v.detach().cpu().numpy(), 2e-5), k
