@@ -507,6 +507,32 @@ int hugs_b200_mlp_pack(const float* W, const float* bias, int n_true, int n_pad,
                        hugs_b200_stream_t stream);
 int hugs_b200_mlp_chains_forward(int rows, const float* x, int ldx, int Kx, int n_chains,
                                  const hugs_b200_mlp_chain* chains, hugs_b200_stream_t stream);
+/* Backward of the same chains (what autograd runs through the reference's Linear / GELU modules): from the
+ * gradients of the head outputs and the pre-activations the forward call saved, per layer
+ * dW^T [K, N] and db [N] are ADDED to caller-zeroed buffers (N: the layer's width rounded up to 32; the
+ * caller transposes / trims) and every chain writes its share of dL/dx [rows, Kx].  packed_t: the layer's
+ * weight through hugs_b200_mlp_pack_t (W^T, split for 3xTF32). */
+typedef struct hugs_b200_mlp_bwd_out {
+    const float* dptr;      /* NULL: this output has no gradient */
+    int ld, col0, ncols, act;
+} hugs_b200_mlp_bwd_out;
+typedef struct hugs_b200_mlp_bwd_layer {
+    int K, N;
+    const float* packed_t;
+    const float* z_prev;    /* [rows, K] pre-activations of the layer below; NULL for the first layer */
+    float* dWt;             /* [K, N] */
+    float* db;              /* [N] */
+} hugs_b200_mlp_bwd_layer;
+typedef struct hugs_b200_mlp_bwd_chain {
+    int n_layers, n_outs;
+    hugs_b200_mlp_bwd_layer layer[4];
+    hugs_b200_mlp_bwd_out out[3];
+    const float* z_head;    /* [rows, N_head] */
+    float* dx;              /* [rows, Kx] or NULL */
+} hugs_b200_mlp_bwd_chain;
+int hugs_b200_mlp_pack_t(const float* W, int n_true, int k_true, int n_pad, float* packed, hugs_b200_stream_t stream);
+int hugs_b200_mlp_chains_backward(int rows, const float* x, int ldx, int Kx, int n_chains,
+                                  const hugs_b200_mlp_bwd_chain* chains, hugs_b200_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Densification statistics after a backward pass, one launch, no host sync.

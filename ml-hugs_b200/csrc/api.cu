@@ -1247,6 +1247,47 @@ int hugs_b200_mlp_chains_forward(int rows, const float* x, int ldx, int Kx, int 
     return launch_mlp_chains(a, static_cast<cudaStream_t>(stream));
 }
 
+int hugs_b200_mlp_pack_t(const float* W, int n_true, int k_true, int n_pad, float* packed, hugs_b200_stream_t stream) {
+    if (!W || !packed || n_true <= 0) {
+        set_error("mlp_pack_t: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    return launch_mlp_pack_t(W, n_true, k_true, n_pad, packed, static_cast<cudaStream_t>(stream));
+}
+
+int hugs_b200_mlp_chains_backward(int rows, const float* x, int ldx, int Kx, int n_chains,
+                                  const hugs_b200_mlp_bwd_chain* chains, hugs_b200_stream_t stream) {
+    if (rows < 0 || n_chains < 1 || n_chains > HB_MLP_MAX_CHAINS || !chains || (rows > 0 && !x)) {
+        set_error("mlp_chains_backward: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    MlpBwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.rows = rows;
+    a.x = x;
+    a.ldx = ldx;
+    a.Kx = Kx;
+    a.n_chains = n_chains;
+    for (int c = 0; c < n_chains; c++) {
+        const hugs_b200_mlp_bwd_chain& src = chains[c];
+        if (src.n_layers < 1 || src.n_layers > HB_MLP_MAX_LAYERS || src.n_outs < 0 || src.n_outs > HB_MLP_MAX_OUTS) {
+            set_error("mlp_chains_backward: chain %d: bad layer / output count", c);
+            return HUGS_B200_EINVAL;
+        }
+        MlpBwdChainArgs& dst = a.chain[c];
+        dst.n_layers = src.n_layers;
+        dst.n_outs = src.n_outs;
+        dst.z_head = src.z_head;
+        dst.dx = src.dx;
+        for (int l = 0; l < src.n_layers; l++)
+            dst.layer[l] = MlpBwdLayerArgs{src.layer[l].K, src.layer[l].N, src.layer[l].packed_t, src.layer[l].z_prev,
+                                           src.layer[l].dWt, src.layer[l].db};
+        for (int o = 0; o < src.n_outs; o++)
+            dst.out[o] = MlpBwdOut{src.out[o].dptr, src.out[o].ld, src.out[o].col0, src.out[o].ncols, src.out[o].act};
+    }
+    return launch_mlp_chains_backward(a, static_cast<cudaStream_t>(stream));
+}
+
 int hugs_b200_densification_stats(int n, const int* radii, const float* grad_means2D, int grad_stride,
                                   float* xyz_gradient_accum, float* denom, float* max_radii2D,
                                   hugs_b200_stream_t stream) {

@@ -252,6 +252,31 @@ struct MlpArgs {
 size_t mlp_packed_floats(int K, int n_pad);
 int launch_mlp_pack(const float* W, const float* bias, int n_true, int n_pad, int K, float* packed, cudaStream_t stream);
 int launch_mlp_chains(const MlpArgs& a, cudaStream_t stream);
+struct MlpBwdOut {       // gradient of one head output: dL/dout[row * ld + (col - col0)]
+    const float* dptr;   // null: no gradient for this output
+    int ld, col0, ncols, act;
+};
+struct MlpBwdLayerArgs {
+    int K, N;               // N padded to a multiple of 32
+    const float* packed_t;  // launch_mlp_pack_t of the layer's weight
+    const float* z_prev;    // [rows x K] pre-activations of the layer below (null for the first layer)
+    float* dWt;             // [K x N] += dW^T (zeroed by the caller)
+    float* db;              // [N] += db
+};
+struct MlpBwdChainArgs {
+    int n_layers, n_outs;
+    MlpBwdLayerArgs layer[HB_MLP_MAX_LAYERS];
+    MlpBwdOut out[HB_MLP_MAX_OUTS];
+    const float* z_head;    // [rows x N_head] pre-activations of the last layer
+    float* dx;              // [rows x Kx] this chain's share of dL/dx (or null)
+};
+struct MlpBwdArgs {
+    int rows, Kx, ldx, n_chains;
+    const float* x;
+    MlpBwdChainArgs chain[HB_MLP_MAX_CHAINS];
+};
+int launch_mlp_pack_t(const float* W, int n_true, int k_true, int n_pad, float* packed, cudaStream_t stream);
+int launch_mlp_chains_backward(const MlpBwdArgs& a, cudaStream_t stream);
 
 int launch_lbs_forward(int F, int N, int J, const float* A, const float* xyz, const float* weights,
                        const float* rotmat, const float* scales, const float* transl, float smpl_scale,

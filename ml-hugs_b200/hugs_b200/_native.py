@@ -162,9 +162,25 @@ class MlpChain(C.Structure):
     _fields_ = [("n_layers", i32), ("n_outs", i32), ("layer", MlpLayer * 4), ("out", MlpOut * 3)]
 
 
+class MlpBwdOut(C.Structure):
+    _fields_ = [("dptr", C.c_void_p), ("ld", i32), ("col0", i32), ("ncols", i32), ("act", i32)]
+
+
+class MlpBwdLayer(C.Structure):
+    _fields_ = [("K", i32), ("N", i32), ("packed_t", C.c_void_p), ("z_prev", C.c_void_p), ("dWt", C.c_void_p),
+                ("db", C.c_void_p)]
+
+
+class MlpBwdChain(C.Structure):
+    _fields_ = [("n_layers", i32), ("n_outs", i32), ("layer", MlpBwdLayer * 4), ("out", MlpBwdOut * 3),
+                ("z_head", C.c_void_p), ("dx", C.c_void_p)]
+
+
 MLP_ACT_NONE, MLP_ACT_GELU, MLP_ACT_SIGMOID = 0, 1, 2
 mlp_packed_floats = _sig("hugs_b200_mlp_packed_floats", C.c_size_t, [i32, i32])
 mlp_pack = _sig("hugs_b200_mlp_pack", i32, [fp, fp, i32, i32, i32, fp, fp])
+mlp_pack_t = _sig("hugs_b200_mlp_pack_t", i32, [fp, i32, i32, i32, fp, fp])
+mlp_chains_backward = _sig("hugs_b200_mlp_chains_backward", i32, [i32, fp, i32, i32, i32, C.POINTER(MlpBwdChain), fp])
 mlp_chains_forward = _sig("hugs_b200_mlp_chains_forward", i32, [i32, fp, i32, i32, i32, C.POINTER(MlpChain), fp])
 
 l1_ssim_forward = _sig("hugs_b200_l1_ssim_forward", i32, [i32, i32, i32, fp, fp, fp, fp, fp])
@@ -237,6 +253,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_layer_bytes", "hugs_b200_layer_layout_of", "hugs_b200_layer_forward", "hugs_b200_rasterize_backward_layer",
     "hugs_b200_rasterize_backward_seg2_layer", "hugs_b200_rasterize_backward_seg2_ex",
     "hugs_b200_mlp_packed_floats", "hugs_b200_mlp_pack", "hugs_b200_mlp_chains_forward",
+    "hugs_b200_mlp_pack_t", "hugs_b200_mlp_chains_backward",
 ]
 
 

@@ -7,8 +7,9 @@ dictionaries -- with ``forward`` running on ``hugs_b200_mlp_chains_forward`` (cs
 accumulators in TMEM, exact GELU in the epilogue).  ``decode_all`` evaluates the three decoders of
 hugs/models/hugs_trimlp.py:205-238 on the tri-plane features in ONE launch.
 
-Backward: the kernel saves every layer's pre-activations; the gradient GEMMs (dX = dZ W, dW = dZ^T A) are
-still torch matmuls on those saved tensors (library GEMMs), not yet tcgen05 kernels of this repository.
+Backward: the forward kernel saves every layer's pre-activations and ``hugs_b200_mlp_chains_backward`` runs
+the whole chain backwards on the same tiles: dA = dZ W (3xTF32), dW^T = A^T dZ (both operands MN-major out
+of the same shared-memory tiles), db by warp shuffles, GELU' in the epilogue.
 Only ``act='gelu'`` (the reference's default and the release configuration) takes the fused path; other
 activations fall back to the reference's own module arithmetic in torch.
 """
@@ -34,9 +35,9 @@ def _stream(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
-def _pad(n, hidden):
-    m = 32 if hidden else 16
-    return (n + m - 1) // m * m
+def _pad(n, hidden=True):
+    # every layer's width is rounded up to 32: the backward kernel walks the widths in 32-element K blocks
+    return (n + 31) // 32 * 32
 
 
 class _Spec:
@@ -61,7 +62,7 @@ class _MlpChains(torch.autograd.Function):
         device = x.device
         x = x.float().contiguous()
         rows, Kx = int(x.shape[0]), int(x.shape[1])
-        need_grad = any(t.requires_grad for t in (x,) + params)
+        need_grad = any(ctx.needs_input_grad)   # all False under torch.no_grad(): no pre-activations are kept
         chains = (N.MlpChain * len(meta))()
         keep, outs, zs = [], [], []
         p = 0
@@ -75,7 +76,7 @@ class _MlpChains(torch.autograd.Function):
                     W, b = params[p].detach().float().contiguous(), params[p + 1].detach().float().contiguous()
                     p += 2
                     n_true = int(W.shape[0])
-                    n_pad = _pad(n_true, hidden=(l + 1 < n_layers))
+                    n_pad = _pad(n_true)
                     packed = torch.empty(int(N.mlp_packed_floats(K, n_pad)), dtype=torch.float32, device=device)
                     N.check(N.mlp_pack(W.data_ptr(), b.data_ptr(), n_true, n_pad, K, packed.data_ptr(), _stream(device)),
                             "mlp_pack")
@@ -111,39 +112,55 @@ class _MlpChains(torch.autograd.Function):
         saved = ctx.saved_tensors
         x, params = saved[0], saved[1:1 + n_params]
         n_z = sum(n for n, _ in meta)
-        zs, outs = saved[1 + n_params:1 + n_params + n_z], saved[1 + n_params + n_z:]
-        dx = torch.zeros_like(x)
-        dparams = [None] * n_params
+        zs = saved[1 + n_params:1 + n_params + n_z]
+        device = x.device
+        rows, Kx = int(x.shape[0]), int(x.shape[1])
+        chains = (N.MlpBwdChain * len(meta))()
+        keep, dWts, dbs, dxs = [], [], [], []
         p = zi = oi = 0
-        for n_layers, slices in meta:
-            Ws = [params[p + 2 * l] for l in range(n_layers)]
-            z = zs[zi:zi + n_layers]
-            # head: dL/dz of the concatenated heads (padded columns carry no gradient)
-            n_head = int(Ws[-1].shape[0])
-            dz = torch.zeros(x.shape[0], n_head, dtype=torch.float32, device=x.device)
-            for s, (_, col0, ncols, act) in enumerate(slices):
-                g = grads[oi + s]
-                if g is None:
-                    continue
-                zz = z[-1][:, col0:col0 + ncols]
-                if act == N.MLP_ACT_GELU:
-                    g = g * _gelu_grad(zz)
-                elif act == N.MLP_ACT_SIGMOID:
-                    y = outs[oi + s]
-                    g = g * y * (1.0 - y)
-                dz[:, col0:col0 + ncols] = g
-            for l in range(n_layers - 1, -1, -1):
-                a_prev = x if l == 0 else F.gelu(z[l - 1][:, :Ws[l].shape[1]])
-                dparams[p + 2 * l] = dz.t() @ a_prev
-                dparams[p + 2 * l + 1] = dz.sum(0)
-                da = dz @ Ws[l]
-                if l == 0:
-                    dx += da
-                else:
-                    dz = da * _gelu_grad(z[l - 1][:, :Ws[l].shape[1]])
-            p += 2 * n_layers
-            zi += n_layers
-            oi += len(slices)
+        with torch.cuda.device(device):
+            for c, (n_layers, slices) in enumerate(meta):
+                ch = chains[c]
+                ch.n_layers, ch.n_outs = n_layers, len(slices)
+                K = Kx
+                for l in range(n_layers):
+                    W = params[p + 2 * l].float().contiguous()
+                    n_true, n_pad = int(W.shape[0]), _pad(int(W.shape[0]))
+                    packed_t = torch.empty(int(N.mlp_packed_floats(n_pad, K)), dtype=torch.float32, device=device)
+                    N.check(N.mlp_pack_t(W.data_ptr(), n_true, K, n_pad, packed_t.data_ptr(), _stream(device)), "mlp_pack_t")
+                    dWt = torch.zeros(K, n_pad, dtype=torch.float32, device=device)
+                    db = torch.zeros(n_pad, dtype=torch.float32, device=device)
+                    keep += [W, packed_t]
+                    dWts.append((dWt, n_true))
+                    dbs.append((db, n_true))
+                    L = ch.layer[l]
+                    L.K, L.N, L.packed_t = K, n_pad, packed_t.data_ptr()
+                    L.z_prev = zs[zi + l - 1].data_ptr() if l > 0 else None
+                    L.dWt, L.db = dWt.data_ptr(), db.data_ptr()
+                    K = n_pad
+                ch.z_head = zs[zi + n_layers - 1].data_ptr()
+                dx = torch.empty(rows, Kx, dtype=torch.float32, device=device)
+                dxs.append(dx)
+                ch.dx = dx.data_ptr()
+                for s, (_, col0, ncols, act) in enumerate(slices):
+                    g = grads[oi + s]
+                    if g is not None:
+                        g = g.float().contiguous()
+                        keep.append(g)
+                    ch.out[s].dptr = g.data_ptr() if g is not None else None
+                    ch.out[s].ld, ch.out[s].col0, ch.out[s].ncols, ch.out[s].act = ncols, col0, ncols, act
+                p += 2 * n_layers
+                zi += n_layers
+                oi += len(slices)
+            if rows > 0:
+                N.check(N.mlp_chains_backward(rows, x.data_ptr(), Kx, Kx, len(meta), chains, _stream(device)),
+                        "mlp_chains_backward")
+        dparams = []
+        for (dWt, n_true), (db, _) in zip(dWts, dbs):
+            dparams += [dWt.t()[:n_true].contiguous(), db[:n_true]]
+        dx = dxs[0] if len(dxs) == 1 else torch.stack(dxs).sum(0)
+        if rows == 0:
+            dx = torch.zeros_like(x)
         return (dx, None, *dparams)
 
 

@@ -1,8 +1,11 @@
 """The decoder MLPs on tcgen05 (csrc/mlp_tc.cu, hugs_b200/decoders.py) against golden vectors generated from
 the reference's own modules (tests/golden/make_golden_decoders.py imports
 hugs/models/modules/decoders.py:24-110 on the CPU, float32).  Tolerances: forward outputs 2e-5 of the
-output's largest magnitude (3xTF32 products, fp32 accumulation in a different order than the CPU GEMM),
-gradients 1e-4 of the gradient's largest magnitude."""
+output's largest magnitude (3xTF32 products, fp32 accumulation in a different order than the CPU GEMM);
+gradients 1e-3 of the gradient's largest magnitude (BASELINE.json's bar for gradients): the backward kernel
+rounds dZ and the activations to tf32 (nearest) for its two products -- measured 2e-4 .. 5e-4 on the 333-row
+golden case and 2e-4 .. 5e-4 at the model's 110 210 rows (a weight gradient is a sum of zero-mean products:
+it grows like the square root of the row count, and so does the rounding error -- the ratio stays ~2^-12 * sqrt 2)."""
 import os
 
 import numpy as np
@@ -54,10 +57,10 @@ def test_decoder_forward_and_backward_match_reference_golden(tag):
         assert _close(res[k].detach().cpu().numpy(), g["%s/out/%s" % (tag, k)], 2e-5), k
         loss = loss + (res[k] * torch.from_numpy(g["%s/w/%s" % (tag, k)]).cuda()).sum()
     loss.backward()
-    assert _close(x.grad.cpu().numpy(), g[tag + "/dx"], 1e-4)
+    assert _close(x.grad.cpu().numpy(), g[tag + "/dx"], 1e-3)
     for name, p in m.named_parameters():
         assert p.grad is not None, name
-        assert _close(p.grad.cpu().numpy(), g["%s/grad/%s" % (tag, name)], 1e-4), name
+        assert _close(p.grad.cpu().numpy(), g["%s/grad/%s" % (tag, name)], 1e-3), name
 
 
 @pytest.mark.gpu
@@ -92,3 +95,46 @@ def test_decoder_row_counts(rows):
         assert got[k].shape == v.shape
         if rows:
             assert _close(got[k].detach().cpu().numpy(), v.detach().cpu().numpy(), 2e-5), k
+
+
+@pytest.mark.gpu
+def test_decoder_full_size_gradients():
+    """110 210 rows, all three decoders in one launch each way, against torch autograd through the same
+    modules' fp32 arithmetic (torch.backends.cuda.matmul.allow_tf32 is off)."""
+    from hugs_b200 import decoders as D
+    assert not torch.backends.cuda.matmul.allow_tf32
+    g = _golden()
+    mods = [_build(t, g, "cuda") for t in ("appearance", "geometry", "deformation")]
+    x0 = torch.randn(110_210, 96, device="cuda", generator=torch.Generator(device="cuda").manual_seed(3)) * 0.7
+
+    def run(fused):
+        for m in mods:
+            m.zero_grad()
+        x = x0.clone().requires_grad_(True)
+        if fused:
+            a, b, c = D.decode_all(x, *mods[:2], mods[2])
+        else:
+            app, geo, dfm = mods
+            h = app.net(x)
+            a = {"shs": app.shs(h), "opacity": app.opacity(h)}
+            h = geo.net(x)
+            b = {"xyz": geo.xyz[1](h), "rotations": geo.rotations[1](h),
+                 "scales": torch.nn.functional.gelu(geo.scales[1](h))}
+            h = dfm.net(x)
+            c = {"lbs_weights": torch.nn.functional.gelu(dfm.skinning(torch.nn.functional.gelu(dfm.skinning_linear(h))))}
+        outs = [a["shs"], a["opacity"], b["xyz"], b["rotations"], b["scales"], c["lbs_weights"]]
+        gen = torch.Generator(device="cuda").manual_seed(11)
+        loss = sum((o * torch.randn(o.shape, device="cuda", generator=gen)).sum() for o in outs)
+        loss.backward()
+        grads = {"x": x.grad.clone()}
+        for t, m in zip(("a", "g", "d"), mods):
+            for n, p in m.named_parameters():
+                grads[t + "." + n] = p.grad.clone()
+        return [o.detach() for o in outs], grads
+
+    outs_f, gf = run(True)
+    outs_t, gt = run(False)
+    for a, b in zip(outs_f, outs_t):
+        assert _close(a.cpu().numpy(), b.cpu().numpy(), 2e-5)
+    for k in gt:
+        assert _close(gf[k].cpu().numpy(), gt[k].cpu().numpy(), 1e-3), k

@@ -42,7 +42,22 @@ def main():
         with torch.no_grad():
             D.decode_all(x, app, geo, dfm)
 
-    out = {"rows": N, "torch_fp32_ms": timed(torch_path), "fused_ms_with_packing": timed(fused)}
+    xg = x.clone().requires_grad_(True)
+
+    def torch_train():
+        h = app.net(xg); o = [app.shs(h), app.opacity(h)]
+        o += [geo.xyz(xg), geo.rotations(xg), torch.nn.functional.gelu(geo.scales(xg))]
+        h = dfm.net(xg)
+        o.append(torch.nn.functional.gelu(dfm.skinning(torch.nn.functional.gelu(dfm.skinning_linear(h)))))
+        sum(t.sum() for t in o).backward()
+
+    def fused_train():
+        a, b, c = D.decode_all(xg, app, geo, dfm)
+        (a["shs"].sum() + a["opacity"].sum() + b["xyz"].sum() + b["rotations"].sum() + b["scales"].sum()
+         + c["lbs_weights"].sum()).backward()
+
+    out = {"rows": N, "torch_fp32_ms": timed(torch_path), "fused_ms_with_packing": timed(fused),
+           "torch_fp32_fwd_bwd_ms": timed(torch_train, 20), "fused_fwd_bwd_ms": timed(fused_train, 20)}
     # the fused launch alone (weights already packed): stage a call by hand
     specs = [d.spec() for d in (app, geo, dfm)]
     with torch.no_grad():
