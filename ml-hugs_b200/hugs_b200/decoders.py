@@ -288,3 +288,26 @@ def decode_all(tri_feats, appearance_dec, geometry_dec, deformation_dec=None):
     if deformation_dec is not None:
         deform = {'lbs_weights': outs[2]['lbs_weights'], 'posedirs': None}
     return outs[0], outs[1], deform
+
+
+def canon_forward(triplane, xyz, appearance_dec, geometry_dec, deformation_dec=None, scaling_multiplier=1.0):
+    """hugs/models/hugs_trimlp.py:205-238 (``canon_forward``) on this repository's kernels: tri-plane features
+    (``hugs_b200.triplane.TriPlane``: one gather kernel) -> the three decoders (ONE tcgen05 launch) -> the
+    reference's result dictionary (``xyz_offsets``, ``scales``, ``rot6d_canon``, ``shs`` [N,16,3], ``opacity``,
+    ``lbs_weights`` after softmax(./0.1), ``posedirs``).  ``hugs_b200.deform_gaussians`` takes it from there
+    (hugs_trimlp.py:470-518)."""
+    tri_feats = triplane(xyz)
+    appearance_out, geometry_out, deformation_out = decode_all(tri_feats, appearance_dec, geometry_dec, deformation_dec)
+    lbs_weights = posedirs = None
+    if deformation_out is not None:
+        lbs_weights = F.softmax(deformation_out['lbs_weights'] / 0.1, dim=-1)
+        posedirs = deformation_out['posedirs']
+    return {
+        'xyz_offsets': geometry_out['xyz'],
+        'scales': geometry_out['scales'] * scaling_multiplier,
+        'rot6d_canon': geometry_out['rotations'],
+        'shs': appearance_out['shs'].reshape(-1, 16, 3),
+        'opacity': appearance_out['opacity'],
+        'lbs_weights': lbs_weights,
+        'posedirs': posedirs,
+    }

@@ -138,3 +138,22 @@ def test_decoder_full_size_gradients():
         assert _close(a.cpu().numpy(), b.cpu().numpy(), 2e-5)
     for k in gt:
         assert _close(gf[k].cpu().numpy(), gt[k].cpu().numpy(), 1e-3), k
+
+
+@pytest.mark.gpu
+def test_canon_forward_keys_and_shapes():
+    """tri-plane gather -> decoders -> the dictionary of hugs_trimlp.py:226-238"""
+    from hugs_b200 import decoders as D
+    from hugs_b200.triplane import TriPlane
+    g = _golden()
+    app, geo, dfm = (_build(t, g, "cuda") for t in ("appearance", "geometry", "deformation"))
+    tri = TriPlane(32, resX=64, resY=64, resZ=64).cuda()
+    xyz = (torch.rand(5000, 3, device="cuda") - 0.5) * 0.9
+    out = D.canon_forward(tri, xyz, app, geo, dfm, scaling_multiplier=0.5)
+    assert set(out) == {"xyz_offsets", "scales", "rot6d_canon", "shs", "opacity", "lbs_weights", "posedirs"}
+    assert out["shs"].shape == (5000, 16, 3) and out["opacity"].shape == (5000, 1)
+    assert out["xyz_offsets"].shape == (5000, 3) and out["rot6d_canon"].shape == (5000, 6) and out["scales"].shape == (5000, 3)
+    assert out["lbs_weights"].shape == (5000, 24) and out["posedirs"] is None
+    assert torch.allclose(out["lbs_weights"].sum(-1), torch.ones(5000, device="cuda"), atol=1e-5)
+    feats = tri(xyz)
+    assert torch.equal(out["scales"], geo(feats)["scales"] * 0.5)

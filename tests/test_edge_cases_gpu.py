@@ -176,3 +176,18 @@ def test_workspaces_are_freed_without_the_cyclic_gc():
     finally:
         gc.enable()
     assert grown < (1 << 20), "device memory grew by %d bytes over 10 calls with the cyclic GC off" % grown
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_devices_in_one_process():
+    """Per-device state of the library (count events, stage-timer event pools, shared-memory opt-ins): a
+    process that rasterizes on cuda:0 and then on cuda:1 gets the same image on both."""
+    import diff_gaussian_rasterization as dgr
+    imgs = []
+    for dev in ("cuda:0", "cuda:1"):
+        sc = scenes.make_scene(3000, 1000, 320, 200, 300.0, seed=77, device=dev)
+        with torch.cuda.device(dev):
+            out = scenes.run_module(sc, dgr, backward=True)
+            torch.cuda.synchronize(dev)
+        imgs.append(out["color"].cpu())
+    assert torch.equal(imgs[0], imgs[1])
