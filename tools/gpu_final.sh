@@ -1,15 +1,14 @@
 #!/bin/bash
-# Round-end check on one GPU: smoke, GPU suite, both bench arms with default flags.  usage: bash tools/gpu_final.sh TAG
-TAG=${1:-rXX}
-O=gpurun_out
-mkdir -p $O
-python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $O/${TAG}_smoke.log
-timeout 1500 python -m pytest tests -m gpu -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -2 $O/${TAG}_pytest.log
-timeout 900 python bench.py --impl reference --steps 10 --warmup 3 > $O/${TAG}_ref.json 2> $O/${TAG}_ref.err; echo "ref rc=$?"
-timeout 900 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"
+# What the driver runs at round end, on one box: GPU tests, smoke(), both bench arms with default arguments.
+TAG=${1:-rXX}; O=gpurun_out; mkdir -p $O
+timeout 1800 python -m pytest tests -m gpu -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 $O/${TAG}_pytest.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $O/${TAG}_smoke.log
+timeout 900 python bench.py --impl reference > $O/${TAG}_bench_ref.json 2> $O/${TAG}_bench_ref.err; echo "ref rc=$?"
+timeout 900 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"; tail -2 $O/${TAG}_bench.err
 python - <<PY
 import json
-r=json.load(open("$O/${TAG}_ref.json")); d=json.load(open("$O/${TAG}_bench.json"))
-print("ref", r.get("value"), r.get("e2e",{}).get("value"), r.get("ms_per_step"))
-print("ours", d["value"], d["e2e"]["value"], d["ms_per_step"], d["roofline"]["kernel"], d["roofline"]["frac"], d["cpu_baseline"]["value"], d["gpu_launches"], d["clocks"])
+a=json.load(open("$O/${TAG}_bench.json")); r=json.load(open("$O/${TAG}_bench_ref.json"))
+print("ours", a["value"], a["e2e"]["value"], "ref", r["value"], r["e2e"]["value"], "ratio", a["value"]/r["value"], a["e2e"]["value"]/r["e2e"]["value"])
+print(a["roofline"]["kernel"], a["roofline"]["bound"], a["roofline"]["frac"], a["roofline"].get("issue_frac"), a["cpu_baseline"])
+print({k:v["ms"] for k,v in a["stages"].items()})
 PY
