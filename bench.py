@@ -240,11 +240,12 @@ class Replica:
         # models as two segments
         self.P = sum(t.shape[0] for t in opac)
         self.buf = None
-        # HB_TWO_SEG=1: hand the rasterizer the two models as two segments with gradient sinks on every
-        # direct input.  Measured (profiles/r02_i): not faster on one GPU -- with two streams per rank the
-        # torch.cat / AccumulateGrad kernels it removes already run beside the issue-bound blend kernels of the
-        # other stream, while the sinks' reductions and the per-segment launches add 0.04 ms of kernel time
-        self.two_seg = self.render2 is not None and self.training and os.environ.get("HB_TWO_SEG", "1") == "1"
+        # human + scene: the rasterizer gets the two models as two segments (no torch.cat) with gradient sinks on
+        # every direct input (no per-view AccumulateGrad kernels); HB_TWO_SEG=0 switches back to the
+        # concatenated call for comparison (measured: 751 vs 766 frames/s, 706 vs 742 end to end)
+        # (a single model -- human only -- has nothing to concatenate: the plain rasterizer call is less host work)
+        self.two_seg = (self.render2 is not None and self.training and self.n_human > 0 and self.n_scene > 0
+                        and os.environ.get("HB_TWO_SEG", "1") == "1")
         if self.two_seg:
             self._init_two_segments(wl, device, leaf)
         else:
