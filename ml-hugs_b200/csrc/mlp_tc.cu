@@ -13,13 +13,15 @@
 //   * operands live in the canonical K-major SWIZZLE_128B layout (rows of 32 tf32 = 128 bytes, 8-row
 //     groups of 1024 bytes, 16-byte chunk c of row r stored at chunk c ^ (r & 7)); one K block of 32 is one
 //     16 KB tile.  The weights are split and laid out ONCE per call by mlp_pack_kernel (they are 0.4 MB and
-//     stay in L2), so a CTA stages a weight block with plain 16-byte copies, double-buffered against the
-//     MMAs of the previous block (tcgen05.commit -> mbarrier says when a buffer may be overwritten);
-//   * epilogue: thread t owns row t (TMEM lane t): tcgen05.ld 16 columns at a time, + bias, exact GELU
-//     (erf, as torch.nn.GELU()), then either hi/lo split straight back into the A tiles of the next layer
+//     stay in L2), so a CTA stages a weight block with cp.async, three stages deep: blocks j + 1 and j + 2
+//     (possibly the next layer's) are in flight while block j is multiplied (tcgen05.commit -> mbarrier says
+//     when a stage may be overwritten);
+//   * epilogue: a thread owns a row (TMEM lane) and a quarter of the columns: tcgen05.ld 16 columns at a
+//     time, + bias, GELU with erf to 1.5e-7 (torch.nn.GELU() is the erf form), then either hi/lo split
+//     straight back into the A tiles of the next layer
 //     or, for the heads, row-contiguous stores to the outputs; optionally the pre-activations are saved
 //     for the backward pass.
-// Shared memory: A_hi 64 KB + A_lo 64 KB + two weight stages of 32 KB = 192 KB -> one CTA per SM;
+// Shared memory: A_hi 64 KB + A_lo 64 KB + three weight stages of 32 KB = 224 KB -> one CTA per SM;
 // TMEM: 128 columns.
 #include "common.cuh"
 
@@ -34,7 +36,8 @@ constexpr int kTileRows = 128;
 constexpr int kKB = 32;                       // tf32 per 128-byte swizzle row = one K block
 constexpr uint32_t kBlockBytes = 128 * 128;   // one K block of a 128-row operand tile
 constexpr uint32_t kOffAhi = 0, kOffAlo = 4 * kBlockBytes, kOffW = 8 * kBlockBytes;   // W: [2 stages][hi, lo]
-constexpr uint32_t kOffBias = kOffW + 4 * kBlockBytes;
+constexpr int kFwdStages = 3;                  // weight stages of the forward kernel (the backward one uses two)
+constexpr uint32_t kOffBias = kOffW + 2 * kFwdStages * kBlockBytes;
 constexpr uint32_t kOffBar = kOffBias + 512;
 constexpr uint32_t kMlpSmemBytes = kOffBar + 64 + 1024;   // + slack for the 1024-byte alignment of the base
 constexpr int kTmemCols = 128;
@@ -105,7 +108,24 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
 #pragma unroll
     for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
-__device__ __forceinline__ float gelu_exact(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// erf by Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, far inside the 2e-5 the outputs are held to):
+// branch-free, one reciprocal and one exponential -- libdevice's erff is a two-branch routine of ~45
+// instructions, and the epilogues (one GELU per activation) were bound by it.  e2 = exp(-x^2) is returned too:
+// the GELU derivative needs it.
+__device__ __forceinline__ float erf_as(float x, float& e2) {
+    const float ax = fabsf(x);
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, ax, 1.0f));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    e2 = __expf(-ax * ax);
+    return copysignf(1.0f - p * t * e2, x);
+}
+__device__ __forceinline__ float gelu_exact(float x) {
+    float e2;
+    return 0.5f * x * (1.0f + erf_as(x * 0.70710678118654752f, e2));
+}
 __device__ __forceinline__ float sigmoid_exact(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 }  // namespace
@@ -191,12 +211,10 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(const MlpArgs
     const int row0 = (int)blockIdx.x * kTileRows;
     const int row = row0 + (int)rloc;         // the row this thread owns in every epilogue
     const bool row_ok = row < a.rows;
-    const uint32_t bar[2] = {base + kOffBar, base + kOffBar + 8};
-    const uint32_t tmem_slot = base + kOffBar + 16;
+    const uint32_t tmem_slot = base + kOffBar + 32;
 
     if (tid == 0) {
-        mbar_init(bar[0], 1);
-        mbar_init(bar[1], 1);
+        for (uint32_t b = 0; b < (uint32_t)kFwdStages; b++) mbar_init(base + kOffBar + 8u * b, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {   // one warp allocates the accumulator columns and gives the permit back
@@ -244,14 +262,18 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(const MlpArgs
     first_blk[0] = 0;
     for (int l = 0; l < ch.n_layers; l++) first_blk[l + 1] = first_blk[l] + ch.layer[l].K / kKB;
     const int n_blk = first_blk[ch.n_layers];
-    uint32_t ncommit[2] = {0u, 0u};
+    // (scalars: an array indexed by the stage would live in local memory)
+    uint32_t nc0 = 0u, nc1 = 0u, nc2 = 0u;
+    auto ncommit = [&](uint32_t b) { return b == 0u ? nc0 : (b == 1u ? nc1 : nc2); };
+    auto bar_of = [&](uint32_t b) { return base + kOffBar + 8u * b; };
     int issued = 0;
-    auto request = [&](int j) {   // copies of chain block j -> stage j & 1 (after the MMAs that last read it)
+    auto request = [&](int j) {   // copies of chain block j -> stage j % 3 (after the MMAs that last read it)
         int l = 0;
         while (j >= first_blk[l + 1]) l++;
         const MlpLayerArgs& Lj = ch.layer[l];
-        const uint32_t b = (uint32_t)j & 1u;
-        if (ncommit[b] > 0u) mbar_wait(bar[b], (ncommit[b] - 1u) & 1u);
+        const uint32_t b = (uint32_t)j % (uint32_t)kFwdStages;
+        const uint32_t nc = ncommit(b);
+        if (nc > 0u) mbar_wait(bar_of(b), (nc - 1u) & 1u);
         const uint32_t t16 = (uint32_t)Lj.N * 8u;   // 16-byte words of one hi (or lo) weight tile
         const uint4* src = reinterpret_cast<const uint4*>(Lj.packed + (size_t)(j - first_blk[l]) * 2 * Lj.N * kKB);
         const uint32_t w_hi = base + kOffW + b * 2u * kBlockBytes, w_lo = w_hi + kBlockBytes;
@@ -263,6 +285,10 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(const MlpArgs
     };
     request(0);
     issued = 1;
+    if (n_blk > 1) {
+        request(1);
+        issued = 2;
+    }
     for (int l = 0; l < ch.n_layers; l++) {
         const MlpLayerArgs& L = ch.layer[l];
         const int nkb = L.K / kKB, N = L.N;
@@ -270,13 +296,16 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(const MlpArgs
         uint32_t last_b = 0;
         for (int kb = 0; kb < nkb; kb++) {
             const int j = first_blk[l] + kb;
-            const uint32_t b = (uint32_t)j & 1u;
+            const uint32_t b = (uint32_t)j % (uint32_t)kFwdStages;
             last_b = b;
-            if (issued <= j + 1 && j + 1 < n_blk) {   // next block (possibly the next layer's first) on its way
-                request(j + 1);
-                issued = j + 2;
+            if (issued <= j + 2 && j + 2 < n_blk) {   // two blocks ahead (possibly the next layer's) on their way
+                request(j + 2);
+                issued = j + 3;
             }
-            if (issued > j + 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
+            // groups still allowed in flight: the blocks after j that have been requested
+            const int ahead = issued - (j + 1);
+            if (ahead >= 2) asm volatile("cp.async.wait_group 2;" ::: "memory");
+            else if (ahead == 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
             else asm volatile("cp.async.wait_group 0;" ::: "memory");
             const uint32_t w_hi = base + kOffW + b * 2u * kBlockBytes, w_lo = w_hi + kBlockBytes;
             // generic-proxy writes (these and the epilogue's A tiles) -> visible to the tensor core's async proxy
@@ -294,12 +323,14 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(const MlpArgs
                     umma_tf32(tmem, dAl, dBh, idesc, 1u);
                     umma_tf32(tmem, dAh, dBl, idesc, 1u);
                 }
-                umma_commit(bar[b]);   // arrives when every MMA issued so far has completed
+                umma_commit(bar_of(b));   // arrives when every MMA issued so far has completed
             }
-            ncommit[b]++;
+            if (b == 0u) nc0++;
+            else if (b == 1u) nc1++;
+            else nc2++;
         }
         // the layer's accumulator is complete when the last commit has arrived
-        mbar_wait(bar[last_b], (ncommit[last_b] - 1u) & 1u);
+        mbar_wait(bar_of(last_b), (ncommit(last_b) - 1u) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
         // ---- epilogue: thread t <-> row t <-> TMEM lane t -----------------------------------------
@@ -434,7 +465,9 @@ constexpr uint32_t kOffR2 = 8 * kBlockBytes;
 constexpr int kBwdTmemCols = 256;
 
 __device__ __forceinline__ float gelu_grad(float z) {
-    return 0.5f * (1.0f + erff(z * 0.70710678118654752f)) + z * expf(-0.5f * z * z) * 0.3989422804014327f;
+    float e2;   // exp(-z^2 / 2), shared by the two terms
+    const float erf_v = erf_as(z * 0.70710678118654752f, e2);
+    return fmaf(z * 0.3989422804014327f, e2, 0.5f * (1.0f + erf_v));
 }
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
