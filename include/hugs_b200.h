@@ -31,13 +31,23 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define HUGS_B200_ABI_VERSION 9
+#define HUGS_B200_ABI_VERSION 10
 
 #define HUGS_B200_EINVAL   (-1)  /* bad argument (null pointer, negative size, ...)          */
 #define HUGS_B200_ENOMEM   (-2)  /* a resize callback returned NULL                          */
 #define HUGS_B200_EUNSUP   (-3)  /* unsupported configuration (e.g. SH degree > 3)           */
 
 /* Opaque CUDA stream handle (cudaStream_t). NULL = legacy default stream. */
+/* The `debug` argument of the rasterizer entry points is a flag word (0 / 1 keep the reference's meaning):
+ *   HUGS_B200_FLAG_DEBUG    synchronise after every stage and attribute asynchronous faults to it
+ *                           (CHECK_CUDA, cuda_rasterizer/auxiliary.h:166-173);
+ *   HUGS_B200_FLAG_CLAMP01  the renderer's clamp(image, 0, 1) (hugs/renderer/gs_renderer.py:153) in the blend
+ *                           kernels: the forward call stores the clamped image (and the layer's, if any) plus one
+ *                           mask byte per pixel in the image workspace; a backward call made with the same flag
+ *                           takes dL/d(clamped image) and gives the clamped channels no gradient. */
+#define HUGS_B200_FLAG_DEBUG   1
+#define HUGS_B200_FLAG_CLAMP01 2
+
 typedef void* hugs_b200_stream_t;
 
 /* Grow-callback: must return a device pointer to at least `nbytes` bytes (256-B aligned), valid

@@ -156,6 +156,7 @@ ImageView carve_image(char* base, int W, int H) {
     v.accum_alpha = take<float>(p, n);
     v.n_contrib = take<uint32_t>(p, n);
     v.ranges = take<uint2>(p, tiles);
+    v.clamp_mask = take<uint8_t>(p, n);   // appended after every exported offset
     v.total = (size_t)(p - base);
     return v;
 }
@@ -191,6 +192,7 @@ LayerView carve_layer(char* base, int R, int n_layer, int W, int H) {
     v.n_contrib = take<uint32_t>(p, pix);
     v.ranges = take<uint2>(p, tiles);
     v.grad_pack = take<float>(p, 8 * (size_t)(n_layer > 0 ? n_layer : 0));
+    v.clamp_mask = take<uint8_t>(p, pix);
     v.total = (size_t)(p - base);
     return v;
 }
@@ -529,6 +531,8 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                 float* out_color, int* radii, int debug, hugs_b200_stream_t stream_,
                                 int* num_rendered) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const bool clamp01 = (debug & HUGS_B200_FLAG_CLAMP01) != 0;   // `debug` doubles as a flag word
+    debug &= HUGS_B200_FLAG_DEBUG;
     if (num_rendered) *num_rendered = 0;
     if (!geometry_buffer || !binning_buffer || !image_buffer || !num_rendered) {
         set_error("rasterize_forward: null callback / output");
@@ -755,7 +759,8 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         HB_STAGE(launch_render_forward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y,
                                        P > 0 ? geom.means2D : nullptr, feature_ptr, stride,
                                        P > 0 ? geom.conic_opacity : nullptr, img.accum_alpha, img.n_contrib,
-                                       background, out_color, bin.hit_words, stream),
+                                       background, out_color, bin.hit_words, stream,
+                                       clamp01 ? img.clamp_mask : nullptr),
                  ST_RENDER_FWD);
         if (!R_known) {
             const int rc = wait_R();
@@ -810,6 +815,8 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
                                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                                  float* dL_drot, int debug, hugs_b200_stream_t stream_, int dL_dsh_accumulate) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const bool clamp01 = (debug & HUGS_B200_FLAG_CLAMP01) != 0;   // the forward call was made with the same flag
+    debug &= HUGS_B200_FLAG_DEBUG;
     if (P < 0 || R < 0 || width <= 0 || height <= 0) {
         set_error("rasterize_backward: bad sizes");
         return HUGS_B200_EINVAL;
@@ -858,7 +865,8 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
         if (R <= 0) return 0;
         return launch_render_backward(img.ranges, bin.list, width, height, cam.grid_x, cam.grid_y, background,
                                       geom.means2D, geom.conic_opacity, color_ptr, stride, img.accum_alpha,
-                                      img.n_contrib, bin.hit_words, dL_dpix, geom.grad_pack, opac_target, stream);
+                                      img.n_contrib, bin.hit_words, dL_dpix, geom.grad_pack, opac_target, stream,
+                                      clamp01 ? img.clamp_mask : nullptr);
     };
     HB_STAGE(blend_backward(), ST_RENDER_BWD);
     // The layer's blend backward: same kernel on the filtered lists, gradients into the layer's own packed
@@ -881,7 +889,7 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
             return launch_render_backward(lay.ranges, lay.list, width, height, cam.grid_x, cam.grid_y, L->background,
                                           geom.means2D, geom.conic_opacity, color_ptr, stride, lay.accum_alpha,
                                           lay.n_contrib, lay.hit_words, L->dL_dpix, lay.grad_pack, opac_target,
-                                          stream);
+                                          stream, clamp01 ? lay.clamp_mask : nullptr);
         };
         HB_STAGE(layer_backward(), ST_RENDER_BWD);
         pack2 = lay.grad_pack;
@@ -961,6 +969,8 @@ int hugs_b200_layer_forward(int P, int n_layer, const float* background, int wid
                             size_t binning_bytes, char* image_buffer, char* layer_buffer, size_t layer_bytes,
                             float* out_color, int debug, hugs_b200_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const bool clamp01 = (debug & HUGS_B200_FLAG_CLAMP01) != 0;
+    debug &= HUGS_B200_FLAG_DEBUG;
     if (P <= 0 || n_layer < 0 || n_layer > P || width <= 0 || height <= 0 || !background || !out_color || !geom_buffer ||
         !binning_buffer || !image_buffer || !layer_buffer) {
         set_error("layer_forward: bad arguments");
@@ -982,7 +992,7 @@ int hugs_b200_layer_forward(int P, int n_layer, const float* background, int wid
              ST_RANGES);
     HB_STAGE(launch_render_forward(lay.ranges, lay.list, width, height, grid_x, grid_y, geom.means2D, feature_ptr, stride,
                                    geom.conic_opacity, lay.accum_alpha, lay.n_contrib, background, out_color,
-                                   lay.hit_words, stream),
+                                   lay.hit_words, stream, clamp01 ? lay.clamp_mask : nullptr),
              ST_RENDER_FWD);
     return 0;
 }

@@ -72,6 +72,7 @@ struct ImageView {
     float* accum_alpha;
     uint32_t* n_contrib;
     uint2* ranges;
+    uint8_t* clamp_mask;   // [W*H] bit c: channel c of the pixel was clamped to [0, 1] (written only when asked for)
     size_t total;
 };
 struct LayerView {   // second image of the first n Gaussians (layer.cu)
@@ -81,6 +82,7 @@ struct LayerView {   // second image of the first n Gaussians (layer.cu)
     uint32_t* n_contrib;  // [W*H]
     uint2* ranges;        // [tiles]
     float* grad_pack;     // [n][8] the layer's share of the packed blend gradients
+    uint8_t* clamp_mask;  // [W*H] as ImageView::clamp_mask, for the layer's image
     size_t total;
 };
 struct BinningView {
@@ -185,13 +187,13 @@ int launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, 
 int launch_render_forward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
                           const float2* means2D, const float* colors, int color_stride,
                           const float4* conic_opacity, float* final_T, uint32_t* n_contrib,
-                          const float* bg, float* out_color, uint32_t* hit_words, cudaStream_t stream);
+                          const float* bg, float* out_color, uint32_t* hit_words, cudaStream_t stream, uint8_t* clamp_mask = nullptr);
 int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int W, int H, int grid_x, int grid_y,
                            const float* bg, const float2* means2D, const float4* conic_opacity,
                            const float* colors, int color_stride, const float* final_T,
                            const uint32_t* n_contrib, const uint32_t* hit_words, const float* dL_dpix,
                            float* grad_pack /*[P,8], zeroed*/, float* dL_dopacity /*[P], zeroed*/,
-                           cudaStream_t stream);
+                           cudaStream_t stream, const uint8_t* clamp_mask = nullptr);
 // Two-segment calls: the per-segment launches of a per-Gaussian kernel are collected here and issued as ONE
 // launch (flush_*): the human segment alone (110 k rows) is too small a grid to fill the machine.
 struct SegBatch {

@@ -71,6 +71,9 @@ __device__ __forceinline__ void red_add_f1(float* p, float a) {
 
 constexpr float kLog2e = 1.4426950408889634f;
 
+// CLAMP: the incoming gradient is that of the CLAMPED image; channels the forward pass clamped (mask byte per
+// pixel, render_forward.cu) get none -- torch.clamp's backward, without the elementwise pass.
+template <bool CLAMP>
 __global__ void __launch_bounds__(kBlendThreads, 4)
     render_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
                            int grid_x, const float* __restrict__ bg, const float2* __restrict__ means2D,
@@ -78,7 +81,7 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
                            int color_stride, const float* __restrict__ final_T,
                            const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ hit_words,
                            const float* __restrict__ dL_dpix, float* __restrict__ grad_pack,
-                           float* __restrict__ dL_dopacity) {
+                           float* __restrict__ dL_dopacity, const uint8_t* __restrict__ clamp_mask) {
     __shared__ BwdWarpSmem s_all[kBwdWarps];
 
     const unsigned tile_x = blockIdx.x, tile_y = blockIdx.y;
@@ -111,6 +114,12 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
         dLp0 = __ldg(dL_dpix + pix_id);
         dLp1 = __ldg(dL_dpix + plane + pix_id);
         dLp2 = __ldg(dL_dpix + 2 * plane + pix_id);
+        if (CLAMP) {
+            const unsigned m = __ldg(clamp_mask + pix_id);
+            if (m & 1u) dLp0 = 0.f;
+            if (m & 2u) dLp1 = 0.f;
+            if (m & 4u) dLp2 = 0.f;
+        }
     }
     sts_f4(s_pixc + lane * 16u, dLp0, dLp1, dLp2, 0.f);
     // alpha also decides how much of the background colour is added (backward.cu:531-534)
@@ -283,11 +292,18 @@ int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int 
                            const float* bg, const float2* means2D, const float4* conic_opacity, const float* colors,
                            int color_stride, const float* final_T, const uint32_t* n_contrib,
                            const uint32_t* hit_words, const float* dL_dpix, float* grad_pack, float* dL_dopacity,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, const uint8_t* clamp_mask) {
     const dim3 grid((unsigned)grid_x, (unsigned)grid_y, 1);
-    render_backward_kernel<<<grid, kBlendThreads, 0, stream>>>(ranges, point_list, W, H, grid_x, bg, means2D,
-                                                               conic_opacity, colors, color_stride, final_T, n_contrib,
-                                                               hit_words, dL_dpix, grad_pack, dL_dopacity);
+    if (clamp_mask != nullptr)
+        render_backward_kernel<true><<<grid, kBlendThreads, 0, stream>>>(ranges, point_list, W, H, grid_x, bg, means2D,
+                                                                         conic_opacity, colors, color_stride, final_T,
+                                                                         n_contrib, hit_words, dL_dpix, grad_pack,
+                                                                         dL_dopacity, clamp_mask);
+    else
+        render_backward_kernel<false><<<grid, kBlendThreads, 0, stream>>>(ranges, point_list, W, H, grid_x, bg, means2D,
+                                                                          conic_opacity, colors, color_stride, final_T,
+                                                                          n_contrib, hit_words, dL_dpix, grad_pack,
+                                                                          dL_dopacity, nullptr);
     HB_LAUNCH_OK("render_backward", stream, false);
     return 0;
 }

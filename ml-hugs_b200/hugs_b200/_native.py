@@ -207,6 +207,7 @@ materialize_sorted_keys = _sig("hugs_b200_materialize_sorted_keys", i32,
                                [i32, i32, i32, i32, fp, fp, C.c_size_t, fp])
 binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_size_t, i32, i32])
 BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE, BINNING_TILESORT = 0, 1, 2, 3
+FLAG_DEBUG, FLAG_CLAMP01 = 1, 2   # the flag word passed in the entry points' `debug` argument
 set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
 
 sort_bits = _sig("hugs_b200_sort_bits", i32, [i32, i32])

@@ -18,17 +18,17 @@ import ctypes as C
 import torch
 
 from . import _native as N
-from .rasterizer import _Workspace, _f32c, _stream_ptr
+from .rasterizer import _Workspace, _f32c, _stream_ptr, clamp_active, flags_of
 
 
-def _layer_forward(P, n_layer, bg_layer, W, H, colors, geom, binning, img, debug, device):
+def _layer_forward(P, n_layer, bg_layer, W, H, colors, geom, binning, img, flags, device):
     nbytes = int(N.layer_bytes(n_layer, int(binning.numel()), W, H))
     layer = torch.empty(nbytes, dtype=torch.uint8, device=device)
     out = torch.empty(3, H, W, dtype=torch.float32, device=device)
     with torch.cuda.device(device):
         rc = N.layer_forward(P, n_layer, N.ptr(bg_layer), W, H, N.ptr(colors), N.ptr(geom), N.ptr(binning),
                              int(binning.numel()), N.ptr(img), layer.data_ptr(), nbytes, out.data_ptr(),
-                             int(bool(debug)), _stream_ptr(device))
+                             int(flags), _stream_ptr(device))
     N.check(rc, "layer_forward")
     return out, layer
 
@@ -72,6 +72,7 @@ class _RasterizeWithLayer(torch.autograd.Function):
         if not means3D.is_cuda:
             raise RuntimeError("hugs_b200 has no CPU path: means3D must be a CUDA tensor")
         ctx.set_materialize_grads(False)   # an image nobody differentiates costs no blend backward
+        ctx.clamp = clamp_active()
         s, device = raster_settings, means3D.device
         P = int(means3D.shape[0])
         if P == 0:
@@ -90,9 +91,9 @@ class _RasterizeWithLayer(torch.autograd.Function):
             N.ptr(means3D), N.ptr(sh), N.ptr(colors_precomp), N.ptr(opacities), N.ptr(scales),
             float(s.scale_modifier), N.ptr(rotations), None, N.ptr(view), N.ptr(proj), N.ptr(campos),
             float(s.tanfovx), float(s.tanfovy), int(bool(s.prefiltered)), color.data_ptr(), radii.data_ptr(),
-            int(bool(s.debug)), _stream_ptr(device), C.byref(nr)), device)
-        layer_color, layer = _layer_forward(P, n_layer, bg_layer, W, H, colors_precomp, geom, binning, img, s.debug,
-                                            device)
+            flags_of(s.debug, ctx.clamp), _stream_ptr(device), C.byref(nr)), device)
+        layer_color, layer = _layer_forward(P, n_layer, bg_layer, W, H, colors_precomp, geom, binning, img,
+                                            flags_of(s.debug, ctx.clamp), device)
         ctx.raster_settings, ctx.num_rendered, ctx.sizes = s, R, (P, M, H, W, n_layer)
         ctx.save_for_backward(radii, geom, binning, img, layer, bg, bg_layer, view, proj, campos, means3D, sh,
                               colors_precomp, scales, rotations)
@@ -113,8 +114,8 @@ class _RasterizeWithLayer(torch.autograd.Function):
                 P, int(s.sh_degree), M, int(ctx.num_rendered), N.ptr(bg), W, H, N.ptr(means3D), N.ptr(sh),
                 N.ptr(colors_precomp), N.ptr(scales), float(s.scale_modifier), N.ptr(rotations), None, N.ptr(view),
                 N.ptr(proj), N.ptr(campos), float(s.tanfovx), float(s.tanfovy), radii.data_ptr(), N.ptr(geom),
-                N.ptr(binning), int(binning.numel()), N.ptr(img), dL.data_ptr(), *_grad_ptrs(g), int(bool(s.debug)),
-                _stream_ptr(device), 0, n_layer, N.ptr(bg_layer), layer.data_ptr(), int(layer.numel()), N.ptr(dLl))
+                N.ptr(binning), int(binning.numel()), N.ptr(img), dL.data_ptr(), *_grad_ptrs(g),
+                flags_of(s.debug, ctx.clamp), _stream_ptr(device), 0, n_layer, N.ptr(bg_layer), layer.data_ptr(), int(layer.numel()), N.ptr(dLl))
         N.check(rc, "rasterize_with_layer backward")
         has = lambda t: t is not None and t.numel() != 0  # noqa: E731
         return (g["means3D"], g["means2D"], g["sh"] if has(sh) else None, g["colors"] if has(colors_precomp) else None,
@@ -140,6 +141,7 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
         if not all(x.is_cuda for x in t):
             raise RuntimeError("hugs_b200 has no CPU path: segment tensors must be CUDA tensors")
         ctx.set_materialize_grads(False)
+        ctx.clamp = clamp_active()
         from .segments import sinks_of
         ctx.sinks, ctx.sunk = sinks_of(a, b)
         device = a[0].device
@@ -162,8 +164,9 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
             g.callback, None, bn.callback, None, i.callback, None, int(s.sh_degree), M, N.ptr(bg), W, H,
             P0, *[N.ptr(x) for x in a], P1, *[N.ptr(x) for x in b], float(s.scale_modifier), N.ptr(view),
             N.ptr(proj), N.ptr(campos), float(s.tanfovx), float(s.tanfovy), int(bool(s.prefiltered)),
-            color.data_ptr(), radii.data_ptr(), int(bool(s.debug)), _stream_ptr(device), C.byref(nr)), device)
-        layer_color, layer = _layer_forward(P, n_layer, bg_layer, W, H, None, geom, binning, img, s.debug, device)
+            color.data_ptr(), radii.data_ptr(), flags_of(s.debug, ctx.clamp), _stream_ptr(device), C.byref(nr)), device)
+        layer_color, layer = _layer_forward(P, n_layer, bg_layer, W, H, None, geom, binning, img,
+                                            flags_of(s.debug, ctx.clamp), device)
         ctx.raster_settings, ctx.num_rendered, ctx.sizes = s, R, (P0, P1, M, H, W, n_layer)
         ctx.save_for_backward(radii, geom, binning, img, layer, bg, bg_layer, view, proj, campos, *a, *b)
         ctx.mark_non_differentiable(radii)
@@ -185,7 +188,7 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
                 P1, N.ptr(b[0]), N.ptr(b[1]), N.ptr(b[3]), N.ptr(b[4]),
                 float(s.scale_modifier), N.ptr(view), N.ptr(proj), N.ptr(campos), float(s.tanfovx), float(s.tanfovy),
                 radii.data_ptr(), N.ptr(geom), N.ptr(binning), int(binning.numel()), N.ptr(img), dL.data_ptr(),
-                *_grad_ptrs(g), int(bool(s.debug)), _stream_ptr(device),
+                *_grad_ptrs(g), flags_of(s.debug, ctx.clamp), _stream_ptr(device),
                 n_layer, N.ptr(bg_layer), layer.data_ptr(), int(layer.numel()), N.ptr(dLl),
                 C.byref(ctx.sinks) if ctx.sinks is not None else None)
         N.check(rc, "rasterize_two_segments_with_layer backward")

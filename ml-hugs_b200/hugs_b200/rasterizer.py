@@ -12,7 +12,9 @@ Reference being mirrored:
 All device memory (inputs, outputs, the three opaque workspaces) is torch-owned; the native side
 receives raw pointers plus torch's current CUDA stream.
 """
+import contextlib
 import ctypes as C
+import threading
 from types import SimpleNamespace
 from typing import NamedTuple
 
@@ -37,6 +39,31 @@ def _f32c(t, device=None):
     if t.dtype != torch.float32:
         t = t.float()
     return t.contiguous()
+
+
+_opts = threading.local()
+
+
+@contextlib.contextmanager
+def output_clamp(enabled=True):
+    """Rasterizer calls made inside this context return the image already clamped to [0, 1]
+    (hugs/renderer/gs_renderer.py:153 does ``torch.clamp(rendered_image, 0.0, 1.0)`` right after the call) and
+    their backward pass treats the incoming gradient as that of the clamped image: the clamp and its
+    backward mask run inside the blend kernels (HUGS_B200_FLAG_CLAMP01) instead of as two elementwise passes."""
+    prev = getattr(_opts, "clamp", False)
+    _opts.clamp = bool(enabled)
+    try:
+        yield
+    finally:
+        _opts.clamp = prev
+
+
+def clamp_active():
+    return getattr(_opts, "clamp", False)
+
+
+def flags_of(debug, clamp):
+    return (N.FLAG_DEBUG if debug else 0) | (N.FLAG_CLAMP01 if clamp else 0)
 
 
 def _stream_ptr(device):
@@ -117,7 +144,7 @@ def rasterize_gaussians_forward(
             N.ptr(scales), float(scale_modifier), N.ptr(rotations), N.ptr(cov3D_precomp),
             N.ptr(viewmatrix), N.ptr(projmatrix), N.ptr(campos),
             float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-            out_color.data_ptr(), radii.data_ptr(), int(bool(debug)), _stream_ptr(device),
+            out_color.data_ptr(), radii.data_ptr(), flags_of(debug, clamp_active()), _stream_ptr(device),
             C.byref(num_rendered),
         )
     for ws in (geom, binning, img):
@@ -131,7 +158,7 @@ def rasterize_gaussians_forward(
 def rasterize_gaussians_backward(
     background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
     projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
-    imageBuffer, debug, sh_grad_out=None, sh_grad_accumulate=False,
+    imageBuffer, debug, sh_grad_out=None, sh_grad_accumulate=False, clamp=False,
 ):
     """Same 21 arguments and 8 return values as the reference's ``_C.rasterize_gaussians_backward``
     (rasterize_points.h:40-62): (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
@@ -195,7 +222,7 @@ def rasterize_gaussians_backward(
                 dL_dmeans2D.data_ptr(), dL_dconic.data_ptr(), dL_dopacity.data_ptr(), dL_dcolors.data_ptr(),
                 dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), N.ptr(dL_dsh), dL_dscales.data_ptr(),
                 dL_drotations.data_ptr(),
-                int(bool(debug)), _stream_ptr(device), int(bool(sh_grad_accumulate)),
+                flags_of(debug, clamp), _stream_ptr(device), int(bool(sh_grad_accumulate)),
             )
         N.check(rc, "rasterize_gaussians_backward")
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
@@ -396,6 +423,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = raster_settings
         ctx.num_rendered = num_rendered
         ctx.sh_sink = _sink_of(sh)
+        ctx.clamp = clamp_active()   # the image handed out is clamped: backward masks its gradient
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               geomBuffer, binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
@@ -433,6 +461,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         # view-batched training: the SH gradient goes straight into the attached sink (ShGradSink)
         sink = ctx.sh_sink
         kw = {} if sink is None else dict(sh_grad_out=sink.buffer, sh_grad_accumulate=not sink.fresh)
+        if ctx.clamp:
+            kw["clamp"] = True
         if raster_settings.debug:
             cpu_args = cpu_deep_copy_tuple(args)  # Copy them before they can be corrupted
             try:

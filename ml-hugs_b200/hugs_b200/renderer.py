@@ -13,7 +13,7 @@ import math
 import torch
 
 from . import _native as N
-from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer, output_clamp
 
 
 def render(means3D, feats, opacity, scales, rotations, data, scaling_modifier=1.0, bg_color=None,
@@ -47,17 +47,19 @@ def render(means3D, feats, opacity, scales, rotations, data, scaling_modifier=1.
         debug=False,
     )
     rasterizer = GaussianRasterizer(raster_settings=raster_settings)
-    rendered_image, radii = rasterizer(
-        means3D=means3D,
-        means2D=screenspace_points,
-        shs=shs,
-        opacities=opacity,
-        scales=scales,
-        rotations=rotations,
-        colors_precomp=rgb,
-    )
+    # torch.clamp(rendered_image, 0.0, 1.0) of gs_renderer.py:153 happens inside the blend kernels
+    with output_clamp():
+        rendered_image, radii = rasterizer(
+            means3D=means3D,
+            means2D=screenspace_points,
+            shs=shs,
+            opacities=opacity,
+            scales=scales,
+            rotations=rotations,
+            colors_precomp=rgb,
+        )
     return {
-        "render": torch.clamp(rendered_image, 0.0, 1.0),
+        "render": rendered_image,
         "viewspace_points": screenspace_points,
         "visibility_filter": radii > 0,
         "radii": radii,
@@ -88,15 +90,16 @@ def _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_
         prefiltered=False, debug=False)
     seg = lambda o: (o['xyz'], o['shs'], o['opacity'], o['scales'], o['rotq'])  # noqa: E731
     human_image = None
-    if human_separate:
-        rendered_image, human_image, radii = rasterize_two_segments_with_layer(
-            seg(human_gs_out), seg(scene_gs_out), screenspace_points, settings,
-            human_bg_color if human_bg_color is not None else bg_color)
-    else:
-        rendered_image, radii = rasterize_two_segments(seg(human_gs_out), seg(scene_gs_out), screenspace_points,
-                                                       settings)
+    with output_clamp():   # both images come back clamped to [0, 1] (gs_renderer.py:153)
+        if human_separate:
+            rendered_image, human_image, radii = rasterize_two_segments_with_layer(
+                seg(human_gs_out), seg(scene_gs_out), screenspace_points, settings,
+                human_bg_color if human_bg_color is not None else bg_color)
+        else:
+            rendered_image, radii = rasterize_two_segments(seg(human_gs_out), seg(scene_gs_out), screenspace_points,
+                                                           settings)
     pkg = {
-        "render": torch.clamp(rendered_image, 0.0, 1.0),
+        "render": rendered_image,
         "viewspace_points": screenspace_points,
         "visibility_filter": radii > 0,
         "radii": radii,
@@ -109,7 +112,7 @@ def _render_two_segments(human_gs_out, scene_gs_out, data, scaling_modifier, bg_
 def _add_human_layer(pkg, human_image, radii, n_human):
     # the keys gs_renderer.py:80-82 copies from its second render(); radii are per Gaussian and do not
     # depend on which other Gaussians are rendered with it
-    pkg['human_img'] = torch.clamp(human_image, 0.0, 1.0)
+    pkg['human_img'] = human_image   # clamped by the kernel
     pkg['human_radii'] = radii[:n_human]
     pkg['human_visibility_filter'] = pkg['human_radii'] > 0
 
@@ -134,11 +137,12 @@ def _render_with_human_layer(args, n_human, data, scaling_modifier, bg_color, hu
         scale_modifier=scaling_modifier, viewmatrix=data['world_view_transform'],
         projmatrix=data['full_proj_transform'], sh_degree=active_sh_degree, campos=data['camera_center'],
         prefiltered=False, debug=False)
-    rendered_image, human_image, radii = rasterize_with_layer(
-        means3D, screenspace_points, args['opacity'], args['scales'], args['rotations'], settings, n_human,
-        human_bg_color if human_bg_color is not None else bg_color, shs=shs, colors_precomp=rgb)
+    with output_clamp():
+        rendered_image, human_image, radii = rasterize_with_layer(
+            means3D, screenspace_points, args['opacity'], args['scales'], args['rotations'], settings, n_human,
+            human_bg_color if human_bg_color is not None else bg_color, shs=shs, colors_precomp=rgb)
     pkg = {
-        "render": torch.clamp(rendered_image, 0.0, 1.0),
+        "render": rendered_image,
         "viewspace_points": screenspace_points,
         "visibility_filter": radii > 0,
         "radii": radii,

@@ -13,7 +13,7 @@ import ctypes as C
 import torch
 
 from . import _native as N
-from .rasterizer import _Workspace, _f32c, _stream_ptr, grad_sink_of
+from .rasterizer import _Workspace, _f32c, _stream_ptr, clamp_active, flags_of, grad_sink_of
 
 _NAMES = ("means3D", "shs", "opacities", "scales", "rotations")
 _SINK_FIELDS = ("means3D", "sh", "opacity", "scales", "rotations")   # hugs_b200_grad_sinks, in _NAMES order
@@ -40,6 +40,7 @@ class _RasterizeTwoSegments(torch.autograd.Function):
         if not all(x.is_cuda for x in t):
             raise RuntimeError("hugs_b200 has no CPU path: segment tensors must be CUDA tensors")
         ctx.sinks, ctx.sunk = sinks_of(a, b)
+        ctx.clamp = clamp_active()
         device = a[0].device
         a = [_f32c(x, device) for x in a]
         b = [_f32c(x, device) for x in b]
@@ -69,7 +70,7 @@ class _RasterizeTwoSegments(torch.autograd.Function):
                     P0, *[N.ptr(x) for x in a], P1, *[N.ptr(x) for x in b],
                     float(s.scale_modifier), N.ptr(view), N.ptr(proj), N.ptr(campos),
                     float(s.tanfovx), float(s.tanfovy), int(bool(s.prefiltered)),
-                    color.data_ptr(), radii.data_ptr(), int(bool(s.debug)), _stream_ptr(device),
+                    color.data_ptr(), radii.data_ptr(), flags_of(s.debug, ctx.clamp), _stream_ptr(device),
                     C.byref(num_rendered))
             for ws in (geom, binning, img):
                 ws.release()
@@ -107,7 +108,7 @@ class _RasterizeTwoSegments(torch.autograd.Function):
                     dL.data_ptr(),
                     g["means2D"].data_ptr(), g["conic"].data_ptr(), g["opacity"].data_ptr(), g["colors"].data_ptr(),
                     g["means3D"].data_ptr(), g["cov3D"].data_ptr(), g["sh"].data_ptr(), g["scales"].data_ptr(),
-                    g["rotations"].data_ptr(), int(bool(s.debug)), _stream_ptr(device),
+                    g["rotations"].data_ptr(), flags_of(s.debug, ctx.clamp), _stream_ptr(device),
                     0, None, None, 0, None, C.byref(ctx.sinks) if ctx.sinks is not None else None)
             N.check(rc, "rasterize_two_segments backward")
         return (g["means2D"], None, *segment_grads(g, P0, ctx.sunk))

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     missing = [s for s in declared_symbols() if not hasattr(lib, s)]
     assert not missing, "declared in include/hugs_b200.h but not exported: %s" % missing
     assert set(N.EXPORTED_SYMBOLS) <= set(declared_symbols())
-    assert N.abi_version() == 9
+    assert N.abi_version() == 10
 
 
 def test_sort_bits_match_reference_rule():

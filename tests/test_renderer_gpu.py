@@ -253,3 +253,39 @@ def test_two_segments_argument_errors():
         rasterize_two_segments(seg, bad, m2d, settings)
     with pytest.raises(RuntimeError, match="no CPU path"):
         rasterize_two_segments([x.cpu() for x in seg], seg, m2d, settings)
+
+
+@pytest.mark.parametrize("separate", [False, True])
+def test_fused_clamp_equals_torch_clamp_forward_and_backward(separate):
+    """hugs/renderer/gs_renderer.py:153: the clamp inside the blend kernels (HUGS_B200_FLAG_CLAMP01) gives the
+    image of torch.clamp bit for bit and its gradient mask (SH colours exceed [0, 1] on many pixels of this
+    scene, a zero background puts others exactly on 0)."""
+    import diff_gaussian_rasterization as dgr
+    from hugs_b200 import layer, renderer
+    n_h, n_s = 1500, 2500
+    sc = scenes.make_scene(n_s, n_h, 320, 200, 300.0, seed=15, device="cuda")
+    sc["shs"] = sc["shs"] * 2.5          # push colours out of range
+    sc["bg"] = torch.zeros(3, device="cuda")
+    data = _data_of(sc)
+    human, scene = _gs_out(sc, 0, n_h), _gs_out(sc, n_h, n_h + n_s)
+    hbg = torch.tensor([1.0, 0.0, 0.5], device="cuda")
+    pkg = renderer.render_human_scene(data, human, scene, sc["bg"], human_bg_color=hbg, render_human_separate=separate)
+    # the same through the unfused route: raw images + torch.clamp
+    human2, scene2 = _gs_out(sc, 0, n_h), _gs_out(sc, n_h, n_h + n_s)
+    settings = scenes.settings_of(sc, dgr)
+    seg = lambda o: (o['xyz'], o['shs'], o['opacity'], o['scales'], o['rotq'])  # noqa: E731
+    m2d = torch.zeros(n_h + n_s, 3, device="cuda", requires_grad=True)
+    raw, raw_h, _ = layer.rasterize_two_segments_with_layer(seg(human2), seg(scene2), m2d, settings, hbg)
+    want, want_h = raw.clamp(0.0, 1.0), raw_h.clamp(0.0, 1.0)
+    assert float((raw < 0).float().mean()) + float((raw > 1).float().mean()) > 0.01   # the clamp does something
+    assert torch.equal(pkg["render"], want)
+    loss, loss2 = (pkg["render"] * sc["dL_dcolor"]).sum(), (want * sc["dL_dcolor"]).sum()
+    if separate:
+        assert torch.equal(pkg["human_img"], want_h)
+        loss, loss2 = loss + (pkg["human_img"] * sc["dL_dcolor"].flip(1)).sum(), loss2 + (want_h * sc["dL_dcolor"].flip(1)).sum()
+    loss.backward()
+    loss2.backward()
+    for k in ("xyz", "shs", "opacity", "scales", "rotq"):
+        for a, b in ((human[k], human2[k]), (scene[k], scene2[k])):
+            assert refutil.rel_err(a.grad.cpu().numpy(), b.grad.cpu().numpy()) < 1e-5, k
+    assert refutil.rel_err(pkg["viewspace_points"].grad.cpu().numpy(), m2d.grad.cpu().numpy()) < 1e-5
