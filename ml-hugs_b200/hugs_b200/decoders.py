@@ -8,10 +8,11 @@ accumulators in TMEM, exact GELU in the epilogue).  ``decode_all`` evaluates the
 hugs/models/hugs_trimlp.py:205-238 on the tri-plane features in ONE launch.
 
 Backward: the forward kernel saves every layer's pre-activations and ``hugs_b200_mlp_chains_backward`` runs
-the whole chain backwards on the same tiles: dA = dZ W (3xTF32), dW^T = A^T dZ (both operands MN-major out
-of the same shared-memory tiles), db by warp shuffles, GELU' in the epilogue.
-Only ``act='gelu'`` (the reference's default and the release configuration) takes the fused path; other
-activations fall back to the reference's own module arithmetic in torch.
+the whole chain backwards on the same tiles: dA = dZ W against the packed W^T, dW^T = A^T dZ from transposed
+K-major tiles, db by warp shuffles, GELU' in the epilogue.
+Only ``act='gelu'`` (the reference's default and the release configuration) takes the fused path; the other
+activations (and the pose-corrective blend shapes, off in the release configuration) run the module's own
+arithmetic on the GPU.  There is no CPU path: CPU inputs raise.
 """
 import ctypes as C
 import math
@@ -29,6 +30,11 @@ def _act_module(act):
     if act not in _ACTS:
         raise ValueError("activation %r is not supported (the reference's 'sine' needs its SineActivation)" % (act,))
     return _ACTS[act]()
+
+
+def _require_cuda(x):
+    if not x.is_cuda:
+        raise RuntimeError("hugs_b200 has no CPU path: decoder inputs must be CUDA tensors")
 
 
 def _stream(device):
@@ -203,7 +209,8 @@ class AppearanceDecoder(nn.Module):
                      [("shs", 0, 48, N.MLP_ACT_NONE), ("opacity", 48, 1, N.MLP_ACT_SIGMOID)])
 
     def forward(self, x):
-        if self.act != 'gelu' or not x.is_cuda:
+        _require_cuda(x)
+        if self.act != 'gelu':   # not the release configuration: the module's own arithmetic, on the GPU
             h = self.net(x)
             return {'shs': self.shs(h), 'opacity': self.opacity(h)}
         return run_chains(x, [self.spec()])[0]
@@ -237,7 +244,8 @@ class DeformationDecoder(nn.Module):
                      _lin(self.skinning), [("lbs_weights", 0, 24, N.MLP_ACT_GELU)])
 
     def forward(self, x):
-        if self.act != 'gelu' or not x.is_cuda or not self.disable_posedirs:
+        _require_cuda(x)
+        if self.act != 'gelu' or not self.disable_posedirs:
             h = self.net(x)
             posedirs = None
             if not self.disable_posedirs:
@@ -269,7 +277,8 @@ class GeometryDecoder(nn.Module):
                       ("scales", 9, ns, N.MLP_ACT_GELU)])
 
     def forward(self, x):
-        if self.act != 'gelu' or not x.is_cuda:
+        _require_cuda(x)
+        if self.act != 'gelu':
             return {'xyz': self.xyz(x), 'rotations': self.rotations(x), 'scales': F.gelu(self.scales(x))}
         return run_chains(x, [self.spec()])[0]
 
@@ -278,7 +287,8 @@ def decode_all(tri_feats, appearance_dec, geometry_dec, deformation_dec=None):
     """The decoder part of hugs/models/hugs_trimlp.py:205-238 (canon_forward) in ONE launch:
     returns (appearance_out, geometry_out, deformation_out | None) with the reference's keys."""
     decs = [appearance_dec, geometry_dec] + ([deformation_dec] if deformation_dec is not None else [])
-    fused = tri_feats.is_cuda and all(d.act == 'gelu' for d in decs) and \
+    _require_cuda(tri_feats)
+    fused = all(d.act == 'gelu' for d in decs) and \
         (deformation_dec is None or deformation_dec.disable_posedirs)
     if not fused:
         return (appearance_dec(tri_feats), geometry_dec(tri_feats),
