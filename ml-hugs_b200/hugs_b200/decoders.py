@@ -54,9 +54,6 @@ class _Spec:
         self.hidden, self.head, self.slices = hidden, head, slices
 
 
-def _gelu_grad(z):
-    return 0.5 * (1.0 + torch.erf(z * (1.0 / math.sqrt(2.0)))) + z * torch.exp(-0.5 * z * z) * (1.0 / math.sqrt(2.0 * math.pi))
-
 
 class _MlpChains(torch.autograd.Function):
     """forward(ctx, x, specs_meta, *tensors): tensors = per chain, per layer (W, b) in order (head last)."""
