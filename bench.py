@@ -256,6 +256,10 @@ class Replica:
         if not hasattr(self, "sh_sink"):
             self.sh_sink = None
         self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
+        # the device-resident step of the two-segment path (every gradient lands in the flat buffer that exists
+        # before the capture) is replayed as ONE CUDA graph (hugs_b200.dp.GraphedStep); HB_GRAPH=0 runs it eagerly
+        self.use_graph = self.two_seg and os.environ.get("HB_GRAPH", "1") == "1"
+        self.graphed = None
         # views of a step alternate between `n_streams` CUDA streams: the issue-bound blend kernels of one
         # view overlap the latency- and HBM-bound binning / per-Gaussian kernels of the next
         self.n_streams = max(1, int(os.environ.get("HB_STREAMS", "2"))) if sh_sink else 1
@@ -445,7 +449,7 @@ class Replica:
             inp["loss_event"].record()
         return loss
 
-    def _dp_step(self, forward_of_view, after_view=None):
+    def _dp_step(self, forward_of_view, after_view=None, exchange=True):
         """The product's data-parallel step (hugs_b200.dp.dp_step): clear the flat gradient buffer, this rank's
         views over the streams, backward of each, ONE allreduce of the flat buffer."""
         from hugs_b200 import dp
@@ -456,7 +460,8 @@ class Replica:
             self.last_nodes[v], self.last_radii_v[v] = int(self.last_node.num_rendered), self.last_radii
             return loss
         dp.dp_step(render_view, list(range(self.views)), self.buf, 0, 1,
-                   streams=self.streams if self.n_streams > 1 else (), read_loss=False, after_view=after_view)
+                   streams=self.streams if self.n_streams > 1 else (), read_loss=False, after_view=after_view,
+                   exchange=exchange)
 
     def _deform_all(self, As):
         """animation: the rank's pose frames of the step through ONE batched LBS call when the
@@ -469,9 +474,21 @@ class Replica:
         return xyz, rotq, hsc
 
     def step_resident(self):
-        """One step: every view of this rank's share of the view batch, gradients accumulated."""
+        """One step: every view of this rank's share of the view batch, gradients accumulated.  The two-segment
+        path replays the local part of the step as one CUDA graph and does the gradient exchange after it."""
+        if self.use_graph and self.buf is not None:
+            if self.graphed is None:
+                from hugs_b200 import dp
+                self.graphed = dp.GraphedStep(lambda: self._step_resident_eager(exchange=False),
+                                              streams=self.n_streams, sinks_only=True)
+            self.graphed.replay()
+            self.buf.allreduce()
+            return
+        self._step_resident_eager()
+
+    def _step_resident_eager(self, exchange=True):
         if self.buf is not None:
-            return self._dp_step(lambda v: self._forward(dict(self.devs[v])))
+            return self._dp_step(lambda v: self._forward(dict(self.devs[v])), exchange=exchange)
         self.zero_grad()
         if self.mode == "animation" and self.lbs_frames is not None:
             if not hasattr(self, "A_all"):
@@ -865,8 +882,8 @@ def main():
         rep.step_e2e()
         rep.allreduce_grads()
 
-    for _ in range(max(args.warmup, 3)):
-        step_resident()
+    use_graph, rep.use_graph = rep.use_graph, False
+    step_resident()   # one eager step: the pair counts below come from it (a captured step reports capacities)
     torch.cuda.synchronize(device)
     # pair / visible counts: mean over this rank's views (they size the per-stage algorithmic bytes)
     visible = int(round(sum(int((r > 0).sum()) for r in rep.last_radii_v) / V))
@@ -882,12 +899,20 @@ def main():
             inp["projmatrix"], rep.tanfovx, rep.tanfovy, H, W, rep.shs, 3, inp["campos"], False, False)[0]
         del m3, sc_, rq
 
+    _native.launch_count(1)
+    step_resident()
+    torch.cuda.synchronize(device)
+    launches_per_step = int(_native.launch_count(1))   # counted on an eager step: a replay launches the same kernels
+    rep.use_graph = use_graph
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    torch.cuda.synchronize(device)
+
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
-    _native.launch_count(1)
     ms = timed_loop(step_resident, args.steps, device, barrier)
-    launches = int(_native.launch_count(1))
+    launches = launches_per_step * args.steps
     for _ in range(2):
         step_e2e()
     rep.drain_e2e()
@@ -909,8 +934,9 @@ def main():
     if rep.buf is not None:
         rep.buf.exchange_events = rep.comm_events
     n_streams, rep.n_streams = rep.n_streams, 1
+    use_graph, rep.use_graph = rep.use_graph, False   # the stage events are not part of a captured step
     ms_staged = timed_loop(step_resident, args.steps, device, barrier)
-    rep.n_streams = n_streams
+    rep.n_streams, rep.use_graph = n_streams, use_graph
     _native.stage_timing_enable(0)
     stage_ms = _native.read_stage_times(reset=True)
     # data-parallel accounting (this pass only): time inside the gradient exchange per step -- waiting for
@@ -995,7 +1021,9 @@ def main():
         "n_gpus": n_gpus, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4),
         "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": dict(config, P=rep.P, R=R, visible=visible, sort_bits=sort_bits),
-        "impl": {"name": "ours", "cuda_streams_per_rank": rep.n_streams},
+        "impl": {"name": "ours", "cuda_streams_per_rank": rep.n_streams,
+                 "cuda_graph": ("value: the rank's local step is one CUDA-graph replay, allreduce outside it; "
+                                "e2e: eager") if rep.use_graph else None},
         "e2e": {"value": round(total_frames / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": int(rep.d2h_bytes),
                 "result_read_back": "loss (4 B) per view" if training else "the rendered image (3xHxW f32) per frame",

@@ -591,6 +591,11 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     uint32_t* R_dev = nullptr;   // tilesort: pair count; multisplit: level-1 entry count
     int* pinned = pinned_counter();
     cudaEvent_t ev = count_event();
+    bool capturing = false;   // CUDA-graph capture in progress on the caller's stream
+    {
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &st) == cudaSuccess) capturing = (st == cudaStreamCaptureStatusActive);
+    }
     if (P > 0) {
         if (!pinned || !ev) {
             set_error("rasterize_forward: could not create the pinned counter / event");
@@ -627,8 +632,10 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         // The number of (Gaussian, tile) pairs must reach the host (rasterizer_impl.cu:281).  The preprocess
         // kernel has summed it (and the level-1 entry count): async copy into pinned memory on the caller's
         // stream + an event, instead of a blocking cudaMemcpy after the scan.
-        HB_CUDA_OK(cudaMemcpyAsync(pinned, geom.pair_counts, 2 * sizeof(int), cudaMemcpyDeviceToHost, stream));
-        HB_CUDA_OK(cudaEventRecord(ev, stream));
+        if (!capturing) {
+            HB_CUDA_OK(cudaMemcpyAsync(pinned, geom.pair_counts, 2 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+            HB_CUDA_OK(cudaEventRecord(ev, stream));
+        }
         if (multisplit || tilesort) {
             HB_STAGE(launch_depth_argsort(reinterpret_cast<const uint32_t*>(geom.depths), geom.dsort_keys_tmp,
                                           geom.dsort_vals_tmp, geom.sorted_depths, geom.perm, P, geom.dsort_temp,
@@ -659,6 +666,20 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     // checked before returning and an overflow is redone with the exact size.
     int cap = 0, cap1 = 0;
     if (P > 0 && (multisplit || tilesort) && async) cap = capacity_hint(P, width, height, &cap1);
+    // Under CUDA-graph capture the host cannot wait for the count at all: the call is enqueued for the
+    // remembered capacity and reports it as num_rendered (an upper bound; every kernel reads the real count on
+    // the device, lists beyond the capacity are truncated).  One uncaptured call with the same (P, W, H) must
+    // have gone before, so that a capacity is known.
+    if (capturing) {
+        if (cap <= 0 && P > 0) {
+            set_error("rasterize_forward: stream capture needs a known pair capacity -- run the same (P, W, H) once "
+                      "outside the capture first (binning mode ASYNC)");
+            return HUGS_B200_EUNSUP;
+        }
+        R = cap;
+        R1 = cap1;
+        R_known = true;
+    }
     if (cap <= 0 && !R_known) {
         const int rc = wait_R();
         if (rc) return rc;
@@ -770,7 +791,7 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
         cap = R;  // the hint was too small: redo the binning with the exact size
         cap1 = R1;
     }
-    if (P > 0) update_capacity_hint(P, width, height, R, R1);
+    if (P > 0 && !capturing) update_capacity_hint(P, width, height, R, R1);
     *num_rendered = R;
     return 0;
 }

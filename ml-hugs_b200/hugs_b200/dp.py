@@ -123,7 +123,7 @@ class FlatGradBuffer:
 
 
 def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, world_size: int,
-            group=None, streams: Sequence = (), read_loss: bool = True, after_view=None):
+            group=None, streams: Sequence = (), read_loss: bool = True, after_view=None, exchange: bool = True):
     """One data-parallel step: ``render_view(v)`` must return the scalar loss tensor of view ``v``
     (forward through LBS + rasterizer); this rank handles ``shard_views`` of ``views``, calls
     backward on each loss (gradients accumulate in ``buf``), then allreduces.  Returns the local
@@ -135,7 +135,9 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     accumulation.  The losses are summed on the device and read once, after the last view
     (``read_loss=False``: not read at all -- the host does not wait for the step -- and the device-side
     list of losses is returned instead).  ``after_view(v)`` is called on the view's stream once its backward
-    pass has been enqueued (e.g. to record the event that releases the view's input buffers)."""
+    pass has been enqueued (e.g. to record the event that releases the view's input buffers).
+    ``exchange=False`` leaves the allreduce to the caller (``buf.allreduce()``): the local part of the step can
+    then be captured in a CUDA graph (``GraphedStep``) with the collective outside it."""
     buf.zero_()
     mine = shard_views(len(views), rank, world_size)
 
@@ -153,7 +155,8 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
 
     if not streams:
         losses = [one(views[i]) for i in mine]
-        buf.allreduce(group)
+        if exchange:
+            buf.allreduce(group)
         if not read_loss:
             return losses
         return float(sum(float(x) for x in losses))
@@ -166,10 +169,52 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
             losses.append(one(views[i]))
     for s in streams:
         main.wait_stream(s)
-    buf.allreduce(group)
+    if exchange:
+        buf.allreduce(group)
     if not read_loss:
         return losses
     return float(torch.stack(losses).sum()) if losses else 0.0
+
+
+class GraphedStep:
+    """One training step over device-resident inputs, captured once into a CUDA graph and replayed.
+
+    ``step_fn()`` (e.g. ``lambda: dp_step(render_view, views, buf, 0, 1, read_loss=False, exchange=False)``)
+    must read its per-view inputs from tensors whose addresses do not change between replays (refill them in
+    place) and must not read anything back on the host.  The rasterizer takes part in the capture: under
+    capture its forward call is enqueued for the pair capacity remembered from the uncaptured warm-up calls
+    and does not wait for the pair count (csrc/api.cu); every kernel reads the real count on the device.
+    What a replay saves is the host side of the step (Python, autograd bookkeeping, ~60 launches per view):
+    it matters when the step is host-bound (small models) and a few per cent when the GPU is the limit.
+    The gradient exchange of a multi-rank step stays outside the graph (``exchange=False``, then
+    ``buf.allreduce()``).
+
+    Limits (measured, tools/graph_bisect.py): the step must accumulate its gradients through gradient sinks
+    into buffers that exist before the capture (``FlatGradBuffer`` in-place mode, the two-segment calls), or
+    run on ONE stream.  A captured step whose parameters get their ``.grad`` from autograd's AccumulateGrad
+    with views on two streams replayed with corrupted gradients and illegal addresses (the tensors autograd
+    adopts during capture live in the graph's private pool), so ``GraphedStep`` refuses ``streams > 1``
+    unless ``sinks_only=True`` says every parameter gradient goes through a sink."""
+
+    def __init__(self, step_fn, warmup: int = 3, streams: int = 1, sinks_only: bool = False):
+        if streams > 1 and not sinks_only:
+            raise ValueError("GraphedStep: a step over several streams can only be captured when every gradient "
+                             "goes through a gradient sink (sinks_only=True)")
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):   # warm-up off the capture stream: allocator pools, capacity hints, lazy inits
+            for _ in range(max(1, warmup)):
+                step_fn()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.result = step_fn()
+
+    def replay(self):
+        self.graph.replay()
+        return self.result
 
 
 def init_from_env(backend: str = None):

@@ -1,0 +1,95 @@
+"""CUDA-graph capture of a whole data-parallel step (hugs_b200.dp.GraphedStep): the rasterizer's forward call is
+capture-aware (csrc/api.cu: under capture it is enqueued for the remembered pair capacity and never waits for
+the pair count), so forward + backward of several views over two streams replay as ONE graph.  The replayed
+gradients equal the eager step's (summation order of the reductions aside)."""
+import pytest
+import torch
+
+import refutil
+import scenes
+
+pytestmark = pytest.mark.gpu
+NAMES = ("means3D", "shs", "opacity", "scales", "rotations")
+
+
+def _setup(n_h, n_s, W, H, n_views, seed):
+    from hugs_b200 import dp
+    views = [scenes.make_scene(n_s, n_h, W, H, 300.0, seed=seed, device="cuda", view=v, n_views=n_views)
+             for v in range(n_views)]
+    params = {}
+    for k in NAMES:
+        params["h_" + k] = views[0][k][:n_h].detach().clone().contiguous().requires_grad_(True)
+        params["s_" + k] = views[0][k][n_h:].detach().clone().contiguous().requires_grad_(True)
+    buf = dp.FlatGradBuffer(params)
+    buf.attach_sinks(list(params))
+    return views, params, buf
+
+
+def _render_view(views, params):
+    import diff_gaussian_rasterization as dgr
+    from hugs_b200 import segments
+
+    def render(v):
+        sc = views[v]
+        seg = lambda t: tuple(params[t + k] for k in NAMES)  # noqa: E731
+        P = params["h_means3D"].shape[0] + params["s_means3D"].shape[0]
+        m2d = torch.empty(P, 3, device="cuda", requires_grad=True)
+        color, _ = segments.rasterize_two_segments(seg("h_"), seg("s_"), m2d, scenes.settings_of(sc, dgr))
+        return (color * sc["dL_dcolor"]).sum()
+    return render
+
+
+def test_graphed_step_replays_the_eager_gradients():
+    from hugs_b200 import dp
+    n_views = 4
+    views, params, buf = _setup(3000, 7000, 320, 200, n_views, seed=71)
+    render = _render_view(views, params)
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    ids = list(range(n_views))
+    try:
+        dp.dp_step(render, ids, buf, 0, 1, streams=streams, read_loss=False)
+        torch.cuda.synchronize()
+        ref = buf.flat.clone()
+        assert float(ref.abs().max()) > 0
+        step = dp.GraphedStep(lambda: dp.dp_step(render, ids, buf, 0, 1, streams=streams, read_loss=False,
+                                                 exchange=False), streams=2, sinks_only=True)
+        for _ in range(5):
+            losses = step.replay()
+            torch.cuda.synchronize()
+            err = refutil.rel_err(buf.flat.cpu().numpy(), ref.cpu().numpy())
+            assert err < 1e-5, err
+            assert len(losses) == n_views and all(bool(torch.isfinite(x)) for x in losses)
+        # new inputs at the same addresses: the replay follows them
+        for sc in views:
+            sc["dL_dcolor"].mul_(2.0)
+        step.replay()
+        torch.cuda.synchronize()
+        err = refutil.rel_err(buf.flat.cpu().numpy(), 2.0 * ref.cpu().numpy())
+        assert err < 1e-5, err
+    finally:
+        import hugs_b200
+        for t in params.values():
+            hugs_b200.detach_grad_sink(t)
+
+
+def test_capture_without_a_known_capacity_is_refused():
+    """The first call for a (P, W, H) cannot be captured: no pair capacity is known yet (clear error, and the
+    capture is left in a state torch can end)."""
+    import diff_gaussian_rasterization as dgr
+    sc = scenes.make_scene(1237, 0, 136, 72, 150.0, seed=72, device="cuda")   # a (P, W, H) no other test uses
+    settings = scenes.settings_of(sc, dgr)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with pytest.raises(RuntimeError, match="capture"):
+        with torch.cuda.graph(g):
+            with torch.no_grad():
+                dgr.GaussianRasterizer(settings)(
+                    means3D=sc["means3D"], means2D=torch.zeros_like(sc["means3D"]), opacities=sc["opacity"],
+                    shs=sc["shs"], scales=sc["scales"], rotations=sc["rotations"])
+    torch.cuda.synchronize()
+
+
+def test_graphed_step_refuses_two_streams_without_sinks():
+    from hugs_b200 import dp
+    with pytest.raises(ValueError, match="sink"):
+        dp.GraphedStep(lambda: None, streams=2)
