@@ -307,6 +307,17 @@ size_t hugs_b200_scan_temp_bytes(int n);
 int hugs_b200_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, size_t temp_bytes,
                              hugs_b200_stream_t stream);
 
+/* The same scan without any temp storage from the caller and without any allocation: the look-back state
+ * lives in a file-scope device array of the library (16.3 KB per GPU, held until exit).  No counterpart in
+ * the reference: added for callers that cannot call cudaMalloc (CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  n > HUGS_B200_SCAN_STATIC_MAX_ITEMS is
+ * rejected (HUGS_B200_EUNSUP, message in hugs_b200_last_error).  in/out: device pointers, 16-byte aligned.
+ * Every call shares the array: calls that overlap on the GPU (different streams or host threads) race --
+ * serialise them.  Same result as hugs_b200_inclusive_scan, bit for bit. */
+#define HUGS_B200_SCAN_STATIC_MAX_ITEMS (1 << 24)
+int hugs_b200_inclusive_scan_static_max_items(void);
+int hugs_b200_inclusive_scan_static(const uint32_t* in, uint32_t* out, int n, hugs_b200_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * SMPL linear-blend-skinning deformation of the human Gaussians (fused).  Replaces the PyTorch
  * chain  lbs_extra (hugs/models/modules/lbs.py:19-73, with disable_posedirs=True: v_posed=v_shaped)

@@ -7,7 +7,10 @@
 // of a running tile has already started (forward progress for the look-back spin).  Per-tile
 // state is one 64-bit word (flag << 32 | value) so flag and value are read atomically.
 // Algorithmic traffic: 4 B read + 4 B written per item.
+#include "../../include/hugs_b200.h"
 #include "common.cuh"
+
+#include <atomic>
 
 namespace hb {
 
@@ -162,3 +165,68 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, void* temp, 
 }
 
 }  // namespace hb
+
+// ---------------------------------------------------------------------------------------------------------
+// hugs_b200_inclusive_scan_static: the same scan with its look-back state in a file-scope device array, for
+// callers that cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).  No
+// counterpart in the reference.  Nothing below allocates.
+// Every GPU that loads the library holds the array (16.3 KB) until exit.  All calls share it: calls that
+// overlap on the GPU (two streams, two host threads) race on it -- serialise them.
+namespace hb {
+namespace {
+constexpr int kStaticScanMaxItems = HUGS_B200_SCAN_STATIC_MAX_ITEMS;
+// what scan_temp_bytes(kStaticScanMaxItems) asks for: ticket block + one word per tile, rounded up
+constexpr size_t kStaticScanBytes =
+    (256 + sizeof(unsigned long long) * (size_t)(kStaticScanMaxItems / kScanTile) + HB_ALIGN - 1) / HB_ALIGN * HB_ALIGN;
+static_assert(kStaticScanMaxItems % kScanTile == 0, "whole tiles");
+
+static __device__ __align__(256) unsigned char g_scan_scratch[kStaticScanBytes];
+
+constexpr int kMaxDevices = 64;
+std::atomic<void*> g_scan_scratch_ptr[kMaxDevices];   // device address of g_scan_scratch, per device
+
+// In host code `g_scan_scratch` is only a handle for the runtime: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+int static_scan_scratch(void** out) {
+    int dev = -1;
+    HB_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("inclusive_scan_static: device ordinal %d out of range", dev);
+        return HUGS_B200_EUNSUP;
+    }
+    void* p = g_scan_scratch_ptr[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        HB_CUDA_OK(cudaGetSymbolAddress(&p, g_scan_scratch));
+        if (p == nullptr) {
+            set_error("inclusive_scan_static: cudaGetSymbolAddress returned a null address");
+            return HUGS_B200_EUNSUP;
+        }
+        g_scan_scratch_ptr[dev].store(p, std::memory_order_release);   // (same value from every thread)
+    }
+    *out = p;
+    return 0;
+}
+}  // namespace
+}  // namespace hb
+
+extern "C" int hugs_b200_inclusive_scan_static_max_items(void) { return hb::kStaticScanMaxItems; }
+
+extern "C" int hugs_b200_inclusive_scan_static(const uint32_t* in, uint32_t* out, int n, hugs_b200_stream_t stream) {
+    if (n < 0 || (n > 0 && (!in || !out))) {
+        hb::set_error("inclusive_scan_static: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    if (n > hb::kStaticScanMaxItems) {
+        hb::set_error("inclusive_scan_static: %d items exceed the static scratch's maximum of %d "
+                      "(use hugs_b200_inclusive_scan with caller-provided temp storage)", n, hb::kStaticScanMaxItems);
+        return HUGS_B200_EUNSUP;
+    }
+    if (n == 0) return 0;
+    void* scratch = nullptr;
+    const int rc = hb::static_scan_scratch(&scratch);
+    if (rc) return rc;
+    // launch_inclusive_scan clears the state it uses (ticket + one word per tile, cudaMemsetAsync on `stream`):
+    // the array keeps the last call's contents otherwise
+    return hb::launch_inclusive_scan(in, out, n, scratch, hb::kStaticScanBytes, static_cast<cudaStream_t>(stream),
+                                     nullptr);
+}

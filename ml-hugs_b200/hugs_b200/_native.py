@@ -216,6 +216,8 @@ scan_temp_bytes = _sig("hugs_b200_scan_temp_bytes", C.c_size_t, [i32])
 sort_pairs = _sig("hugs_b200_sort_pairs", i32, [fp, fp, fp, fp, i32, i32, fp, C.c_size_t, fp])
 sort_pairs_range = _sig("hugs_b200_sort_pairs_range", i32, [fp, fp, fp, fp, i32, i32, i32, fp, C.c_size_t, fp])
 inclusive_scan = _sig("hugs_b200_inclusive_scan", i32, [fp, fp, i32, fp, C.c_size_t, fp])
+inclusive_scan_static = _sig("hugs_b200_inclusive_scan_static", i32, [fp, fp, i32, fp])
+inclusive_scan_static_max_items = _sig("hugs_b200_inclusive_scan_static_max_items", i32, [])
 
 lbs_forward = _sig("hugs_b200_lbs_forward", i32, [
     i32, i32, i32, fp, fp, fp, fp, fp, fp, C.c_float, fp, fp, fp, fp, fp])
@@ -245,6 +247,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_geom_layout_of", "hugs_b200_image_layout_of", "hugs_b200_binning_layout_of",
     "hugs_b200_sort_bits", "hugs_b200_sort_temp_bytes", "hugs_b200_sort_pairs", "hugs_b200_sort_pairs_range",
     "hugs_b200_scan_temp_bytes", "hugs_b200_inclusive_scan",
+    "hugs_b200_inclusive_scan_static", "hugs_b200_inclusive_scan_static_max_items",
     "hugs_b200_lbs_forward", "hugs_b200_lbs_backward",
     "hugs_b200_l1_ssim_forward", "hugs_b200_l1_ssim_backward",
     "hugs_b200_knn_temp_bytes", "hugs_b200_knn_mean_dist2",
