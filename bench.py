@@ -290,9 +290,16 @@ class Replica:
         # stalls the device (what a training loop's prefetcher / async logger does).
         self.copy_stream = torch.cuda.Stream(device)
         big = [k for k in ("G", "Gh") if k in self.hosts[0]]
-        self.G_dev = [{k: torch.empty_like(self.devs[0][k]) for k in big} for _ in range(2)]
-        self.G_ready = [torch.cuda.Event() for _ in range(2)]
-        self.step_done = [None, None]
+        # (four buffers: with views on two streams, the upload for view k may start when view k-4 is done, a
+        # whole view ahead of the forward pass that needs it; HB_E2E_GBUF=2 is round 1's double buffer)
+        self.n_gbuf = max(2, int(os.environ.get("HB_E2E_GBUF", "4")))
+        self.G_dev = [{k: torch.empty_like(self.devs[0][k]) for k in big} for _ in range(self.n_gbuf)]
+        self.G_ready = [torch.cuda.Event() for _ in range(self.n_gbuf)]
+        self.step_done = [None] * self.n_gbuf
+        # the small per-view inputs (camera, joint transforms) of ALL of a step's views travel as ONE pinned
+        # record at the start of the step: a per-view copy would queue behind the 25 MB uploads on the H2D engine
+        self.prefetch_small = os.environ.get("HB_E2E_SMALL_ONCE", "1") == "1"
+        self._small_all = None
         self.loss_host = [torch.zeros(1).pin_memory() for _ in range(4)]
         self.loss_ready = [None] * 4
         # e2e plumbing (rendering): every frame's image goes to one of four pinned host buffers
@@ -301,6 +308,42 @@ class Replica:
         self.images_read = 0
         self.e2e_step = 0
         self.losses = []
+        self.e2e_blocks = None
+        if self.use_graph:
+            self._pack_inputs_into_blocks()
+
+    def _pack_inputs_into_blocks(self):
+        """Graph replay reads the step's inputs at fixed addresses: the per-view inputs of the whole step live in a
+        few contiguous device blocks (the small ones in one [views, L] record, every field padded to 16 bytes),
+        each with a pinned host block and a device staging block of the same shape (see _step_e2e_graphed)."""
+        dev, V = self.device, self.views
+        small_keys = [k for k in self.hosts[0] if k not in ("G", "Gh")]
+        offs, off = {}, 0
+        for k in small_keys:
+            offs[k] = off
+            off += (self.hosts[0][k].numel() + 3) // 4 * 4
+        small_host = torch.zeros(V, off).pin_memory()
+        for v in range(V):
+            for k in small_keys:
+                t = self.hosts[v][k]
+                small_host[v, offs[k]:offs[k] + t.numel()] = t.reshape(-1)
+        small_dev = small_host.to(dev)
+        self.e2e_blocks = [(small_host, torch.empty_like(small_dev), small_dev)]
+        for v in range(V):
+            for k in small_keys:
+                t = self.hosts[v][k]
+                self.devs[v][k] = small_dev[v, offs[k]:offs[k] + t.numel()].view(t.shape)
+        for k in ("G", "Gh"):
+            if k in self.hosts[0]:
+                host_all = torch.stack([h[k] for h in self.hosts]).pin_memory()
+                dev_all = host_all.to(dev)
+                self.e2e_blocks.append((host_all, torch.empty_like(dev_all), dev_all))
+                for v in range(V):
+                    self.devs[v][k] = dev_all[v]
+        self._e2e_graph = None
+        # what the graphed e2e step moves: the blocks (fields padded to 16 bytes) up, the views' losses down
+        self.h2d_bytes = sum(b[0].numel() * b[0].element_size() for b in self.e2e_blocks)
+        self.d2h_bytes = 4 * V
 
     def _init_flat(self, device):
         """Our training arm: the product's data-parallel plumbing (hugs_b200.dp).  ONE flat gradient buffer
@@ -459,9 +502,9 @@ class Replica:
             loss = forward_of_view(v)
             self.last_nodes[v], self.last_radii_v[v] = int(self.last_node.num_rendered), self.last_radii
             return loss
-        dp.dp_step(render_view, list(range(self.views)), self.buf, 0, 1,
-                   streams=self.streams if self.n_streams > 1 else (), read_loss=False, after_view=after_view,
-                   exchange=exchange)
+        return dp.dp_step(render_view, list(range(self.views)), self.buf, 0, 1,
+                   streams=self.streams if self.n_streams > 1 else (), read_loss=False,
+                          after_view=after_view, exchange=exchange)
 
     def _deform_all(self, As):
         """animation: the rank's pose frames of the step through ONE batched LBS call when the
@@ -477,11 +520,7 @@ class Replica:
         """One step: every view of this rank's share of the view batch, gradients accumulated.  The two-segment
         path replays the local part of the step as one CUDA graph and does the gradient exchange after it."""
         if self.use_graph and self.buf is not None:
-            if self.graphed is None:
-                from hugs_b200 import dp
-                self.graphed = dp.GraphedStep(lambda: self._step_resident_eager(exchange=False),
-                                              streams=self.n_streams, sinks_only=True)
-            self.graphed.replay()
+            self._graphed_step().replay()
             self.buf.allreduce()
             return
         self._step_resident_eager()
@@ -520,13 +559,71 @@ class Replica:
             self.last_nodes[v] = self.last_node
             self.last_radii_v[v] = self.last_radii
 
+    def _graphed_step(self):
+        if self.graphed is None:
+            from hugs_b200 import dp
+            self.graphed = dp.GraphedStep(lambda: self._step_resident_eager(exchange=False),
+                                          streams=self.n_streams, sinks_only=True)
+        return self.graphed
+
+    def _prefetch(self):
+        """The NEXT step's inputs, pinned host blocks -> device staging blocks, on the copy stream (behind the
+        copy that emptied the staging blocks): runs while the current step is replayed."""
+        g = self._e2e_graph
+        with torch.cuda.stream(self.copy_stream):
+            if g["free"] is not None:
+                self.copy_stream.wait_event(g["free"])
+            for host_b, stage_b, _ in self.e2e_blocks:
+                stage_b.copy_(host_b, non_blocking=True)
+            g["staged"].record(self.copy_stream)
+
+    def _step_e2e_graphed(self):
+        """End to end with the step replayed as a CUDA graph: the step's inputs arrive from pinned host memory in
+        the staging blocks (uploaded on the copy stream during the previous step, the loader pattern: one
+        upload per step, K uploads in K timed steps), are copied device-to-device to where the graph reads them
+        (~0.06 ms for 200 MB), the graph is replayed, the gradients are exchanged, and the views' losses go to a
+        pinned slot that the host reads two steps later."""
+        if self._e2e_graph is None:
+            self._e2e_graph = dict(free=None, staged=torch.cuda.Event(), k=0, done=[None, None],
+                                   pinned=[torch.zeros(self.views).pin_memory() for _ in range(2)])
+            self._prefetch()
+        g = self._e2e_graph
+        slot = g["k"] % 2
+        if g["done"][slot] is not None:   # the losses of step k - 2
+            g["done"][slot].synchronize()
+            self.losses.extend(g["pinned"][slot].tolist())
+        main = torch.cuda.current_stream(self.device)
+        main.wait_event(g["staged"])
+        with torch.no_grad():
+            for _, stage_b, dev_b in self.e2e_blocks:
+                dev_b.copy_(stage_b)
+        g["free"] = torch.cuda.Event()
+        g["free"].record(main)
+        self._prefetch()
+        losses = self._graphed_step().replay()
+        self.buf.allreduce()
+        g["pinned"][slot].copy_(torch.stack(losses), non_blocking=True)
+        g["done"][slot] = torch.cuda.Event()
+        g["done"][slot].record(main)
+        g["k"] += 1
+
     def step_e2e(self):
+        if self.use_graph and self.e2e_blocks is not None and self.buf is not None:
+            return self._step_e2e_graphed()
         if self.buf is not None:
             def release(v):   # the view's backward has been enqueued: its G buffer may be refilled after it
                 done = torch.cuda.Event()
                 done.record()
                 self.step_done[self._g_slot[v]] = done
             self._g_slot = {}
+            self._small_dev = None
+            if self.prefetch_small:
+                if self._small_all is None:
+                    recs = [torch.cat([t.reshape(-1) for k, t in h.items() if k not in ("G", "Gh", "_packed")])
+                            for h in self.hosts]
+                    self._small_len = int(recs[0].numel())
+                    self._small_all = torch.stack(recs).pin_memory()
+                self._small_dev = self._small_all.to(self.device, non_blocking=True)
             return self._dp_step(lambda v: self.frame_e2e(self.hosts[v], forward_only=True, view=v), release)
         self.zero_grad()
         dall = None
@@ -552,7 +649,7 @@ class Replica:
         """One frame with every per-frame input copied from pinned host memory (camera, joint
         transforms on the compute stream; G on the copy stream) and the result read back on the host:
         the loss when training, the IMAGE when rendering."""
-        i = self.e2e_step % 2
+        i = self.e2e_step % self.n_gbuf
         main = torch.cuda.current_stream(self.device)
         big = ("G", "Gh", "_packed")
         if self.training:
@@ -564,9 +661,12 @@ class Replica:
                 self.G_ready[i].record(self.copy_stream)
         # camera + joint transforms travel as ONE pinned record (one async copy instead of five)
         small = [(k, v) for k, v in host.items() if k not in big and not (deformed is not None and k == "A")]
-        if "_packed" not in host:
-            host["_packed"] = torch.cat([v.reshape(-1) for _, v in small]).pin_memory()
-        rec = host["_packed"].to(self.device, non_blocking=True)
+        if forward_only and getattr(self, "_small_dev", None) is not None:
+            rec = self._small_dev[view]   # uploaded with the other views' records when the step began
+        else:
+            if "_packed" not in host:
+                host["_packed"] = torch.cat([v.reshape(-1) for _, v in small]).pin_memory()
+            rec = host["_packed"].to(self.device, non_blocking=True)
         inp, off = {}, 0
         for k, v in small:
             inp[k] = rec[off:off + v.numel()].view(v.shape)
@@ -605,6 +705,13 @@ class Replica:
 
     def drain_e2e(self):
         """Read the results still pending (called inside the timed region, after the last step)."""
+        g = getattr(self, "_e2e_graph", None)
+        if g is not None:
+            for j in (g["k"], g["k"] + 1):   # step k - 2, then step k - 1
+                if g["done"][j % 2] is not None:
+                    g["done"][j % 2].synchronize()
+                    g["done"][j % 2] = None
+                    self.losses.extend(g["pinned"][j % 2].tolist())
         for s in range(4):
             if self.loss_ready[s] is not None:
                 self.loss_ready[s].synchronize()
@@ -1023,7 +1130,9 @@ def main():
         "config": dict(config, P=rep.P, R=R, visible=visible, sort_bits=sort_bits),
         "impl": {"name": "ours", "cuda_streams_per_rank": rep.n_streams,
                  "cuda_graph": ("value: the rank's local step is one CUDA-graph replay, allreduce outside it; "
-                                "e2e: eager") if rep.use_graph else None},
+                                "e2e: inputs prefetched one step ahead on a copy stream into staging blocks, "
+                                "device-to-device copy, the same graph replay, losses read two steps later")
+                 if rep.use_graph else None},
         "e2e": {"value": round(total_frames / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": int(rep.d2h_bytes),
                 "result_read_back": "loss (4 B) per view" if training else "the rendered image (3xHxW f32) per frame",

@@ -93,3 +93,34 @@ def test_graphed_step_refuses_two_streams_without_sinks():
     from hugs_b200 import dp
     with pytest.raises(ValueError, match="sink"):
         dp.GraphedStep(lambda: None, streams=2)
+
+
+def test_bench_graphed_e2e_step_reads_the_same_losses_and_gradients_as_the_eager_loop(monkeypatch):
+    """bench.py's end-to-end step with the graph (inputs prefetched into staging blocks, device-to-device copy,
+    replay, losses read two steps later) against its eager e2e loop, same workload and inputs."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    dev = torch.device("cuda", 0)
+
+    def run(graph):
+        monkeypatch.setenv("HB_GRAPH", "1" if graph else "0")
+        wl = bench.make_workload("smoke_256", 0, 1, dev, views=4)
+        rep = bench.Replica(wl, dev, bench.our_impl(), sh_sink=True)
+        assert rep.two_seg and rep.use_graph == graph
+        rep.use_graph = False
+        rep.step_resident()          # what bench.main does first: an eager step
+        rep.use_graph = graph
+        for _ in range(4):
+            rep.step_e2e()
+        rep.drain_e2e()
+        torch.cuda.synchronize()
+        return list(rep.losses), rep.buf.flat.clone()
+
+    l0, g0 = run(False)
+    l1, g1 = run(True)
+    assert len(l0) == len(l1) == 16
+    for a, b in zip(l0, l1):
+        assert abs(a - b) <= 1e-5 * max(abs(a), 1.0), (a, b)
+    assert refutil.rel_err(g1.cpu().numpy(), g0.cpu().numpy()) < 1e-5
