@@ -59,6 +59,7 @@ WORKLOADS = {
     "pose_animation_300": _w(110210, 0, mode="animation", frames=300),       # configs[4]
     "human_only_256": _w(110210, 0, 256, 256, 187.0, cpu="torch"),           # configs[0]: the CPU-runnable case
     "smoke_256": _w(4096, 20000, 256, 256, 187.0),
+    "smoke_human_256": _w(4096, 0, 256, 256, 187.0),
     "smoke_separate_256": _w(4096, 20000, 256, 256, 187.0, mode="train_separate"),
     "smoke_forward_256": _w(0, 30000, 256, 256, 187.0, mode="forward"),
     "smoke_animation_256": _w(4096, 0, 256, 256, 187.0, mode="animation", frames=12),
@@ -258,8 +259,11 @@ class Replica:
         self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
         # the device-resident step of the two-segment path (every gradient lands in the flat buffer that exists
         # before the capture) is replayed as ONE CUDA graph (hugs_b200.dp.GraphedStep); HB_GRAPH=0 runs it eagerly
-        self.use_graph = self.two_seg and os.environ.get("HB_GRAPH", "1") == "1"
+        # (a single model's step -- AccumulateGrad-based -- is captured on ONE stream: DESIGN.md, graph limits)
+        self.use_graph = (self.render2 is not None and self.training and self.buf is not None
+                          and os.environ.get("HB_GRAPH", "1") == "1")
         self.graphed = None
+        self._graph_grads = None
         # views of a step alternate between `n_streams` CUDA streams: the issue-bound blend kernels of one
         # view overlap the latency- and HBM-bound binning / per-Gaussian kernels of the next
         self.n_streams = max(1, int(os.environ.get("HB_STREAMS", "2"))) if sh_sink else 1
@@ -520,8 +524,7 @@ class Replica:
         """One step: every view of this rank's share of the view batch, gradients accumulated.  The two-segment
         path replays the local part of the step as one CUDA graph and does the gradient exchange after it."""
         if self.use_graph and self.buf is not None:
-            self._graphed_step().replay()
-            self.buf.allreduce()
+            self._replay()
             return
         self._step_resident_eager()
 
@@ -562,9 +565,25 @@ class Replica:
     def _graphed_step(self):
         if self.graphed is None:
             from hugs_b200 import dp
-            self.graphed = dp.GraphedStep(lambda: self._step_resident_eager(exchange=False),
-                                          streams=self.n_streams, sinks_only=True)
+            n = self.n_streams
+            if not self.two_seg:
+                self.n_streams = 1
+            try:
+                self.graphed = dp.GraphedStep(lambda: self._step_resident_eager(exchange=False),
+                                              streams=self.n_streams, sinks_only=self.two_seg)
+            finally:
+                self.n_streams = n
+            if self.buf.gather:   # the graph writes the tensors autograd adopted as .grad during the capture
+                self._graph_grads = {k: p.grad for k, p in self.buf.params.items() if k not in self.buf.sunk}
         return self.graphed
+
+    def _replay(self):
+        out = self._graphed_step().replay()
+        if self._graph_grads is not None:   # (an eager step in between -- the staged pass -- re-points .grad)
+            for k, g in self._graph_grads.items():
+                self.buf.params[k].grad = g
+        self.buf.allreduce()
+        return out
 
     def _prefetch(self):
         """The NEXT step's inputs, pinned host blocks -> device staging blocks, on the copy stream (behind the
@@ -600,8 +619,7 @@ class Replica:
         g["free"] = torch.cuda.Event()
         g["free"].record(main)
         self._prefetch()
-        losses = self._graphed_step().replay()
-        self.buf.allreduce()
+        losses = self._replay()
         g["pinned"][slot].copy_(torch.stack(losses), non_blocking=True)
         g["done"][slot] = torch.cuda.Event()
         g["done"][slot].record(main)
@@ -1129,9 +1147,10 @@ def main():
         "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": dict(config, P=rep.P, R=R, visible=visible, sort_bits=sort_bits),
         "impl": {"name": "ours", "cuda_streams_per_rank": rep.n_streams,
-                 "cuda_graph": ("value: the rank's local step is one CUDA-graph replay, allreduce outside it; "
+                 "cuda_graph": ("value: the rank's local step is one CUDA-graph replay (%s), allreduce outside it; "
                                 "e2e: inputs prefetched one step ahead on a copy stream into staging blocks, "
-                                "device-to-device copy, the same graph replay, losses read two steps later")
+                                "device-to-device copy, the same graph replay, losses read two steps later"
+                                % ("views over 2 streams" if rep.two_seg else "one stream"))
                  if rep.use_graph else None},
         "e2e": {"value": round(total_frames / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": int(rep.d2h_bytes),

@@ -95,7 +95,8 @@ def test_graphed_step_refuses_two_streams_without_sinks():
         dp.GraphedStep(lambda: None, streams=2)
 
 
-def test_bench_graphed_e2e_step_reads_the_same_losses_and_gradients_as_the_eager_loop(monkeypatch):
+@pytest.mark.parametrize("workload,two_seg", [("smoke_256", True), ("smoke_human_256", False)])
+def test_bench_graphed_e2e_step_reads_the_same_losses_and_gradients_as_the_eager_loop(monkeypatch, workload, two_seg):
     """bench.py's end-to-end step with the graph (inputs prefetched into staging blocks, device-to-device copy,
     replay, losses read two steps later) against its eager e2e loop, same workload and inputs."""
     import os
@@ -106,9 +107,9 @@ def test_bench_graphed_e2e_step_reads_the_same_losses_and_gradients_as_the_eager
 
     def run(graph):
         monkeypatch.setenv("HB_GRAPH", "1" if graph else "0")
-        wl = bench.make_workload("smoke_256", 0, 1, dev, views=4)
+        wl = bench.make_workload(workload, 0, 1, dev, views=4)
         rep = bench.Replica(wl, dev, bench.our_impl(), sh_sink=True)
-        assert rep.two_seg and rep.use_graph == graph
+        assert rep.two_seg == two_seg and rep.use_graph == graph
         rep.use_graph = False
         rep.step_resident()          # what bench.main does first: an eager step
         rep.use_graph = graph
@@ -116,7 +117,8 @@ def test_bench_graphed_e2e_step_reads_the_same_losses_and_gradients_as_the_eager
             rep.step_e2e()
         rep.drain_e2e()
         torch.cuda.synchronize()
-        return list(rep.losses), rep.buf.flat.clone()
+        grads = torch.cat([g.detach().reshape(-1) for g in rep.buf.grads().values() if g is not None]).clone()
+        return list(rep.losses), grads
 
     l0, g0 = run(False)
     l1, g1 = run(True)
