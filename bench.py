@@ -269,7 +269,15 @@ class Replica:
         # (measured under graph replay, frames/s resident / end to end: 1 stream 756 / 734, 2: 807 / 797,
         # 3: 817 / 810, 4: 822 / 817, 6: 819 / 813, 8: 820 / 819; eager 4 streams 773 / 744)
         self.n_streams = max(1, int(os.environ.get("HB_STREAMS", "4"))) if sh_sink else 1
-        self.streams = [torch.cuda.Stream(device) for _ in range(self.n_streams)] if self.n_streams > 1 else []
+        # HB_PRIO=1: the views' streams are high-priority streams and the blend kernels are launched at the lowest
+        # priority (hugs_b200_set_blend_priority): the other views' short kernels run in the CTA slots a blend
+        # kernel frees instead of waiting behind its 8 160-CTA grid
+        self.prio = self.render2 is not None and self.n_streams > 1 and os.environ.get("HB_PRIO", "1") == "1"
+        if self.n_streams > 1 and self.render2 is not None:
+            from hugs_b200 import dp
+            self.streams = dp.view_streams(self.n_streams, device, prioritise=self.prio)
+        else:
+            self.streams = [torch.cuda.Stream(device) for _ in range(self.n_streams)] if self.n_streams > 1 else []
         self.means2D = torch.zeros(self.P, 3, device=device, requires_grad=self.training and not self.two_seg)
         # per-frame inputs: pinned host copies (for e2e) and resident device copies (for value)
         self.tanfovx, self.tanfovy = wl["cam"]["tanfovx"], wl["cam"]["tanfovy"]

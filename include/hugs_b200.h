@@ -274,6 +274,15 @@ int hugs_b200_binning_layout_of(int R, int width, int height, hugs_b200_binning_
 #define HUGS_B200_BINNING_TILESORT  3
 int hugs_b200_set_binning_mode(int mode);
 
+/* Launch priority of the two blend kernels (render forward / backward).  They fill every register of every SM
+ * for hundreds of microseconds; a caller that runs several views on several HIGH-priority streams
+ * (cudaStreamCreateWithPriority) can have the blend kernels launched at a lower priority than those streams'
+ * (enable = 1, priority = e.g. the least priority of cudaDeviceGetStreamPriorityRange), so that the other views'
+ * short latency-bound kernels take the CTA slots a blend kernel frees instead of queueing behind its grid.
+ * enable = 0 (the default): plain launches at the stream's priority.  Process-wide; returns the previous
+ * enable flag.  No counterpart in the reference (it runs one view on one stream). */
+int hugs_b200_set_blend_priority(int enable, int priority);
+
 /* ---------------------------------------------------------------------------------------------
  * Stand-alone stages, exported so each can be parity-tested and timed on its own.
  * ------------------------------------------------------------------------------------------- */

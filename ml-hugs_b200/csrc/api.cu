@@ -234,6 +234,14 @@ static cudaEvent_t count_event() {
 
 static std::atomic<int> g_binning_mode{HUGS_B200_BINNING_ASYNC};
 
+// launch priority of the blend kernels: unset (plain launches) unless hugs_b200_set_blend_priority says otherwise
+static std::atomic<int> g_blend_prio_set{0};
+static std::atomic<int> g_blend_prio{0};
+bool blend_priority(int* priority) {
+    *priority = g_blend_prio.load(std::memory_order_relaxed);
+    return g_blend_prio_set.load(std::memory_order_relaxed) != 0;
+}
+
 // Pair-count history per (P, W, H): capacity = recent maximum + 25 % slack, decaying slowly.
 struct CapacityHint {
     int P, W, H, cap, cap1;   // cap: (Gaussian, tile) pairs; cap1: level-1 (Gaussian, super-tile) entries
@@ -794,6 +802,11 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     if (P > 0 && !capturing) update_capacity_hint(P, width, height, R, R1);
     *num_rendered = R;
     return 0;
+}
+
+int hugs_b200_set_blend_priority(int enable, int priority) {
+    g_blend_prio.store(priority);
+    return g_blend_prio_set.exchange(enable ? 1 : 0);
 }
 
 int hugs_b200_materialize_sorted_keys(int P, int R, int width, int height, char* geom_buffer, char* binning_buffer,

@@ -190,7 +190,7 @@ __device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c,
 //     as twelve 512-byte contiguous stores (zero rows for culled Gaussians included), instead of
 //     twelve 16-byte stores per thread at a 192-byte stride.
 // Two segments in one launch: blocks [0, nb0) work on a0, the rest on a1 (see preprocess.cu).
-__global__ void __launch_bounds__(kPbThreads, 4)
+__global__ void __launch_bounds__(kPbThreads, 5)
     preprocess_backward_kernel(const PreBwdArgs a0, const PreBwdArgs a1, const int nb0) {
     const bool second = (int)blockIdx.x >= nb0;
     const PreBwdArgs& a = second ? a1 : a0;

@@ -295,15 +295,13 @@ int launch_render_backward(const uint2* ranges, const uint32_t* point_list, int 
                            cudaStream_t stream, const uint8_t* clamp_mask) {
     const dim3 grid((unsigned)grid_x, (unsigned)grid_y, 1);
     if (clamp_mask != nullptr)
-        render_backward_kernel<true><<<grid, kBlendThreads, 0, stream>>>(ranges, point_list, W, H, grid_x, bg, means2D,
-                                                                         conic_opacity, colors, color_stride, final_T,
-                                                                         n_contrib, hit_words, dL_dpix, grad_pack,
-                                                                         dL_dopacity, clamp_mask);
+        launch_blend(render_backward_kernel<true>, grid, stream, ranges, point_list, W, H, grid_x, bg, means2D,
+                     conic_opacity, colors, color_stride, final_T, n_contrib, hit_words, dL_dpix, grad_pack, dL_dopacity,
+                     clamp_mask);
     else
-        render_backward_kernel<false><<<grid, kBlendThreads, 0, stream>>>(ranges, point_list, W, H, grid_x, bg, means2D,
-                                                                          conic_opacity, colors, color_stride, final_T,
-                                                                          n_contrib, hit_words, dL_dpix, grad_pack,
-                                                                          dL_dopacity, nullptr);
+        launch_blend(render_backward_kernel<false>, grid, stream, ranges, point_list, W, H, grid_x, bg, means2D,
+                     conic_opacity, colors, color_stride, final_T, n_contrib, hit_words, dL_dpix, grad_pack, dL_dopacity,
+                     (const uint8_t*)nullptr);
     HB_LAUNCH_OK("render_backward", stream, false);
     return 0;
 }

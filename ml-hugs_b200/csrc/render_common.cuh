@@ -5,6 +5,31 @@
 namespace hb {
 
 constexpr int kBlendThreads = 256;  // one thread per pixel of a 16x16 tile
+
+// Launch of a blend kernel.  Both blend kernels fill every register of every SM for hundreds of microseconds; a
+// caller that runs several views on several streams can ask for them to be launched at a LOWER priority than its
+// streams' (hugs_b200_set_blend_priority), so that the short latency-bound kernels of the other views (binning,
+// scans, per-Gaussian passes) get the CTA slots the blend kernel frees instead of queueing behind its grid.
+bool blend_priority(int* priority);   // api.cu
+template <typename... KArgs, typename... Args>
+static inline void launch_blend(void (*kernel)(KArgs...), dim3 grid, cudaStream_t stream, Args... args) {
+    int prio = 0;
+    if (!blend_priority(&prio)) {
+        kernel<<<grid, kBlendThreads, 0, stream>>>(args...);
+        return;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kBlendThreads, 1, 1);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributePriority;
+    attr[0].val.priority = prio;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);   // (the error, if any, is picked up by HB_LAUNCH_OK)
+}
 constexpr int kBlendBatch = 256;    // Gaussians staged in shared memory per round
 
 // Pixel <-> thread mapping.  The reference uses a (16,16) block, i.e. a warp covers a 16x2 strip

@@ -209,6 +209,7 @@ binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_siz
 BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE, BINNING_TILESORT = 0, 1, 2, 3
 FLAG_DEBUG, FLAG_CLAMP01 = 1, 2   # the flag word passed in the entry points' `debug` argument
 set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
+set_blend_priority = _sig("hugs_b200_set_blend_priority", i32, [i32, i32])
 
 sort_bits = _sig("hugs_b200_sort_bits", i32, [i32, i32])
 sort_temp_bytes = _sig("hugs_b200_sort_temp_bytes", C.c_size_t, [i32])
@@ -239,7 +240,7 @@ def read_stage_times(reset=True):
 
 
 EXPORTED_SYMBOLS = [
-    "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode", "hugs_b200_materialize_sorted_keys",
+    "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode", "hugs_b200_set_blend_priority", "hugs_b200_materialize_sorted_keys",
     "hugs_b200_stage_timing_enable", "hugs_b200_stage_timing_read", "hugs_b200_stage_name",
     "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
     "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_rasterize_backward_acc",

@@ -126,3 +126,35 @@ def test_bench_graphed_e2e_step_reads_the_same_losses_and_gradients_as_the_eager
     for a, b in zip(l0, l1):
         assert abs(a - b) <= 1e-5 * max(abs(a), 1.0), (a, b)
     assert refutil.rel_err(g1.cpu().numpy(), g0.cpu().numpy()) < 1e-5
+
+
+def test_blend_priority_changes_the_launch_and_nothing_else():
+    """hugs_b200.dp.view_streams: high-priority streams + the blend kernels launched at the lowest priority
+    (hugs_b200_set_blend_priority, cudaLaunchKernelEx with a priority attribute): same image bit for bit,
+    same gradients up to the order of the reductions."""
+    import diff_gaussian_rasterization as dgr
+    from hugs_b200 import _native as N, dp
+    sc = scenes.make_scene(6000, 2000, 320, 200, 300.0, seed=73, device="cuda")
+    settings = scenes.settings_of(sc, dgr)
+
+    def render():
+        leaves = {k: sc[k].detach().clone().requires_grad_(True) for k in NAMES}
+        color, _ = dgr.GaussianRasterizer(settings)(
+            means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"], requires_grad=True),
+            opacities=leaves["opacity"], shs=leaves["shs"], scales=leaves["scales"], rotations=leaves["rotations"])
+        (color * sc["dL_dcolor"]).sum().backward()
+        return color.detach(), leaves
+
+    c0, l0 = render()
+    torch.cuda.synchronize()
+    streams = dp.view_streams(2)
+    try:
+        streams[0].wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(streams[0]):
+            c1, l1 = render()
+        torch.cuda.synchronize()
+    finally:
+        assert N.set_blend_priority(0, 0) == 1
+    assert torch.equal(c0, c1)
+    for k in NAMES:
+        assert refutil.rel_err(l1[k].grad.cpu().numpy(), l0[k].grad.cpu().numpy()) < 1e-5, k
