@@ -75,6 +75,12 @@ const char* hugs_b200_last_error(void);
  * NULL subject to the reference's exactly-one-of rule.  out_color is [3,H,W], radii is int32[P].
  * *num_rendered receives R.  debug != 0 synchronises and checks after every stage
  * (CR/auxiliary.h:166-173).
+ * CUDA-graph capture (no counterpart in the reference, whose forward blocks on a D2H copy of R): when `stream`
+ * is being captured, the call is enqueued for the pair capacity remembered from earlier uncaptured calls with
+ * the same (P, width, height) on this host thread, never waits, copies nothing to the host, and reports that
+ * capacity in *num_rendered (an upper bound of R; every kernel reads the real count on the device).  Without
+ * such an earlier call it returns HUGS_B200_EUNSUP.  The resize callbacks are called during the capture: what
+ * they return must stay valid for every replay.
  * ------------------------------------------------------------------------------------------- */
 int hugs_b200_rasterize_forward(
     hugs_b200_resize_fn geometry_buffer, void* geometry_user,
