@@ -11,12 +11,21 @@
 //   * the hits are taken 16 at a time and every batch runs in two phases with two thread layouts:
 //       phase 1, lane = pixel.  The sequential part of backward.cu:486-535 (transmittance,
 //         colour-behind recurrence, dL/dalpha).  Per (pixel, Gaussian) it leaves just two numbers
-//         in shared memory: w = alpha T (the weight of the pixel's dL/dpixel in dL/dcolour) and
-//         Z = G dL/dalpha (every geometric gradient is o Z times a polynomial in the pixel offset);
+//         in shared memory (one 8-byte store): w = alpha T (the weight of the pixel's dL/dpixel in
+//         dL/dcolour) and Z = G dL/dalpha (every geometric gradient is o Z times a polynomial in the
+//         pixel offset).  A lane that is not hit runs the same instructions with alpha = 0 and G = 0,
+//         which leaves its T and colour-behind unchanged and its two outputs zero without a select
+//         each.  (Evaluating the exponent as a quadratic in the pixel's position inside the sub-tile,
+//         five FMAs, was tried: its rounding error of ~1e-5 widens the band in which a pixel at
+//         alpha = 1/255 is classified differently from the forward pass a hundredfold, and gradients
+//         at full size left the 1e-3 bar.  The exponent is the forward pass's formula.)
 //       phase 2, lane = Gaussian (half-warp h takes the pixels 16h..16h+15).  Each lane runs down
-//         its Gaussian's row of w and Z and accumulates the 9 sums in registers -- no cross-lane
-//         reduction per hit (round 1's kernel spent 43 of its 111 instructions per (warp, Gaussian)
-//         in a 9-value shuffle butterfly); one shuffle per sum and batch joins the two halves;
+//         its Gaussian's row of (w, Z) and accumulates in registers -- no cross-lane reduction per
+//         hit (round 1's kernel spent 43 of its 111 instructions per (warp, Gaussian) in a 9-value
+//         shuffle butterfly).  The geometric sums are taken as RAW moments of Z over the integer
+//         pixel position (sum Z, sum Z i, sum Z i^2 per row pair: one add and two FMAs with immediate
+//         operands per pixel) and shifted to the Gaussian's centre once per lane and batch; one
+//         shuffle per sum joins the two halves;
 //   * a (warp, Gaussian) ends in two 16-byte vector reductions into a packed 32-byte gradient record
 //     (colour 3, mean2D 2, conic 3) plus one scalar reduction for the opacity; the per-Gaussian
 //     backward kernel reads the record (one sector) and writes the reference's arrays;
@@ -36,13 +45,18 @@ namespace {
 constexpr int kBwdG = 16;                       // Gaussians per batch
 constexpr int kBwdWarps = kBlendThreads / 32;  // 8
 
+constexpr uint32_t kRecBytes = 48;   // (x, y, A', B') (C', opacity, r, g) (b, list position, Gaussian index, -):
+                                     // 12-word stride, so the 16 lanes that store / read one record each do not collide
+constexpr uint32_t kRowBytes = 272;  // 32 x (w, Z) + 16: rows 0..7 start 4 banks apart, so the 128-bit reads of
+                                     // phase 2 (8 lanes = 8 rows, same column) touch every bank once
+
 struct __align__(16) BwdWarpSmem {
-    float4 rec[kBwdG][3];   // (x, y, A', B') (C', opacity, r, g) (b, list position, Gaussian index, -)
-    float sw[kBwdG][32];    // w of (Gaussian k, pixel p) at column (p + 4k) & 31
-    float sz[kBwdG][32];    // Z, same layout
-    float4 pixc[32];        // dL/dpixel of the warp's 32 pixels
-    uint32_t slot[kBwdG];   // list positions of the batch being assembled, descending
+    float4 rec[kBwdG][kRecBytes / 16];
+    float2 wz[kBwdG][kRowBytes / 8];   // (w, Z) of (Gaussian k, pixel p) at [k][p]
+    float4 pixc[32];                   // dL/dpixel of the warp's 32 pixels
+    uint32_t slot[kBwdG];              // list positions of the batch being assembled, descending
 };
+static_assert(sizeof(BwdWarpSmem) * kBwdWarps <= 48 * 1024, "static shared memory");
 
 __device__ __forceinline__ float ex2_ftz(float x) {
     float y;
@@ -59,8 +73,8 @@ __device__ __forceinline__ float2 lds_f2(uint32_t addr) {
     asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr) : "memory");
     return v;
 }
-__device__ __forceinline__ void sts_f1(uint32_t addr, float v) {
-    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+__device__ __forceinline__ void sts_f2(uint32_t addr, float a, float b) {
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
 }
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -102,8 +116,7 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
 
     BwdWarpSmem& s = s_all[warp];
     const uint32_t s_rec = (uint32_t)__cvta_generic_to_shared(&s.rec[0][0]);
-    const uint32_t s_sw = (uint32_t)__cvta_generic_to_shared(&s.sw[0][0]);
-    const uint32_t s_sz = (uint32_t)__cvta_generic_to_shared(&s.sz[0][0]);
+    const uint32_t s_wz = (uint32_t)__cvta_generic_to_shared(&s.wz[0][0]);
     const uint32_t s_pixc = (uint32_t)__cvta_generic_to_shared(&s.pixc[0]);
 
     const uint2 range = __ldg(ranges + tile_id);
@@ -132,8 +145,10 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
     const float ddelx_dx = 0.5f * W;
     const float ddely_dy = 0.5f * H;
 
-    // phase-2 identity of this lane: Gaussian e of the batch, pixels 16 half .. 16 half + 15
+    // phase-2 identity of this lane: Gaussian e of the batch, pixels 16 half .. 16 half + 15 (rows 2 half, 2 half + 1)
     const unsigned e = lane & 15u, half = lane >> 4;
+    const uint32_t p2_row = s_wz + e * kRowBytes + half * 128u;   // this lane's 16 (w, Z) pairs
+    const uint32_t p2_pix = s_pixc + half * 256u;                 // and the 16 pixels they belong to
     const float org_x = pm.x0, org_y = pm.y0 + 2.f * (float)half;
 
     // ---- the warp's hit masks, most distant list positions first ----------------------------------
@@ -187,7 +202,7 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
             const uint32_t pos = s.slot[lane];
             const uint32_t id = __ldg(point_list + range.x + pos);
             const StagedGaussian g = load_gaussian(id, means2D, conic_opacity, colors, color_stride);
-            const uint32_t a = s_rec + lane * 48u;
+            const uint32_t a = s_rec + lane * kRecBytes;
             sts_f4(a, g.xy.x, g.xy.y, g.co.x * (-0.5f * kLog2e), g.co.y * (-kLog2e));
             sts_f4(a + 16, g.co.z * (-0.5f * kLog2e), g.co.w, g.r, g.g);
             sts_f4(a + 32, g.b, __uint_as_float(pos), __uint_as_float(id), 0.f);
@@ -197,7 +212,7 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
         // ---- phase 1: lane = pixel --------------------------------------------------------------
 #pragma unroll 2
         for (int k = 0; k < n; k++) {
-            const uint32_t a = s_rec + (uint32_t)k * 48u;
+            const uint32_t a = s_rec + (uint32_t)k * kRecBytes;
             const float4 g0 = lds_f4(a);       // x, y, A', B'
             const float4 g1 = lds_f4(a + 16);  // C', opacity, r, g
             const float2 g2 = lds_f2(a + 32);  // b, list position
@@ -208,59 +223,63 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
             // clamp: a lane outside the footprint must not make inf (1 - alpha >= 0.01; a G that
             // underflows belongs to a lane that is not hit)
             const float G = ex2_ftz(fminf(p2, 0.f));
-            const float alpha = fminf(0.99f, g1.y * G);
+            const float oG = g1.y * G;
             // Skip if this one is behind the last contributor of this pixel, or was skipped by it in
-            // the forward pass (backward.cu:486-501).
-            const bool hit = (__float_as_uint(g2.y) < last_contributor) && !(p2 > 0.0f) && !(alpha < 1.0f / 255.0f);
+            // the forward pass (backward.cu:486-501: power > 0, alpha < 1/255).
+            const bool hit = (__float_as_uint(g2.y) < last_contributor) && !(p2 > 0.0f) && !(oG < 1.0f / 255.0f);
+            // a lane that is not hit runs the same instructions with alpha = 0 and G = 0: its T, its colour
+            // behind and its two outputs come out unchanged / zero without a select each
+            const float alpha = hit ? fminf(0.99f, oG) : 0.f;
+            const float Gh = hit ? G : 0.f;
             const float rcp = rcp_ftz(1.f - alpha);
             if (hit) T *= rcp;
             const float d0 = g1.z - acc0, d1 = g1.w - acc1, d2 = g2.x - acc2;
             float dL_dalpha = fmaf(d2, dLp2, fmaf(d1, dLp1, d0 * dLp0));
             dL_dalpha = fmaf(dL_dalpha, T, bg_term * rcp);
-            const float w = hit ? alpha * T : 0.f;
-            const float Z = hit ? G * dL_dalpha : 0.f;
-            if (hit) {
-                acc0 = fmaf(alpha, d0, acc0);
-                acc1 = fmaf(alpha, d1, acc1);
-                acc2 = fmaf(alpha, d2, acc2);
-            }
-            const uint32_t col = ((lane + 4u * (uint32_t)k) & 31u) * 4u + (uint32_t)k * 128u;
-            sts_f1(s_sw + col, w);
-            sts_f1(s_sz + col, Z);
+            acc0 = fmaf(alpha, d0, acc0);
+            acc1 = fmaf(alpha, d1, acc1);
+            acc2 = fmaf(alpha, d2, acc2);
+            sts_f2(s_wz + (uint32_t)k * kRowBytes + lane * 8u, alpha * T, Gh * dL_dalpha);
         }
         __syncwarp();
 
         // ---- phase 2: lane = (Gaussian e, half of the pixels) ----------------------------------
         {
-            const float4 r0 = lds_f4(s_rec + e * 48u);       // x, y, A', B'
-            const float4 r1 = lds_f4(s_rec + e * 48u + 16);  // C', opacity, -, -
-            const float gxl = r0.x - org_x, gyl = r0.y - org_y;
-            float c0 = 0.f, c1 = 0.f, c2 = 0.f, M0 = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f;
+            // raw moments of Z over the integer pixel position, rows 2 half (s0, t0) and 2 half + 1 (s1, t1):
+            // s = sum Z, t = sum Z i, u = sum Z i^2 (both rows)
+            float c0 = 0.f, c1 = 0.f, c2 = 0.f, s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f, u = 0.f;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const uint32_t col = ((16u * half + 4u * (uint32_t)j + 4u * e) & 31u) * 4u + e * 128u;
-                const float4 w4 = lds_f4(s_sw + col);
-                const float4 z4 = lds_f4(s_sz + col);
-                const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
-                const float zv[4] = {z4.x, z4.y, z4.z, z4.w};
+            for (int j = 0; j < 8; j++) {
+                const float4 q = lds_f4(p2_row + 16u * (uint32_t)j);   // (w, Z) of pixels 2j, 2j + 1
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int sidx = 4 * j + i;  // pixel 16 half + sidx sits at (sidx & 7, 2 half + (sidx >> 3))
-                    const float4 pc = lds_f4(s_pixc + (16u * half + (uint32_t)sidx) * 16u);
-                    c0 = fmaf(wv[i], pc.x, c0);
-                    c1 = fmaf(wv[i], pc.y, c1);
-                    c2 = fmaf(wv[i], pc.z, c2);
-                    const float dx = gxl - (float)(sidx & 7);
-                    const float dy = gyl - (float)(sidx >> 3);
-                    const float zx = zv[i] * dx, zy = zv[i] * dy;
-                    M0 += zv[i];
-                    Sx += zx;
-                    Sy += zy;
-                    Sxx = fmaf(zx, dx, Sxx);
-                    Sxy = fmaf(zx, dy, Sxy);
-                    Syy = fmaf(zy, dy, Syy);
+                for (int h = 0; h < 2; h++) {
+                    const int sidx = 2 * j + h;  // pixel 16 half + sidx sits at (sidx & 7, 2 half + (sidx >> 3))
+                    const float wv = h ? q.z : q.x, zv = h ? q.w : q.y;
+                    const float4 pc = lds_f4(p2_pix + 16u * (uint32_t)sidx);
+                    c0 = fmaf(wv, pc.x, c0);
+                    c1 = fmaf(wv, pc.y, c1);
+                    c2 = fmaf(wv, pc.z, c2);
+                    const int i = sidx & 7;
+                    if ((sidx >> 3) == 0) {
+                        s0 += zv;
+                        if (i) t0 = fmaf(zv, (float)i, t0);
+                    } else {
+                        s1 += zv;
+                        if (i) t1 = fmaf(zv, (float)i, t1);
+                    }
+                    if (i) u = fmaf(zv, (float)(i * i), u);
                 }
             }
+            // shift to the Gaussian's centre: dx = gxl - i, dy = gyl - r (r = 0, 1 within this lane's two rows)
+            const float4 r0 = lds_f4(s_rec + e * kRecBytes);       // x, y, A', B'
+            const float gxl = r0.x - org_x, gyl = r0.y - org_y;
+            const float m00 = s0 + s1, m10 = t0 + t1;   // m01 = m02 = s1, m11 = t1, m20 = u
+            float M0 = m00;
+            float Sx = fmaf(gxl, m00, -m10);
+            float Sy = fmaf(gyl, m00, -s1);
+            float Sxx = fmaf(gxl, fmaf(gxl, m00, -2.f * m10), u);
+            float Syy = fmaf(gyl, fmaf(gyl, m00, -2.f * s1), s1);
+            float Sxy = fmaf(gxl, Sy, fmaf(-gyl, m10, t1));
             c0 += __shfl_xor_sync(0xffffffffu, c0, 16);
             c1 += __shfl_xor_sync(0xffffffffu, c1, 16);
             c2 += __shfl_xor_sync(0xffffffffu, c2, 16);
@@ -271,12 +290,13 @@ __global__ void __launch_bounds__(kBlendThreads, 4)
             Sxy += __shfl_xor_sync(0xffffffffu, Sxy, 16);
             Syy += __shfl_xor_sync(0xffffffffu, Syy, 16);
             if ((int)lane < n) {
+                const float2 r1 = lds_f2(s_rec + e * kRecBytes + 16);        // C', opacity
                 const float cA = r0.z * (-2.f / kLog2e), cB = r0.w * (-1.f / kLog2e), cC = r1.x * (-2.f / kLog2e);
                 const float o = r1.y;
                 // X = dL/dG G dx = o Z dx, Y likewise; dG/ddelx = -G dx A - G dy B,
                 // dG/ddely = -G dy C - G dx B (backward.cu:520-521)
                 const float X = o * Sx, Y = o * Sy;
-                const size_t id = __float_as_uint(lds_f1(s_rec + e * 48u + 40));
+                const size_t id = __float_as_uint(lds_f1(s_rec + e * kRecBytes + 40));
                 float* rec = grad_pack + id * 8;
                 red_add_v4(rec, c0, c1, c2, -(cA * X + cB * Y) * ddelx_dx);
                 red_add_v4(rec + 4, -(cC * Y + cB * X) * ddely_dy, -0.5f * o * Sxx, -0.5f * o * Sxy, -0.5f * o * Syy);
