@@ -77,5 +77,51 @@ def raw(path):
         print(" ".join("%9s" % o for o in out) + "  " + r[iK][:60])
 
 
+
+STAGE_OF = [  # kernel-name fragment -> bench.py stage
+    ("lbs_forward_kernel", "lbs_forward"), ("lbs_backward_kernel", "lbs_backward"),
+    ("preprocess_backward_kernel", "preprocess_backward"), ("preprocess_kernel", "preprocess"),
+    ("radix_", "sort_pairs"), ("inclusive_scan_kernel", "inclusive_scan"), ("duplicate_", "duplicate_with_keys"),
+    ("tile_ranges", "tile_split"), ("l2_", "tile_split"),
+    ("render_forward_kernel", "render_forward"), ("render_backward_kernel", "render_backward"),
+]
+
+
+def traffic(path, source):
+    """profiles/ncu_dram_traffic.json (read by bench.py for roofline.traffic / issue_frac) from the raw page of
+    the one-frame --set full capture: per stage, DRAM bytes and duration summed over its launches, issue-active
+    duration-weighted."""
+    import json
+    rows = list(csv.reader(open(path)))
+    hdr, units = rows[0], rows[1]
+    col = {m: hdr.index(m) for m in ("Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum",
+                                     "dram__bytes_write.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active")}
+
+    def num(r, m, scale):
+        i = col[m]
+        return float(r[i].replace(",", "")) * scale.get(units[i], 1.0)
+
+    by, us, iss = defaultdict(float), defaultdict(float), defaultdict(float)
+    for r in rows[2:]:
+        stage = next((s for frag, s in STAGE_OF if frag in r[col["Kernel Name"]]), None)
+        if stage is None:
+            continue
+        t = num(r, "gpu__time_duration.sum", {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3})
+        b = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        by[stage] += num(r, "dram__bytes_read.sum", b) + num(r, "dram__bytes_write.sum", b)
+        us[stage] += t
+        iss[stage] += t * num(r, "smsp__issue_active.avg.pct_of_peak_sustained_active", {})
+    out = {"source": source,
+           "bytes_per_frame": {s: int(round(v, -5)) for s, v in by.items()},
+           "issue_active_pct": {s: round(iss[s] / us[s], 1) for s in us},
+           "issue_source": "same capture, smsp__issue_active.avg.pct_of_peak_sustained_active (duration-weighted over "
+                           "the stage's launches)",
+           "ncu_us_per_frame": {s: round(v, 1) for s, v in us.items()}}
+    print(json.dumps(out, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3])
+    else:
+        {"launches": launches, "raw": raw}[sys.argv[1]](sys.argv[2])

@@ -19,6 +19,7 @@ def main():
     _native.set_binning_mode(mode)
     rep = bench.Replica(bench.make_workload(workload, 0, 1, dev), dev, bench.our_impl(), sh_sink=True)
     rep.n_streams = 1
+    rep.use_graph = False   # one eager frame on one stream: every kernel is a plain launch for ncu
     for _ in range(3):
         rep.step_resident()
     torch.cuda.synchronize()
