@@ -259,7 +259,6 @@ class Replica:
         self.comm_events = None  # [(start, end)] of the allreduce, when the staged pass asks for it
         # the device-resident step of the two-segment path (every gradient lands in the flat buffer that exists
         # before the capture) is replayed as ONE CUDA graph (hugs_b200.dp.GraphedStep); HB_GRAPH=0 runs it eagerly
-        # (a single model's step -- AccumulateGrad-based -- is captured on ONE stream: DESIGN.md, graph limits)
         self.use_graph = (self.render2 is not None and self.training and self.buf is not None
                           and os.environ.get("HB_GRAPH", "1") == "1")
         self.graphed = None
@@ -575,14 +574,7 @@ class Replica:
     def _graphed_step(self):
         if self.graphed is None:
             from hugs_b200 import dp
-            n = self.n_streams
-            if not self.two_seg:
-                self.n_streams = 1
-            try:
-                self.graphed = dp.GraphedStep(lambda: self._step_resident_eager(exchange=False),
-                                              streams=self.n_streams, sinks_only=self.two_seg)
-            finally:
-                self.n_streams = n
+            self.graphed = dp.GraphedStep(lambda: self._step_resident_eager(exchange=False))
             if self.buf.gather:   # the graph writes the tensors autograd adopted as .grad during the capture
                 self._graph_grads = {k: p.grad for k, p in self.buf.params.items() if k not in self.buf.sunk}
         return self.graphed
@@ -1160,7 +1152,7 @@ def main():
                  "cuda_graph": ("value: the rank's local step is one CUDA-graph replay (%s), allreduce outside it; "
                                 "e2e: inputs prefetched one step ahead on a copy stream into staging blocks, "
                                 "device-to-device copy, the same graph replay, losses read two steps later"
-                                % ("views over 2 streams" if rep.two_seg else "one stream"))
+                                % ("views over %d streams" % rep.n_streams))
                  if rep.use_graph else None},
         "e2e": {"value": round(total_frames / (ms_e2e * 1e-3), 3), "unit": UNIT,
                 "h2d_bytes_per_step": int(rep.h2d_bytes), "d2h_bytes_per_step": int(rep.d2h_bytes),

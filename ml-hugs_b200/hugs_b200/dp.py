@@ -10,6 +10,8 @@ shard frames with no collective at all.
 """
 from typing import Dict, Iterable, List, Sequence
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -123,7 +125,8 @@ class FlatGradBuffer:
 
 
 def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, world_size: int,
-            group=None, streams: Sequence = (), read_loss: bool = True, after_view=None, exchange: bool = True):
+            group=None, streams: Sequence = (), read_loss: bool = True, after_view=None, exchange: bool = True,
+            pin_accumulators: bool = True):
     """One data-parallel step: ``render_view(v)`` must return the scalar loss tensor of view ``v``
     (forward through LBS + rasterizer); this rank handles ``shard_views`` of ``views``, calls
     backward on each loss (gradients accumulate in ``buf``), then allreduces.  Returns the local
@@ -131,8 +134,9 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
 
     ``streams`` (CUDA only): the rank's views alternate between these streams, so the issue-bound
     blend kernels of one view overlap the latency- and HBM-bound binning / per-Gaussian kernels of
-    the next (measured +5 % frames/s with two streams on B200); autograd orders the gradient
-    accumulation.  The losses are summed on the device and read once, after the last view
+    the next (measured +5 % frames/s with two streams on B200).  Gradients that go through sinks are added
+    atomically; the AccumulateGrad nodes of the other parameters are pinned to the step's main stream
+    (``pin_accumulators``, below), which orders their additions.  The losses are summed on the device and read once, after the last view
     (``read_loss=False``: not read at all -- the host does not wait for the step -- and the device-side
     list of losses is returned instead).  ``after_view(v)`` is called on the view's stream once its backward
     pass has been enqueued (e.g. to record the event that releases the view's input buffers).
@@ -161,6 +165,20 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
             return losses
         return float(sum(float(x) for x in losses))
     main = torch.cuda.current_stream()
+    # Parameters WITHOUT a gradient sink accumulate through autograd's AccumulateGrad, which runs on the stream
+    # that was current when the node was created -- a view's stream, if the node is created inside the view --
+    # and nothing orders the in-place additions of two views on two streams with each other, nor the first
+    # view's write of a gradient tensor with the second view's addition to it.  Eagerly the host's pacing hides
+    # it; a captured step replayed without that pacing produced wrong gradients and faults within 50 replays
+    # (tools/graph_bisect.py, profiles/r02_aw_graph_bisect.txt, r02_bp_pin.txt).  Creating the nodes HERE, on the
+    # step's main stream, and keeping them alive for the step makes every such accumulation run on the main
+    # stream, in order; autograd makes the main stream wait for the gradient's producer each time (0.5 % of
+    # the headline step).  Sinks need none of this: their additions are atomic.
+    pinned = []
+    if pin_accumulators and os.environ.get("HB_PIN_ACC", "1") == "1":   # (the switch is for tools/graph_bisect.py)
+        torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)   # the mismatch is the point
+        pinned = [p.expand_as(p).grad_fn.next_functions[0][0] for n, p in buf.params.items()
+                  if n not in buf.sunk and p.requires_grad]
     for s in streams:
         s.wait_stream(main)
     losses = []
@@ -169,6 +187,7 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
             losses.append(one(views[i]))
     for s in streams:
         main.wait_stream(s)
+    del pinned
     if exchange:
         buf.allreduce(group)
     if not read_loss:
@@ -204,17 +223,12 @@ class GraphedStep:
     The gradient exchange of a multi-rank step stays outside the graph (``exchange=False``, then
     ``buf.allreduce()``).
 
-    Limits (measured, tools/graph_bisect.py): the step must accumulate its gradients through gradient sinks
-    into buffers that exist before the capture (``FlatGradBuffer`` in-place mode, the two-segment calls), or
-    run on ONE stream.  A captured step whose parameters get their ``.grad`` from autograd's AccumulateGrad
-    with views on two streams replayed with corrupted gradients and illegal addresses (the tensors autograd
-    adopts during capture live in the graph's private pool), so ``GraphedStep`` refuses ``streams > 1``
-    unless ``sinks_only=True`` says every parameter gradient goes through a sink."""
+    A step whose views run on several streams can be captured as long as its gradient accumulation is ordered on
+    the device rather than by the host's pacing: ``dp_step`` does that (gradient sinks are atomic, the other
+    parameters' AccumulateGrad nodes are pinned to the main stream).  Without it the same step replays with
+    corrupted gradients (tools/graph_bisect.py)."""
 
-    def __init__(self, step_fn, warmup: int = 3, streams: int = 1, sinks_only: bool = False):
-        if streams > 1 and not sinks_only:
-            raise ValueError("GraphedStep: a step over several streams can only be captured when every gradient "
-                             "goes through a gradient sink (sinks_only=True)")
+    def __init__(self, step_fn, warmup: int = 3):
         cur = torch.cuda.current_stream()
         side = torch.cuda.Stream()
         side.wait_stream(cur)

@@ -52,7 +52,7 @@ def test_graphed_step_replays_the_eager_gradients():
         ref = buf.flat.clone()
         assert float(ref.abs().max()) > 0
         step = dp.GraphedStep(lambda: dp.dp_step(render, ids, buf, 0, 1, streams=streams, read_loss=False,
-                                                 exchange=False), streams=2, sinks_only=True)
+                                                 exchange=False))
         for _ in range(5):
             losses = step.replay()
             torch.cuda.synchronize()
@@ -89,10 +89,37 @@ def test_capture_without_a_known_capacity_is_refused():
     torch.cuda.synchronize()
 
 
-def test_graphed_step_refuses_two_streams_without_sinks():
+def test_graphed_step_without_sinks_over_two_streams():
+    """Parameters without gradient sinks (autograd's AccumulateGrad) and views on two streams: dp_step pins the
+    accumulation nodes to the main stream, which orders the additions on the device -- the captured step
+    replays the eager gradients (without the pinning it replayed garbage within 50 steps)."""
+    import diff_gaussian_rasterization as dgr
     from hugs_b200 import dp
-    with pytest.raises(ValueError, match="sink"):
-        dp.GraphedStep(lambda: None, streams=2)
+    n_views = 4
+    views = [scenes.make_scene(9000, 0, 320, 200, 300.0, seed=74, device="cuda", view=v, n_views=n_views)
+             for v in range(n_views)]
+    params = {k: views[0][k].detach().clone().contiguous().requires_grad_(True) for k in NAMES}
+    buf = dp.FlatGradBuffer(params, gather=True)
+
+    def render(v):
+        sc = views[v]
+        color, _ = dgr.GaussianRasterizer(scenes.settings_of(sc, dgr))(
+            means3D=params["means3D"], means2D=torch.zeros_like(params["means3D"], requires_grad=True),
+            opacities=params["opacity"], shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        return (color * sc["dL_dcolor"]).sum()
+
+    streams = dp.view_streams(2, prioritise=False)
+    ids = list(range(n_views))
+    dp.dp_step(render, ids, buf, 0, 1, streams=streams, read_loss=False)
+    torch.cuda.synchronize()
+    ref = {k: p.grad.clone() for k, p in params.items()}
+    step = dp.GraphedStep(lambda: dp.dp_step(render, ids, buf, 0, 1, streams=streams, read_loss=False, exchange=False))
+    adopted = {k: p.grad for k, p in params.items()}   # the tensors autograd adopted as .grad during the capture
+    for _ in range(30):
+        step.replay()
+    torch.cuda.synchronize()
+    for k in NAMES:
+        assert refutil.rel_err(adopted[k].cpu().numpy(), ref[k].cpu().numpy()) < 1e-5, k
 
 
 @pytest.mark.parametrize("workload,two_seg", [("smoke_256", True), ("smoke_human_256", False)])

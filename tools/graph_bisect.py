@@ -3,8 +3,8 @@
     python tools/graph_bisect.py VARIANT [steps]      one variant in this process
     python tools/graph_bisect.py all [steps]          every variant, each in its own process (twice)
 
-A variant builds bench.Replica for a 256x256 workload, captures the resident step (hugs_b200.dp.GraphedStep,
-with its two-stream guard overridden), replays it `steps` times with a device synchronize after every replay
+A variant builds bench.Replica for a 256x256 workload, captures the resident step (hugs_b200.dp.GraphedStep;
+HB_PIN_ACC=0 switches dp_step's pinning of the AccumulateGrad nodes off, which is what made it fail), replays it `steps` times with a device synchronize after every replay
 (so the failing step is known) and compares the parameter gradients of every replay with the eager step's.
 Result of the round-2 run: profiles/r02_aw_graph_bisect.txt."""
 import os
@@ -58,8 +58,7 @@ def run(variant, steps):
             rep.step_resident()
         else:
             if graphed is None:
-                graphed = dp.GraphedStep(lambda: rep._step_resident_eager(exchange=False), streams=rep.n_streams,
-                                         sinks_only=True)
+                graphed = dp.GraphedStep(lambda: rep._step_resident_eager(exchange=False))
             graphed.replay()
             if rep.buf is not None and rep.buf.gather:   # the graph writes the tensors autograd adopted in capture
                 if adopted is None:
