@@ -517,7 +517,8 @@ class Replica:
             return loss
         return dp.dp_step(render_view, list(range(self.views)), self.buf, 0, 1,
                    streams=self.streams if self.n_streams > 1 else (), read_loss=False,
-                          after_view=after_view, exchange=exchange)
+                          after_view=after_view, exchange=exchange,
+                          pin_accumulators=os.environ.get("HB_PIN_ACC", "1") == "1")   # (0: tools/graph_bisect.py)
 
     def _deform_all(self, As):
         """animation: the rank's pose frames of the step through ONE batched LBS call when the

@@ -10,8 +10,6 @@ shard frames with no collective at all.
 """
 from typing import Dict, Iterable, List, Sequence
 
-import os
-
 import torch
 import torch.distributed as dist
 
@@ -175,7 +173,7 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     # stream, in order; autograd makes the main stream wait for the gradient's producer each time (0.5 % of
     # the headline step).  Sinks need none of this: their additions are atomic.
     pinned = []
-    if pin_accumulators and os.environ.get("HB_PIN_ACC", "1") == "1":   # (the switch is for tools/graph_bisect.py)
+    if pin_accumulators:
         torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)   # the mismatch is the point
         pinned = [p.expand_as(p).grad_fn.next_functions[0][0] for n, p in buf.params.items()
                   if n not in buf.sunk and p.requires_grad]
