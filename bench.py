@@ -518,7 +518,8 @@ class Replica:
         return dp.dp_step(render_view, list(range(self.views)), self.buf, 0, 1,
                    streams=self.streams if self.n_streams > 1 else (), read_loss=False,
                           after_view=after_view, exchange=exchange,
-                          pin_accumulators=os.environ.get("HB_PIN_ACC", "1") == "1")   # (0: tools/graph_bisect.py)
+                          pin_accumulators=os.environ.get("HB_PIN_ACC", "1") == "1",   # (0: tools/graph_bisect.py)
+                          defer_scene=self.two_seg and os.environ.get("HB_DEFER", "1") == "1")
 
     def _deform_all(self, As):
         """animation: the rank's pose frames of the step through ONE batched LBS call when the

@@ -47,6 +47,7 @@ extern "C" {
  *                           takes dL/d(clamped image) and gives the clamped channels no gradient. */
 #define HUGS_B200_FLAG_DEBUG   1
 #define HUGS_B200_FLAG_CLAMP01 2
+#define HUGS_B200_FLAG_DEFER_SEG1 4   /* backward of a two-segment call: see hugs_b200_scene_backward_views */
 
 typedef void* hugs_b200_stream_t;
 
@@ -511,6 +512,28 @@ int hugs_b200_rasterize_backward_seg2_ex(int D, int M, int R, const float* backg
                                          char* layer_buffer, size_t layer_bytes, const float* dL_dpix_layer,
                                          const hugs_b200_grad_sinks* sinks);
 
+/* The scene segment's per-Gaussian backward for ALL views of a view-batched training step in one launch (no
+ * counterpart in the reference, which trains on one view per step).  A backward call made with
+ * HUGS_B200_FLAG_DEFER_SEG1 in `debug` (two segments, all five sinks of segment 1 set) runs the blend backward
+ * and segment 0's per-Gaussian backward only and leaves segment 1's share in the view's geometry workspace
+ * (packed records, clamp bits, opacity scratch).  When the last view of the step has done so, this call reads
+ * every scene Gaussian's parameters and SH row ONCE, walks the views, and adds the summed gradients to the sinks
+ * once -- ~110 B per Gaussian and view instead of 744.  Per view: its camera, its radii [P0+P1] and its geometry
+ * workspace (unchanged since the view's backward call).  The deferring backward call still writes segment 1's
+ * rows of dL_dmean2D (the screen-space gradient it reports); its dL_dconic, dL_dcolor and dL_dcov3D rows are
+ * not produced.  Must be ordered after every view's backward call on the device (same stream, or an event). */
+typedef struct hugs_b200_scene_view {
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    float tan_fovx, tan_fovy;
+    const int* radii;
+    char* geom_buffer;
+} hugs_b200_scene_view;
+int hugs_b200_scene_backward_views(int n_views, const hugs_b200_scene_view* views, int P0, int P1, int D, int M,
+                                   int width, int height, const float* means3D1, const float* shs1,
+                                   const float* scales1, float scale_modifier, const float* rotations1,
+                                   const hugs_b200_grad_sinks* sinks, hugs_b200_stream_t stream);
 
 /* ---- fused decoder MLPs on the tensor cores (tcgen05 / TMEM, 3xTF32) -----------------------------------
  * Replaces the torch.nn.Linear / GELU chains of hugs/models/modules/decoders.py:24-110 (AppearanceDecoder

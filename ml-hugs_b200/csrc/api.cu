@@ -850,6 +850,7 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
                                  float* dL_drot, int debug, hugs_b200_stream_t stream_, int dL_dsh_accumulate) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool clamp01 = (debug & HUGS_B200_FLAG_CLAMP01) != 0;   // the forward call was made with the same flag
+    const bool defer1 = (debug & HUGS_B200_FLAG_DEFER_SEG1) != 0;  // segment 1 is left to hugs_b200_scene_backward_views
     debug &= HUGS_B200_FLAG_DEBUG;
     if (P < 0 || R < 0 || width <= 0 || height <= 0) {
         set_error("rasterize_backward: bad sizes");
@@ -887,6 +888,12 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
     // an opacity sink it goes through a scratch array of the geometry workspace first.
     const hugs_b200_grad_sinks* sinks = tl_seg2 ? tl_sinks : nullptr;
     const bool opac_scratch = sinks && (sinks->opacity[0] || sinks->opacity[1]);
+    if (defer1 && !(tl_seg2 && sinks && sinks->means3D[1] && sinks->sh[1] && sinks->opacity[1] && sinks->scales[1] &&
+                    sinks->rotations[1])) {
+        set_error("rasterize_backward: HUGS_B200_FLAG_DEFER_SEG1 needs a two-segment call with all five sinks of "
+                  "segment 1");
+        return HUGS_B200_EINVAL;
+    }
     float* const opac_target = opac_scratch ? geom.grad_opac : dL_dopacity;
     auto blend_backward = [&]() -> int {
         if (opac_scratch) {   // grad_pack and grad_opac are neighbours: one fill
@@ -936,6 +943,11 @@ int hugs_b200_rasterize_backward_acc(int P, int D, int M, int R, const float* ba
         for (int seg = 0; seg < 2; seg++) {
             const int n = seg == 0 ? s2->P0 : P - s2->P0;
             if (n <= 0) continue;
+            if (defer1 && seg == 1) {   // only what the caller is owed at once: the view's screen-space gradient
+                const int rc = launch_unpack_mean2d(n, radii + r0, geom.grad_pack + 8 * r0, dL_dmean2D + 3 * r0, stream);
+                if (rc) return rc;
+                continue;
+            }
             const size_t o = seg == 0 ? 0 : r0;   // first row of the segment in the joint arrays
             PreBwdExtra ex;
             ex.grad_pack2 = pack2 ? pack2 + 8 * o : nullptr;
@@ -1240,6 +1252,43 @@ int hugs_b200_rasterize_backward_seg2_ex(int D, int M, int R, const float* backg
         dL_dpix_layer);
     tl_sinks = nullptr;
     return rc;
+}
+
+int hugs_b200_scene_backward_views(int n_views, const hugs_b200_scene_view* views, int P0, int P1, int D, int M,
+                                   int width, int height, const float* means3D1, const float* shs1,
+                                   const float* scales1, float scale_modifier, const float* rotations1,
+                                   const hugs_b200_grad_sinks* sinks, hugs_b200_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (n_views < 0 || P0 < 0 || P1 < 0 || width <= 0 || height <= 0 || (n_views > 0 && !views)) {
+        set_error("scene_backward_views: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    if (n_views == 0 || P1 == 0) return 0;
+    if (!means3D1 || !shs1 || !scales1 || !rotations1 || !sinks || !sinks->means3D[1] || !sinks->sh[1] ||
+        !sinks->opacity[1] || !sinks->scales[1] || !sinks->rotations[1]) {
+        set_error("scene_backward_views: null pointer (segment 1 needs its four input arrays and all five sinks)");
+        return HUGS_B200_EINVAL;
+    }
+    const int P = P0 + P1;
+    std::vector<SceneViewHost> host((size_t)n_views);
+    for (int v = 0; v < n_views; v++) {
+        const hugs_b200_scene_view& in = views[v];
+        if (!in.viewmatrix || !in.projmatrix || !in.cam_pos || !in.radii || !in.geom_buffer) {
+            set_error("scene_backward_views: view %d: null pointer", v);
+            return HUGS_B200_EINVAL;
+        }
+        const GeomView geom = carve_geom(in.geom_buffer, P);
+        SceneViewHost& h = host[(size_t)v];
+        h.cam = make_camera(in.viewmatrix, in.projmatrix, in.cam_pos, width, height, in.tan_fovx, in.tan_fovy);
+        h.radii = in.radii + P0;
+        h.grad_pack = geom.grad_pack + 8 * (size_t)P0;
+        h.clamped = geom.clamped + P0;
+        h.opac_scratch = geom.grad_opac + P0;
+    }
+    StageScope scope(ST_PREPROCESS_BWD, stream);
+    return launch_scene_backward_views(P1, D, M, n_views, host.data(), means3D1, shs1, scales1, rotations1,
+                                       scale_modifier, sinks->means3D[1], sinks->sh[1], sinks->scales[1],
+                                       sinks->rotations[1], sinks->opacity[1], stream);
 }
 
 size_t hugs_b200_mlp_packed_floats(int K, int n_pad) {

@@ -221,6 +221,19 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                                float* dL_drot, bool sh_accumulate, cudaStream_t stream,
                                const struct PreBwdExtra* extra = nullptr, SegBatch* batch = nullptr);
+// The scene segment's per-Gaussian backward for all views of a step in one launch (preprocess_backward.cu).
+struct SceneViewHost {
+    Camera cam;
+    const int* radii;            // scene rows of the view's arrays
+    const float* grad_pack;
+    const uint8_t* clamped;
+    const float* opac_scratch;
+};
+int launch_unpack_mean2d(int P, const int* radii, const float* grad_pack, float* dL_dmean2D, cudaStream_t stream);
+int launch_scene_backward_views(int P, int D, int M, int n_views, const SceneViewHost* views, const float* means3D,
+                                const float* shs, const float* scales, const float* rotations, float scale_modifier,
+                                float* g_mean, float* g_sh, float* g_scale, float* g_rot, float* g_opac,
+                                cudaStream_t stream);
 int launch_layer_filter(int num_tiles, const uint2* ranges, const uint32_t* list, int n_layer, uint32_t* list_out,
                         uint2* ranges_out, cudaStream_t stream);
 

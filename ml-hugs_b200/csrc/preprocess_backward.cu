@@ -567,6 +567,319 @@ __global__ void __launch_bounds__(kPbThreads, 5)
         if (a.dL_drot != nullptr && !acc_rot) reinterpret_cast<float4*>(a.dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
+
+// =========================================================================================================
+// The scene segment's per-Gaussian backward for ALL views of a training step in one launch
+// (hugs_b200_scene_backward_views).  A view-batched step runs the kernel above once per view: every launch
+// reads the Gaussian's SH row (192 B) and its parameters again and adds its gradients to the parameters'
+// accumulation buffers (read-modify-write of 236 B at the DRAM), 744 B per Gaussian and VIEW in all.  The scene
+// Gaussians are leaves with gradient sinks and the same parameters in every view, so their share can wait
+// until the step's last blend backward has run: this kernel then reads a Gaussian's parameters and SH row
+// ONCE, walks the views (per view: the radius, the blend backward's 32-byte record, the clamp bits and the
+// opacity scratch, 41 B), sums dL/dcov3D, dL/dmean and
+// dL/dopacity in registers and dL/dsh in a shared-memory row, and adds each sum to its sink once: ~120 B per
+// Gaussian and view at 8 views.  Same arithmetic as the per-view kernel, view by view; only the order of the
+// additions differs.
+// What a deferred view still owes its caller at once: the screen-space gradient it reports (means2D.grad,
+// the densification statistic of hugs/trainer) -- the packed record's two mean2D words, zero for culled rows.
+__global__ void __launch_bounds__(256) unpack_mean2d_kernel(int P, const int* __restrict__ radii,
+                                                            const float* __restrict__ grad_pack,
+                                                            float* __restrict__ dL_dmean2D) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P) return;
+    float x = 0.f, y = 0.f;
+    if (__ldg(radii + idx) > 0) {
+        x = __ldg(grad_pack + 8 * (size_t)idx + 3);
+        y = __ldg(grad_pack + 8 * (size_t)idx + 4);
+    }
+    dL_dmean2D[3 * (size_t)idx + 0] = x;
+    dL_dmean2D[3 * (size_t)idx + 1] = y;
+    dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+}
+
+constexpr int kMaxViews = 16;
+struct SceneViewRec {
+    const float* view;
+    const float* proj;
+    const float* campos;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    const int* radii;            // the scene rows of the view's radii
+    const float* grad_pack;      // [P,8], scene rows of the view's geometry workspace
+    const uint8_t* clamped;      // [P]
+    const float* opac_scratch;   // [P]
+};
+struct SceneViewsArgs {
+    int P, D, M, V;
+    const float* means3D;
+    const float* shs;
+    const float* scales;
+    const float* rotations;
+    float scale_modifier;
+    float* g_mean;    // sinks: [P,3]
+    float* g_sh;      //        [P,16,3]
+    float* g_scale;   //        [P,3]
+    float* g_rot;     //        [P,4]
+    float* g_opac;    //        [P]
+    SceneViewRec v[kMaxViews];
+};
+constexpr int kSvSmemBytes = 2 * kPbThreads * kPbRowBytes;   // SH rows | dL/dsh accumulation rows
+
+__global__ void __launch_bounds__(kPbThreads, 4) scene_backward_views_kernel(const SceneViewsArgs a) {
+    extern __shared__ __align__(16) unsigned char s_rows[];
+    __shared__ float s_cam[kMaxViews][36];
+    for (int i = (int)threadIdx.x; i < a.V * 35; i += kPbThreads) {
+        const int v = i / 35, j = i - 35 * v;
+        s_cam[v][j] = j < 16 ? __ldg(a.v[v].view + j) : (j < 32 ? __ldg(a.v[v].proj + j - 16) : __ldg(a.v[v].campos + j - 32));
+    }
+    const int idx = blockIdx.x * kPbThreads + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const bool valid = idx < a.P;
+    unsigned mask = 0;   // bit v: visible in view v
+    if (valid)
+        for (int v = 0; v < a.V; v++) mask |= (__ldg(a.v[v].radii + idx) > 0 ? 1u : 0u) << v;
+    const int nf = 3 * (a.D + 1) * (a.D + 1);
+    const int nv = (nf + 3) >> 2;
+    const uint32_t s_warp = (uint32_t)__cvta_generic_to_shared(s_rows) + warp * 32u * kPbRowBytes;
+    const uint32_t s_acc_warp = s_warp + kPbThreads * kPbRowBytes;
+    const size_t warp_row0 = (size_t)blockIdx.x * kPbThreads + warp * 32u;
+    const unsigned alive = __ballot_sync(0xffffffffu, mask != 0u);
+    if (alive != 0u) {
+        const float4* g_warp = reinterpret_cast<const float4*>(a.shs) + 12 * warp_row0;
+        unsigned row = lane / 12u, col = lane % 12u;  // 16-byte word 32 j + lane = (row, col)
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            if (((alive >> row) & 1u) && (int)col < nv)
+                cp_async16(s_warp + row * kPbRowBytes + col * 16u, g_warp + 32 * j + lane);
+            col += 8u;
+            row += 2u;
+            if (col >= 12u) {
+                col -= 12u;
+                row += 1u;
+            }
+        }
+    }
+    const uint32_t mine = s_warp + lane * kPbRowBytes, mine_acc = s_acc_warp + lane * kPbRowBytes;
+#pragma unroll
+    for (int i = 0; i < 12; i++) sts128(mine_acc + 16u * i, 0.f, 0.f, 0.f, 0.f);
+    __syncthreads();  // s_cam
+
+    float mx = 0.f, my = 0.f, mz = 0.f, sx = 0.f, sy = 0.f, sz = 0.f, qr = 0.f, qx = 0.f, qy = 0.f, qz = 0.f;
+    float R[3][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+    float cov3[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (mask != 0u) {
+        mx = __ldg(a.means3D + 3 * (size_t)idx + 0);
+        my = __ldg(a.means3D + 3 * (size_t)idx + 1);
+        mz = __ldg(a.means3D + 3 * (size_t)idx + 2);
+        sx = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 0);
+        sy = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 1);
+        sz = a.scale_modifier * __ldg(a.scales + 3 * (size_t)idx + 2);
+        qr = __ldg(a.rotations + 4 * (size_t)idx + 0);
+        qx = __ldg(a.rotations + 4 * (size_t)idx + 1);
+        qy = __ldg(a.rotations + 4 * (size_t)idx + 2);
+        qz = __ldg(a.rotations + 4 * (size_t)idx + 3);
+        R[0][0] = 1.f - 2.f * (qy * qy + qz * qz);
+        R[0][1] = 2.f * (qx * qy - qr * qz);
+        R[0][2] = 2.f * (qx * qz + qr * qy);
+        R[1][0] = 2.f * (qx * qy + qr * qz);
+        R[1][1] = 1.f - 2.f * (qx * qx + qz * qz);
+        R[1][2] = 2.f * (qy * qz - qr * qx);
+        R[2][0] = 2.f * (qx * qz - qr * qy);
+        R[2][1] = 2.f * (qy * qz + qr * qx);
+        R[2][2] = 1.f - 2.f * (qx * qx + qy * qy);
+        const float s[3] = {sx, sy, sz};
+        float Mm[3][3];
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int r = 0; r < 3; r++) Mm[c][r] = s[r] * R[c][r];
+        cov3[0] = Mm[0][0] * Mm[0][0] + Mm[0][1] * Mm[0][1] + Mm[0][2] * Mm[0][2];
+        cov3[1] = Mm[0][0] * Mm[1][0] + Mm[0][1] * Mm[1][1] + Mm[0][2] * Mm[1][2];
+        cov3[2] = Mm[0][0] * Mm[2][0] + Mm[0][1] * Mm[2][1] + Mm[0][2] * Mm[2][2];
+        cov3[3] = Mm[1][0] * Mm[1][0] + Mm[1][1] * Mm[1][1] + Mm[1][2] * Mm[1][2];
+        cov3[4] = Mm[1][0] * Mm[2][0] + Mm[1][1] * Mm[2][1] + Mm[1][2] * Mm[2][2];
+        cov3[5] = Mm[2][0] * Mm[2][0] + Mm[2][1] * Mm[2][1] + Mm[2][2] * Mm[2][2];
+    }
+    cp_async_wait_all();
+    __syncwarp();
+
+    float dmean_x = 0.f, dmean_y = 0.f, dmean_z = 0.f, dopac = 0.f;
+    float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int v = 0; v < a.V; v++) {
+        const SceneViewRec& w = a.v[v];
+        if (!((mask >> v) & 1u)) continue;   // culled in this view (or not a Gaussian at all)
+        const float* V = s_cam[v];
+        const float* Pm = s_cam[v] + 16;
+        const float4 pk0 = __ldg(reinterpret_cast<const float4*>(w.grad_pack) + 2 * (size_t)idx);
+        const float4 pk1 = __ldg(reinterpret_cast<const float4*>(w.grad_pack) + 2 * (size_t)idx + 1);
+        const uint8_t cl = __ldg(w.clamped + idx);
+        dopac += __ldg(w.opac_scratch + idx);
+        const float g2x = pk0.w, g2y = pk1.x;
+        float dRGB[3];
+        dRGB[0] = (cl & 1) ? 0.f : pk0.x;
+        dRGB[1] = (cl & 2) ? 0.f : pk0.y;
+        dRGB[2] = (cl & 4) ? 0.f : pk0.z;
+
+        // ---- cov2D backward (backward.cu:144-274), as in preprocess_backward_kernel ------------------
+        const float dcon_x = pk1.y, dcon_y = pk1.z, dcon_z = pk1.w;
+        float tx = V[0] * mx + V[4] * my + V[8] * mz + V[12];
+        float ty = V[1] * mx + V[5] * my + V[9] * mz + V[13];
+        const float tz = V[2] * mx + V[6] * my + V[10] * mz + V[14];
+        const float limx = 1.3f * w.tan_fovx;
+        const float limy = 1.3f * w.tan_fovy;
+        const float txtz = tx / tz;
+        const float tytz = ty / tz;
+        tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+        ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+        const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+        const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+        const float hx = w.focal_x, hy = w.focal_y;
+        const float J00 = hx / tz, J02 = -(hx * tx) / (tz * tz);
+        const float J11 = hy / tz, J12 = -(hy * ty) / (tz * tz);
+        const float T00 = V[0] * J00 + V[2] * J02, T01 = V[4] * J00 + V[6] * J02, T02 = V[8] * J00 + V[10] * J02;
+        const float T10 = V[1] * J11 + V[2] * J12, T11 = V[5] * J11 + V[6] * J12, T12 = V[9] * J11 + V[10] * J12;
+        const float V00 = cov3[0], V01 = cov3[1], V02 = cov3[2], V11 = cov3[3], V12 = cov3[4], V22 = cov3[5];
+        const float TV00 = T00 * V00 + T01 * V01 + T02 * V02;
+        const float TV01 = T00 * V01 + T01 * V11 + T02 * V12;
+        const float TV02 = T00 * V02 + T01 * V12 + T02 * V22;
+        const float TV10 = T10 * V00 + T11 * V01 + T12 * V02;
+        const float TV11 = T10 * V01 + T11 * V11 + T12 * V12;
+        const float TV12 = T10 * V02 + T11 * V12 + T12 * V22;
+        const float ca = TV00 * T00 + TV01 * T01 + TV02 * T02 + 0.3f;
+        const float cb = TV10 * T00 + TV11 * T01 + TV12 * T02;
+        const float cc = TV10 * T10 + TV11 * T11 + TV12 * T12 + 0.3f;
+        const float denom = ca * cc - cb * cb;
+        float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        if (denom2inv != 0.f) {
+            dL_da = denom2inv * (-cc * cc * dcon_x + 2.f * cb * cc * dcon_y + (denom - ca * cc) * dcon_z);
+            dL_dc = denom2inv * (-ca * ca * dcon_z + 2.f * ca * cb * dcon_y + (denom - ca * cc) * dcon_x);
+            dL_db = denom2inv * 2.f * (cb * cc * dcon_x - (denom + 2.f * cb * cb) * dcon_y + ca * cb * dcon_z);
+            dcov[0] += T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc;
+            dcov[3] += T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc;
+            dcov[5] += T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc;
+            dcov[1] += 2.f * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2.f * T10 * T11 * dL_dc;
+            dcov[2] += 2.f * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2.f * T10 * T12 * dL_dc;
+            dcov[4] += 2.f * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2.f * T11 * T12 * dL_dc;
+        }
+        const float dL_dT00 = 2.f * TV00 * dL_da + TV10 * dL_db;
+        const float dL_dT01 = 2.f * TV01 * dL_da + TV11 * dL_db;
+        const float dL_dT02 = 2.f * TV02 * dL_da + TV12 * dL_db;
+        const float dL_dT10 = 2.f * TV10 * dL_dc + TV00 * dL_db;
+        const float dL_dT11 = 2.f * TV11 * dL_dc + TV01 * dL_db;
+        const float dL_dT12 = 2.f * TV12 * dL_dc + TV02 * dL_db;
+        const float dL_dJ00 = V[0] * dL_dT00 + V[4] * dL_dT01 + V[8] * dL_dT02;
+        const float dL_dJ02 = V[2] * dL_dT00 + V[6] * dL_dT01 + V[10] * dL_dT02;
+        const float dL_dJ11 = V[1] * dL_dT10 + V[5] * dL_dT11 + V[9] * dL_dT12;
+        const float dL_dJ12 = V[2] * dL_dT10 + V[6] * dL_dT11 + V[10] * dL_dT12;
+        const float itz = 1.f / tz;
+        const float itz2 = itz * itz;
+        const float itz3 = itz2 * itz;
+        const float dL_dtx = x_grad_mul * -hx * itz2 * dL_dJ02;
+        const float dL_dty = y_grad_mul * -hy * itz2 * dL_dJ12;
+        const float dL_dtz = -hx * itz2 * dL_dJ00 - hy * itz2 * dL_dJ11 + (2.f * hx * tx) * itz3 * dL_dJ02 +
+                             (2.f * hy * ty) * itz3 * dL_dJ12;
+        float vm_x = V[0] * dL_dtx + V[1] * dL_dty + V[2] * dL_dtz;
+        float vm_y = V[4] * dL_dtx + V[5] * dL_dty + V[6] * dL_dtz;
+        float vm_z = V[8] * dL_dtx + V[9] * dL_dty + V[10] * dL_dtz;
+        {   // projection path (backward.cu:370-387)
+            const float m_hw = Pm[3] * mx + Pm[7] * my + Pm[11] * mz + Pm[15];
+            const float m_w = 1.0f / (m_hw + 0.0000001f);
+            const float mul1 = (Pm[0] * mx + Pm[4] * my + Pm[8] * mz + Pm[12]) * m_w * m_w;
+            const float mul2 = (Pm[1] * mx + Pm[5] * my + Pm[9] * mz + Pm[13]) * m_w * m_w;
+            vm_x += (Pm[0] * m_w - Pm[3] * mul1) * g2x + (Pm[1] * m_w - Pm[3] * mul2) * g2y;
+            vm_y += (Pm[4] * m_w - Pm[7] * mul1) * g2x + (Pm[5] * m_w - Pm[7] * mul2) * g2y;
+            vm_z += (Pm[8] * m_w - Pm[11] * mul1) * g2x + (Pm[9] * m_w - Pm[11] * mul2) * g2y;
+        }
+        // ---- SH backward (backward.cu:20-139): the row is re-read from shared memory for every view ---
+        {
+            float sh[48], gsh[48];
+#pragma unroll
+            for (int i = 0; i < 12; i++) {
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (i < nv) t = lds128(mine + 16u * i);
+                sh[4 * i + 0] = t.x;
+                sh[4 * i + 1] = t.y;
+                sh[4 * i + 2] = t.z;
+                sh[4 * i + 3] = t.w;
+            }
+            sh_backward(a.D, sh, mx - V[32], my - V[33], mz - V[34], dRGB, gsh, vm_x, vm_y, vm_z);
+#pragma unroll
+            for (int i = 0; i < 12; i++) {
+                const float4 t = lds128(mine_acc + 16u * i);
+                sts128(mine_acc + 16u * i, t.x + gsh[4 * i], t.y + gsh[4 * i + 1], t.z + gsh[4 * i + 2], t.w + gsh[4 * i + 3]);
+            }
+        }
+        dmean_x += vm_x;
+        dmean_y += vm_y;
+        dmean_z += vm_z;
+    }
+    __syncwarp();
+    // dL/dsh: the accumulated rows of the warp's visible Gaussians, 512 contiguous bytes per warp instruction
+    {
+        float4* g_out = reinterpret_cast<float4*>(a.g_sh) + 12 * warp_row0;
+        unsigned row = lane / 12u, col = lane % 12u;
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            if ((alive >> row) & 1u) {
+                const float4 t = lds128(s_acc_warp + row * kPbRowBytes + col * 16u);
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(g_out + 32 * j + lane), "f"(t.x),
+                             "f"(t.y), "f"(t.z), "f"(t.w)
+                             : "memory");
+            }
+            col += 8u;
+            row += 2u;
+            if (col >= 12u) {
+                col -= 12u;
+                row += 1u;
+            }
+        }
+    }
+    if (mask == 0u) return;
+    red_f1(a.g_opac + idx, dopac);
+    put3(a.g_mean + 3 * (size_t)idx, dmean_x, dmean_y, dmean_z, true);
+    // ---- cov3D backward (backward.cu:278-341), once, on the views' summed dL/dcov3D --------------------
+    {
+        const float s[3] = {sx, sy, sz};
+        float Mm[3][3];
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int r = 0; r < 3; r++) Mm[c][r] = s[r] * R[c][r];
+        float dS[3][3];
+        dS[0][0] = dcov[0];
+        dS[0][1] = dS[1][0] = 0.5f * dcov[1];
+        dS[0][2] = dS[2][0] = 0.5f * dcov[2];
+        dS[1][1] = dcov[3];
+        dS[1][2] = dS[2][1] = 0.5f * dcov[4];
+        dS[2][2] = dcov[5];
+        float dM[3][3];
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int r = 0; r < 3; r++)
+                dM[c][r] = 2.f * (Mm[0][r] * dS[c][0] + Mm[1][r] * dS[c][1] + Mm[2][r] * dS[c][2]);
+        float dsc[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) dsc[k] = R[0][k] * dM[0][k] + R[1][k] * dM[1][k] + R[2][k] * dM[2][k];
+        put3(a.g_scale + 3 * (size_t)idx, dsc[0], dsc[1], dsc[2], true);
+        float Mt[3][3];
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+#pragma unroll
+            for (int r = 0; r < 3; r++) Mt[c][r] = dM[r][c] * s[c];
+        float4 dq;
+        dq.x = 2.f * qz * (Mt[0][1] - Mt[1][0]) + 2.f * qy * (Mt[2][0] - Mt[0][2]) + 2.f * qx * (Mt[1][2] - Mt[2][1]);
+        dq.y = 2.f * qy * (Mt[1][0] + Mt[0][1]) + 2.f * qz * (Mt[2][0] + Mt[0][2]) + 2.f * qr * (Mt[1][2] - Mt[2][1]) -
+               4.f * qx * (Mt[2][2] + Mt[1][1]);
+        dq.z = 2.f * qx * (Mt[1][0] + Mt[0][1]) + 2.f * qr * (Mt[2][0] - Mt[0][2]) + 2.f * qz * (Mt[1][2] + Mt[2][1]) -
+               4.f * qy * (Mt[2][2] + Mt[0][0]);
+        dq.w = 2.f * qr * (Mt[0][1] - Mt[1][0]) + 2.f * qx * (Mt[2][0] + Mt[0][2]) + 2.f * qy * (Mt[1][2] + Mt[2][1]) -
+               4.f * qz * (Mt[1][1] + Mt[0][0]);
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(reinterpret_cast<float4*>(a.g_rot) + idx),
+                     "f"(dq.x), "f"(dq.y), "f"(dq.z), "f"(dq.w)
+                     : "memory");
+    }
+}
 }  // namespace
 
 int launch_preprocess_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
@@ -642,6 +955,71 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
     preprocess_backward_kernel<<<cdiv(P, kPbThreads), kPbThreads, a.sh_vec4 ? kPbSmemBytes : 0, stream>>>(
         a, a, cdiv(P, kPbThreads));
     HB_LAUNCH_OK("preprocess_backward", stream, false);
+    return 0;
+}
+
+int launch_unpack_mean2d(int P, const int* radii, const float* grad_pack, float* dL_dmean2D, cudaStream_t stream) {
+    if (P <= 0) return 0;
+    unpack_mean2d_kernel<<<cdiv(P, 256), 256, 0, stream>>>(P, radii, grad_pack, dL_dmean2D);
+    HB_LAUNCH_OK("unpack_mean2d", stream, false);
+    return 0;
+}
+
+int launch_scene_backward_views(int P, int D, int M, int n_views, const SceneViewHost* views, const float* means3D,
+                                const float* shs, const float* scales, const float* rotations, float scale_modifier,
+                                float* g_mean, float* g_sh, float* g_scale, float* g_rot, float* g_opac,
+                                cudaStream_t stream) {
+    if (P <= 0 || n_views <= 0) return 0;
+    if (M != 16 || ((reinterpret_cast<uintptr_t>(shs) | reinterpret_cast<uintptr_t>(g_sh) |
+                     reinterpret_cast<uintptr_t>(g_rot)) & 15u)) {
+        set_error("scene_backward_views: needs M == 16 and 16-byte aligned shs / SH sink / rotation sink");
+        return -3;
+    }
+    {  // opt in to > 48 KB of dynamic shared memory, once per device
+        static bool configured[64] = {false};
+        int dev = 0;
+        HB_CUDA_OK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !configured[dev]) {
+            HB_CUDA_OK(cudaFuncSetAttribute(scene_backward_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            kSvSmemBytes));
+            if (dev >= 0 && dev < 64) configured[dev] = true;
+        }
+    }
+    for (int first = 0; first < n_views; first += kMaxViews) {
+        SceneViewsArgs a;
+        memset(&a, 0, sizeof(a));
+        a.P = P;
+        a.D = D;
+        a.M = M;
+        a.V = n_views - first < kMaxViews ? n_views - first : kMaxViews;
+        a.means3D = means3D;
+        a.shs = shs;
+        a.scales = scales;
+        a.rotations = rotations;
+        a.scale_modifier = scale_modifier;
+        a.g_mean = g_mean;
+        a.g_sh = g_sh;
+        a.g_scale = g_scale;
+        a.g_rot = g_rot;
+        a.g_opac = g_opac;
+        for (int v = 0; v < a.V; v++) {
+            const SceneViewHost& h = views[first + v];
+            SceneViewRec& r = a.v[v];
+            r.view = h.cam.view;
+            r.proj = h.cam.proj;
+            r.campos = h.cam.campos;
+            r.tan_fovx = h.cam.tan_fovx;
+            r.tan_fovy = h.cam.tan_fovy;
+            r.focal_x = h.cam.focal_x;
+            r.focal_y = h.cam.focal_y;
+            r.radii = h.radii;
+            r.grad_pack = h.grad_pack;
+            r.clamped = h.clamped;
+            r.opac_scratch = h.opac_scratch;
+        }
+        scene_backward_views_kernel<<<cdiv(P, kPbThreads), kPbThreads, kSvSmemBytes, stream>>>(a);
+        HB_LAUNCH_OK("scene_backward_views", stream, false);
+    }
     return 0;
 }
 

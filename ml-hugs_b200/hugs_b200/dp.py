@@ -124,7 +124,7 @@ class FlatGradBuffer:
 
 def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, world_size: int,
             group=None, streams: Sequence = (), read_loss: bool = True, after_view=None, exchange: bool = True,
-            pin_accumulators: bool = True):
+            pin_accumulators: bool = True, defer_scene: bool = False):
     """One data-parallel step: ``render_view(v)`` must return the scalar loss tensor of view ``v``
     (forward through LBS + rasterizer); this rank handles ``shard_views`` of ``views``, calls
     backward on each loss (gradients accumulate in ``buf``), then allreduces.  Returns the local
@@ -138,10 +138,17 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     (``read_loss=False``: not read at all -- the host does not wait for the step -- and the device-side
     list of losses is returned instead).  ``after_view(v)`` is called on the view's stream once its backward
     pass has been enqueued (e.g. to record the event that releases the view's input buffers).
+    ``defer_scene=True``: the scene segment's per-Gaussian backward of two-segment renders is run ONCE for
+    all of the rank's views, after the last of them (``hugs_b200.segments.defer_scene_backward``: the scene
+    Gaussians' parameters and SH rows are then read once per step instead of once per view, and their
+    gradients added to the sinks once).
     ``exchange=False`` leaves the allreduce to the caller (``buf.allreduce()``): the local part of the step can
     then be captured in a CUDA graph (``GraphedStep``) with the collective outside it."""
     buf.zero_()
     mine = shard_views(len(views), rank, world_size)
+    import contextlib
+    from . import segments
+    deferral = segments.defer_scene_backward() if defer_scene else contextlib.nullcontext()
 
     def one(view):
         # in a function of its own: the view's graph must be gone before the next view's forward pass runs
@@ -156,7 +163,8 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
         return out
 
     if not streams:
-        losses = [one(views[i]) for i in mine]
+        with deferral:
+            losses = [one(views[i]) for i in mine]
         if exchange:
             buf.allreduce(group)
         if not read_loss:
@@ -180,11 +188,12 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     for s in streams:
         s.wait_stream(main)
     losses = []
-    for k, i in enumerate(mine):
-        with torch.cuda.stream(streams[k % len(streams)]):
-            losses.append(one(views[i]))
-    for s in streams:
-        main.wait_stream(s)
+    with deferral:   # (its exit runs the deferred scene backward: on the main stream, after the views' streams)
+        for k, i in enumerate(mine):
+            with torch.cuda.stream(streams[k % len(streams)]):
+                losses.append(one(views[i]))
+        for s in streams:
+            main.wait_stream(s)
     del pinned
     if exchange:
         buf.allreduce(group)

@@ -142,8 +142,9 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
             raise RuntimeError("hugs_b200 has no CPU path: segment tensors must be CUDA tensors")
         ctx.set_materialize_grads(False)
         ctx.clamp = clamp_active()
-        from .segments import sinks_of
+        from .segments import batch_for, sinks_of
         ctx.sinks, ctx.sunk = sinks_of(a, b)
+        ctx.batch = batch_for(ctx.sunk, int(b[0].shape[0]))
         device = a[0].device
         a = [_f32c(x, device) for x in a]
         b = [_f32c(x, device) for x in b]
@@ -188,11 +189,14 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
                 P1, N.ptr(b[0]), N.ptr(b[1]), N.ptr(b[3]), N.ptr(b[4]),
                 float(s.scale_modifier), N.ptr(view), N.ptr(proj), N.ptr(campos), float(s.tanfovx), float(s.tanfovy),
                 radii.data_ptr(), N.ptr(geom), N.ptr(binning), int(binning.numel()), N.ptr(img), dL.data_ptr(),
-                *_grad_ptrs(g), flags_of(s.debug, ctx.clamp), _stream_ptr(device),
+                *_grad_ptrs(g), flags_of(s.debug, ctx.clamp) | (N.FLAG_DEFER_SEG1 if ctx.batch is not None else 0),
+                _stream_ptr(device),
                 n_layer, N.ptr(bg_layer), layer.data_ptr(), int(layer.numel()), N.ptr(dLl),
                 C.byref(ctx.sinks) if ctx.sinks is not None else None)
         N.check(rc, "rasterize_two_segments_with_layer backward")
-        from .segments import segment_grads
+        from .segments import defer_record, segment_grads
+        if ctx.batch is not None:
+            defer_record(ctx.batch, s, view, proj, campos, radii, geom, b, P0, P1, M, H, W, ctx.sinks)
         return (g["means2D"], None, None, None, *segment_grads(g, P0, ctx.sunk))
 
 

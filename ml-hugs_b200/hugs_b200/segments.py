@@ -8,6 +8,7 @@ render -- 236 B per Gaussian read and written again, plus the split of every gra
 concatenation, bit for bit; each input's gradient comes back as a view of the joint gradient array.
 SH colours with scales / rotations only (what that renderer passes).
 """
+import contextlib
 import ctypes as C
 
 import torch
@@ -33,6 +34,74 @@ def sinks_of(raw_a, raw_b):
     return (st if any_sink else None), flags
 
 
+class SceneBackwardBatch:
+    """The scene segment's per-Gaussian backward of a whole view-batched step, run ONCE
+    (hugs_b200_scene_backward_views).  While a batch is active (``defer_scene_backward``), the backward pass of
+    every two-segment render whose segment-1 inputs all have gradient sinks runs the blend backward and the
+    human segment's per-Gaussian backward only, and leaves its record here; ``finish()`` -- on a stream that is
+    ordered after every view's backward pass -- then reads each scene Gaussian's parameters and SH row once,
+    walks the views and adds the summed gradients to the sinks once (~120 B per Gaussian and view instead of
+    744).  A view's ``means2D.grad`` is complete when its own backward pass returns."""
+
+    def __init__(self):
+        self.views, self.common = [], None
+
+    def add(self, view, common):
+        if self.common is not None and self.common["key"] != common["key"]:
+            self.finish()   # another pair of models: what has been collected goes first
+        self.common = common
+        self.views.append(view)
+
+    def finish(self):
+        if not self.views:
+            return
+        c, views = self.common, self.views
+        self.views, self.common = [], None
+        arr = (N.SceneView * len(views))()
+        for rec, v in zip(arr, views):
+            rec.viewmatrix, rec.projmatrix, rec.cam_pos = v["view"].data_ptr(), v["proj"].data_ptr(), v["campos"].data_ptr()
+            rec.tan_fovx, rec.tan_fovy = v["tanfovx"], v["tanfovy"]
+            rec.radii, rec.geom_buffer = v["radii"].data_ptr(), v["geom"].data_ptr()
+        b = c["b"]
+        device = b[0].device
+        with torch.cuda.device(device):
+            rc = N.scene_backward_views(len(views), arr, c["P0"], c["P1"], c["D"], c["M"], c["W"], c["H"],
+                                        N.ptr(b[0]), N.ptr(b[1]), N.ptr(b[3]), c["scale_modifier"], N.ptr(b[4]),
+                                        C.byref(c["sinks"]), _stream_ptr(device))
+        N.check(rc, "scene_backward_views")
+
+
+_batch = None   # the active SceneBackwardBatch (set on the thread that runs the forward passes)
+
+
+def batch_for(sunk, P1):
+    """The active batch if this render's scene segment can be deferred (all five of its inputs sunk), else None.
+    Called in the forward pass, on the caller's thread: the backward pass runs on autograd's."""
+    return _batch if (_batch is not None and all(sunk[5:]) and P1 > 0) else None
+
+
+def defer_record(batch, s, view, proj, campos, radii, geom, b, P0, P1, M, H, W, sinks):
+    batch.add(
+        dict(view=view, proj=proj, campos=campos, tanfovx=float(s.tanfovx), tanfovy=float(s.tanfovy), radii=radii,
+             geom=geom),
+        dict(key=(tuple(x.data_ptr() for x in b), P0, P1, M, H, W, int(s.sh_degree)), b=b, P0=P0, P1=P1,
+             D=int(s.sh_degree), M=M, W=W, H=H, scale_modifier=float(s.scale_modifier), sinks=sinks))
+
+
+@contextlib.contextmanager
+def defer_scene_backward():
+    """``with defer_scene_backward() as batch:`` around the views of a step; ``batch.finish()`` once every
+    view's backward pass has been enqueued and the current stream is ordered after all of them (the context
+    exit calls it too)."""
+    global _batch
+    prev, _batch = _batch, SceneBackwardBatch()
+    try:
+        yield _batch
+    finally:
+        batch, _batch = _batch, prev
+        batch.finish()
+
+
 class _RasterizeTwoSegments(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means2D, raster_settings, *t):
@@ -41,6 +110,7 @@ class _RasterizeTwoSegments(torch.autograd.Function):
             raise RuntimeError("hugs_b200 has no CPU path: segment tensors must be CUDA tensors")
         ctx.sinks, ctx.sunk = sinks_of(a, b)
         ctx.clamp = clamp_active()
+        ctx.batch = batch_for(ctx.sunk, int(b[0].shape[0]))
         device = a[0].device
         a = [_f32c(x, device) for x in a]
         b = [_f32c(x, device) for x in b]
@@ -108,9 +178,13 @@ class _RasterizeTwoSegments(torch.autograd.Function):
                     dL.data_ptr(),
                     g["means2D"].data_ptr(), g["conic"].data_ptr(), g["opacity"].data_ptr(), g["colors"].data_ptr(),
                     g["means3D"].data_ptr(), g["cov3D"].data_ptr(), g["sh"].data_ptr(), g["scales"].data_ptr(),
-                    g["rotations"].data_ptr(), flags_of(s.debug, ctx.clamp), _stream_ptr(device),
+                    g["rotations"].data_ptr(),
+                    flags_of(s.debug, ctx.clamp) | (N.FLAG_DEFER_SEG1 if ctx.batch is not None else 0),
+                    _stream_ptr(device),
                     0, None, None, 0, None, C.byref(ctx.sinks) if ctx.sinks is not None else None)
             N.check(rc, "rasterize_two_segments backward")
+            if ctx.batch is not None:
+                defer_record(ctx.batch, s, view, proj, campos, radii, geom, b, P0, P1, M, H, W, ctx.sinks)
         return (g["means2D"], None, *segment_grads(g, P0, ctx.sunk))
 
 

@@ -93,3 +93,64 @@ def test_flat_grad_buffer_with_sinks_and_an_empty_scene():
     finally:
         for k in NAMES:
             hugs_b200.detach_grad_sink(h1[k])
+
+
+@pytest.mark.parametrize("n_views,two_streams,with_layer", [(3, False, False), (5, True, False), (3, True, True)])
+def test_deferred_scene_backward_over_all_views(n_views, two_streams, with_layer):
+    """hugs_b200.segments.defer_scene_backward / hugs_b200_scene_backward_views: the scene segment's per-Gaussian
+    backward run once for all views of a step leaves the same sums in the sinks as one run per view, and the
+    same per-view screen-space gradients (means2D.grad), scene rows included."""
+    import diff_gaussian_rasterization as dgr
+    import hugs_b200
+    from hugs_b200 import segments
+    n_h, n_s, W, H = 3000, 9000, 320, 200
+    views = [scenes.make_scene(n_s, n_h, W, H, 300.0, seed=63, device="cuda", view=v, n_views=n_views)
+             for v in range(n_views)]
+    seg = lambda d: (d["means3D"], d["shs"], d["opacity"], d["scales"], d["rotations"])  # noqa: E731
+
+    def run(deferred):
+        h, s = _segments(views[0], n_h)
+        for d in (h, s):
+            for k in NAMES:
+                hugs_b200.attach_grad_sink(d[k])
+        m2ds = []
+        try:
+            streams = [torch.cuda.Stream(), torch.cuda.Stream()] if two_streams else [torch.cuda.current_stream()]
+            main = torch.cuda.current_stream()
+            for st in streams:
+                st.wait_stream(main)
+            ctx = segments.defer_scene_backward() if deferred else contextlib.nullcontext()
+            with ctx:
+                for i, sc in enumerate(views):
+                    with torch.cuda.stream(streams[i % len(streams)]):
+                        m2d = torch.empty(n_h + n_s, 3, device="cuda", requires_grad=True)
+                        if with_layer:
+                            from hugs_b200 import layer
+                            hbg = torch.tensor([0.2, 0.9, 0.4], device="cuda")
+                            color, color_h, _ = layer.rasterize_two_segments_with_layer(
+                                seg(h), seg(s), m2d, scenes.settings_of(sc, dgr), hbg)
+                            ((color * sc["dL_dcolor"]).sum() + (color_h * sc["dL_dcolor"].flip(2)).sum()).backward()
+                        else:
+                            color, _ = segments.rasterize_two_segments(seg(h), seg(s), m2d, scenes.settings_of(sc, dgr))
+                            (color * sc["dL_dcolor"]).sum().backward()
+                        m2ds.append(m2d)
+                for st in streams:
+                    main.wait_stream(st)
+            torch.cuda.synchronize()
+            return ({("h", k): h[k].grad.clone() for k in NAMES} | {("s", k): s[k].grad.clone() for k in NAMES},
+                    [m.grad.clone() for m in m2ds])
+        finally:
+            for d in (h, s):
+                for k in NAMES:
+                    hugs_b200.detach_grad_sink(d[k])
+
+    import contextlib
+    g0, m0 = run(False)
+    g1, m1 = run(True)
+    for key in g0:
+        assert float(g0[key].abs().max()) > 0, key
+        err = refutil.rel_err(g1[key].cpu().numpy(), g0[key].cpu().numpy())
+        assert err < 1e-5, (key, err)
+    for a, b in zip(m0, m1):   # (the blend backward's reductions differ in order between the two runs)
+        assert refutil.rel_err(b.cpu().numpy(), a.cpu().numpy()) < 1e-5
+        assert torch.equal(a == 0, b == 0)
