@@ -505,7 +505,13 @@ class Replica:
             inp["loss_event"].record()
         return loss
 
-    def _dp_step(self, forward_of_view, after_view=None, exchange=True):
+    def _settings(self, inp):
+        return self.module.GaussianRasterizationSettings(
+            image_height=self.H, image_width=self.W, tanfovx=self.tanfovx, tanfovy=self.tanfovy, bg=inp["bg"],
+            scale_modifier=1.0, viewmatrix=inp["viewmatrix"], projmatrix=inp["projmatrix"], sh_degree=3,
+            campos=inp["campos"], prefiltered=False, debug=False)
+
+    def _dp_step(self, forward_of_view, after_view=None, exchange=True, prepass=False):
         """The product's data-parallel step (hugs_b200.dp.dp_step): clear the flat gradient buffer, this rank's
         views over the streams, backward of each, ONE allreduce of the flat buffer."""
         from hugs_b200 import dp
@@ -519,7 +525,16 @@ class Replica:
                    streams=self.streams if self.n_streams > 1 else (), read_loss=False,
                           after_view=after_view, exchange=exchange,
                           pin_accumulators=os.environ.get("HB_PIN_ACC", "1") == "1",   # (0: tools/graph_bisect.py)
-                          defer_scene=self.two_seg and os.environ.get("HB_DEFER", "1") == "1")
+                          defer_scene=self.two_seg and os.environ.get("HB_DEFER", "1") == "1",
+                          scene_prepass=self._scene_prepass if (prepass and self.two_seg and self.n_scene > 0
+                                                                and os.environ.get("HB_PREPASS", "1") == "1") else None)
+
+    def _scene_prepass(self):
+        """The scene segment preprocessed for all of the step's (device-resident) cameras in one launch."""
+        from hugs_b200 import segments
+        return segments.scene_prepass([self._settings(dv) for dv in self.devs],
+                                      (self.s_means, self.s_shs, self.s_opacity, self.s_scales, self.s_rots),
+                                      self.n_human)
 
     def _deform_all(self, As):
         """animation: the rank's pose frames of the step through ONE batched LBS call when the
@@ -541,7 +556,7 @@ class Replica:
 
     def _step_resident_eager(self, exchange=True):
         if self.buf is not None:
-            return self._dp_step(lambda v: self._forward(dict(self.devs[v])), exchange=exchange)
+            return self._dp_step(lambda v: self._forward(dict(self.devs[v])), exchange=exchange, prepass=True)
         self.zero_grad()
         if self.mode == "animation" and self.lbs_frames is not None:
             if not hasattr(self, "A_all"):

@@ -48,6 +48,7 @@ extern "C" {
 #define HUGS_B200_FLAG_DEBUG   1
 #define HUGS_B200_FLAG_CLAMP01 2
 #define HUGS_B200_FLAG_DEFER_SEG1 4   /* backward of a two-segment call: see hugs_b200_scene_backward_views */
+#define HUGS_B200_FLAG_SEG1_PREPROCESSED 8   /* forward of a two-segment call: see hugs_b200_preprocess_scene_views */
 
 typedef void* hugs_b200_stream_t;
 
@@ -527,13 +528,24 @@ typedef struct hugs_b200_scene_view {
     const float* projmatrix;
     const float* cam_pos;
     float tan_fovx, tan_fovy;
-    const int* radii;
-    char* geom_buffer;
+    int* radii;          /* [P0+P1] of the view */
+    char* geom_buffer;   /* the view's geometry workspace */
 } hugs_b200_scene_view;
 int hugs_b200_scene_backward_views(int n_views, const hugs_b200_scene_view* views, int P0, int P1, int D, int M,
                                    int width, int height, const float* means3D1, const float* shs1,
                                    const float* scales1, float scale_modifier, const float* rotations1,
                                    const hugs_b200_grad_sinks* sinks, hugs_b200_stream_t stream);
+/* The forward counterpart: the scene segment's preprocess (CR/forward.cu:155-256) for ALL views of a step in one
+ * launch -- parameters and SH row read once per Gaussian, the 3D covariance built once, the cameras walked; per
+ * (Gaussian, camera) the arithmetic of the per-view kernel, operation for operation.  For every view it clears
+ * the pair counts of the view's geometry workspace (geom_buffer: hugs_b200_geom_layout_of(P0 + P1).total bytes,
+ * owned by the caller), fills segment 1's rows of it and of radii [P0+P1], and adds segment 1's share of the
+ * counts.  The view's forward call is then made with HUGS_B200_FLAG_SEG1_PREPROCESSED and a geometry callback
+ * that returns that same buffer: it preprocesses segment 0 only and carries on from there. */
+int hugs_b200_preprocess_scene_views(int n_views, const hugs_b200_scene_view* views, int P0, int P1, int D, int M,
+                                     int width, int height, const float* means3D1, const float* shs1,
+                                     const float* opacities1, const float* scales1, float scale_modifier,
+                                     const float* rotations1, int prefiltered, hugs_b200_stream_t stream);
 
 /* ---- fused decoder MLPs on the tensor cores (tcgen05 / TMEM, 3xTF32) -----------------------------------
  * Replaces the torch.nn.Linear / GELU chains of hugs/models/modules/decoders.py:24-110 (AppearanceDecoder

@@ -540,6 +540,9 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                                 int* num_rendered) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const bool clamp01 = (debug & HUGS_B200_FLAG_CLAMP01) != 0;   // `debug` doubles as a flag word
+    // segment 1's rows of the geometry workspace (and its share of the pair counts) are already there:
+    // hugs_b200_preprocess_scene_views
+    const bool seg1_done = (debug & HUGS_B200_FLAG_SEG1_PREPROCESSED) != 0;
     debug &= HUGS_B200_FLAG_DEBUG;
     if (num_rendered) *num_rendered = 0;
     if (!geometry_buffer || !binning_buffer || !image_buffer || !num_rendered) {
@@ -615,7 +618,11 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
             return HUGS_B200_ENOMEM;
         }
         geom = carve_geom(geom_base, P);
-        HB_CUDA_OK(cudaMemsetAsync(geom.pair_counts, 0, 2 * sizeof(uint32_t), stream));
+        if (seg1_done && !tl_seg2) {
+            set_error("rasterize_forward: HUGS_B200_FLAG_SEG1_PREPROCESSED needs a two-segment call");
+            return HUGS_B200_EINVAL;
+        }
+        if (!seg1_done) HB_CUDA_OK(cudaMemsetAsync(geom.pair_counts, 0, 2 * sizeof(uint32_t), stream));
 
         if (const SecondSegment* s2 = tl_seg2) {
             // both segments in ONE launch (SegBatch): the human segment alone would be a 431-block grid
@@ -625,7 +632,7 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
                 if (s2->P0 > 0)
                     rc = launch_preprocess(s2->P0, D, M, means3D, scales, scale_modifier, rotations, opacities, shs,
                                            nullptr, nullptr, cam, radii, geom, prefiltered != 0, stream, &batch);
-                if (rc == 0 && P - s2->P0 > 0)
+                if (rc == 0 && P - s2->P0 > 0 && !seg1_done)
                     rc = launch_preprocess(P - s2->P0, D, M, s2->means3D, s2->scales, scale_modifier, s2->rotations,
                                            s2->opacities, s2->shs, nullptr, nullptr, cam, radii + s2->P0,
                                            geom_rows_from(geom, s2->P0), prefiltered != 0, stream, &batch);
@@ -1252,6 +1259,42 @@ int hugs_b200_rasterize_backward_seg2_ex(int D, int M, int R, const float* backg
         dL_dpix_layer);
     tl_sinks = nullptr;
     return rc;
+}
+
+int hugs_b200_preprocess_scene_views(int n_views, const hugs_b200_scene_view* views, int P0, int P1, int D, int M,
+                                     int width, int height, const float* means3D1, const float* shs1,
+                                     const float* opacities1, const float* scales1, float scale_modifier,
+                                     const float* rotations1, int prefiltered, hugs_b200_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (n_views < 0 || P0 < 0 || P1 < 0 || width <= 0 || height <= 0 || (n_views > 0 && !views)) {
+        set_error("preprocess_scene_views: bad arguments");
+        return HUGS_B200_EINVAL;
+    }
+    if (n_views == 0) return 0;
+    if (P1 > 0 && (!means3D1 || !shs1 || !opacities1 || !scales1 || !rotations1)) {
+        set_error("preprocess_scene_views: null pointer (segment 1 needs its five input arrays)");
+        return HUGS_B200_EINVAL;
+    }
+    const int P = P0 + P1;
+    std::vector<PreViewHost> host((size_t)n_views);
+    for (int v = 0; v < n_views; v++) {
+        const hugs_b200_scene_view& in = views[v];
+        if (!in.viewmatrix || !in.projmatrix || !in.cam_pos || !in.radii || !in.geom_buffer) {
+            set_error("preprocess_scene_views: view %d: null pointer", v);
+            return HUGS_B200_EINVAL;
+        }
+        const GeomView geom = carve_geom(in.geom_buffer, P);
+        // the counts start here; the view's forward call (HUGS_B200_FLAG_SEG1_PREPROCESSED) adds segment 0's share
+        HB_CUDA_OK(cudaMemsetAsync(geom.pair_counts, 0, 2 * sizeof(uint32_t), stream));
+        PreViewHost& h = host[(size_t)v];
+        h.cam = make_camera(in.viewmatrix, in.projmatrix, in.cam_pos, width, height, in.tan_fovx, in.tan_fovy);
+        h.radii = const_cast<int*>(in.radii) + P0;
+        h.g = geom_rows_from(geom, P0);
+    }
+    if (P1 == 0) return 0;
+    StageScope scope(ST_PREPROCESS, stream);
+    return launch_preprocess_views(P1, D, M, n_views, host.data(), means3D1, scales1, scale_modifier, rotations1,
+                                   opacities1, shs1, prefiltered != 0, stream);
 }
 
 int hugs_b200_scene_backward_views(int n_views, const hugs_b200_scene_view* views, int P0, int P1, int D, int M,

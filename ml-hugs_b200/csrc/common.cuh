@@ -221,6 +221,15 @@ int launch_preprocess_backward(int P, int D, int M, const float* means3D, const 
                                float* dL_dcolor, float* dL_dcov3D, float* dL_dsh, float* dL_dscale,
                                float* dL_drot, bool sh_accumulate, cudaStream_t stream,
                                const struct PreBwdExtra* extra = nullptr, SegBatch* batch = nullptr);
+// The scene segment's preprocess for all views of a step in one launch (preprocess.cu).
+struct PreViewHost {
+    Camera cam;
+    int* radii;     // scene rows of the view's radii
+    GeomView g;     // the view's geometry workspace, per-Gaussian arrays moved to the scene rows
+};
+int launch_preprocess_views(int P, int D, int M, int n_views, const PreViewHost* views, const float* means3D,
+                            const float* scales, float scale_modifier, const float* rotations, const float* opacities,
+                            const float* shs, bool prefiltered, cudaStream_t stream);
 // The scene segment's per-Gaussian backward for all views of a step in one launch (preprocess_backward.cu).
 struct SceneViewHost {
     Camera cam;

@@ -390,6 +390,327 @@ __global__ void __launch_bounds__(kPreThreads, 6)
     }
 }
 
+// =========================================================================================================
+// The scene segment's preprocess for ALL views of a view-batched step in one launch
+// (hugs_b200_preprocess_scene_views).  The per-view kernel above reads a Gaussian's parameters (44 B) and SH row
+// (192 B) for every view and writes 75 B; the scene Gaussians are the same in every view, so this kernel reads
+// them ONCE, builds the 3D covariance once, and walks the cameras: same arithmetic per (Gaussian, camera),
+// operation for operation, hence bit-identical outputs.  The SH row is fetched (cp.async into shared memory)
+// only if some view sees the Gaussian, and evaluated per view that does.
+constexpr int kMaxPreViews = 16;
+struct PreViewOut {
+    const float* view;
+    const float* proj;
+    const float* campos;
+    int W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    int grid_x, grid_y;
+    int* radii;
+    float* depths;
+    float2* means2D;
+    float4* conic_opacity;
+    float4* rgb;
+    uint8_t* clamped;
+    uint32_t* tiles_touched;
+    uint2* rects;
+    uint32_t* st_touched;
+    uint32_t* pair_counts;
+};
+struct PreViewsArgs {
+    int P, D, M, V;
+    const float* means3D;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* opacities;
+    const float* shs;
+    int prefiltered;
+    int rot_vec4;
+    PreViewOut v[kMaxPreViews];
+};
+
+__global__ void __launch_bounds__(kPreThreads, 5) preprocess_views_kernel(const PreViewsArgs a) {
+    extern __shared__ __align__(16) unsigned char s_rows[];  // [128][208 B] SH rows
+    __shared__ float s_cam[kMaxPreViews][36];
+    for (int i = (int)threadIdx.x; i < a.V * 35; i += kPreThreads) {
+        const int v = i / 35, j = i - 35 * v;
+        s_cam[v][j] = j < 16 ? __ldg(a.v[v].view + j) : (j < 32 ? __ldg(a.v[v].proj + j - 16) : __ldg(a.v[v].campos + j - 32));
+    }
+    __syncthreads();
+    const int idx = blockIdx.x * kPreThreads + threadIdx.x;
+    const bool valid = idx < a.P;
+    float px = 0.f, py = 0.f, pz = 0.f, opacity = 0.f;
+    float cov3[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (valid) {
+        px = __ldg(a.means3D + 3 * (size_t)idx + 0);
+        py = __ldg(a.means3D + 3 * (size_t)idx + 1);
+        pz = __ldg(a.means3D + 3 * (size_t)idx + 2);
+        const float sx = __ldg(a.scales + 3 * (size_t)idx + 0);
+        const float sy = __ldg(a.scales + 3 * (size_t)idx + 1);
+        const float sz = __ldg(a.scales + 3 * (size_t)idx + 2);
+        float4 q;
+        if (a.rot_vec4) {
+            q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+        } else {
+            q.x = __ldg(a.rotations + 4 * (size_t)idx + 0);
+            q.y = __ldg(a.rotations + 4 * (size_t)idx + 1);
+            q.z = __ldg(a.rotations + 4 * (size_t)idx + 2);
+            q.w = __ldg(a.rotations + 4 * (size_t)idx + 3);
+        }
+        opacity = __ldg(a.opacities + idx);
+        // 3D covariance (forward.cu:204-213): the same for every camera
+        cov3d_from_scale_rot(sx, sy, sz, a.scale_modifier, q.x, q.y, q.z, q.w, cov3);
+    }
+    unsigned mask = 0;   // bit v: visible in view v
+    for (int v = 0; v < a.V; v++) {
+        const PreViewOut& w = a.v[v];
+        const float* V = s_cam[v];
+        const float* Pm = s_cam[v] + 16;
+        bool vis = false;
+        float depth = 0.f, pix_x = 0.f, pix_y = 0.f, conic_x = 0.f, conic_y = 0.f, conic_z = 0.f;
+        int radius = 0;
+        unsigned tiles = 0, rx0 = 0, rx1 = 0, ry0 = 0, ry1 = 0;
+        if (valid) do {
+            // in_frustum (auxiliary.h:139-164): near-plane cull on view-space z only.
+            depth = RN_ADD(dot3_rn(V[2], px, V[6], py, V[10], pz), V[14]);
+            if (depth <= 0.2f) {
+                if (a.prefiltered) {
+                    printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+                    __trap();
+                }
+                break;
+            }
+
+            // Projection (forward.cu:197-200).
+            const float hx = RN_ADD(dot3_rn(Pm[0], px, Pm[4], py, Pm[8], pz), Pm[12]);
+            const float hy = RN_ADD(dot3_rn(Pm[1], px, Pm[5], py, Pm[9], pz), Pm[13]);
+            const float hw = RN_ADD(dot3_rn(Pm[3], px, Pm[7], py, Pm[11], pz), Pm[15]);
+            const float p_w = __frcp_rn(RN_ADD(hw, 0.0000001f));
+            const float proj_x = RN_MUL(hx, p_w);
+            const float proj_y = RN_MUL(hy, p_w);
+
+
+            // 2D covariance, EWA (forward.cu:74-113).
+            const float tz = depth;
+            float tx = RN_ADD(dot3_rn(V[0], px, V[4], py, V[8], pz), V[12]);
+            float ty = RN_ADD(dot3_rn(V[1], px, V[5], py, V[9], pz), V[13]);
+            const float limx = RN_MUL(w.tan_fovx, 1.3f);
+            const float limy = RN_MUL(w.tan_fovy, 1.3f);
+            const float txtz = RN_DIV(tx, tz);
+            const float tytz = RN_DIV(ty, tz);
+            tx = RN_MUL(fminf(limx, fmaxf(-limx, txtz)), tz);
+            ty = RN_MUL(fminf(limy, fmaxf(-limy, tytz)), tz);
+            const float tz2 = RN_MUL(tz, tz);
+            const float J00 = RN_DIV(w.focal_x, tz);
+            const float J02 = RN_DIV(-RN_MUL(w.focal_x, tx), tz2);
+            const float J11 = RN_DIV(w.focal_y, tz);
+            const float J12 = RN_DIV(-RN_MUL(w.focal_y, ty), tz2);
+            // T = W * J with W[c][r] = view[c + 4r]; only the two non-zero columns of J matter.
+            const float T00 = RN_FMA(V[2], J02, RN_MUL(V[0], J00));
+            const float T01 = RN_FMA(V[6], J02, RN_MUL(V[4], J00));
+            const float T02 = RN_FMA(V[10], J02, RN_MUL(V[8], J00));
+            const float T10 = RN_FMA(V[2], J12, RN_MUL(V[1], J11));
+            const float T11 = RN_FMA(V[6], J12, RN_MUL(V[5], J11));
+            const float T12 = RN_FMA(V[10], J12, RN_MUL(V[9], J11));
+            // X = T^T Vrk^T : X[c][r] = T[r][0]Vrk[0][c] + T[r][1]Vrk[1][c] + T[r][2]Vrk[2][c]
+            const float X00 = dot3_rn(T00, cov3[0], T01, cov3[1], T02, cov3[2]);
+            const float X10 = dot3_rn(T00, cov3[1], T01, cov3[3], T02, cov3[4]);
+            const float X20 = dot3_rn(T00, cov3[2], T01, cov3[4], T02, cov3[5]);
+            const float X01 = dot3_rn(T10, cov3[0], T11, cov3[1], T12, cov3[2]);
+            const float X11 = dot3_rn(T10, cov3[1], T11, cov3[3], T12, cov3[4]);
+            const float X21 = dot3_rn(T10, cov3[2], T11, cov3[4], T12, cov3[5]);
+            // cov = X T : cov[c][r] = X[0][r]T[c][0] + X[1][r]T[c][1] + X[2][r]T[c][2]; low-pass +0.3
+            const float cx = RN_ADD(dot3_rn(X00, T00, X10, T01, X20, T02), 0.3f);
+            const float cy = dot3_rn(X01, T00, X11, T01, X21, T02);
+            const float cz = RN_ADD(dot3_rn(X01, T10, X11, T11, X21, T12), 0.3f);
+
+            // Invert (forward.cu:219-223).
+            const float det = RN_FMA(cx, cz, -RN_MUL(cy, cy));
+            if (det == 0.0f) break;
+            const float det_inv = __frcp_rn(det);
+            conic_x = RN_MUL(cz, det_inv);
+            conic_y = RN_MUL(cy, -det_inv);
+            conic_z = RN_MUL(cx, det_inv);
+
+            // Screen-space extent (forward.cu:229-237).
+            const float mid = RN_MUL(RN_ADD(cx, cz), 0.5f);
+            const float sq = __fsqrt_rn(fmaxf(0.1f, RN_FMA(mid, mid, -det)));
+            const float lambda1 = RN_ADD(mid, sq);
+            const float lambda2 = RN_ADD(mid, -sq);
+            const float radius_f = ceilf(RN_MUL(__fsqrt_rn(fmaxf(lambda1, lambda2)), 3.f));
+            radius = (int)radius_f;
+            // ndc2Pix is evaluated in double in the reference (auxiliary.h:41-44).
+            pix_x = (float)__dmul_rn(__fma_rn(__dadd_rn((double)proj_x, 1.0), (double)w.W, -1.0), 0.5);
+            pix_y = (float)__dmul_rn(__fma_rn(__dadd_rn((double)proj_y, 1.0), (double)w.H, -1.0), 0.5);
+            // getRect (auxiliary.h:46-56): float maths on an int radius, truncation, clamp to the grid.
+            const float rf = (float)radius;
+            const unsigned gx = (unsigned)w.grid_x, gy = (unsigned)w.grid_y;
+            const unsigned min_x = min(gx, (unsigned)max(0, (int)RN_MUL(RN_ADD(pix_x, -rf), 0.0625f)));
+            const unsigned min_y = min(gy, (unsigned)max(0, (int)RN_MUL(RN_ADD(pix_y, -rf), 0.0625f)));
+            const unsigned max_x =
+                min(gx, (unsigned)max(0, (int)RN_MUL(RN_ADD(RN_ADD(RN_ADD(pix_x, rf), 16.f), -1.f), 0.0625f)));
+            const unsigned max_y =
+                min(gy, (unsigned)max(0, (int)RN_MUL(RN_ADD(RN_ADD(RN_ADD(pix_y, rf), 16.f), -1.f), 0.0625f)));
+            tiles = (max_x - min_x) * (max_y - min_y);
+            if (tiles == 0) break;
+            rx0 = min_x;
+            rx1 = max_x;
+            ry0 = min_y;
+            ry1 = max_y;
+            vis = true;
+        } while (0);
+        if (valid && !vis) {
+            w.radii[idx] = 0;
+            w.tiles_touched[idx] = 0;
+            w.depths[idx] = __uint_as_float(0xFFFFFFFFu);  // depth-sort key of a culled Gaussian: last
+        }
+        if (vis) {
+            mask |= 1u << v;
+            w.depths[idx] = depth;
+            w.radii[idx] = radius;
+            w.means2D[idx] = make_float2(pix_x, pix_y);
+            w.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opacity);
+            w.tiles_touched[idx] = tiles;
+        }
+        if (w.rects != nullptr) {
+            unsigned st = 0;
+            if (vis) st = (((rx1 + 7u) >> 3) - (rx0 >> 3)) * (((ry1 + 3u) >> 2) - (ry0 >> 2));
+            if (valid) {
+                w.rects[idx] = vis ? make_uint2(rx0 | (rx1 << 16), ry0 | (ry1 << 16)) : make_uint2(0u, 0u);
+                w.st_touched[idx] = st;
+            }
+            const unsigned sum_t = __reduce_add_sync(0xffffffffu, vis ? tiles : 0u);
+            const unsigned sum_s = __reduce_add_sync(0xffffffffu, st);
+            if ((threadIdx.x & 31u) == 0u && sum_t != 0u) {
+                atomicAdd(w.pair_counts + 0, sum_t);
+                atomicAdd(w.pair_counts + 1, sum_s);
+            }
+        }
+    }
+    // Colour (forward.cu:241-247), per view that sees the Gaussian
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const unsigned alive = __ballot_sync(0xffffffffu, mask != 0u);
+    if (alive == 0u) return;
+    const int nf = 3 * (a.D + 1) * (a.D + 1);
+    const int nv = (nf + 3) >> 2;
+    const uint32_t s_warp = (uint32_t)__cvta_generic_to_shared(s_rows) + warp * 32u * kShRowBytes;
+    {
+        const float4* g_warp = reinterpret_cast<const float4*>(a.shs) + 12 * ((size_t)blockIdx.x * kPreThreads + warp * 32u);
+        unsigned row = lane / 12u, col = lane % 12u;  // 16-byte word 32 j + lane = (row, col)
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            if (((alive >> row) & 1u) && (int)col < nv)
+                cp_async16(s_warp + row * kShRowBytes + col * 16u, g_warp + 32 * j + lane);
+            col += 8u;
+            row += 2u;
+            if (col >= 12u) {
+                col -= 12u;
+                row += 1u;
+            }
+        }
+        cp_async_wait_all();
+        __syncwarp();
+    }
+    if (mask == 0u) return;
+    float sh[48];
+    {
+        const uint32_t mine = s_warp + lane * kShRowBytes;
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i < nv) {
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(mine + 16u * i));
+            }
+            sh[4 * i + 0] = t.x;
+            sh[4 * i + 1] = t.y;
+            sh[4 * i + 2] = t.z;
+            sh[4 * i + 3] = t.w;
+        }
+    }
+    for (int v = 0; v < a.V; v++) {
+        if (!((mask >> v) & 1u)) continue;
+        const PreViewOut& w = a.v[v];
+        const float* V = s_cam[v];
+        float dx = px - V[32], dy = py - V[33], dz = pz - V[34];
+        const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+        dx = dx / len;
+        dy = dy / len;
+        dz = dz / len;
+        float c[3];
+        eval_sh(a.D, sh, dx, dy, dz, c);
+        uint8_t m = 0;
+        if (c[0] < 0.f) m |= 1;
+        if (c[1] < 0.f) m |= 2;
+        if (c[2] < 0.f) m |= 4;
+        w.clamped[idx] = m;
+        w.rgb[idx] = make_float4(fmaxf(c[0], 0.f), fmaxf(c[1], 0.f), fmaxf(c[2], 0.f), 0.f);
+    }
+}
+
+int launch_preprocess_views(int P, int D, int M, int n_views, const PreViewHost* views, const float* means3D,
+                            const float* scales, float scale_modifier, const float* rotations, const float* opacities,
+                            const float* shs, bool prefiltered, cudaStream_t stream) {
+    if (P <= 0 || n_views <= 0) return 0;
+    if (M != 16 || (reinterpret_cast<uintptr_t>(shs) & 15u)) {
+        set_error("preprocess_views: needs M == 16 and 16-byte aligned shs");
+        return -3;
+    }
+    {  // opt in to > 48 KB of dynamic shared memory, once per device
+        static bool configured[64] = {false};
+        int dev = 0;
+        HB_CUDA_OK(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !configured[dev]) {
+            HB_CUDA_OK(cudaFuncSetAttribute(preprocess_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            kPreSmemBytes));
+            if (dev >= 0 && dev < 64) configured[dev] = true;
+        }
+    }
+    for (int first = 0; first < n_views; first += kMaxPreViews) {
+        PreViewsArgs a;
+        memset(&a, 0, sizeof(a));
+        a.P = P;
+        a.D = D;
+        a.M = M;
+        a.V = n_views - first < kMaxPreViews ? n_views - first : kMaxPreViews;
+        a.means3D = means3D;
+        a.scales = scales;
+        a.scale_modifier = scale_modifier;
+        a.rotations = rotations;
+        a.opacities = opacities;
+        a.shs = shs;
+        a.prefiltered = prefiltered ? 1 : 0;
+        a.rot_vec4 = (reinterpret_cast<uintptr_t>(rotations) & 15u) == 0 ? 1 : 0;
+        for (int v = 0; v < a.V; v++) {
+            const PreViewHost& h = views[first + v];
+            PreViewOut& o = a.v[v];
+            o.view = h.cam.view;
+            o.proj = h.cam.proj;
+            o.campos = h.cam.campos;
+            o.W = h.cam.W;
+            o.H = h.cam.H;
+            o.tan_fovx = h.cam.tan_fovx;
+            o.tan_fovy = h.cam.tan_fovy;
+            o.focal_x = h.cam.focal_x;
+            o.focal_y = h.cam.focal_y;
+            o.grid_x = h.cam.grid_x;
+            o.grid_y = h.cam.grid_y;
+            o.radii = h.radii;
+            o.depths = h.g.depths;
+            o.means2D = h.g.means2D;
+            o.conic_opacity = h.g.conic_opacity;
+            o.rgb = h.g.rgb;
+            o.clamped = h.g.clamped;
+            o.tiles_touched = h.g.tiles_touched;
+            o.rects = h.g.rects;
+            o.st_touched = h.g.st_touched;
+            o.pair_counts = h.g.pair_counts;
+        }
+        preprocess_views_kernel<<<cdiv(P, kPreThreads), kPreThreads, kPreSmemBytes, stream>>>(a);
+        HB_LAUNCH_OK("preprocess_views", stream, false);
+    }
+    return 0;
+}
+
 int launch_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_modifier,
                       const float* rotations, const float* opacities, const float* shs,
                       const float* cov3D_precomp, const float* colors_precomp, const Camera& cam, int* radii,

@@ -156,6 +156,9 @@ class SceneView(C.Structure):
                 ("geom_buffer", C.c_void_p)]
 
 
+preprocess_scene_views = _sig("hugs_b200_preprocess_scene_views", i32,
+                              [i32, C.POINTER(SceneView), i32, i32, i32, i32, i32, i32, fp, fp, fp, fp, C.c_float, fp,
+                               i32, fp])
 scene_backward_views = _sig("hugs_b200_scene_backward_views", i32,
                             [i32, C.POINTER(SceneView), i32, i32, i32, i32, i32, i32, fp, fp, fp, C.c_float, fp,
                              C.POINTER(GradSinks), fp])
@@ -219,7 +222,7 @@ materialize_sorted_keys = _sig("hugs_b200_materialize_sorted_keys", i32,
                                [i32, i32, i32, i32, fp, fp, C.c_size_t, fp])
 binning_capacity_of = _sig("hugs_b200_binning_capacity_of", C.c_size_t, [C.c_size_t, i32, i32])
 BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE, BINNING_TILESORT = 0, 1, 2, 3
-FLAG_DEBUG, FLAG_CLAMP01, FLAG_DEFER_SEG1 = 1, 2, 4   # the flag word passed in the entry points' `debug` argument
+FLAG_DEBUG, FLAG_CLAMP01, FLAG_DEFER_SEG1, FLAG_SEG1_PREPROCESSED = 1, 2, 4, 8   # the flag word passed in the entry points' `debug` argument
 set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
 set_blend_priority = _sig("hugs_b200_set_blend_priority", i32, [i32, i32])
 
@@ -261,7 +264,7 @@ EXPORTED_SYMBOLS = [
     "hugs_b200_sort_bits", "hugs_b200_sort_temp_bytes", "hugs_b200_sort_pairs", "hugs_b200_sort_pairs_range",
     "hugs_b200_scan_temp_bytes", "hugs_b200_inclusive_scan",
     "hugs_b200_inclusive_scan_static", "hugs_b200_inclusive_scan_static_max_items",
-    "hugs_b200_scene_backward_views",
+    "hugs_b200_scene_backward_views", "hugs_b200_preprocess_scene_views",
     "hugs_b200_lbs_forward", "hugs_b200_lbs_backward",
     "hugs_b200_l1_ssim_forward", "hugs_b200_l1_ssim_backward",
     "hugs_b200_knn_temp_bytes", "hugs_b200_knn_mean_dist2",

@@ -124,7 +124,7 @@ class FlatGradBuffer:
 
 def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, world_size: int,
             group=None, streams: Sequence = (), read_loss: bool = True, after_view=None, exchange: bool = True,
-            pin_accumulators: bool = True, defer_scene: bool = False):
+            pin_accumulators: bool = True, defer_scene: bool = False, scene_prepass=None):
     """One data-parallel step: ``render_view(v)`` must return the scalar loss tensor of view ``v``
     (forward through LBS + rasterizer); this rank handles ``shard_views`` of ``views``, calls
     backward on each loss (gradients accumulate in ``buf``), then allreduces.  Returns the local
@@ -142,6 +142,9 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     all of the rank's views, after the last of them (``hugs_b200.segments.defer_scene_backward``: the scene
     Gaussians' parameters and SH rows are then read once per step instead of once per view, and their
     gradients added to the sinks once).
+    ``scene_prepass``: a callable returning ``hugs_b200.segments.scene_prepass(settings of every view, scene
+    segment, n_human)``; it is entered on the main stream before the views start, so that the scene segment is
+    preprocessed for all of the rank's cameras in one launch.
     ``exchange=False`` leaves the allreduce to the caller (``buf.allreduce()``): the local part of the step can
     then be captured in a CUDA graph (``GraphedStep``) with the collective outside it."""
     buf.zero_()
@@ -163,7 +166,10 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
         return out
 
     if not streams:
-        with deferral:
+        with contextlib.ExitStack() as stack:
+            if scene_prepass is not None:
+                stack.enter_context(scene_prepass())
+            stack.enter_context(deferral)
             losses = [one(views[i]) for i in mine]
         if exchange:
             buf.allreduce(group)
@@ -171,6 +177,9 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
             return losses
         return float(sum(float(x) for x in losses))
     main = torch.cuda.current_stream()
+    stack = contextlib.ExitStack()
+    if scene_prepass is not None:
+        stack.enter_context(scene_prepass())   # on the main stream, before the views' streams fork from it
     # Parameters WITHOUT a gradient sink accumulate through autograd's AccumulateGrad, which runs on the stream
     # that was current when the node was created -- a view's stream, if the node is created inside the view --
     # and nothing orders the in-place additions of two views on two streams with each other, nor the first
@@ -188,7 +197,8 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     for s in streams:
         s.wait_stream(main)
     losses = []
-    with deferral:   # (its exit runs the deferred scene backward: on the main stream, after the views' streams)
+    with stack:
+        stack.enter_context(deferral)   # (its exit runs the deferred scene backward: on the main stream, after the joins)
         for k, i in enumerate(mine):
             with torch.cuda.stream(streams[k % len(streams)]):
                 losses.append(one(views[i]))

@@ -74,13 +74,18 @@ class _Workspace:
     """Resize callback target: allocates a uint8 CUDA tensor of the requested size and hands its
     pointer to the native side (the reference's resizeFunctional, rasterize_points.cu:27-33)."""
 
-    def __init__(self, device):
+    def __init__(self, device, preset=None):
         self.device = device
         self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
         self.error = None
 
         def _resize(_user, nbytes):
             try:
+                if preset is not None:   # a buffer that is already (partly) filled: segments.scene_prepass
+                    if int(preset.numel()) != int(nbytes):
+                        raise RuntimeError("preset workspace of %d bytes, %d wanted" % (preset.numel(), nbytes))
+                    self.tensor = preset
+                    return self.tensor.data_ptr()
                 self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
                 return self.tensor.data_ptr()
             except Exception as ex:  # surfaced by the caller as RuntimeError

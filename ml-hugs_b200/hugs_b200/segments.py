@@ -102,6 +102,68 @@ def defer_scene_backward():
         batch.finish()
 
 
+class ScenePrepass:
+    """The scene segment's preprocess of a whole view-batched step, run ONCE (hugs_b200_preprocess_scene_views):
+    every scene Gaussian's parameters and SH row are read once and the cameras walked, instead of one full
+    pass per view.  ``scene_prepass(settings_list, segment1, P0)`` fills, for every view, the scene rows of a
+    geometry workspace and of ``radii``; the two-segment renders made inside the context with one of those
+    cameras (same viewmatrix / projmatrix / campos tensors, same scene tensors) pick their workspace up here,
+    preprocess the human segment only and carry on.  Bit-identical lists and ranges; the image to 1e-6 (the SH
+    evaluation is the same source compiled into another kernel)."""
+
+    def __init__(self, settings_list, segment1, P0):
+        b = [segment1[k] for k in _NAMES] if isinstance(segment1, dict) else list(segment1)
+        device = b[0].device
+        b = [_f32c(x, device) for x in b]
+        s0 = settings_list[0]
+        P1, M = int(b[0].shape[0]), int(b[1].shape[1])
+        H, W = int(s0.image_height), int(s0.image_width)
+        lay = N.GeomLayout()
+        N.geom_layout_of(P0 + P1, C.byref(lay))
+        self.entries, self.scene_ptrs = {}, tuple(x.data_ptr() for x in b)
+        arr = (N.SceneView * len(settings_list))()
+        keep = []
+        for rec, s in zip(arr, settings_list):
+            if (int(s.image_height), int(s.image_width), int(s.sh_degree), float(s.scale_modifier), bool(s.prefiltered)) \
+                    != (H, W, int(s0.sh_degree), float(s0.scale_modifier), bool(s0.prefiltered)):
+                raise ValueError("scene_prepass: the views must share image size, SH degree, scale modifier")
+            view, proj, campos = (_f32c(x, device) for x in (s.viewmatrix, s.projmatrix, s.campos))
+            geom = torch.empty(int(lay.total), dtype=torch.uint8, device=device)
+            radii = torch.empty(P0 + P1, dtype=torch.int32, device=device)
+            rec.viewmatrix, rec.projmatrix, rec.cam_pos = view.data_ptr(), proj.data_ptr(), campos.data_ptr()
+            rec.tan_fovx, rec.tan_fovy = float(s.tanfovx), float(s.tanfovy)
+            rec.radii, rec.geom_buffer = radii.data_ptr(), geom.data_ptr()
+            keep.append((view, proj, campos))
+            self.entries[(view.data_ptr(), proj.data_ptr(), campos.data_ptr(), P0, P1, H, W)] = (geom, radii)
+        with torch.cuda.device(device):
+            rc = N.preprocess_scene_views(len(settings_list), arr, P0, P1, int(s0.sh_degree), M, W, H,
+                                          N.ptr(b[0]), N.ptr(b[1]), N.ptr(b[2]), N.ptr(b[3]),
+                                          float(s0.scale_modifier), N.ptr(b[4]), int(bool(s0.prefiltered)),
+                                          _stream_ptr(device))
+        N.check(rc, "preprocess_scene_views")
+
+    def take(self, view, proj, campos, P0, P1, H, W, b):
+        """(geometry workspace, radii) prepared for this camera and these scene tensors, or None (used once)."""
+        if tuple(x.data_ptr() for x in b) != self.scene_ptrs:
+            return None
+        return self.entries.pop((view.data_ptr(), proj.data_ptr(), campos.data_ptr(), P0, P1, H, W), None)
+
+
+_prepass = None   # the active ScenePrepass
+
+
+@contextlib.contextmanager
+def scene_prepass(settings_list, segment1, P0):
+    """``with scene_prepass([settings of every view of the step], scene_segment, n_human):`` around the step's
+    two-segment renders; must be entered on a stream the views' streams are ordered after."""
+    global _prepass
+    prev, _prepass = _prepass, ScenePrepass(settings_list, segment1, P0)
+    try:
+        yield _prepass
+    finally:
+        _prepass = prev
+
+
 class _RasterizeTwoSegments(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means2D, raster_settings, *t):
@@ -124,8 +186,10 @@ class _RasterizeTwoSegments(torch.autograd.Function):
         H, W, M = int(s.image_height), int(s.image_width), int(a[1].shape[1])
         bg, view, proj, campos = (_f32c(x, device) for x in (s.bg, s.viewmatrix, s.projmatrix, s.campos))
         P = P0 + P1
-        radii = torch.empty(P, dtype=torch.int32, device=device)
-        geom, binning, img = _Workspace(device), _Workspace(device), _Workspace(device)
+        ready = _prepass.take(view, proj, campos, P0, P1, H, W, b) if (_prepass is not None and P1 > 0) else None
+        radii = ready[1] if ready is not None else torch.empty(P, dtype=torch.int32, device=device)
+        geom = _Workspace(device, preset=ready[0] if ready is not None else None)
+        binning, img = _Workspace(device), _Workspace(device)
         if P == 0:
             for ws in (geom, binning, img):
                 ws.release()
@@ -140,8 +204,9 @@ class _RasterizeTwoSegments(torch.autograd.Function):
                     P0, *[N.ptr(x) for x in a], P1, *[N.ptr(x) for x in b],
                     float(s.scale_modifier), N.ptr(view), N.ptr(proj), N.ptr(campos),
                     float(s.tanfovx), float(s.tanfovy), int(bool(s.prefiltered)),
-                    color.data_ptr(), radii.data_ptr(), flags_of(s.debug, ctx.clamp), _stream_ptr(device),
-                    C.byref(num_rendered))
+                    color.data_ptr(), radii.data_ptr(),
+                    flags_of(s.debug, ctx.clamp) | (N.FLAG_SEG1_PREPROCESSED if ready is not None else 0),
+                    _stream_ptr(device), C.byref(num_rendered))
             for ws in (geom, binning, img):
                 ws.release()
                 if ws.error is not None:

@@ -154,3 +154,41 @@ def test_deferred_scene_backward_over_all_views(n_views, two_streams, with_layer
     for a, b in zip(m0, m1):   # (the blend backward's reductions differ in order between the two runs)
         assert refutil.rel_err(b.cpu().numpy(), a.cpu().numpy()) < 1e-5
         assert torch.equal(a == 0, b == 0)
+
+
+def test_scene_prepass_matches_the_per_view_preprocess():
+    """hugs_b200.segments.scene_prepass / hugs_b200_preprocess_scene_views: the scene segment preprocessed for
+    all cameras of a step in one launch gives every view the same radii (bit for bit), the same image (to 1e-6:
+    the SH evaluation is compiled into another kernel) and the same gradients as its own preprocess."""
+    import diff_gaussian_rasterization as dgr
+    from hugs_b200 import segments
+    n_h, n_s, W, H, n_views = 3000, 9000, 320, 200, 5
+    views = [scenes.make_scene(n_s, n_h, W, H, 300.0, seed=64, device="cuda", view=v, n_views=n_views)
+             for v in range(n_views)]
+    seg = lambda d: (d["means3D"], d["shs"], d["opacity"], d["scales"], d["rotations"])  # noqa: E731
+    settings = [scenes.settings_of(sc, dgr) for sc in views]
+
+    def run(prepass):
+        h, s = _segments(views[0], n_h)
+        out = []
+        ctx = segments.scene_prepass(settings, seg(s), n_h) if prepass else contextlib.nullcontext()
+        with ctx as pp:
+            for sc, st in zip(views, settings):
+                m2d = torch.empty(n_h + n_s, 3, device="cuda", requires_grad=True)
+                color, radii = segments.rasterize_two_segments(seg(h), seg(s), m2d, st)
+                (color * sc["dL_dcolor"]).sum().backward()
+                out.append((color.detach().clone(), radii.clone(), m2d.grad.clone()))
+            if prepass:
+                assert not pp.entries   # every view picked its workspace up
+        torch.cuda.synchronize()
+        return out, {("h", k): h[k].grad.clone() for k in NAMES} | {("s", k): s[k].grad.clone() for k in NAMES}
+
+    import contextlib
+    o0, g0 = run(False)
+    o1, g1 = run(True)
+    for (c0, r0, m0), (c1, r1, m1) in zip(o0, o1):
+        assert torch.equal(r0, r1)
+        assert float((c0 - c1).abs().max()) < 1e-6
+        assert refutil.rel_err(m1.cpu().numpy(), m0.cpu().numpy()) < 1e-5
+    for key in g0:
+        assert refutil.rel_err(g1[key].cpu().numpy(), g0[key].cpu().numpy()) < 1e-5, key
