@@ -33,8 +33,8 @@ def _layer_forward(P, n_layer, bg_layer, W, H, colors, geom, binning, img, flags
     return out, layer
 
 
-def _run_forward(call, device):
-    geom, binning, img = _Workspace(device), _Workspace(device), _Workspace(device)
+def _run_forward(call, device, geom_preset=None):
+    geom, binning, img = _Workspace(device, preset=geom_preset), _Workspace(device), _Workspace(device)
     num_rendered = C.c_int(0)
     with torch.cuda.device(device):
         rc = call(geom, binning, img, num_rendered)
@@ -159,13 +159,18 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
         H, W, M = int(s.image_height), int(s.image_width), int(a[1].shape[1])
         bg, view, proj, campos, bg_layer = (_f32c(x, device) for x in (s.bg, s.viewmatrix, s.projmatrix, s.campos,
                                                                        bg_layer))
-        radii = torch.empty(P, dtype=torch.int32, device=device)
+        from . import segments as _seg
+        ready = (_seg._prepass.take(view, proj, campos, P0, P1, H, W, b)
+                 if (_seg._prepass is not None and P1 > 0) else None)   # segments.scene_prepass
+        radii = ready[1] if ready is not None else torch.empty(P, dtype=torch.int32, device=device)
         color = torch.empty(3, H, W, dtype=torch.float32, device=device)
+        fwd_flags = flags_of(s.debug, ctx.clamp) | (N.FLAG_SEG1_PREPROCESSED if ready is not None else 0)
         R, geom, binning, img = _run_forward(lambda g, bn, i, nr: N.rasterize_forward_seg2(
             g.callback, None, bn.callback, None, i.callback, None, int(s.sh_degree), M, N.ptr(bg), W, H,
             P0, *[N.ptr(x) for x in a], P1, *[N.ptr(x) for x in b], float(s.scale_modifier), N.ptr(view),
             N.ptr(proj), N.ptr(campos), float(s.tanfovx), float(s.tanfovy), int(bool(s.prefiltered)),
-            color.data_ptr(), radii.data_ptr(), flags_of(s.debug, ctx.clamp), _stream_ptr(device), C.byref(nr)), device)
+            color.data_ptr(), radii.data_ptr(), fwd_flags, _stream_ptr(device), C.byref(nr)), device,
+            geom_preset=ready[0] if ready is not None else None)
         layer_color, layer = _layer_forward(P, n_layer, bg_layer, W, H, None, geom, binning, img,
                                             flags_of(s.debug, ctx.clamp), device)
         ctx.raster_settings, ctx.num_rendered, ctx.sizes = s, R, (P0, P1, M, H, W, n_layer)

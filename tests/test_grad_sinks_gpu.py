@@ -156,7 +156,8 @@ def test_deferred_scene_backward_over_all_views(n_views, two_streams, with_layer
         assert torch.equal(a == 0, b == 0)
 
 
-def test_scene_prepass_matches_the_per_view_preprocess():
+@pytest.mark.parametrize("with_layer", [False, True])
+def test_scene_prepass_matches_the_per_view_preprocess(with_layer):
     """hugs_b200.segments.scene_prepass / hugs_b200_preprocess_scene_views: the scene segment preprocessed for
     all cameras of a step in one launch gives every view the same radii (bit for bit), the same image (to 1e-6:
     the SH evaluation is compiled into another kernel) and the same gradients as its own preprocess."""
@@ -175,8 +176,15 @@ def test_scene_prepass_matches_the_per_view_preprocess():
         with ctx as pp:
             for sc, st in zip(views, settings):
                 m2d = torch.empty(n_h + n_s, 3, device="cuda", requires_grad=True)
-                color, radii = segments.rasterize_two_segments(seg(h), seg(s), m2d, st)
-                (color * sc["dL_dcolor"]).sum().backward()
+                if with_layer:
+                    from hugs_b200 import layer
+                    hbg = torch.tensor([0.2, 0.9, 0.4], device="cuda")
+                    color, color_h, radii = layer.rasterize_two_segments_with_layer(seg(h), seg(s), m2d, st, hbg)
+                    ((color * sc["dL_dcolor"]).sum() + (color_h * sc["dL_dcolor"].flip(2)).sum()).backward()
+                    color = torch.cat([color, color_h])
+                else:
+                    color, radii = segments.rasterize_two_segments(seg(h), seg(s), m2d, st)
+                    (color * sc["dL_dcolor"]).sum().backward()
                 out.append((color.detach().clone(), radii.clone(), m2d.grad.clone()))
             if prepass:
                 assert not pp.entries   # every view picked its workspace up
