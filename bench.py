@@ -820,10 +820,26 @@ def reference_impl():
 # ------------------------------------------------------------------------------------------------
 # roofline accounting (algorithmic bytes: SURVEY.md 8(d) / DESIGN.md "Algorithmic bytes")
 # ------------------------------------------------------------------------------------------------
-def stage_bytes(P, visible, R, W, H, n_human, sort_bits, views=1, sh_sink=False):
+def stage_bytes(P, visible, R, W, H, n_human, sort_bits, views=1, sh_sink=False, batched_scene=False):
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     culled = P - visible
     passes = (sort_bits + 7) // 8
+    out = _stage_bytes(P, visible, culled, R, W, H, tiles, passes, n_human, views, sh_sink)
+    if batched_scene and P > n_human:
+        # The scene segment's per-Gaussian passes run ONCE per step for all `views` views (csrc/preprocess.cu:
+        # preprocess_views_kernel, csrc/preprocess_backward.cu: scene_backward_views_kernel): per frame, the
+        # human rows as before plus the scene's once-per-step bytes divided by the views and its per-view bytes.
+        Ps = P - n_human
+        vis_s = visible * Ps // P
+        vis_h, cul_s = visible - vis_s, Ps - vis_s
+        cul_h = n_human - vis_h
+        out["preprocess"] = (311 * vis_h + 20 * cul_h) + 236 * Ps // views + 75 * vis_s + 20 * cul_s
+        out["preprocess_backward"] = ((751 * vis_h + 68 * cul_h) + (236 + 2 * 236) * Ps // views + 41 * vis_s + 4 * Ps
+                                      + 24 * Ps)   # (the last term: the per-view unpack of the screen-space gradient)
+    return out
+
+
+def _stage_bytes(P, visible, culled, R, W, H, tiles, passes, n_human, views, sh_sink):
     return {
         "lbs_forward": 172 * n_human,
         "preprocess": 311 * visible + 20 * culled,
@@ -1112,7 +1128,9 @@ def main():
 
     peak, peak_kind = peaks()
     sort_bits = int(_native.sort_bits(W, H))
-    nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits, views=V, sh_sink=(rep.sh_sink is not None or rep.buf is not None))
+    nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits, views=V, sh_sink=(rep.sh_sink is not None or rep.buf is not None),
+                         batched_scene=rep.two_seg and os.environ.get("HB_DEFER", "1") == "1"
+                         and os.environ.get("HB_PREPASS", "1") == "1")
     stages = {}
     for name, (tot, calls) in stage_ms.items():
         if calls == 0:
@@ -1166,6 +1184,7 @@ def main():
         "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": dict(config, P=rep.P, R=R, visible=visible, sort_bits=sort_bits),
         "impl": {"name": "ours", "cuda_streams_per_rank": rep.n_streams,
+                 "batched_scene_passes": bool(rep.two_seg and os.environ.get("HB_DEFER", "1") == "1"),
                  "cuda_graph": ("value: the rank's local step is one CUDA-graph replay (%s), allreduce outside it; "
                                 "e2e: inputs prefetched one step ahead on a copy stream into staging blocks, "
                                 "device-to-device copy, the same graph replay, losses read two steps later"
