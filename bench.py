@@ -820,11 +820,17 @@ def reference_impl():
 # ------------------------------------------------------------------------------------------------
 # roofline accounting (algorithmic bytes: SURVEY.md 8(d) / DESIGN.md "Algorithmic bytes")
 # ------------------------------------------------------------------------------------------------
-def stage_bytes(P, visible, R, W, H, n_human, sort_bits, views=1, sh_sink=False, batched_scene=False):
+def stage_bytes(P, visible, R, W, H, n_human, sort_bits, views=1, sh_sink=False, batched_scene=False, R1=None):
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     culled = P - visible
     passes = (sort_bits + 7) // 8
     out = _stage_bytes(P, visible, culled, R, W, H, tiles, passes, n_human, views, sh_sink)
+    if R1 is not None:
+        # The two-level multisplit (csrc/binning2.cu) never sorts the R pairs: `sort_pairs` is the argsort of the P
+        # depth words (histogram + four 8-bit passes over key + index) plus ONE 8-bit pass over the R1 level-1
+        # (Gaussian, super-tile) entries; `duplicate_with_keys` emits those entries.
+        out["sort_pairs"] = 8 * P + 4 * 16 * P + 24 * R1
+        out["duplicate_with_keys"] = 24 * P + 8 * R1
     if batched_scene and P > n_human:
         # The scene segment's per-Gaussian passes run ONCE per step for all `views` views (csrc/preprocess.cu:
         # preprocess_views_kernel, csrc/preprocess_backward.cu: scene_backward_views_kernel): per frame, the
@@ -1046,6 +1052,7 @@ def main():
     step_resident()   # one eager step: the pair counts below come from it (a captured step reports capacities)
     torch.cuda.synchronize(device)
     # pair / visible counts: mean over this rank's views (they size the per-stage algorithmic bytes)
+    R1 = _native.last_pair_counts()[1] or None   # level-1 entries of the last view's forward call (default binning mode)
     visible = int(round(sum(int((r > 0).sum()) for r in rep.last_radii_v) / V))
     if training:
         R = int(round(sum(int(nd if isinstance(nd, int) else nd.num_rendered) for nd in rep.last_nodes) / V))
@@ -1130,7 +1137,7 @@ def main():
     sort_bits = int(_native.sort_bits(W, H))
     nbytes = stage_bytes(rep.P, visible, R, W, H, n_human, sort_bits, views=V, sh_sink=(rep.sh_sink is not None or rep.buf is not None),
                          batched_scene=rep.two_seg and os.environ.get("HB_DEFER", "1") == "1"
-                         and os.environ.get("HB_PREPASS", "1") == "1")
+                         and os.environ.get("HB_PREPASS", "1") == "1", R1=R1)
     stages = {}
     for name, (tot, calls) in stage_ms.items():
         if calls == 0:
@@ -1177,6 +1184,7 @@ def main():
                              "with events on; the timed region above alternates views over %d streams)"
                              % (args.steps * V, ms_staged / (args.steps * V), rep.n_streams)}
     frame_bytes = sum(nbytes[k] for k in stages)
+    survey_bytes = (902 * rep.P + 288 * R + 40 * W * H) if training else frame_bytes
     total_frames = frames_per_step * args.steps
     line = {
         "metric": metric_of(args.workload), "value": round(total_frames / (ms * 1e-3), 3), "unit": UNIT,
@@ -1199,9 +1207,14 @@ def main():
         "clocks": clocks,
         "roofline": roofline,
         "stages": stages,
-        "frame": {"algorithmic_bytes": int(frame_bytes),
+        # `algorithmic_bytes`: SURVEY.md 8(d)'s per-frame model of the REFERENCE's structure (902 P + 288 R + 40 W H),
+        # the yardstick every round is measured on; `own_structure_bytes`: the sum of `stages[*].bytes`, what this
+        # implementation's structure needs (no sort over the pairs, scene passes once per step)
+        "frame": {"algorithmic_bytes": int(survey_bytes),
                   "ms": round(ms * n_gpus / total_frames, 4),
-                  "hbm_frac": round(frame_bytes / (ms * n_gpus / total_frames * 1e-3) / 1e9 / peak, 4)},
+                  "hbm_frac": round(survey_bytes / (ms * n_gpus / total_frames * 1e-3) / 1e9 / peak, 4),
+                  "own_structure_bytes": int(frame_bytes),
+                  "own_structure_hbm_frac": round(frame_bytes / (ms * n_gpus / total_frames * 1e-3) / 1e9 / peak, 4)},
     }
     if n_gpus == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_of(args.workload, args.cpu_baseline_seconds)

@@ -291,6 +291,11 @@ int hugs_b200_set_binning_mode(int mode);
  * enable flag.  No counterpart in the reference (it runs one view on one stream). */
 int hugs_b200_set_blend_priority(int enable, int priority);
 
+/* The pair counts the last uncaptured hugs_b200_rasterize_forward* call of this host thread read back, once the
+ * call has returned: (Gaussian, tile) pairs (= *num_rendered) and the (Gaussian, super-tile) entries of the
+ * two-level binning's first level.  Measurement only (bench.py sizes its per-stage byte counts with them). */
+int hugs_b200_last_pair_counts(int* pairs, int* level1_entries);
+
 /* ---------------------------------------------------------------------------------------------
  * Stand-alone stages, exported so each can be parity-tested and timed on its own.
  * ------------------------------------------------------------------------------------------- */

@@ -811,6 +811,16 @@ int hugs_b200_rasterize_forward(hugs_b200_resize_fn geometry_buffer, void* geome
     return 0;
 }
 
+int hugs_b200_last_pair_counts(int* pairs, int* level1_entries) {
+    // what the last uncaptured forward call of this host thread read back: (Gaussian, tile) pairs and
+    // (Gaussian, super-tile) entries of the two-level binning
+    int* pinned = pinned_counter();
+    if (!pinned) return HUGS_B200_ENOMEM;
+    if (pairs) *pairs = pinned[0];
+    if (level1_entries) *level1_entries = pinned[1];
+    return 0;
+}
+
 int hugs_b200_set_blend_priority(int enable, int priority) {
     g_blend_prio.store(priority);
     return g_blend_prio_set.exchange(enable ? 1 : 0);

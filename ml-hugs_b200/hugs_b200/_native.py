@@ -225,6 +225,14 @@ BINNING_ASYNC, BINNING_SYNC, BINNING_REFERENCE, BINNING_TILESORT = 0, 1, 2, 3
 FLAG_DEBUG, FLAG_CLAMP01, FLAG_DEFER_SEG1, FLAG_SEG1_PREPROCESSED = 1, 2, 4, 8   # the flag word passed in the entry points' `debug` argument
 set_binning_mode = _sig("hugs_b200_set_binning_mode", i32, [i32])
 set_blend_priority = _sig("hugs_b200_set_blend_priority", i32, [i32, i32])
+_last_pair_counts = _sig("hugs_b200_last_pair_counts", i32, [C.POINTER(i32), C.POINTER(i32)])
+
+
+def last_pair_counts():
+    """(pairs, level-1 entries) of this thread's last uncaptured forward call."""
+    r, r1 = i32(0), i32(0)
+    check(_last_pair_counts(C.byref(r), C.byref(r1)), "last_pair_counts")
+    return int(r.value), int(r1.value)
 
 sort_bits = _sig("hugs_b200_sort_bits", i32, [i32, i32])
 sort_temp_bytes = _sig("hugs_b200_sort_temp_bytes", C.c_size_t, [i32])
@@ -255,7 +263,7 @@ def read_stage_times(reset=True):
 
 
 EXPORTED_SYMBOLS = [
-    "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode", "hugs_b200_set_blend_priority", "hugs_b200_materialize_sorted_keys",
+    "hugs_b200_binning_capacity_of", "hugs_b200_set_binning_mode", "hugs_b200_set_blend_priority", "hugs_b200_last_pair_counts", "hugs_b200_materialize_sorted_keys",
     "hugs_b200_stage_timing_enable", "hugs_b200_stage_timing_read", "hugs_b200_stage_name",
     "hugs_b200_abi_version", "hugs_b200_last_error", "hugs_b200_launch_count",
     "hugs_b200_rasterize_forward", "hugs_b200_rasterize_backward", "hugs_b200_rasterize_backward_acc",
