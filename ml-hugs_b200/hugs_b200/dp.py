@@ -8,6 +8,7 @@ allreduce(sum) of the flat gradient buffer (NCCL over NVLink/NVSwitch on the GPU
 tests).  Nothing else is exchanged: forward-only configs (novel-pose animation, scene rendering)
 shard frames with no collective at all.
 """
+import contextlib
 from typing import Dict, Iterable, List, Sequence
 
 import torch
@@ -149,7 +150,6 @@ def dp_step(render_view, views: Sequence[int], buf: FlatGradBuffer, rank: int, w
     then be captured in a CUDA graph (``GraphedStep``) with the collective outside it."""
     buf.zero_()
     mine = shard_views(len(views), rank, world_size)
-    import contextlib
     from . import segments
     deferral = segments.defer_scene_backward() if defer_scene else contextlib.nullcontext()
 

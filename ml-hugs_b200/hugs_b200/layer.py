@@ -159,9 +159,8 @@ class _RasterizeTwoSegmentsWithLayer(torch.autograd.Function):
         H, W, M = int(s.image_height), int(s.image_width), int(a[1].shape[1])
         bg, view, proj, campos, bg_layer = (_f32c(x, device) for x in (s.bg, s.viewmatrix, s.projmatrix, s.campos,
                                                                        bg_layer))
-        from . import segments as _seg
-        ready = (_seg._prepass.take(view, proj, campos, P0, P1, H, W, b)
-                 if (_seg._prepass is not None and P1 > 0) else None)   # segments.scene_prepass
+        from .segments import take_prepared
+        ready = take_prepared(view, proj, campos, P0, P1, H, W, b)   # segments.scene_prepass
         radii = ready[1] if ready is not None else torch.empty(P, dtype=torch.int32, device=device)
         color = torch.empty(3, H, W, dtype=torch.float32, device=device)
         fwd_flags = flags_of(s.debug, ctx.clamp) | (N.FLAG_SEG1_PREPROCESSED if ready is not None else 0)

@@ -152,6 +152,13 @@ class ScenePrepass:
 _prepass = None   # the active ScenePrepass
 
 
+def take_prepared(view, proj, campos, P0, P1, H, W, b):
+    """(geometry workspace, radii) the active scene_prepass holds for this camera and these scene tensors, or None."""
+    if _prepass is None or P1 <= 0:
+        return None
+    return _prepass.take(view, proj, campos, P0, P1, H, W, b)
+
+
 @contextlib.contextmanager
 def scene_prepass(settings_list, segment1, P0):
     """``with scene_prepass([settings of every view of the step], scene_segment, n_human):`` around the step's
@@ -186,7 +193,7 @@ class _RasterizeTwoSegments(torch.autograd.Function):
         H, W, M = int(s.image_height), int(s.image_width), int(a[1].shape[1])
         bg, view, proj, campos = (_f32c(x, device) for x in (s.bg, s.viewmatrix, s.projmatrix, s.campos))
         P = P0 + P1
-        ready = _prepass.take(view, proj, campos, P0, P1, H, W, b) if (_prepass is not None and P1 > 0) else None
+        ready = take_prepared(view, proj, campos, P0, P1, H, W, b)
         radii = ready[1] if ready is not None else torch.empty(P, dtype=torch.int32, device=device)
         geom = _Workspace(device, preset=ready[0] if ready is not None else None)
         binning, img = _Workspace(device), _Workspace(device)
