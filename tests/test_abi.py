@@ -104,3 +104,24 @@ def test_product_never_touches_the_oracle():
                         continue  # the docstring that states the rule
                     bad.append(os.path.join(base, f))
     assert not bad, bad
+
+
+def test_ctypes_structures_match_the_header():
+    """The ctypes mirrors of the header's structs: sizes of an LP64 C compiler for the declared fields, and the
+    argument checks of the view-batched entry points answer without a GPU."""
+    import ctypes as C
+
+    from hugs_b200 import _native as N
+    assert C.sizeof(N.GradSinks) == 5 * 2 * 8                 # hugs_b200_grad_sinks: five float*[2]
+    assert C.sizeof(N.SceneView) == 3 * 8 + 2 * 4 + 2 * 8     # hugs_b200_scene_view: 3 pointers, 2 floats, 2 pointers
+    header = open(os.path.join(ROOT, "include", "hugs_b200.h")).read()
+    body = header[header.index("typedef struct hugs_b200_scene_view {"):header.index("} hugs_b200_scene_view;")]
+    fields = [ln.split(";")[0].split()[-1].lstrip("*") for ln in body.splitlines()[1:] if ";" in ln]
+    assert fields == ["viewmatrix", "projmatrix", "cam_pos", "tan_fovy", "radii", "geom_buffer"]   # tan_fovx shares a line
+    assert [n for n, _ in N.SceneView._fields_] == ["viewmatrix", "projmatrix", "cam_pos", "tan_fovx", "tan_fovy", "radii",
+                                                    "geom_buffer"]
+    assert N.scene_backward_views(-1, None, 0, 0, 3, 16, 16, 16, None, None, None, 1.0, None, None, None) == -1
+    assert N.preprocess_scene_views(2, None, 0, 8, 3, 16, 16, 16, None, None, None, None, 1.0, None, 0, None) == -1
+    assert N.scene_backward_views(0, None, 0, 8, 3, 16, 16, 16, None, None, None, 1.0, None, None, None) == 0
+    assert N.FLAG_DEFER_SEG1 == 4 and N.FLAG_SEG1_PREPROCESSED == 8
+    assert "#define HUGS_B200_FLAG_DEFER_SEG1 4" in header and "#define HUGS_B200_FLAG_SEG1_PREPROCESSED 8" in header
